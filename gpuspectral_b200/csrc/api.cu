@@ -1,0 +1,783 @@
+// api.cu — the extern "C" layer of include/gpuspectral_b200.h: context, scene upload,
+// acceleration-structure builds, ray batches, framebuffer read-back, diagnostic entry points.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "bsdf.cuh"
+#include "context.h"
+#include "traverse.cuh"
+
+namespace gsb {
+
+static thread_local std::string g_lastError;
+void setLastError(const std::string& msg) { g_lastError = msg; }
+
+namespace {
+
+template <class F>
+gsb_status guarded(F&& f) {
+    try {
+        return f();
+    } catch (const CudaFailure& e) {
+        char buf[512];
+        snprintf(buf, sizeof(buf), "CUDA error %d (%s) at %s:%d: %s", (int)e.err, cudaGetErrorString(e.err), e.file, e.line, e.what);
+        setLastError(buf);
+        return GSB_ERR_CUDA;
+    } catch (const std::bad_alloc&) {
+        setLastError("out of host memory");
+        return GSB_ERR_OOM;
+    } catch (const std::exception& e) {
+        setLastError(e.what());
+        return GSB_ERR_INVALID;
+    }
+}
+
+gsb_status fail(gsb_status st, const std::string& msg) {
+    setLastError(msg);
+    return st;
+}
+
+const uint32_t kBsdfStride[GSB_BSDF_TYPE_COUNT] = {
+    sizeof(gsb_diffuse_bsdf), sizeof(gsb_smooth_dielectric_bsdf), sizeof(gsb_smooth_conductor_bsdf), sizeof(gsb_smooth_plastic_bsdf),
+    sizeof(gsb_rough_conductor_bsdf), sizeof(gsb_smooth_floor_bsdf), sizeof(gsb_rough_floor_bsdf), sizeof(gsb_rough_plastic_bsdf)};
+
+template <class T>
+T* uploadArray(const T* host, size_t count, cudaStream_t s) {
+    void* p = nullptr;
+    GSB_CUDA(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+    if (count) GSB_CUDA(cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, s));
+    return (T*)p;
+}
+
+struct Bind {
+    int prev = -1;
+    explicit Bind(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+    }
+    ~Bind() {}
+};
+
+// ---- kernels of this translation unit ----------------------------------------------------------------
+template <bool ANYHIT, bool STATS>
+__global__ void __launch_bounds__(128) k_traceBatch(SceneDev sc, const gsb_ray* __restrict__ rays, uint32_t n, gsb_hit* __restrict__ hits,
+                                                    unsigned long long* stats) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    TraceStats ts = {0u, 0u, 0u};
+    if (i < n) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(rays) + 2 * (size_t)i);
+        const float4 b = __ldg(reinterpret_cast<const float4*>(rays) + 2 * (size_t)i + 1);
+        HitRecord h;
+        traceRay<ANYHIT, STATS>(sc, a.x, a.y, a.z, b.x, b.y, b.z, a.w, b.w, h, &ts, (uint32_t*)&stats[ST_OVERFLOW]);
+        gsb_hit o;
+        if (ANYHIT) {
+            o.t = 0.0f; o.u = 0.0f; o.v = 0.0f;
+            o.inst = h.inst == GSB_NO_HIT ? GSB_NO_HIT : 0u;
+            o.prim = o.inst;
+        } else {
+            o.t = h.t; o.u = h.u; o.v = h.v; o.inst = h.inst; o.prim = h.prim;
+        }
+        hits[i] = o;
+    }
+    if (STATS) {
+        uint32_t nn = ts.nodes, nt = ts.tris, ni = ts.insts, nr = i < n ? 1u : 0u;
+        for (int o = 16; o > 0; o >>= 1) {
+            nn += __shfl_xor_sync(0xffffffffu, nn, o);
+            nt += __shfl_xor_sync(0xffffffffu, nt, o);
+            ni += __shfl_xor_sync(0xffffffffu, ni, o);
+            nr += __shfl_xor_sync(0xffffffffu, nr, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&stats[ST_NODES], (unsigned long long)nn);
+            atomicAdd(&stats[ST_TRIS], (unsigned long long)nt);
+            atomicAdd(&stats[ST_INSTS], (unsigned long long)ni);
+            atomicAdd(&stats[ST_RAYS], (unsigned long long)nr);
+        }
+    }
+}
+
+__global__ void k_resolve(const float4* __restrict__ accum, uint32_t npix, float4* __restrict__ hdr, uchar4* __restrict__ ldr) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    const float4 a = accum[p];
+    const float inv = a.w > 0.0f ? 1.0f / a.w : 0.0f;
+    const float3 c = f3(a.x * inv, a.y * inv, a.z * inv);
+    if (hdr) hdr[p] = make_float4(c.x, c.y, c.z, 1.0f);
+    if (ldr) {
+        // linear -> sRGB 8-bit UNORM, the conversion the B8G8R8A8_SRGB swapchain applies on write
+        auto enc = [](float v) {
+            float e;
+            if (!(v > 0.0f)) e = 0.0f;
+            else if (v >= 1.0f) e = 1.0f;
+            else e = v <= 0.0031308f ? 12.92f * v : 1.055f * powf(v, 1.0f / 2.4f) - 0.055f;
+            return (unsigned char)floorf(e * 255.0f + 0.5f);
+        };
+        ldr[p] = make_uchar4(enc(c.x), enc(c.y), enc(c.z), 255);
+    }
+}
+
+__global__ void k_testRng(const uint32_t* idx, const uint32_t* ts, uint32_t n, uint32_t nDraws, uint32_t* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t* o = out + (size_t)i * (1 + nDraws);
+    uint32_t rng = pcgHash(tea(idx[i], ts[i]));
+    o[0] = rng;
+    for (uint32_t k = 0; k < nDraws; k++) o[1 + k] = randPcg(rng);
+}
+
+__global__ void k_testCamera(SceneDev sc, uint32_t W, uint32_t H, const uint32_t* px, const uint32_t* py, uint32_t n, gsb_ray* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float sx = (float)W, sy = (float)H;
+    const float fx = (float)px[i] - sx / 2.0f;
+    const float fy = (float)py[i] - sy / 2.0f;
+    const float z = (fmaxf(sx, sy) / 2.0f) / tanf(sc.fov / 2.0f);
+    const float3 dir = normalize(f3(-fx, fy, z));
+    const float* V = sc.view;
+    float3 d = f3(V[0] * dir.x + V[4] * dir.y + V[8] * dir.z, V[1] * dir.x + V[5] * dir.y + V[9] * dir.z,
+                  V[2] * dir.x + V[6] * dir.y + V[10] * dir.z);
+    d.y *= -1.0f;
+    gsb_ray r;
+    r.origin[0] = sc.eye[0]; r.origin[1] = sc.eye[1]; r.origin[2] = sc.eye[2];
+    r.dir[0] = d.x; r.dir[1] = d.y; r.dir[2] = d.z;
+    r.tmin = 0.0f;
+    r.tmax = 1e10f;
+    out[i] = r;
+}
+
+__global__ void k_testBsdfSample(SceneDev sc, uint32_t handle, const float* wo, const uint32_t* seed, uint32_t n, float* wi, float* f,
+                                 float* pdf, uint32_t* isDelta, uint32_t* seedOut) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t rng = seed[i];
+    float3 w = f3(0.0f);
+    BSDFOutput res;
+    res.bsdf = f3(0.0f); res.pdf = 0.0f; res.isDelta = false;
+    sampleBSDF(sc, handle, rng, f3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]), w, res);
+    wi[3 * i] = w.x; wi[3 * i + 1] = w.y; wi[3 * i + 2] = w.z;
+    f[3 * i] = res.bsdf.x; f[3 * i + 1] = res.bsdf.y; f[3 * i + 2] = res.bsdf.z;
+    pdf[i] = res.pdf;
+    isDelta[i] = res.isDelta ? 1u : 0u;
+    seedOut[i] = rng;
+}
+
+__global__ void k_testBsdfEval(SceneDev sc, uint32_t handle, const float* wo, const float* wi, uint32_t n, float* f, float* pdf, uint32_t* isDelta) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    BSDFOutput res;
+    res.bsdf = f3(0.0f); res.pdf = 0.0f; res.isDelta = false;
+    evalBSDF(sc, handle, f3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]), f3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]), res);
+    f[3 * i] = res.bsdf.x; f[3 * i + 1] = res.bsdf.y; f[3 * i + 2] = res.bsdf.z;
+    pdf[i] = res.pdf;
+    isDelta[i] = res.isDelta ? 1u : 0u;
+}
+
+__global__ void k_testSampleLight(SceneDev sc, const float* pos, const uint32_t* seed, uint32_t n, float* lpos, float* emission, float* pdf, uint32_t* seedOut) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t rng = seed[i];
+    bool have;
+    const LightOutput r = sampleLight(sc, rng, f3(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]), have);
+    lpos[3 * i] = r.position.x; lpos[3 * i + 1] = r.position.y; lpos[3 * i + 2] = r.position.z;
+    emission[3 * i] = r.emission.x; emission[3 * i + 1] = r.emission.y; emission[3 * i + 2] = r.emission.z;
+    pdf[i] = r.pdf;
+    seedOut[i] = rng;
+}
+
+// device scratch that frees itself
+struct Scratch {
+    std::vector<void*> ptrs;
+    template <class T>
+    T* alloc(size_t count) {
+        void* p = nullptr;
+        GSB_CUDA(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+        ptrs.push_back(p);
+        return (T*)p;
+    }
+    template <class T>
+    T* upload(const T* host, size_t count, cudaStream_t s) {
+        T* p = alloc<T>(count);
+        if (count) GSB_CUDA(cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, s));
+        return p;
+    }
+    ~Scratch() {
+        for (void* p : ptrs) cudaFree(p);
+    }
+};
+
+void ensureStats(gsb_context* ctx) {
+    if (ctx->wf.stats) return;
+    void* p = nullptr;
+    GSB_CUDA(cudaMalloc(&p, ST_COUNT * sizeof(unsigned long long)));
+    ctx->wf.stats = (unsigned long long*)p;
+    GSB_CUDA(cudaMemsetAsync(ctx->wf.stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
+}
+
+bool sceneReady(gsb_context* ctx) { return ctx->haveInstances && ctx->tlas.buffer; }
+
+void checkOverflow(gsb_context* ctx) {
+    unsigned long long ov = 0;
+    GSB_CUDA(cudaMemcpyAsync(&ov, &ctx->wf.stats[ST_OVERFLOW], sizeof(ov), cudaMemcpyDeviceToHost, ctx->stream));
+    GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ov) {
+        GSB_CUDA(cudaMemsetAsync(&ctx->wf.stats[ST_OVERFLOW], 0, sizeof(ov), ctx->stream));
+        throw std::runtime_error("traversal stack overflow: BVH deeper than the traversal stack");
+    }
+}
+
+}  // namespace
+}  // namespace gsb
+
+using namespace gsb;
+
+SceneDev gsb_context::sceneDev() const {
+    SceneDev sc;
+    memset(&sc, 0, sizeof(sc));
+    sc.tlasNodes = tlas.buffer;
+    sc.tlasInst = reinterpret_cast<const TraceInstance*>(tlas.buffer + tlas.leafOffset16);
+    sc.shadeInst = dShade;
+    sc.instBsdf = dInstBsdf;
+    for (int t = 0; t < GSB_BSDF_TYPE_COUNT; t++) sc.bsdf[t] = dBsdf[t];
+    sc.lights = dLights;
+    sc.numLights = numLights;
+    sc.numInstances = (uint32_t)instances.size();
+    memcpy(sc.eye, eye, sizeof(eye));
+    memcpy(sc.view, view, sizeof(view));
+    sc.fov = fov;
+    sc.params = params;
+    return sc;
+}
+
+extern "C" {
+
+const char* gsb_last_error(void) { return g_lastError.c_str(); }
+const char* gsb_version(void) { return "gpuspectral_b200 0.1 (sm_100a)"; }
+
+gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx) {
+    if (!out_ctx) return fail(GSB_ERR_INVALID, "gsb_create: out_ctx is null");
+    *out_ctx = nullptr;
+    return guarded([&]() -> gsb_status {
+        int count = 0;
+        cudaError_t e = cudaGetDeviceCount(&count);
+        if (e != cudaSuccess || count == 0)
+            return fail(GSB_ERR_CUDA, std::string("gsb_create: no CUDA device available (") + cudaGetErrorString(e) + ")");
+        if (device_ordinal < 0 || device_ordinal >= count) return fail(GSB_ERR_INVALID, "gsb_create: device ordinal out of range");
+        GSB_CUDA(cudaSetDevice(device_ordinal));
+        gsb_context* ctx = new gsb_context();
+        ctx->device = device_ordinal;
+        GSB_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        ensureStats(ctx);
+        *out_ctx = ctx;
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_destroy(gsb_context* ctx) {
+    if (!ctx) return GSB_OK;
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        cudaStreamSynchronize(ctx->stream);
+        for (MeshRec& m : ctx->meshes) {
+            if (!m.alive) continue;
+            cudaFree(m.vpos);
+            cudaFree(m.vnrm);
+            freeBvh(m.blas);
+        }
+        freeBvh(ctx->tlas);
+        cudaFree(ctx->dShade);
+        cudaFree(ctx->dInstBsdf);
+        for (void* p : ctx->dBsdf) cudaFree(p);
+        cudaFree(ctx->dLights);
+        cudaFree(ctx->dAccum);
+        freeWavefront(ctx);
+        cudaStreamDestroy(ctx->stream);
+        delete ctx;
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_mesh_create(gsb_context* ctx, const float* positions3, const float* normals3, uint32_t nverts, uint32_t* out_mesh) {
+    if (!ctx || !out_mesh) return fail(GSB_ERR_INVALID, "gsb_mesh_create: null argument");
+    if (nverts % 3 != 0) return fail(GSB_ERR_INVALID, "gsb_mesh_create: vertex count is not a multiple of 3");
+    if (nverts && (!positions3 || !normals3)) return fail(GSB_ERR_INVALID, "gsb_mesh_create: null vertex arrays");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        MeshRec m;
+        m.alive = true;
+        m.ntris = nverts / 3;
+        std::vector<float4> p4(nverts), n4(nverts);
+        for (uint32_t i = 0; i < nverts; i++) {
+            p4[i] = make_float4(positions3[3 * (size_t)i], positions3[3 * (size_t)i + 1], positions3[3 * (size_t)i + 2], 0.0f);
+            n4[i] = make_float4(normals3[3 * (size_t)i], normals3[3 * (size_t)i + 1], normals3[3 * (size_t)i + 2], 0.0f);
+        }
+        m.vpos = uploadArray(p4.data(), nverts, ctx->stream);
+        m.vnrm = uploadArray(n4.data(), nverts, ctx->stream);
+        buildBlas(m.vpos, m.ntris, ctx->stream, m.blas);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        uint32_t id = (uint32_t)ctx->meshes.size();
+        for (uint32_t k = 0; k < ctx->meshes.size(); k++)
+            if (!ctx->meshes[k].alive) { id = k; break; }
+        if (id == ctx->meshes.size()) ctx->meshes.push_back(m);
+        else ctx->meshes[id] = m;
+        *out_mesh = id;
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_mesh_destroy(gsb_context* ctx, uint32_t mesh) {
+    if (!ctx || mesh >= ctx->meshes.size() || !ctx->meshes[mesh].alive) return fail(GSB_ERR_INVALID, "gsb_mesh_destroy: bad mesh handle");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        for (const gsb_instance& in : ctx->instances)
+            if (in.mesh == mesh) {
+                ctx->haveInstances = false;  // the scene referenced it: force a new gsb_scene_set_instances
+                break;
+            }
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        MeshRec& m = ctx->meshes[mesh];
+        cudaFree(m.vpos);
+        cudaFree(m.vnrm);
+        freeBvh(m.blas);
+        m = MeshRec();
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_scene_set_bsdfs(gsb_context* ctx, uint32_t type, const void* params, uint32_t count) {
+    if (!ctx || type >= GSB_BSDF_TYPE_COUNT) return fail(GSB_ERR_INVALID, "gsb_scene_set_bsdfs: bad type");
+    if (count && !params) return fail(GSB_ERR_INVALID, "gsb_scene_set_bsdfs: null params");
+    if (count > 65536) return fail(GSB_ERR_INVALID, "gsb_scene_set_bsdfs: more than 65536 records of one type (16-bit handle index)");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->dBsdf[type]);
+        ctx->dBsdf[type] = uploadArray((const uint8_t*)params, (size_t)count * kBsdfStride[type], ctx->stream);
+        ctx->bsdfCount[type] = count;
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_scene_set_lights(gsb_context* ctx, const gsb_triangle_light* lights, uint32_t count) {
+    if (!ctx || (count && !lights)) return fail(GSB_ERR_INVALID, "gsb_scene_set_lights: null argument");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->dLights);
+        ctx->dLights = uploadArray(lights, count, ctx->stream);
+        ctx->numLights = count;
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instances, uint32_t count) {
+    if (!ctx || (count && !instances)) return fail(GSB_ERR_INVALID, "gsb_scene_set_instances: null argument");
+    for (uint32_t i = 0; i < count; i++) {
+        if (instances[i].mesh >= ctx->meshes.size() || !ctx->meshes[instances[i].mesh].alive)
+            return fail(GSB_ERR_INVALID, "gsb_scene_set_instances: instance " + std::to_string(i) + " references an unknown mesh");
+        if ((instances[i].bsdf >> 16) >= GSB_BSDF_TYPE_COUNT)
+            return fail(GSB_ERR_INVALID, "gsb_scene_set_instances: instance " + std::to_string(i) + " has an unknown BSDF type");
+    }
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->instances.assign(instances, instances + count);
+        std::vector<ShadeInstance> shade(count);
+        std::vector<TraceInstance> trace(count);
+        std::vector<uint32_t> handles(count);
+        std::vector<float> wlo(3 * (size_t)count), whi(3 * (size_t)count);
+        for (bool& u : ctx->typeUsed) u = false;
+        for (uint32_t i = 0; i < count; i++) {
+            const gsb_instance& in = instances[i];
+            const MeshRec& mesh = ctx->meshes[in.mesh];
+            const float* T = in.transform;  // column-major: T[c*4 + r]
+            double M[3][4];
+            for (int r = 0; r < 3; r++)
+                for (int c = 0; c < 4; c++) M[r][c] = T[c * 4 + r];
+            // inverse of the linear part by cofactors, float64, rounded once to float32
+            const double c00 = M[1][1] * M[2][2] - M[1][2] * M[2][1], c01 = M[1][2] * M[2][0] - M[1][0] * M[2][2],
+                         c02 = M[1][0] * M[2][1] - M[1][1] * M[2][0];
+            const double det = M[0][0] * c00 + M[0][1] * c01 + M[0][2] * c02;
+            const double id = 1.0 / det;
+            double inv[3][3];
+            inv[0][0] = c00 * id;
+            inv[1][0] = c01 * id;
+            inv[2][0] = c02 * id;
+            inv[0][1] = (M[0][2] * M[2][1] - M[0][1] * M[2][2]) * id;
+            inv[1][1] = (M[0][0] * M[2][2] - M[0][2] * M[2][0]) * id;
+            inv[2][1] = (M[0][1] * M[2][0] - M[0][0] * M[2][1]) * id;
+            inv[0][2] = (M[0][1] * M[1][2] - M[0][2] * M[1][1]) * id;
+            inv[1][2] = (M[0][2] * M[1][0] - M[0][0] * M[1][2]) * id;
+            inv[2][2] = (M[0][0] * M[1][1] - M[0][1] * M[1][0]) * id;
+            ShadeInstance& sh = shade[i];
+            TraceInstance& tr = trace[i];
+            for (int r = 0; r < 3; r++) {
+                sh.o2w[r] = make_float4((float)M[r][0], (float)M[r][1], (float)M[r][2], (float)M[r][3]);
+                // rows of inverse(transpose(M))'s 3x3 = columns of inv
+                sh.nrm[r] = make_float4((float)inv[0][r], (float)inv[1][r], (float)inv[2][r], in.emission[r]);
+                const double tw = -(inv[r][0] * M[0][3] + inv[r][1] * M[1][3] + inv[r][2] * M[2][3]);
+                tr.w2o[r] = make_float4((float)inv[r][0], (float)inv[r][1], (float)inv[r][2], (float)tw);
+            }
+            sh.vpos = mesh.vpos;
+            sh.vnrm = mesh.vnrm;
+            sh.bsdf = in.bsdf;
+            sh.twofaced = in.twofaced;
+            sh.pad[0] = sh.pad[1] = 0;
+            tr.blas = mesh.blas.buffer;
+            tr.triOffset16 = mesh.blas.leafOffset16;
+            tr.instId = i;
+            handles[i] = in.bsdf;
+            ctx->typeUsed[in.bsdf >> 16] = true;
+            // padded world bounds of the padded object box
+            double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+            for (int corner = 0; corner < 8; corner++) {
+                const double p[3] = {(corner & 1) ? mesh.blas.hi[0] : mesh.blas.lo[0], (corner & 2) ? mesh.blas.hi[1] : mesh.blas.lo[1],
+                                     (corner & 4) ? mesh.blas.hi[2] : mesh.blas.lo[2]};
+                for (int r = 0; r < 3; r++) {
+                    const double w = M[r][0] * p[0] + M[r][1] * p[1] + M[r][2] * p[2] + M[r][3];
+                    lo[r] = std::fmin(lo[r], w);
+                    hi[r] = std::fmax(hi[r], w);
+                }
+            }
+            double scale = 0.0;
+            for (int a = 0; a < 3; a++) scale = std::fmax(scale, std::fmax(std::fabs(lo[a]), std::fabs(hi[a])));
+            const double pad = scale * (double)kBoxPadRel;
+            for (int a = 0; a < 3; a++) {
+                wlo[3 * (size_t)i + a] = std::nextafter((float)(lo[a] - pad), -INFINITY);
+                whi[3 * (size_t)i + a] = std::nextafter((float)(hi[a] + pad), INFINITY);
+            }
+        }
+        cudaFree(ctx->dShade);
+        cudaFree(ctx->dInstBsdf);
+        ctx->dShade = uploadArray(shade.data(), count, ctx->stream);
+        ctx->dInstBsdf = uploadArray(handles.data(), count, ctx->stream);
+        freeBvh(ctx->tlas);
+        buildTlas(wlo.data(), whi.data(), trace.data(), count, ctx->stream, ctx->tlas);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->haveInstances = true;
+        double ms = ctx->tlas.buildMs;
+        std::vector<bool> seen(ctx->meshes.size(), false);
+        for (uint32_t i = 0; i < count; i++)
+            if (!seen[instances[i].mesh]) { seen[instances[i].mesh] = true; ms += ctx->meshes[instances[i].mesh].blas.buildMs; }
+        ctx->lastBuildMs = ms;
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_set_camera(gsb_context* ctx, const float eye[3], const float to_world[16], float fov_radians) {
+    if (!ctx || !eye || !to_world) return fail(GSB_ERR_INVALID, "gsb_set_camera: null argument");
+    memcpy(ctx->eye, eye, sizeof(float) * 3);
+    memcpy(ctx->view, to_world, sizeof(float) * 16);
+    ctx->fov = fov_radians;
+    return GSB_OK;
+}
+
+gsb_status gsb_default_params(gsb_params* out) {
+    if (!out) return fail(GSB_ERR_INVALID, "gsb_default_params: null argument");
+    out->max_depth = 50;
+    out->rr_start = 10;
+    out->cutoff = 20.0f;
+    out->nee = 1;
+    return GSB_OK;
+}
+
+gsb_status gsb_set_params(gsb_context* ctx, const gsb_params* params) {
+    if (!ctx || !params) return fail(GSB_ERR_INVALID, "gsb_set_params: null argument");
+    if (params->max_depth < 0 || params->max_depth > 65000) return fail(GSB_ERR_INVALID, "gsb_set_params: max_depth out of range");
+    ctx->params = *params;
+    return GSB_OK;
+}
+
+gsb_status gsb_get_bvh_stats(gsb_context* ctx, gsb_bvh_stats* out) {
+    if (!ctx || !out) return fail(GSB_ERR_INVALID, "gsb_get_bvh_stats: null argument");
+    memset(out, 0, sizeof(*out));
+    std::vector<bool> seen(ctx->meshes.size(), false);
+    for (const gsb_instance& in : ctx->instances) {
+        const MeshRec& m = ctx->meshes[in.mesh];
+        out->instanced_triangles += m.ntris;
+        if (seen[in.mesh]) continue;
+        seen[in.mesh] = true;
+        out->num_meshes++;
+        out->unique_triangles += m.ntris;
+        out->blas_nodes += m.blas.numNodes;
+        out->bvh_bytes += m.blas.bytes;
+        out->sah_cost_before += m.blas.sahBefore;
+        out->sah_cost_after += m.blas.sahAfter;
+    }
+    out->num_instances = ctx->instances.size();
+    out->tlas_nodes = ctx->tlas.numNodes;
+    out->bvh_bytes += ctx->tlas.bytes;
+    out->build_ms = ctx->lastBuildMs;
+    return GSB_OK;
+}
+
+gsb_status gsb_render(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t first_sample, uint32_t num_samples, uint32_t sample_stride) {
+    if (!ctx) return fail(GSB_ERR_INVALID, "gsb_render: null context");
+    if (width == 0 || height == 0 || (uint64_t)width * height > (1ull << 28)) return fail(GSB_ERR_INVALID, "gsb_render: bad frame size");
+    if (sample_stride == 0) return fail(GSB_ERR_INVALID, "gsb_render: sample_stride must be >= 1");
+    if (!sceneReady(ctx)) return fail(GSB_ERR_STATE, "gsb_render: no scene (call gsb_scene_set_instances first)");
+    for (const gsb_instance& in : ctx->instances)
+        if ((in.bsdf & 0xffffu) >= ctx->bsdfCount[in.bsdf >> 16])
+            return fail(GSB_ERR_STATE, "gsb_render: an instance references a BSDF record that was not uploaded");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        renderImpl(ctx, width, height, first_sample, num_samples, sample_stride);
+        checkOverflow(ctx);
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_clear(gsb_context* ctx) {
+    if (!ctx) return fail(GSB_ERR_INVALID, "gsb_clear: null context");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        if (ctx->dAccum) GSB_CUDA(cudaMemsetAsync(ctx->dAccum, 0, (size_t)ctx->width * ctx->height * sizeof(float4), ctx->stream));
+        GSB_CUDA(cudaMemsetAsync(ctx->wf.stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_synchronize(gsb_context* ctx) {
+    if (!ctx) return fail(GSB_ERR_INVALID, "gsb_synchronize: null context");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
+static gsb_status readImage(gsb_context* ctx, float* hdr, uint8_t* ldr) {
+    if (!ctx || (!hdr && !ldr)) return fail(GSB_ERR_INVALID, "gsb_read: null argument");
+    if (!ctx->dAccum) return fail(GSB_ERR_STATE, "gsb_read: nothing rendered yet");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        const uint32_t npix = ctx->width * ctx->height;
+        Scratch sc;
+        float4* dHdr = hdr ? sc.alloc<float4>(npix) : nullptr;
+        uchar4* dLdr = ldr ? sc.alloc<uchar4>(npix) : nullptr;
+        k_resolve<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(ctx->dAccum, npix, dHdr, dLdr);
+        if (hdr) GSB_CUDA(cudaMemcpyAsync(hdr, dHdr, (size_t)npix * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+        if (ldr) GSB_CUDA(cudaMemcpyAsync(ldr, dLdr, (size_t)npix * sizeof(uchar4), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_read_hdr(gsb_context* ctx, float* out_rgba) { return readImage(ctx, out_rgba, nullptr); }
+gsb_status gsb_read_ldr(gsb_context* ctx, uint8_t* out_rgba8) { return readImage(ctx, nullptr, out_rgba8); }
+
+gsb_status gsb_device_sum_ptr(gsb_context* ctx, void** out_ptr, size_t* out_bytes) {
+    if (!ctx || !out_ptr || !out_bytes) return fail(GSB_ERR_INVALID, "gsb_device_sum_ptr: null argument");
+    if (!ctx->dAccum) return fail(GSB_ERR_STATE, "gsb_device_sum_ptr: nothing rendered yet");
+    *out_ptr = ctx->dAccum;
+    *out_bytes = (size_t)ctx->width * ctx->height * sizeof(float4);
+    return GSB_OK;
+}
+
+gsb_status gsb_get_counters(gsb_context* ctx, gsb_counters* out) {
+    if (!ctx || !out) return fail(GSB_ERR_INVALID, "gsb_get_counters: null argument");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        unsigned long long h[ST_COUNT];
+        GSB_CUDA(cudaMemcpyAsync(h, ctx->wf.stats, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        out->paths = h[ST_PATHS];
+        out->extension_rays = h[ST_EXT];
+        out->shadow_rays = h[ST_SHADOW];
+        out->iterations = h[ST_ITERS];
+        out->nodes_visited = h[ST_NODES];
+        out->tris_tested = h[ST_TRIS];
+        out->inst_entered = h[ST_INSTS];
+        out->rays_counted = h[ST_RAYS];
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_reset_counters(gsb_context* ctx) {
+    if (!ctx) return fail(GSB_ERR_INVALID, "gsb_reset_counters: null context");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        GSB_CUDA(cudaMemsetAsync(ctx->wf.stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_set_profiling(gsb_context* ctx, int enabled) {
+    if (!ctx) return fail(GSB_ERR_INVALID, "gsb_set_profiling: null context");
+    ctx->profiling = enabled != 0;
+    return GSB_OK;
+}
+
+gsb_status gsb_last_render_ms(gsb_context* ctx, double out_ms[5]) {
+    if (!ctx || !out_ms) return fail(GSB_ERR_INVALID, "gsb_last_render_ms: null argument");
+    for (int k = 0; k < 5; k++) out_ms[k] = ctx->lastRenderMs[k];
+    return GSB_OK;
+}
+
+static gsb_status traceBatch(gsb_context* ctx, const gsb_ray* rays, uint32_t count, gsb_hit* out_hits, int any_hit, bool stats,
+                             int repeats, double* out_ms) {
+    if (!ctx || (count && !rays)) return fail(GSB_ERR_INVALID, "gsb_trace_batch: null argument");
+    if (!sceneReady(ctx)) return fail(GSB_ERR_STATE, "gsb_trace_batch: no scene (call gsb_scene_set_instances first)");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        Scratch scr;
+        gsb_ray* dRays = scr.upload(rays, count, ctx->stream);
+        gsb_hit* dHits = scr.alloc<gsb_hit>(count);
+        const SceneDev sc = ctx->sceneDev();
+        const int grid = (int)((count + 127) / 128);
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (out_ms) {
+            GSB_CUDA(cudaEventCreate(&e0));
+            GSB_CUDA(cudaEventCreate(&e1));
+        }
+        for (int r = 0; r < repeats + (out_ms ? 1 : 0); r++) {
+            if (out_ms && r == 1) GSB_CUDA(cudaEventRecord(e0, ctx->stream));  // launch 0 is a warm-up
+            if (count == 0) break;
+            if (stats) {
+                if (any_hit) k_traceBatch<true, true><<<grid, 128, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats);
+                else k_traceBatch<false, true><<<grid, 128, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats);
+            } else {
+                if (any_hit) k_traceBatch<true, false><<<grid, 128, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats);
+                else k_traceBatch<false, false><<<grid, 128, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats);
+            }
+        }
+        GSB_CUDA(cudaGetLastError());
+        if (out_ms) {
+            GSB_CUDA(cudaEventRecord(e1, ctx->stream));
+            GSB_CUDA(cudaEventSynchronize(e1));
+            float ms = 0.0f;
+            GSB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+            *out_ms = repeats > 0 ? (double)ms / repeats : 0.0;
+            cudaEventDestroy(e0);
+            cudaEventDestroy(e1);
+        }
+        if (out_hits && count) GSB_CUDA(cudaMemcpyAsync(out_hits, dHits, (size_t)count * sizeof(gsb_hit), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        checkOverflow(ctx);
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_trace_batch(gsb_context* ctx, const gsb_ray* rays, uint32_t count, gsb_hit* out_hits, int any_hit) {
+    if (count && !out_hits) return fail(GSB_ERR_INVALID, "gsb_trace_batch: null output");
+    return traceBatch(ctx, rays, count, out_hits, any_hit, false, 1, nullptr);
+}
+
+gsb_status gsb_trace_batch_stats(gsb_context* ctx, const gsb_ray* rays, uint32_t count, gsb_hit* out_hits, int any_hit) {
+    if (count && !out_hits) return fail(GSB_ERR_INVALID, "gsb_trace_batch_stats: null output");
+    return traceBatch(ctx, rays, count, out_hits, any_hit, true, 1, nullptr);
+}
+
+gsb_status gsb_trace_batch_timed(gsb_context* ctx, const gsb_ray* rays, uint32_t count, int any_hit, int repeats, double* out_ms_per_launch) {
+    if (!out_ms_per_launch || repeats < 1) return fail(GSB_ERR_INVALID, "gsb_trace_batch_timed: bad argument");
+    return traceBatch(ctx, rays, count, nullptr, any_hit, false, repeats, out_ms_per_launch);
+}
+
+// ---- diagnostics ------------------------------------------------------------------------------------
+gsb_status gsb_test_rng(gsb_context* ctx, const uint32_t* idx, const uint32_t* timestamp, uint32_t n, uint32_t n_draws, uint32_t* out) {
+    if (!ctx || !idx || !timestamp || !out) return fail(GSB_ERR_INVALID, "gsb_test_rng: null argument");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        Scratch scr;
+        uint32_t* dIdx = scr.upload(idx, n, ctx->stream);
+        uint32_t* dTs = scr.upload(timestamp, n, ctx->stream);
+        uint32_t* dOut = scr.alloc<uint32_t>((size_t)n * (1 + n_draws));
+        k_testRng<<<(n + 127) / 128, 128, 0, ctx->stream>>>(dIdx, dTs, n, n_draws, dOut);
+        GSB_CUDA(cudaMemcpyAsync(out, dOut, (size_t)n * (1 + n_draws) * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_test_camera_rays(gsb_context* ctx, uint32_t width, uint32_t height, const uint32_t* px, const uint32_t* py, uint32_t n, gsb_ray* out) {
+    if (!ctx || !px || !py || !out) return fail(GSB_ERR_INVALID, "gsb_test_camera_rays: null argument");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        Scratch scr;
+        uint32_t* dx = scr.upload(px, n, ctx->stream);
+        uint32_t* dy = scr.upload(py, n, ctx->stream);
+        gsb_ray* dOut = scr.alloc<gsb_ray>(n);
+        k_testCamera<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->sceneDev(), width, height, dx, dy, n, dOut);
+        GSB_CUDA(cudaMemcpyAsync(out, dOut, (size_t)n * sizeof(gsb_ray), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
+static bool handleOk(gsb_context* ctx, uint32_t handle) {
+    return (handle >> 16) < GSB_BSDF_TYPE_COUNT && (handle & 0xffffu) < ctx->bsdfCount[handle >> 16];
+}
+
+gsb_status gsb_test_bsdf_sample(gsb_context* ctx, uint32_t handle, const float* wo, const uint32_t* seed, uint32_t n, float* wi, float* f,
+                                float* pdf, uint32_t* is_delta, uint32_t* seed_out) {
+    if (!ctx || !wo || !seed || !wi || !f || !pdf || !is_delta || !seed_out) return fail(GSB_ERR_INVALID, "gsb_test_bsdf_sample: null argument");
+    if (!handleOk(ctx, handle)) return fail(GSB_ERR_INVALID, "gsb_test_bsdf_sample: BSDF handle out of range");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        Scratch scr;
+        float* dWo = scr.upload(wo, 3 * (size_t)n, ctx->stream);
+        uint32_t* dSeed = scr.upload(seed, n, ctx->stream);
+        float* dWi = scr.alloc<float>(3 * (size_t)n);
+        float* dF = scr.alloc<float>(3 * (size_t)n);
+        float* dPdf = scr.alloc<float>(n);
+        uint32_t* dDelta = scr.alloc<uint32_t>(n);
+        uint32_t* dSeedOut = scr.alloc<uint32_t>(n);
+        k_testBsdfSample<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->sceneDev(), handle, dWo, dSeed, n, dWi, dF, dPdf, dDelta, dSeedOut);
+        GSB_CUDA(cudaMemcpyAsync(wi, dWi, 3 * (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaMemcpyAsync(f, dF, 3 * (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaMemcpyAsync(pdf, dPdf, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaMemcpyAsync(is_delta, dDelta, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaMemcpyAsync(seed_out, dSeedOut, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_test_bsdf_eval(gsb_context* ctx, uint32_t handle, const float* wo, const float* wi, uint32_t n, float* f, float* pdf, uint32_t* is_delta) {
+    if (!ctx || !wo || !wi || !f || !pdf || !is_delta) return fail(GSB_ERR_INVALID, "gsb_test_bsdf_eval: null argument");
+    if (!handleOk(ctx, handle)) return fail(GSB_ERR_INVALID, "gsb_test_bsdf_eval: BSDF handle out of range");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        Scratch scr;
+        float* dWo = scr.upload(wo, 3 * (size_t)n, ctx->stream);
+        float* dWi = scr.upload(wi, 3 * (size_t)n, ctx->stream);
+        float* dF = scr.alloc<float>(3 * (size_t)n);
+        float* dPdf = scr.alloc<float>(n);
+        uint32_t* dDelta = scr.alloc<uint32_t>(n);
+        k_testBsdfEval<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->sceneDev(), handle, dWo, dWi, n, dF, dPdf, dDelta);
+        GSB_CUDA(cudaMemcpyAsync(f, dF, 3 * (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaMemcpyAsync(pdf, dPdf, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaMemcpyAsync(is_delta, dDelta, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_test_sample_light(gsb_context* ctx, const float* pos, const uint32_t* seed, uint32_t n, float* lpos, float* emission, float* pdf,
+                                 uint32_t* seed_out) {
+    if (!ctx || !pos || !seed || !lpos || !emission || !pdf || !seed_out) return fail(GSB_ERR_INVALID, "gsb_test_sample_light: null argument");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        Scratch scr;
+        float* dPos = scr.upload(pos, 3 * (size_t)n, ctx->stream);
+        uint32_t* dSeed = scr.upload(seed, n, ctx->stream);
+        float* dL = scr.alloc<float>(3 * (size_t)n);
+        float* dE = scr.alloc<float>(3 * (size_t)n);
+        float* dPdf = scr.alloc<float>(n);
+        uint32_t* dSeedOut = scr.alloc<uint32_t>(n);
+        k_testSampleLight<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->sceneDev(), dPos, dSeed, n, dL, dE, dPdf, dSeedOut);
+        GSB_CUDA(cudaMemcpyAsync(lpos, dL, 3 * (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaMemcpyAsync(emission, dE, 3 * (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaMemcpyAsync(pdf, dPdf, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaMemcpyAsync(seed_out, dSeedOut, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
+}  // extern "C"

@@ -1,0 +1,623 @@
+// bvh_build.cu — GPU construction of the two-level 8-wide BVH (see bvh.h / traverse.cuh).
+//
+// Pipeline per level (bottom: triangles of one mesh; top: instances):
+//   1. primitive boxes (padded) + bounds of the centroids            k_triBoxes / upload
+//   2. 63-bit Morton codes of the centroids                          k_morton
+//   3. radix sort of (code, primitive)                               cub::DeviceRadixSort
+//   4. binary radix tree over the sorted codes (Karras 2012)         k_radixTree
+//   5. bottom-up box fit                                             k_fitBoxes
+//   6. SAH treelet refinement of the binary tree (Karras & Aila 2013) treelet.cuh
+//   7. top-down collapse into 8-wide nodes + octant slot assignment + 8-bit quantisation
+//      (Ylitie, Karras & Laine 2017), level by level                 k_collapse
+//   8. leaf records gathered in node order                           k_packTriangles / k_packInstances
+#include <cub/device/device_radix_sort.cuh>
+
+#include <algorithm>
+#include <cmath>
+#include <vector>
+
+#include "bvh.h"
+
+namespace gsb {
+
+namespace {
+
+bool g_treelets = true;
+
+// ---- helpers ---------------------------------------------------------------------------------
+__host__ __device__ inline uint32_t orderedFromFloat(float f) {
+    uint32_t u;
+#ifdef __CUDA_ARCH__
+    u = __float_as_uint(f);
+#else
+    memcpy(&u, &f, 4);
+#endif
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ inline float floatFromOrdered(uint32_t u) {
+    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+    float f;
+#ifdef __CUDA_ARCH__
+    f = __uint_as_float(u);
+#else
+    memcpy(&f, &u, 4);
+#endif
+    return f;
+}
+
+struct BoundsAcc { uint32_t lo[3], hi[3]; };  // ordered-uint encoded
+
+__global__ void k_initBounds(BoundsAcc* b) {
+    if (threadIdx.x < 3) {
+        b->lo[threadIdx.x] = 0xffffffffu;
+        b->hi[threadIdx.x] = 0u;
+    }
+}
+
+// bounds of all vertices of a triangle soup
+__global__ void k_vertexBounds(const float4* __restrict__ v, uint32_t nverts, BoundsAcc* acc) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nverts; i += gridDim.x * blockDim.x) {
+        const float4 p = __ldg(v + i);
+        lo[0] = fminf(lo[0], p.x); lo[1] = fminf(lo[1], p.y); lo[2] = fminf(lo[2], p.z);
+        hi[0] = fmaxf(hi[0], p.x); hi[1] = fmaxf(hi[1], p.y); hi[2] = fmaxf(hi[2], p.z);
+    }
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+            hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            atomicMin(&acc->lo[a], orderedFromFloat(lo[a]));
+            atomicMax(&acc->hi[a], orderedFromFloat(hi[a]));
+        }
+    }
+}
+
+// padded primitive boxes of triangles
+__global__ void k_triBoxes(const float4* __restrict__ v, uint32_t ntris, float pad, float4* __restrict__ plo, float4* __restrict__ phi) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ntris) return;
+    const float4 a = __ldg(v + 3 * (size_t)i), b = __ldg(v + 3 * (size_t)i + 1), c = __ldg(v + 3 * (size_t)i + 2);
+    plo[i] = make_float4(fminf(a.x, fminf(b.x, c.x)) - pad, fminf(a.y, fminf(b.y, c.y)) - pad, fminf(a.z, fminf(b.z, c.z)) - pad, 0.0f);
+    phi[i] = make_float4(fmaxf(a.x, fmaxf(b.x, c.x)) + pad, fmaxf(a.y, fmaxf(b.y, c.y)) + pad, fmaxf(a.z, fmaxf(b.z, c.z)) + pad, 0.0f);
+}
+
+__device__ inline uint64_t spread21(uint32_t x) {
+    uint64_t v = x & 0x1fffffu;
+    v = (v | v << 32) & 0x1f00000000ffffull;
+    v = (v | v << 16) & 0x1f0000ff0000ffull;
+    v = (v | v << 8) & 0x100f00f00f00f00full;
+    v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+    v = (v | v << 2) & 0x1249249249249249ull;
+    return v;
+}
+
+__global__ void k_morton(const float4* __restrict__ plo, const float4* __restrict__ phi, uint32_t n, float3 cmin, float3 cinv,
+                         uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 lo = plo[i], hi = phi[i];
+    const float cx = (0.5f * (lo.x + hi.x) - cmin.x) * cinv.x;
+    const float cy = (0.5f * (lo.y + hi.y) - cmin.y) * cinv.y;
+    const float cz = (0.5f * (lo.z + hi.z) - cmin.z) * cinv.z;
+    const float s = 2097152.0f;  // 2^21
+    const uint32_t qx = (uint32_t)fminf(fmaxf(cx * s, 0.0f), s - 1.0f);
+    const uint32_t qy = (uint32_t)fminf(fmaxf(cy * s, 0.0f), s - 1.0f);
+    const uint32_t qz = (uint32_t)fminf(fmaxf(cz * s, 0.0f), s - 1.0f);
+    keys[i] = (spread21(qx) << 2) | (spread21(qy) << 1) | spread21(qz);
+    vals[i] = i;
+}
+
+// Binary tree arrays.  Node references: >= 0 internal node index, < 0 leaf at sorted position ~ref.
+struct BinTree {
+    int* left;        // [n-1]
+    int* right;       // [n-1]
+    int* parent;      // [n-1] parent of internal nodes (root: -1)
+    int* leafParent;  // [n]
+    uint32_t* first;  // [n-1] sorted range covered
+    uint32_t* last;   // [n-1]
+    float4* lo;       // [n-1] boxes of internal nodes
+    float4* hi;       // [n-1]
+    uint32_t* flags;  // [n-1] arrival counters
+};
+
+__device__ inline int deltaKeys(const uint64_t* __restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clzll((long long)(a ^ b));
+}
+
+__global__ void k_radixTree(const uint64_t* __restrict__ keys, int n, BinTree t) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (deltaKeys(keys, n, i, i + 1) - deltaKeys(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = deltaKeys(keys, n, i, i - d);
+    int lmax = 2;
+    while (deltaKeys(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int s = lmax / 2; s >= 1; s /= 2)
+        if (deltaKeys(keys, n, i, i + (l + s) * d) > dmin) l += s;
+    const int j = i + l * d;
+    const int dnode = deltaKeys(keys, n, i, j);
+    int s = 0, tt = l;
+    do {
+        tt = (tt + 1) >> 1;
+        if (deltaKeys(keys, n, i, i + (s + tt) * d) > dnode) s += tt;
+    } while (tt > 1);
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    int l_ref, r_ref;
+    if (lo == gamma) { l_ref = ~gamma; t.leafParent[gamma] = i; } else { l_ref = gamma; t.parent[gamma] = i; }
+    if (hi == gamma + 1) { r_ref = ~(gamma + 1); t.leafParent[gamma + 1] = i; } else { r_ref = gamma + 1; t.parent[gamma + 1] = i; }
+    t.left[i] = l_ref;
+    t.right[i] = r_ref;
+    t.first[i] = (uint32_t)lo;
+    t.last[i] = (uint32_t)hi;
+    if (i == 0) t.parent[0] = -1;
+}
+
+__device__ inline void refBox(const BinTree& t, const float4* plo, const float4* phi, const uint32_t* sorted, int ref, float4& lo, float4& hi) {
+    if (ref >= 0) {
+        lo = __ldcg(t.lo + ref);
+        hi = __ldcg(t.hi + ref);
+    } else {
+        const uint32_t p = sorted[~ref];
+        lo = plo[p];
+        hi = phi[p];
+    }
+}
+
+__global__ void k_fitBoxes(BinTree t, const float4* __restrict__ plo, const float4* __restrict__ phi,
+                           const uint32_t* __restrict__ sorted, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int node = t.leafParent[i];
+    while (node >= 0) {
+        __threadfence();
+        if (atomicAdd(&t.flags[node], 1u) == 0u) return;  // first arrival: the sibling will finish
+        float4 alo, ahi, blo, bhi;
+        refBox(t, plo, phi, sorted, t.left[node], alo, ahi);
+        refBox(t, plo, phi, sorted, t.right[node], blo, bhi);
+        t.lo[node] = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.0f);
+        t.hi[node] = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.0f);
+        node = t.parent[node];
+    }
+}
+
+__device__ inline float boxArea(float4 lo, float4 hi) {
+    const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+    return 2.0f * (dx * dy + dy * dz + dz * dx);
+}
+
+// SAH cost of the binary tree: sum of internal-node areas (C_i = 1) + leaf areas (C_t = 1), over root area
+__global__ void k_sahCost(BinTree t, const float4* __restrict__ plo, const float4* __restrict__ phi, int n, double* out) {
+    double acc = 0.0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        if (i < n - 1) acc += 1.2 * (double)boxArea(t.lo[i], t.hi[i]);
+        acc += (double)boxArea(plo[i], phi[i]);
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(out, acc);
+}
+
+}  // namespace
+
+}  // namespace gsb
+
+#include "treelet.cuh"
+
+namespace gsb {
+namespace {
+
+// ---- collapse to 8-wide nodes ---------------------------------------------------------------------
+struct CollapseItem { int binNode; uint32_t outNode; };
+
+struct CollapseArgs {
+    BinTree t;
+    const float4* plo;
+    const float4* phi;
+    const uint32_t* sorted;
+    uint4* nodes;          // output nodes, 5 x uint4 each
+    uint32_t* leafPrim;    // output: primitive index per leaf position
+    uint32_t* counters;    // [0] nodes allocated, [1] leaf positions allocated, [2] next-level item count
+};
+
+__device__ inline uint32_t refCount(const BinTree& t, int ref) { return ref >= 0 ? t.last[ref] - t.first[ref] + 1u : 1u; }
+__device__ inline uint32_t refFirst(const BinTree& t, int ref) { return ref >= 0 ? t.first[ref] : (uint32_t)~ref; }
+
+__device__ void emitNode(const CollapseArgs& a, uint32_t outNode, float4 nlo, float4 nhi, const int* child, int nc,
+                         CollapseItem* next) {
+    // classify + boxes
+    float4 clo[8], chi[8];
+    bool internal[8];
+    for (int k = 0; k < nc; k++) {
+        refBox(a.t, a.plo, a.phi, a.sorted, child[k], clo[k], chi[k]);
+        internal[k] = refCount(a.t, child[k]) > 3u;
+    }
+    // octant slot assignment: slot s (bits x,y,z = 4,2,1) should hold the child lying furthest
+    // towards (+ if bit set, - if clear) on each axis; traversal visits slot^octant in descending order.
+    const float ccx = 0.5f * (nlo.x + nhi.x), ccy = 0.5f * (nlo.y + nhi.y), ccz = 0.5f * (nlo.z + nhi.z);
+    float cost[8][8];
+    for (int k = 0; k < nc; k++) {
+        const float px = 0.5f * (clo[k].x + chi[k].x) - ccx, py = 0.5f * (clo[k].y + chi[k].y) - ccy, pz = 0.5f * (clo[k].z + chi[k].z) - ccz;
+        for (int s = 0; s < 8; s++)
+            cost[k][s] = ((s & 4) ? px : -px) + ((s & 2) ? py : -py) + ((s & 1) ? pz : -pz);
+    }
+    int slotOf[8], childAt[8];
+    for (int s = 0; s < 8; s++) childAt[s] = -1;
+    for (int k = 0; k < nc; k++) slotOf[k] = -1;
+    for (int round = 0; round < nc; round++) {
+        float best = -INFINITY;
+        int bk = -1, bs = -1;
+        for (int k = 0; k < nc; k++) {
+            if (slotOf[k] >= 0) continue;
+            for (int s = 0; s < 8; s++) {
+                if (childAt[s] >= 0) continue;
+                if (cost[k][s] > best) { best = cost[k][s]; bk = k; bs = s; }
+            }
+        }
+        slotOf[bk] = bs;
+        childAt[bs] = bk;
+    }
+    // allocation
+    uint32_t nInternal = 0, nLeafPrims = 0;
+    for (int s = 0; s < 8; s++) {
+        const int k = childAt[s];
+        if (k < 0) continue;
+        if (internal[k]) nInternal++;
+        else nLeafPrims += refCount(a.t, child[k]);
+    }
+    const uint32_t childBase = nInternal ? atomicAdd(&a.counters[0], nInternal) : 0u;
+    const uint32_t leafBase = nLeafPrims ? atomicAdd(&a.counters[1], nLeafPrims) : 0u;
+    const uint32_t itemBase = nInternal ? atomicAdd(&a.counters[2], nInternal) : 0u;
+
+    // quantisation frame
+    const float p[3] = {nlo.x, nlo.y, nlo.z};
+    const float ext[3] = {nhi.x - nlo.x, nhi.y - nlo.y, nhi.z - nlo.z};
+    int e[3];
+    double scale[3];
+    for (int ax = 0; ax < 3; ax++) {
+        int ee = -126;
+        if (ext[ax] > 0.0f) {
+            ee = (int)ceil(log2((double)ext[ax] / 255.0));
+            while (ldexp(255.0, ee) < (double)ext[ax]) ee++;
+            ee = max(ee, -126);
+        }
+        e[ax] = ee;
+        scale[ax] = ldexp(1.0, ee);
+    }
+    uint32_t meta[8], qlo[3][8], qhi[3][8];
+    uint32_t imask = 0, rank = 0, leafOff = 0;
+    for (int s = 0; s < 8; s++) {
+        meta[s] = 0;
+        for (int ax = 0; ax < 3; ax++) { qlo[ax][s] = 0; qhi[ax][s] = 0; }
+        const int k = childAt[s];
+        if (k < 0) continue;
+        const float lo3[3] = {clo[k].x, clo[k].y, clo[k].z}, hi3[3] = {chi[k].x, chi[k].y, chi[k].z};
+        for (int ax = 0; ax < 3; ax++) {
+            double ql = floor(((double)lo3[ax] - (double)p[ax]) / scale[ax]);
+            double qh = ceil(((double)hi3[ax] - (double)p[ax]) / scale[ax]);
+            ql = fmin(fmax(ql, 0.0), 255.0);
+            qh = fmin(fmax(qh, 0.0), 255.0);
+            qlo[ax][s] = (uint32_t)ql;
+            qhi[ax][s] = (uint32_t)qh;
+        }
+        if (internal[k]) {
+            imask |= 1u << s;
+            meta[s] = 0x20u | (24u + (uint32_t)s);
+            next[itemBase + rank] = CollapseItem{child[k], childBase + rank};
+            rank++;
+        } else {
+            const uint32_t cnt = refCount(a.t, child[k]);
+            const uint32_t first = refFirst(a.t, child[k]);
+            meta[s] = (((1u << cnt) - 1u) << 5) | leafOff;
+            for (uint32_t j = 0; j < cnt; j++) a.leafPrim[leafBase + leafOff + j] = a.sorted[first + j];
+            leafOff += cnt;
+        }
+    }
+    auto pack4 = [](const uint32_t* b) { return b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24); };
+    uint4* out = a.nodes + (size_t)outNode * 5;
+    out[0] = make_uint4(__float_as_uint(p[0]), __float_as_uint(p[1]), __float_as_uint(p[2]),
+                        (uint32_t)(e[0] + 127) | ((uint32_t)(e[1] + 127) << 8) | ((uint32_t)(e[2] + 127) << 16) | (imask << 24));
+    out[1] = make_uint4(childBase, leafBase, pack4(meta), pack4(meta + 4));
+    out[2] = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
+    out[3] = make_uint4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
+    out[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
+}
+
+__global__ void k_collapse(CollapseArgs a, const CollapseItem* __restrict__ items, uint32_t nItems, CollapseItem* next) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nItems) return;
+    const CollapseItem it = items[i];
+    const int b = it.binNode;
+    int child[8];
+    int nc = 2;
+    child[0] = a.t.left[b];
+    child[1] = a.t.right[b];
+    // greedily open the internal child with the largest surface area until 8 slots are used
+    while (nc < 8) {
+        float bestArea = -1.0f;
+        int bk = -1;
+        for (int k = 0; k < nc; k++) {
+            if (child[k] < 0) continue;
+            const float ar = boxArea(a.t.lo[child[k]], a.t.hi[child[k]]);
+            if (ar > bestArea) { bestArea = ar; bk = k; }
+        }
+        if (bk < 0) break;
+        const int x = child[bk];
+        child[bk] = a.t.left[x];
+        child[nc++] = a.t.right[x];
+    }
+    emitNode(a, it.outNode, a.t.lo[b], a.t.hi[b], child, nc, next);
+}
+
+// n == 1: a root with a single leaf slot
+__global__ void k_singleLeafRoot(CollapseArgs a) {
+    const int child[1] = {~0};
+    a.counters[1] = 0;
+    emitNode(a, 0u, a.plo[a.sorted[0]], a.phi[a.sorted[0]], child, 1, nullptr);
+}
+
+__global__ void k_emptyRoot(uint4* nodes) {
+    nodes[0] = make_uint4(0u, 0u, 0u, 127u | (127u << 8) | (127u << 16));
+    nodes[1] = make_uint4(0u, 0u, 0u, 0u);
+    nodes[2] = nodes[3] = nodes[4] = make_uint4(0u, 0u, 0u, 0u);
+}
+
+__global__ void k_packTriangles(const uint32_t* __restrict__ leafPrim, uint32_t n, const float4* __restrict__ v, float4* __restrict__ out) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const uint32_t p = leafPrim[k];
+    float4 a = __ldg(v + 3 * (size_t)p), b = __ldg(v + 3 * (size_t)p + 1), c = __ldg(v + 3 * (size_t)p + 2);
+    a.w = __uint_as_float(p);
+    b.w = 0.0f;
+    c.w = 0.0f;
+    out[3 * (size_t)k] = a;
+    out[3 * (size_t)k + 1] = b;
+    out[3 * (size_t)k + 2] = c;
+}
+
+__global__ void k_packInstances(const uint32_t* __restrict__ leafPrim, uint32_t n, const uint4* __restrict__ rec, uint4* __restrict__ out) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const uint32_t p = leafPrim[k];
+#pragma unroll
+    for (int w = 0; w < 4; w++) out[4 * (size_t)k + w] = rec[4 * (size_t)p + w];
+}
+
+template <class T>
+T* dalloc(size_t count, cudaStream_t s) {
+    void* p = nullptr;
+    GSB_CUDA(cudaMallocAsync(&p, std::max<size_t>(count, 1) * sizeof(T), s));
+    return (T*)p;
+}
+
+struct TempPool {
+    cudaStream_t s;
+    std::vector<void*> ptrs;
+    explicit TempPool(cudaStream_t st) : s(st) {}
+    template <class T>
+    T* get(size_t count) {
+        T* p = dalloc<T>(count, s);
+        ptrs.push_back(p);
+        return p;
+    }
+    ~TempPool() {
+        for (void* p : ptrs) cudaFreeAsync(p, s);
+    }
+};
+
+// Generic build over padded primitive boxes already on the device.  Produces the node array
+// (temp, worst-case sized) and the primitive order of the leaves.
+struct GenericResult {
+    uint4* nodes;        // temp, from pool
+    uint32_t numNodes;
+    uint32_t* leafPrim;  // temp, from pool
+};
+
+GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi, uint32_t n, const float cmin[3], const float cmax[3],
+                           cudaStream_t s, DeviceBvh& out) {
+    GenericResult r;
+    r.nodes = pool.get<uint4>((size_t)std::max<uint32_t>(n, 1) * 5);
+    r.leafPrim = pool.get<uint32_t>(n);
+    r.numNodes = 1;
+    if (n == 0) {
+        k_emptyRoot<<<1, 1, 0, s>>>(r.nodes);
+        return r;
+    }
+    const int B = 256;
+    uint64_t* keys = pool.get<uint64_t>(n);
+    uint64_t* keysSorted = pool.get<uint64_t>(n);
+    uint32_t* vals = pool.get<uint32_t>(n);
+    uint32_t* sorted = pool.get<uint32_t>(n);
+    float3 cm = make_float3(cmin[0], cmin[1], cmin[2]);
+    float3 ci;
+    ci.x = cmax[0] > cmin[0] ? 1.0f / (cmax[0] - cmin[0]) : 0.0f;
+    ci.y = cmax[1] > cmin[1] ? 1.0f / (cmax[1] - cmin[1]) : 0.0f;
+    ci.z = cmax[2] > cmin[2] ? 1.0f / (cmax[2] - cmin[2]) : 0.0f;
+    k_morton<<<(n + B - 1) / B, B, 0, s>>>(plo, phi, n, cm, ci, keys, vals);
+    size_t tempBytes = 0;
+    GSB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tempBytes, keys, keysSorted, vals, sorted, (int)n, 0, 63, s));
+    void* temp = pool.get<uint8_t>(tempBytes);
+    GSB_CUDA(cub::DeviceRadixSort::SortPairs(temp, tempBytes, keys, keysSorted, vals, sorted, (int)n, 0, 63, s));
+
+    uint32_t* counters = pool.get<uint32_t>(4);
+    GSB_CUDA(cudaMemsetAsync(counters, 0, 4 * sizeof(uint32_t), s));
+    CollapseArgs ca;
+    ca.plo = plo;
+    ca.phi = phi;
+    ca.sorted = sorted;
+    ca.nodes = r.nodes;
+    ca.leafPrim = r.leafPrim;
+    ca.counters = counters;
+    if (n == 1) {
+        memset(&ca.t, 0, sizeof(ca.t));
+        k_singleLeafRoot<<<1, 1, 0, s>>>(ca);
+        GSB_CUDA(cudaGetLastError());
+        return r;
+    }
+    BinTree t;
+    t.left = pool.get<int>(n - 1);
+    t.right = pool.get<int>(n - 1);
+    t.parent = pool.get<int>(n - 1);
+    t.leafParent = pool.get<int>(n);
+    t.first = pool.get<uint32_t>(n - 1);
+    t.last = pool.get<uint32_t>(n - 1);
+    t.lo = pool.get<float4>(n - 1);
+    t.hi = pool.get<float4>(n - 1);
+    t.flags = pool.get<uint32_t>(n - 1);
+    GSB_CUDA(cudaMemsetAsync(t.flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
+    k_radixTree<<<(n - 1 + B - 1) / B, B, 0, s>>>(keysSorted, (int)n, t);
+    k_fitBoxes<<<(n + B - 1) / B, B, 0, s>>>(t, plo, phi, sorted, (int)n);
+    GSB_CUDA(cudaGetLastError());
+
+    double* dCost = pool.get<double>(2);
+    GSB_CUDA(cudaMemsetAsync(dCost, 0, 2 * sizeof(double), s));
+    const int costBlocks = (int)std::min<uint32_t>((n + B - 1) / B, 1024u);
+    k_sahCost<<<costBlocks, B, 0, s>>>(t, plo, phi, (int)n, dCost);
+    if (g_treelets && n >= 16) {
+        refineTreelets(pool.s, t, plo, phi, sorted, (int)n, [&](size_t bytes) { return (void*)pool.get<uint8_t>(bytes); });
+        k_sahCost<<<costBlocks, B, 0, s>>>(t, plo, phi, (int)n, dCost + 1);
+    }
+
+    // level-synchronous collapse
+    CollapseItem* itemsA = pool.get<CollapseItem>(n);
+    CollapseItem* itemsB = pool.get<CollapseItem>(n);
+    ca.t = t;
+    const CollapseItem rootItem = {0, 0u};
+    GSB_CUDA(cudaMemcpyAsync(itemsA, &rootItem, sizeof(rootItem), cudaMemcpyHostToDevice, s));
+    const uint32_t initCounters[4] = {1u, 0u, 0u, 0u};
+    GSB_CUDA(cudaMemcpyAsync(counters, initCounters, sizeof(initCounters), cudaMemcpyHostToDevice, s));
+    uint32_t nItems = 1;
+    uint32_t hostCounters[4];
+    while (nItems > 0) {
+        k_collapse<<<(nItems + 127) / 128, 128, 0, s>>>(ca, itemsA, nItems, itemsB);
+        GSB_CUDA(cudaMemcpyAsync(hostCounters, counters, sizeof(hostCounters), cudaMemcpyDeviceToHost, s));
+        GSB_CUDA(cudaStreamSynchronize(s));
+        nItems = hostCounters[2];
+        GSB_CUDA(cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), s));
+        std::swap(itemsA, itemsB);
+    }
+    r.numNodes = hostCounters[0];
+    double hostCost[2] = {0, 0};
+    GSB_CUDA(cudaMemcpyAsync(hostCost, dCost, sizeof(hostCost), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA(cudaStreamSynchronize(s));
+    out.sahBefore = hostCost[0];
+    out.sahAfter = (g_treelets && n >= 16) ? hostCost[1] : hostCost[0];
+    return r;
+}
+
+void finishBuffer(const GenericResult& r, uint32_t n, size_t leafBytes, cudaStream_t s, DeviceBvh& out) {
+    const size_t nodeBytes = (size_t)r.numNodes * 80;
+    out.numNodes = r.numNodes;
+    out.numPrims = n;
+    out.leafOffset16 = (uint32_t)(nodeBytes / 16);
+    out.bytes = nodeBytes + (size_t)n * leafBytes;
+    void* buf = nullptr;
+    GSB_CUDA(cudaMalloc(&buf, std::max<size_t>(out.bytes, 16)));
+    out.buffer = (uint4*)buf;
+    GSB_CUDA(cudaMemcpyAsync(out.buffer, r.nodes, nodeBytes, cudaMemcpyDeviceToDevice, s));
+}
+
+}  // namespace
+
+void setTreeletRefinement(bool enabled) { g_treelets = enabled; }
+
+void freeBvh(DeviceBvh& bvh) {
+    if (bvh.buffer) cudaFree(bvh.buffer);
+    bvh = DeviceBvh();
+}
+
+void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out) {
+    cudaEvent_t e0, e1;
+    GSB_CUDA(cudaEventCreate(&e0));
+    GSB_CUDA(cudaEventCreate(&e1));
+    GSB_CUDA(cudaEventRecord(e0, s));
+    {
+        TempPool pool(s);
+        const int B = 256;
+        float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+        float pad = 0.0f;
+        float4* plo = pool.get<float4>(ntris);
+        float4* phi = pool.get<float4>(ntris);
+        if (ntris > 0) {
+            BoundsAcc* acc = pool.get<BoundsAcc>(1);
+            k_initBounds<<<1, 32, 0, s>>>(acc);
+            const uint32_t nverts = ntris * 3;
+            k_vertexBounds<<<(int)std::min<uint32_t>((nverts + B - 1) / B, 2048u), B, 0, s>>>(dVertices, nverts, acc);
+            BoundsAcc h;
+            GSB_CUDA(cudaMemcpyAsync(&h, acc, sizeof(h), cudaMemcpyDeviceToHost, s));
+            GSB_CUDA(cudaStreamSynchronize(s));
+            float scale = 0.0f;
+            for (int a = 0; a < 3; a++) {
+                lo[a] = floatFromOrdered(h.lo[a]);
+                hi[a] = floatFromOrdered(h.hi[a]);
+                scale = std::fmax(scale, std::fmax(std::fabs(lo[a]), std::fabs(hi[a])));
+            }
+            pad = scale * kBoxPadRel;
+            k_triBoxes<<<(ntris + B - 1) / B, B, 0, s>>>(dVertices, ntris, pad, plo, phi);
+        }
+        GenericResult r = buildGeneric(pool, plo, phi, ntris, lo, hi, s, out);
+        finishBuffer(r, ntris, 48, s, out);
+        if (ntris > 0)
+            k_packTriangles<<<(ntris + B - 1) / B, B, 0, s>>>(r.leafPrim, ntris, dVertices,
+                                                              reinterpret_cast<float4*>(out.buffer + out.leafOffset16));
+        GSB_CUDA(cudaGetLastError());
+        for (int a = 0; a < 3; a++) { out.lo[a] = lo[a] - pad; out.hi[a] = hi[a] + pad; }
+    }
+    GSB_CUDA(cudaEventRecord(e1, s));
+    GSB_CUDA(cudaEventSynchronize(e1));
+    GSB_CUDA(cudaEventElapsedTime(&out.buildMs, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+}
+
+void buildTlas(const float* hostLo, const float* hostHi, const TraceInstance* hostRecords, uint32_t n, cudaStream_t s, DeviceBvh& out) {
+    cudaEvent_t e0, e1;
+    GSB_CUDA(cudaEventCreate(&e0));
+    GSB_CUDA(cudaEventCreate(&e1));
+    GSB_CUDA(cudaEventRecord(e0, s));
+    {
+        TempPool pool(s);
+        std::vector<float4> lo4(n), hi4(n);
+        float clo[3] = {INFINITY, INFINITY, INFINITY}, chi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t i = 0; i < n; i++) {
+            lo4[i] = make_float4(hostLo[3 * i], hostLo[3 * i + 1], hostLo[3 * i + 2], 0.0f);
+            hi4[i] = make_float4(hostHi[3 * i], hostHi[3 * i + 1], hostHi[3 * i + 2], 0.0f);
+            for (int a = 0; a < 3; a++) {
+                const float c = 0.5f * (hostLo[3 * i + a] + hostHi[3 * i + a]);
+                clo[a] = std::fmin(clo[a], c);
+                chi[a] = std::fmax(chi[a], c);
+                out.lo[a] = i == 0 ? hostLo[a] : std::fmin(out.lo[a], hostLo[3 * i + a]);
+                out.hi[a] = i == 0 ? hostHi[a] : std::fmax(out.hi[a], hostHi[3 * i + a]);
+            }
+        }
+        float4* plo = pool.get<float4>(n);
+        float4* phi = pool.get<float4>(n);
+        uint4* rec = pool.get<uint4>((size_t)n * 4);
+        if (n > 0) {
+            GSB_CUDA(cudaMemcpyAsync(plo, lo4.data(), (size_t)n * sizeof(float4), cudaMemcpyHostToDevice, s));
+            GSB_CUDA(cudaMemcpyAsync(phi, hi4.data(), (size_t)n * sizeof(float4), cudaMemcpyHostToDevice, s));
+            GSB_CUDA(cudaMemcpyAsync(rec, hostRecords, (size_t)n * sizeof(TraceInstance), cudaMemcpyHostToDevice, s));
+        }
+        GenericResult r = buildGeneric(pool, plo, phi, n, clo, chi, s, out);
+        finishBuffer(r, n, sizeof(TraceInstance), s, out);
+        if (n > 0) k_packInstances<<<(n + 255) / 256, 256, 0, s>>>(r.leafPrim, n, rec, out.buffer + out.leafOffset16);
+        GSB_CUDA(cudaGetLastError());
+        GSB_CUDA(cudaStreamSynchronize(s));  // lo4/hi4 host vectors must outlive the copies
+    }
+    GSB_CUDA(cudaEventRecord(e1, s));
+    GSB_CUDA(cudaEventSynchronize(e1));
+    GSB_CUDA(cudaEventElapsedTime(&out.buildMs, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+}
+
+}  // namespace gsb

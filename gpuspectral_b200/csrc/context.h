@@ -1,0 +1,85 @@
+// context.h — the opaque gsb_context behind the C ABI (internal).
+#pragma once
+
+#include <string>
+#include <vector>
+
+#include "bvh.h"
+#include "common.cuh"
+
+namespace gsb {
+
+struct MeshRec {
+    bool alive = false;
+    uint32_t ntris = 0;
+    float4* vpos = nullptr;  // 3 float4 per triangle, original primitive order
+    float4* vnrm = nullptr;
+    DeviceBvh blas;
+};
+
+// Queue indices inside WavefrontState::qCount
+enum { Q_MATERIAL0 = 0, Q_TERMINATED = GSB_BSDF_TYPE_COUNT, Q_SHADOW = GSB_BSDF_TYPE_COUNT + 1, Q_COUNT = 12 };
+
+// Per-slot path state, structure of arrays.  The 17-word HitPayload of pt_common.glsl:4-14
+// (+ pixel sample index and the hit record) spread over 16-byte and 4-byte streams.
+struct WavefrontState {
+    uint32_t capacity = 0;      // slots allocated
+    float4* rayO = nullptr;     // origin.xyz
+    float4* rayD = nullptr;     // direction.xyz
+    float4* weightDW = nullptr; // weight.xyz, directWeight
+    float4* result = nullptr;   // radiance of the current sample .xyz, flags bits in .w
+    uint32_t* seed = nullptr;
+    uint32_t* sampleK = nullptr;  // index of the sample this slot works on; 0xffffffff = slot retired
+    float4* hitTUVP = nullptr;    // t, u, v, primitive id bits
+    uint32_t* hitInst = nullptr;
+    uint32_t* matQueue = nullptr;   // GSB_BSDF_TYPE_COUNT queues of `capacity` slot ids each
+    uint32_t* termQueue = nullptr;
+    float4* shadowO = nullptr;      // origin.xyz, tmax
+    float4* shadowD = nullptr;      // direction.xyz, slot id bits
+    float4* shadowBase = nullptr;   // emitted without NEE .xyz, directWeight if visible
+    float4* shadowNee = nullptr;    // NEE contribution .xyz
+    float4* laneAccum = nullptr;    // per-slot accumulation when several slots share a pixel
+    uint32_t laneAccumCapacity = 0;
+    uint32_t* qCount = nullptr;     // Q_COUNT queue counters
+    // device statistics block: [0] live slots, [1] retirements this iteration, [2..] totals
+    unsigned long long* stats = nullptr;
+};
+
+enum { ST_LIVE = 0, ST_RETIRED = 1, ST_PATHS = 2, ST_EXT = 3, ST_SHADOW = 4, ST_ITERS = 5, ST_NODES = 6, ST_TRIS = 7, ST_INSTS = 8, ST_RAYS = 9, ST_OVERFLOW = 10, ST_COUNT = 16 };
+
+}  // namespace gsb
+
+struct gsb_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::vector<gsb::MeshRec> meshes;
+    std::vector<gsb_instance> instances;
+    gsb::DeviceBvh tlas;
+    gsb::ShadeInstance* dShade = nullptr;
+    uint32_t* dInstBsdf = nullptr;
+    void* dBsdf[GSB_BSDF_TYPE_COUNT] = {};
+    uint32_t bsdfCount[GSB_BSDF_TYPE_COUNT] = {};
+    bool typeUsed[GSB_BSDF_TYPE_COUNT] = {};
+    gsb_triangle_light* dLights = nullptr;
+    uint32_t numLights = 0;
+    float eye[3] = {0, 0, 0};
+    float view[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    float fov = 1.0f;
+    gsb_params params = {50, 10, 20.0f, 1};
+    bool haveInstances = false;
+    double lastBuildMs = 0.0;
+
+    uint32_t width = 0, height = 0;
+    float4* dAccum = nullptr;  // rgb = sum of samples, a = samples added
+    gsb::WavefrontState wf;
+    bool profiling = false;
+    double lastRenderMs[5] = {0, 0, 0, 0, 0};
+
+    gsb::SceneDev sceneDev() const;
+};
+
+namespace gsb {
+// wavefront.cu
+void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t first, uint32_t count, uint32_t stride);
+void freeWavefront(gsb_context* ctx);
+}  // namespace gsb

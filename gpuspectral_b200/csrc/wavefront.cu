@@ -1,0 +1,498 @@
+// wavefront.cu — the wavefront path tracer.
+//
+// The reference runs one megakernel-by-recursion per pixel (raygen.rgen:29-109 calling
+// rayhit.rchit:666-797 through traceRayEXT).  Here the same per-path state machine is cut
+// into stages that each run as one wide kernel over many paths:
+//
+//   k_extend   closest-hit traversal of every live path's ray  (raygen.rgen:54-58), bins the
+//              hits into one queue per BSDF type, misses (miss.rmiss) into the finish queue
+//   k_shade<T> material-sorted closest-hit shading             (rayhit.rchit:666-797) + the
+//              per-bounce bookkeeping of the raygen loop       (raygen.rgen:59-80)
+//   k_shadow   any-hit traversal of the NEE segments           (rayhit.rchit:737-757)
+//   k_finish   adds finished samples to the image (raygen.rgen:84-108) and starts the slot's
+//              next sample (raygen.rgen:31-48)
+//
+// A slot owns one pixel (or one of K sample lanes of a pixel when the image is small) for the
+// whole call and works through its samples in timestamp order, so image accumulation needs no
+// atomics and is deterministic.  Every path carries its own RNG word; each stage consumes
+// draws in the order the shader does, which makes per-path results match the checker's.
+#include <algorithm>
+#include <cstdio>
+#include <vector>
+
+#include "bsdf.cuh"
+#include "context.h"
+#include "traverse.cuh"
+
+namespace gsb {
+
+namespace {
+
+constexpr int kBlock = 128;
+constexpr uint32_t kRetired = 0xffffffffu;
+constexpr uint32_t kFlagWasDelta = 1u << 16;
+constexpr uint32_t kFlagCountEmitted = 1u << 17;
+
+struct RenderArgs {
+    uint32_t width, height, npix;
+    uint32_t first, count, stride;  // timestamps first + k*stride, k < count
+    uint32_t lanes;                 // slots per pixel
+    uint32_t slots;                 // npix * lanes
+    float4* accum;                  // where slot s accumulates: accum[s] (lanes == 1: the image itself)
+};
+
+// Warp-aggregated append: every lane of the warp must call this (pred false = no push).
+// key selects one of the queue counters; returns the position for lanes with pred.
+GSB_D uint32_t queueSlot(uint32_t* counters, uint32_t key, bool pred) {
+    const uint32_t k = pred ? key : 0xffffu;
+    const uint32_t peers = __match_any_sync(0xffffffffu, k);
+    uint32_t base = 0;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t leader = (uint32_t)__ffs(peers) - 1u;
+    if (pred && lane == leader) base = atomicAdd(&counters[key], (uint32_t)__popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+}
+
+// raygen.rgen:20-48: seed + primary ray + payload initialisation for sample k of the slot's pixel
+GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderArgs& ra, uint32_t slot, uint32_t k) {
+    const uint32_t pixel = slot % ra.npix;
+    const uint32_t x = pixel % ra.width, y = pixel / ra.width;
+    const uint32_t timestamp = ra.first + k * ra.stride;
+    // rayDir(size, fragCoord, fov)
+    const float sx = (float)ra.width, sy = (float)ra.height;
+    const float fx = (float)x - sx / 2.0f;
+    const float fy = (float)y - sy / 2.0f;
+    const float z = (fmaxf(sx, sy) / 2.0f) / tanf(sc.fov / 2.0f);
+    const float3 dir = normalize(f3(-fx, fy, z));
+    const float* V = sc.view;
+    float3 d = f3(V[0] * dir.x + V[4] * dir.y + V[8] * dir.z, V[1] * dir.x + V[5] * dir.y + V[9] * dir.z,
+                  V[2] * dir.x + V[6] * dir.y + V[10] * dir.z);
+    d.y *= -1.0f;
+    wf.seed[slot] = pcgHash(tea(ra.width * y + x, timestamp));
+    wf.rayO[slot] = make_float4(sc.eye[0], sc.eye[1], sc.eye[2], 0.0f);
+    wf.rayD[slot] = make_float4(d.x, d.y, d.z, 0.0f);
+    wf.weightDW[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+    wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kFlagCountEmitted));  // depth 0, wasDelta 0, countEmitted 1
+    wf.sampleK[slot] = k;
+}
+
+__global__ void k_generate(SceneDev sc, WavefrontState wf, RenderArgs ra) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= ra.slots) return;
+    const uint32_t lane = slot / ra.npix;
+    if (lane < ra.count) startPath(sc, wf, ra, slot, lane);
+    else wf.sampleK[slot] = kRetired;
+}
+
+// ---- extend ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState wf, uint32_t slots) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    bool live = slot < slots;
+    if (live) live = wf.sampleK[slot] != kRetired;
+    uint32_t key = 0;
+    if (live) {
+        const float4 o = wf.rayO[slot], d = wf.rayD[slot];
+        HitRecord hit;
+        traceRay<false, false>(sc, o.x, o.y, o.z, d.x, d.y, d.z, 0.0f, 1e10f, hit, nullptr, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+        wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.prim));
+        wf.hitInst[slot] = hit.inst;
+        key = hit.inst == GSB_NO_HIT ? (uint32_t)Q_TERMINATED : (__ldg(sc.instBsdf + hit.inst) >> 16);
+    }
+    const uint32_t pos = queueSlot(wf.qCount, key, live);
+    if (live) {
+        if (key == Q_TERMINATED) wf.termQueue[pos] = slot;
+        else wf.matQueue[(size_t)key * wf.capacity + pos] = slot;
+    }
+}
+
+// ---- shade ----------------------------------------------------------------------------------------
+template <int TYPE>
+__global__ void __launch_bounds__(kBlock) k_shade(SceneDev sc, WavefrontState wf) {
+    const uint32_t count = wf.qCount[TYPE];
+    const uint32_t* queue = wf.matQueue + (size_t)TYPE * wf.capacity;
+    const uint32_t rounds = (count + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
+    for (uint32_t r = 0; r < rounds; r++) {
+        const uint32_t i = (r * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        const bool active = i < count;
+        bool terminate = false, needShadow = false;
+        uint32_t slot = 0;
+        float4 shO, shD, shBase, shNee;
+        if (active) {
+            slot = queue[i];
+            const float4 ro = wf.rayO[slot], rd = wf.rayD[slot];
+            const float4 hit = wf.hitTUVP[slot];
+            const uint32_t inst = wf.hitInst[slot];
+            uint32_t rng = wf.seed[slot];                                         // rayhit.rchit:668
+            float4 wdw = wf.weightDW[slot];
+            float4 res = wf.result[slot];
+            uint32_t flags = __float_as_uint(res.w);
+            float3 weight = xyz(wdw);
+            const float directWeight = wdw.w;
+            const uint32_t prim = __float_as_uint(hit.w);
+
+            // :671-688 instance record, positions through object->world, normals through transformInvT
+            const float4* si = reinterpret_cast<const float4*>(sc.shadeInst + inst);
+            const float4 m0 = __ldg(si), m1 = __ldg(si + 1), m2 = __ldg(si + 2);
+            const float4 n0 = __ldg(si + 3), n1 = __ldg(si + 4), n2 = __ldg(si + 5);
+            const uint4 p0 = __ldg(reinterpret_cast<const uint4*>(si) + 6);
+            const uint4 p1 = __ldg(reinterpret_cast<const uint4*>(si) + 7);
+            const float4* vpos = reinterpret_cast<const float4*>(((uint64_t)p0.y << 32) | p0.x);
+            const float4* vnrm = reinterpret_cast<const float4*>(((uint64_t)p0.w << 32) | p0.z);
+            const uint32_t handle = p1.x, twofaced = p1.y;
+            const float3 emission = f3(n0.w, n1.w, n2.w);
+            float3 pos[3], nrm[3];
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const float4 p = __ldg(vpos + 3 * (size_t)prim + k);
+                const float4 n = __ldg(vnrm + 3 * (size_t)prim + k);
+                pos[k] = f3(m0.x * p.x + m0.y * p.y + m0.z * p.z + m0.w, m1.x * p.x + m1.y * p.y + m1.z * p.z + m1.w,
+                            m2.x * p.x + m2.y * p.y + m2.z * p.z + m2.w);
+                nrm[k] = f3(n0.x * n.x + n0.y * n.y + n0.z * n.z, n1.x * n.x + n1.y * n.y + n1.z * n.z,
+                            n2.x * n.x + n2.y * n.y + n2.z * n.z);
+            }
+            const float3 bary = f3(1.0f - hit.y - hit.z, hit.y, hit.z);               // :690
+            const float3 rayDir = xyz(rd);                                          // :696
+            const float3 position = xyz(ro) + rayDir * hit.x;                        // :692
+            float3 SN = normalize(bary.x * nrm[0] + bary.y * nrm[1] + bary.z * nrm[2]);  // :693
+            float3 N = normalize(cross(pos[1] - pos[0], pos[2] - pos[0]));           // :694
+            if (dot(N, -rayDir) < 0.0f) {                                            // :698-707
+                if (twofaced == 1u && emission.x == 0.0f && emission.y == 0.0f && emission.z == 0.0f) {
+                    N = N * -1.0f;
+                    SN = SN * -1.0f;
+                }
+            }
+            const Onb onb = onbCreate(SN);                                           // :712
+            const float3 wo = normalize(onbTransform(onb, -rayDir));                 // :713
+            BSDFOutput bsdfRes;
+            bsdfRes.bsdf = f3(0.0f); bsdfRes.pdf = 0.0f; bsdfRes.isDelta = false;
+            float3 wi = f3(0.0f);
+            sampleBSDFT<TYPE>(sc, handle & 0xffffu, rng, wo, wi, bsdfRes);            // :716
+            const float NoW = fabsf(wi.z);                                           // :717
+            wi = onbUntransform(onb, wi);                                            // :718
+
+            bool haveLight;
+            const LightOutput lightRes = sampleLight(sc, rng, position, haveLight);  // :720
+            const float3 L = normalize(lightRes.position - position);                // :722
+            const float3 wL = onbTransform(onb, L);                                  // :723
+            const float Ldist = length(lightRes.position - position);                // :724
+            const float NoL = fabsf(dot(SN, L));                                     // :725
+            const float lightPdf = lightRes.pdf;                                     // :726
+            BSDFOutput lightBsdfRes;
+            lightBsdfRes.bsdf = f3(0.0f); lightBsdfRes.pdf = 0.0f; lightBsdfRes.isDelta = false;
+            evalBSDFT<TYPE>(sc, handle & 0xffffu, wo, wL, lightBsdfRes);             // :729
+
+            const bool transmissive = isTransmissionBSDF(TYPE);
+            const float NdotV = dot(N, -rayDir);
+            float3 nee = f3(0.0f);
+            float dwVisible = 1.0f;
+            if (sc.params.nee && haveLight && !bsdfRes.isDelta &&
+                ((NdotV > 0.0f && dot(N, L) > 0.0f) || transmissive)) {              // :734-736
+                needShadow = true;
+                if (lightPdf != 0.0f) {                                              // :750-753, applied if the segment is free
+                    const float w = powerHeuristic(lightPdf, bsdfRes.pdf);
+                    nee = w * NoL * lightBsdfRes.bsdf * weight * lightRes.emission / lightPdf;
+                    dwVisible = powerHeuristic(bsdfRes.pdf, lightPdf);               // :786
+                }
+            }
+            // :760-768 surface emission
+            const float lightFlag = NdotV > 0.0f ? 1.0f : 0.0f;
+            const bool NEE = sc.params.nee != 0;
+            const bool countEmitted = (flags & kFlagCountEmitted) != 0, wasDelta = (flags & kFlagWasDelta) != 0;
+            float3 emitted = f3(0.0f);
+            if (NEE && !countEmitted && !wasDelta) emitted = emitted + directWeight * emission * lightFlag * weight;
+            if (!NEE || countEmitted || wasDelta) emitted = emitted + emission * lightFlag * weight;
+
+            // :770-796 termination tests and next-ray setup
+            bool done = false;
+            if (dot(wi, N) <= 0.0f && !transmissive) done = true;
+            else if (NdotV <= 0.0f && !transmissive) done = true;
+            else if (!isvalidf(bsdfRes.pdf) || !isvalid3(bsdfRes.bsdf) || bsdfRes.pdf == 0.0f) done = true;
+            float3 newO = xyz(ro), newD = rayDir;
+            if (!done) {
+                flags &= ~(kFlagCountEmitted | kFlagWasDelta);
+                newO = position + 0.0001f * faceforward(N, -wi, N);
+                newD = wi;
+                weight = weight * (bsdfRes.bsdf * NoW / bsdfRes.pdf);
+                if (bsdfRes.isDelta) flags |= kFlagWasDelta;
+            }
+            // raygen.rgen:59-80.  The Russian-roulette draw reads a COPY of the payload seed
+            // (rngState = prd.seed is never written back), so the path's stream does not advance.
+            uint32_t depth = flags & 0xffffu;
+            if ((int)depth > sc.params.rr_start) {
+                const float q = fminf(fmaxf(fmaxf(fmaxf(weight.x, weight.y), weight.z), 0.05f), 1.0f);
+                uint32_t rr = rng;
+                if (randUniform(rr) > q) terminate = true;
+                weight = weight / q;
+            }
+            if ((int)depth > sc.params.max_depth) terminate = true;
+            if (done) terminate = true;
+            if (!terminate) flags = (flags & ~0xffffu) | (depth + 1u);
+
+            if (needShadow) {
+                shO = make_float4(position.x, position.y, position.z, Ldist - 0.01f);
+                shD = make_float4(L.x, L.y, L.z, __uint_as_float(slot));
+                shBase = make_float4(emitted.x, emitted.y, emitted.z, dwVisible);
+                shNee = make_float4(nee.x, nee.y, nee.z, 0.0f);
+            } else {
+                const float cutoff = sc.params.cutoff;                               // raygen.rgen:60-63
+                if (emitted.x < cutoff && emitted.y < cutoff && emitted.z < cutoff) {
+                    res.x += emitted.x; res.y += emitted.y; res.z += emitted.z;
+                }
+            }
+            res.w = __uint_as_float(flags);
+            wf.result[slot] = res;
+            wf.seed[slot] = rng;                                                     // rayhit.rchit:759
+            if (!terminate) {
+                wf.rayO[slot] = make_float4(newO.x, newO.y, newO.z, 0.0f);
+                wf.rayD[slot] = make_float4(newD.x, newD.y, newD.z, 0.0f);
+                wf.weightDW[slot] = make_float4(weight.x, weight.y, weight.z, 1.0f);  // directWeight 1 unless the shadow stage finds the light
+            }
+        }
+        const uint32_t sp = queueSlot(wf.qCount, Q_SHADOW, needShadow);
+        if (needShadow) {
+            wf.shadowO[sp] = shO;
+            wf.shadowD[sp] = shD;
+            wf.shadowBase[sp] = shBase;
+            wf.shadowNee[sp] = shNee;
+        }
+        const uint32_t tp = queueSlot(wf.qCount, Q_TERMINATED, terminate);
+        if (terminate) wf.termQueue[tp] = slot;
+    }
+}
+
+// ---- shadow ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState wf) {
+    const uint32_t count = wf.qCount[Q_SHADOW];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const float4 o = wf.shadowO[i], d = wf.shadowD[i];
+        HitRecord hit;
+        traceRay<true, false>(sc, o.x, o.y, o.z, d.x, d.y, d.z, 0.01f, o.w, hit, nullptr, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+        const bool visible = hit.inst == GSB_NO_HIT;
+        const uint32_t slot = __float_as_uint(d.w);
+        const float4 base = wf.shadowBase[i];
+        float3 emitted = f3(0.0f);
+        if (visible) {
+            const float4 nee = wf.shadowNee[i];
+            emitted = emitted + xyz(nee);                                            // rayhit.rchit:752
+            wf.weightDW[slot].w = base.w;                                            // :786 (neeDone)
+        }
+        emitted = emitted + xyz(base);                                               // :763-768
+        const float cutoff = sc.params.cutoff;                                       // raygen.rgen:60-63
+        if (emitted.x < cutoff && emitted.y < cutoff && emitted.z < cutoff) {
+            float4 res = wf.result[slot];
+            res.x += emitted.x; res.y += emitted.y; res.z += emitted.z;
+            wf.result[slot] = res;
+        }
+    }
+}
+
+// ---- finish + regenerate ----------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock) k_finish(SceneDev sc, WavefrontState wf, RenderArgs ra) {
+    const uint32_t count = wf.qCount[Q_TERMINATED];
+    uint32_t retired = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        const uint32_t slot = wf.termQueue[i];
+        const float4 res = wf.result[slot];
+        // raygen.rgen:106-108: a NaN sample leaves the image untouched
+        if (!(isnan(res.x) || isnan(res.y) || isnan(res.z))) {
+            float4 a = ra.accum[slot];
+            a.x += res.x; a.y += res.y; a.z += res.z; a.w += 1.0f;
+            ra.accum[slot] = a;
+        }
+        const uint32_t k = wf.sampleK[slot] + ra.lanes;
+        if (k < ra.count) startPath(sc, wf, ra, slot, k);
+        else { wf.sampleK[slot] = kRetired; retired++; }
+    }
+    for (int o = 16; o > 0; o >>= 1) retired += __shfl_xor_sync(0xffffffffu, retired, o);
+    if ((threadIdx.x & 31) == 0 && retired) atomicAdd(&wf.stats[ST_RETIRED], (unsigned long long)retired);
+}
+
+// one thread: roll the iteration's queue sizes into the totals and clear the queues
+__global__ void k_endIteration(WavefrontState wf) {
+    unsigned long long* st = wf.stats;
+    st[ST_EXT] += st[ST_LIVE];
+    st[ST_SHADOW] += wf.qCount[Q_SHADOW];
+    st[ST_PATHS] += wf.qCount[Q_TERMINATED];
+    st[ST_ITERS] += 1;
+    st[ST_LIVE] -= st[ST_RETIRED];
+    st[ST_RETIRED] = 0;
+    for (int q = 0; q < Q_COUNT; q++) wf.qCount[q] = 0;
+}
+
+__global__ void k_mergeLanes(const float4* __restrict__ laneAccum, uint32_t npix, uint32_t lanes, float4* __restrict__ accum) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    float4 a = accum[p];
+    for (uint32_t l = 0; l < lanes; l++) {
+        const float4 v = laneAccum[(size_t)l * npix + p];
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    accum[p] = a;
+}
+
+template <class T>
+void ensure(T*& p, size_t count) {
+    if (p) cudaFree(p);
+    p = nullptr;
+    void* q = nullptr;
+    GSB_CUDA(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)));
+    p = (T*)q;
+}
+
+void allocWavefront(gsb_context* ctx, uint32_t slots) {
+    WavefrontState& wf = ctx->wf;
+    if (wf.capacity >= slots && wf.qCount) return;
+    const size_t n = slots;
+    ensure(wf.rayO, n); ensure(wf.rayD, n); ensure(wf.weightDW, n); ensure(wf.result, n);
+    ensure(wf.seed, n); ensure(wf.sampleK, n); ensure(wf.hitTUVP, n); ensure(wf.hitInst, n);
+    ensure(wf.matQueue, n * GSB_BSDF_TYPE_COUNT); ensure(wf.termQueue, n);
+    ensure(wf.shadowO, n); ensure(wf.shadowD, n); ensure(wf.shadowBase, n); ensure(wf.shadowNee, n);
+    if (!wf.qCount) ensure(wf.qCount, (size_t)Q_COUNT);
+    if (!wf.stats) {
+        ensure(wf.stats, (size_t)ST_COUNT);
+        GSB_CUDA(cudaMemsetAsync(wf.stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
+    }
+    wf.capacity = slots;
+}
+
+template <int TYPE>
+void launchShade(gsb_context* ctx, const SceneDev& sc, int grid) {
+    k_shade<TYPE><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf);
+}
+
+}  // namespace
+
+void freeWavefront(gsb_context* ctx) {
+    WavefrontState& wf = ctx->wf;
+    void* ptrs[] = {wf.rayO, wf.rayD, wf.weightDW, wf.result, wf.seed, wf.sampleK, wf.hitTUVP, wf.hitInst, wf.matQueue,
+                    wf.termQueue, wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.laneAccum, wf.qCount, wf.stats};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    wf = WavefrontState();
+}
+
+void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t first, uint32_t count, uint32_t stride) {
+    cudaStream_t s = ctx->stream;
+    const uint32_t npix = width * height;
+    if (ctx->width != width || ctx->height != height || !ctx->dAccum) {
+        ensure(ctx->dAccum, (size_t)npix);
+        GSB_CUDA(cudaMemsetAsync(ctx->dAccum, 0, (size_t)npix * sizeof(float4), s));
+        ctx->width = width;
+        ctx->height = height;
+    }
+    if (count == 0) return;
+    // enough slots to fill the machine: about one million paths in flight
+    const uint32_t targetSlots = 1u << 20;
+    uint32_t lanes = std::max<uint32_t>(1u, std::min<uint32_t>(count, (targetSlots + npix - 1) / npix));
+    const uint32_t slots = npix * lanes;
+    allocWavefront(ctx, slots);
+    WavefrontState& wf = ctx->wf;
+    RenderArgs ra;
+    ra.width = width; ra.height = height; ra.npix = npix;
+    ra.first = first; ra.count = count; ra.stride = stride;
+    ra.lanes = lanes; ra.slots = slots;
+    if (lanes == 1) {
+        ra.accum = ctx->dAccum;
+    } else {
+        if (wf.laneAccumCapacity < slots) {
+            ensure(wf.laneAccum, (size_t)slots);
+            wf.laneAccumCapacity = slots;
+        }
+        GSB_CUDA(cudaMemsetAsync(wf.laneAccum, 0, (size_t)slots * sizeof(float4), s));
+        ra.accum = wf.laneAccum;
+    }
+    const SceneDev sc = ctx->sceneDev();
+    GSB_CUDA(cudaMemsetAsync(wf.qCount, 0, Q_COUNT * sizeof(uint32_t), s));
+    const unsigned long long liveInit[2] = {(unsigned long long)npix * std::min<uint32_t>(lanes, count), 0ull};
+    GSB_CUDA(cudaMemcpyAsync(wf.stats, liveInit, sizeof(liveInit), cudaMemcpyHostToDevice, s));
+
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    GSB_CUDA(cudaEventCreate(&evStart));
+    GSB_CUDA(cudaEventCreate(&evStop));
+    GSB_CUDA(cudaEventRecord(evStart, s));
+
+    const int fullGrid = (int)((slots + kBlock - 1) / kBlock);
+    int dev = ctx->device, sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int queueGrid = std::min(fullGrid, sms * 16);
+    k_generate<<<fullGrid, kBlock, 0, s>>>(sc, wf, ra);
+
+    // stage timing (profiling mode): events around every stage of every iteration
+    const bool prof = ctx->profiling;
+    std::vector<cudaEvent_t> pev;
+    auto mark = [&]() {
+        if (!prof) return;
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, s);
+        pev.push_back(e);
+    };
+
+    auto iteration = [&]() {
+        mark();
+        k_extend<<<fullGrid, kBlock, 0, s>>>(sc, wf, slots);
+        mark();
+        if (ctx->typeUsed[0]) launchShade<0>(ctx, sc, queueGrid);
+        if (ctx->typeUsed[1]) launchShade<1>(ctx, sc, queueGrid);
+        if (ctx->typeUsed[2]) launchShade<2>(ctx, sc, queueGrid);
+        if (ctx->typeUsed[3]) launchShade<3>(ctx, sc, queueGrid);
+        if (ctx->typeUsed[4]) launchShade<4>(ctx, sc, queueGrid);
+        if (ctx->typeUsed[5]) launchShade<5>(ctx, sc, queueGrid);
+        if (ctx->typeUsed[6]) launchShade<6>(ctx, sc, queueGrid);
+        if (ctx->typeUsed[7]) launchShade<7>(ctx, sc, queueGrid);
+        mark();
+        k_shadow<<<queueGrid, kBlock, 0, s>>>(sc, wf);
+        mark();
+        k_finish<<<queueGrid, kBlock, 0, s>>>(sc, wf, ra);
+        k_endIteration<<<1, 1, 0, s>>>(wf);
+        mark();
+    };
+
+    // Host loop: batches of iterations; the live-slot count of batch b is read back while batch
+    // b+1 is already queued, so the device never waits for the host.
+    const int batch = 8;
+    unsigned long long* hLive = nullptr;
+    GSB_CUDA(cudaMallocHost(&hLive, 2 * sizeof(unsigned long long)));
+    cudaEvent_t evBatch[2];
+    GSB_CUDA(cudaEventCreate(&evBatch[0]));
+    GSB_CUDA(cudaEventCreate(&evBatch[1]));
+    int b = 0;
+    bool finished = false;
+    while (!finished) {
+        for (int i = 0; i < batch; i++) iteration();
+        GSB_CUDA(cudaMemcpyAsync(&hLive[b & 1], &wf.stats[ST_LIVE], sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+        GSB_CUDA(cudaEventRecord(evBatch[b & 1], s));
+        if (b > 0) {
+            GSB_CUDA(cudaEventSynchronize(evBatch[(b - 1) & 1]));
+            if (hLive[(b - 1) & 1] == 0) finished = true;
+        }
+        b++;
+        if (prof && pev.size() > 200000) break;
+    }
+    if (lanes > 1) k_mergeLanes<<<(npix + 255) / 256, 256, 0, s>>>(wf.laneAccum, npix, lanes, ctx->dAccum);
+    GSB_CUDA(cudaEventRecord(evStop, s));
+    GSB_CUDA(cudaEventSynchronize(evStop));
+    GSB_CUDA(cudaGetLastError());
+    float ms = 0.0f;
+    GSB_CUDA(cudaEventElapsedTime(&ms, evStart, evStop));
+    ctx->lastRenderMs[0] = ms;
+    for (int k = 1; k < 5; k++) ctx->lastRenderMs[k] = 0.0;
+    if (prof) {
+        for (size_t i = 0; i + 4 < pev.size(); i += 5) {
+            for (int k = 0; k < 4; k++) {
+                float t = 0.0f;
+                cudaEventElapsedTime(&t, pev[i + k], pev[i + k + 1]);
+                ctx->lastRenderMs[1 + k] += t;
+            }
+        }
+        for (cudaEvent_t e : pev) cudaEventDestroy(e);
+    }
+    cudaEventDestroy(evBatch[0]);
+    cudaEventDestroy(evBatch[1]);
+    cudaEventDestroy(evStart);
+    cudaEventDestroy(evStop);
+    cudaFreeHost(hLive);
+}
+
+}  // namespace gsb

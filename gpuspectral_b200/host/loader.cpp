@@ -1,0 +1,436 @@
+// loader.cpp — Mitsuba XML (+ OBJ) -> Scene, headless.
+//
+// Follows the conventions of the reference's engine/Loader.cpp (the caller side of the
+// render-path boundary):
+//   :19-64    OBJ -> one vertex per face index, indices 0..n-1 (polygons fan-triangulated)
+//   :145-234  bsdf plugins twosided / diffuse / roughplastic / dielectric / conductor / plastic /
+//             roughconductor; alpha_gpu = sqrt(2) * alpha_xml (:179,:225); R0 = ((ior-1)/(ior+1))^2
+//             (:172-173,:205-206); plastic int_ior default 1.3; conductor `eta` read as a number
+//             (missing -> 0 -> perfect mirror, :193-195); nested bsdfs visited recursively
+//   :269-330  shapes obj / rectangle / cube (+ disk, whose mesh the reference never shipped) in
+//             document order = instance order; row-major to_world -> column-major; `center`
+//             overrides the translation; area emitter -> emission + one TriangleLight per triangle
+//   :331-337  perspective sensor: fov degrees -> radians with a float pi, to_world
+// The XML itself is read by the small parser in xml.cpp (the reference uses TinyParser-Mitsuba):
+// <default>/$name substitution, <ref id>, camelCase -> snake_case property names for scene
+// versions < 2 (tinyparser-mitsuba.cpp:55-77), <transform> made of matrix / translate / scale /
+// rotate / lookat applied in document order.
+#include <cctype>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <map>
+#include <sstream>
+#include <stdexcept>
+
+#include "scene.h"
+#include "xml.h"
+
+namespace gsbhost {
+namespace {
+
+constexpr float kPiF = 3.14159265358979323846f;  // utils/Util.h:5 defines M_PI as a float
+
+std::string readFile(const std::string& path) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) throw std::runtime_error("cannot open " + path);
+    std::stringstream ss;
+    ss << f.rdbuf();
+    return ss.str();
+}
+
+std::string dirOf(const std::string& path) {
+    size_t p = path.find_last_of("/\\");
+    return p == std::string::npos ? std::string(".") : path.substr(0, p);
+}
+
+std::string snakeCase(const std::string& s) {
+    if (s.empty()) return s;
+    std::string out(1, (char)std::tolower((unsigned char)s[0]));
+    for (size_t i = 1; i < s.size(); i++) {
+        if (std::isupper((unsigned char)s[i]) && s[i - 1] != '_' && std::islower((unsigned char)s[i - 1])) out += '_';
+        out += (char)std::tolower((unsigned char)s[i]);
+    }
+    return out;
+}
+
+std::vector<float> parseNumbers(const std::string& s) {
+    std::vector<float> out;
+    const char* p = s.c_str();
+    while (*p) {
+        while (*p && (std::isspace((unsigned char)*p) || *p == ',')) p++;
+        if (!*p) break;
+        char* end = nullptr;
+        float v = std::strtof(p, &end);
+        if (end == p) break;
+        out.push_back(v);
+        p = end;
+    }
+    return out;
+}
+
+struct Ctx {
+    std::string baseDir;
+    bool camelCase = true;  // scene version major < 2
+    std::map<std::string, std::string> defaults;
+    std::map<std::string, const XmlNode*> ids;
+    std::map<std::string, uint32_t> meshCache;
+    Scene* scene = nullptr;
+
+    std::string subst(const std::string& v) const {
+        if (v.find('$') == std::string::npos) return v;
+        std::string out;
+        for (size_t i = 0; i < v.size();) {
+            if (v[i] != '$') { out += v[i++]; continue; }
+            size_t j = i + 1;
+            while (j < v.size() && (std::isalnum((unsigned char)v[j]) || v[j] == '_')) j++;
+            auto it = defaults.find(v.substr(i + 1, j - i - 1));
+            out += it == defaults.end() ? v.substr(i, j - i) : it->second;
+            i = j;
+        }
+        return out;
+    }
+    std::string propName(const XmlNode& n) const {
+        const std::string* nm = n.attr("name");
+        if (!nm) return "";
+        return camelCase ? snakeCase(*nm) : *nm;
+    }
+    const XmlNode* resolve(const XmlNode& n) const {
+        if (n.tag != "ref") return &n;
+        const std::string* id = n.attr("id");
+        if (!id) return nullptr;
+        auto it = ids.find(*id);
+        return it == ids.end() ? nullptr : it->second;
+    }
+    // first direct child that is a property element with this (normalised) name
+    const XmlNode* prop(const XmlNode& parent, const std::string& name) const {
+        for (auto& c : parent.children)
+            if (c->attr("name") && propName(*c) == name) return c.get();
+        return nullptr;
+    }
+    bool number(const XmlNode& parent, const std::string& name, float& out) const {
+        const XmlNode* p = prop(parent, name);
+        if (!p || (p->tag != "float" && p->tag != "integer")) return false;
+        auto v = parseNumbers(subst(p->attrOr("value", "")));
+        if (v.empty()) return false;
+        out = v[0];
+        return true;
+    }
+    // rgb / spectrum (uniform or taken as rgb when 3 values) -> colour; false when absent or a texture
+    bool color(const XmlNode& parent, const std::string& name, float out[3]) const {
+        const XmlNode* p = prop(parent, name);
+        if (!p || (p->tag != "rgb" && p->tag != "spectrum" && p->tag != "srgb" && p->tag != "float")) return false;
+        auto v = parseNumbers(subst(p->attrOr("value", "")));
+        if (v.size() >= 3) { out[0] = v[0]; out[1] = v[1]; out[2] = v[2]; return true; }
+        if (v.size() == 1) { out[0] = out[1] = out[2] = v[0]; return true; }
+        return false;
+    }
+    bool boolean(const XmlNode& parent, const std::string& name, bool fallback) const {
+        const XmlNode* p = prop(parent, name);
+        if (!p || p->tag != "boolean") return fallback;
+        return subst(p->attrOr("value", "")) == "true";
+    }
+    std::string str(const XmlNode& parent, const std::string& name) const {
+        const XmlNode* p = prop(parent, name);
+        return p ? subst(p->attrOr("value", "")) : std::string();
+    }
+    void warn(const std::string& w) const { scene->warnings.push_back(w); }
+};
+
+bool vec3Attr(const Ctx& c, const XmlNode& n, const char* packed, float def, float out[3]) {
+    if (const std::string* v = n.attr(packed)) {
+        auto nums = parseNumbers(c.subst(*v));
+        if (nums.size() >= 3) { out[0] = nums[0]; out[1] = nums[1]; out[2] = nums[2]; return true; }
+        if (nums.size() == 1) { out[0] = out[1] = out[2] = nums[0]; return true; }
+    }
+    bool any = false;
+    const char* names[3] = {"x", "y", "z"};
+    for (int i = 0; i < 3; i++) {
+        out[i] = def;
+        if (const std::string* v = n.attr(names[i])) {
+            auto nums = parseNumbers(c.subst(*v));
+            if (!nums.empty()) { out[i] = nums[0]; any = true; }
+        }
+    }
+    return any;
+}
+
+// <transform>: each child op is left-multiplied onto the running matrix (Mitsuba semantics)
+void parseTransform(const Ctx& c, const XmlNode* t, float* out) {
+    matIdentity(out);
+    if (!t) return;
+    for (auto& op : t->children) {
+        float m[16];
+        matIdentity(m);
+        if (op->tag == "matrix") {
+            auto v = parseNumbers(c.subst(op->attrOr("value", "")));
+            if (v.size() == 16) matFromRowMajor(v.data(), m);
+            else if (v.size() == 9) {
+                const float rm[16] = {v[0], v[1], v[2], 0, v[3], v[4], v[5], 0, v[6], v[7], v[8], 0, 0, 0, 0, 1};
+                matFromRowMajor(rm, m);
+            }
+        } else if (op->tag == "translate") {
+            float d[3];
+            vec3Attr(c, *op, "value", 0.0f, d);
+            matTranslate(d[0], d[1], d[2], m);
+        } else if (op->tag == "scale") {
+            float s[3];
+            if (!vec3Attr(c, *op, "value", 1.0f, s)) s[0] = s[1] = s[2] = 1.0f;
+            matScale(s[0], s[1], s[2], m);
+        } else if (op->tag == "rotate") {
+            float a[3];
+            if (!vec3Attr(c, *op, "axis", 0.0f, a)) { a[0] = 0; a[1] = 0; a[2] = 1; }
+            auto ang = parseNumbers(c.subst(op->attrOr("angle", "0")));
+            matRotate(a[0], a[1], a[2], ang.empty() ? 0.0f : ang[0], m);
+        } else if (op->tag == "lookat" || op->tag == "lookAt") {
+            float o[3], tg[3], up[3] = {0, 0, 1};
+            bool ok = vec3Attr(c, *op, "origin", 0.0f, o) && vec3Attr(c, *op, "target", 0.0f, tg);
+            if (op->attr("up")) vec3Attr(c, *op, "up", 0.0f, up);
+            if (ok) matLookAt(o, tg, up, m);
+        } else {
+            continue;
+        }
+        matMul(m, out, out);
+    }
+}
+
+// Loader.cpp:145-234
+void loadMaterial(Ctx& c, Material& material, const XmlNode& obj) {
+    Scene& scene = *c.scene;
+    const std::string type = obj.attrOr("type", "");
+    auto iorAndR0 = [&](float& ior, float& R0) {
+        float ext = 1.0f;
+        if (c.number(obj, "ext_ior", ext) && std::fabs(ext - 1.0f) > 0.001f) c.warn("unsupported ext ior of plastic");
+        if (!c.number(obj, "int_ior", ior)) ior = 1.3f;
+        R0 = (ior - 1.0f) / (ior + 1.0f);
+        R0 *= R0;
+    };
+    if (type == "twosided") {
+        material.twofaced = true;
+    } else if (type == "diffuse") {
+        gsb_diffuse_bsdf b = {{0.0f, 0.0f, 0.0f}, 0};
+        if (!c.color(obj, "reflectance", b.reflectance)) {
+            if (c.prop(obj, "reflectance")) c.warn("diffuse: textured reflectance is not supported, using 0.5");
+            b.reflectance[0] = b.reflectance[1] = b.reflectance[2] = 0.5f;
+        }
+        material.bsdf = scene.addDiffuseBSDF(b);
+        material.hasBsdf = true;
+    } else if (type == "roughplastic") {
+        gsb_rough_plastic_bsdf b;
+        std::memset(&b, 0, sizeof(b));
+        if (!c.color(obj, "diffuse_reflectance", b.diffuse)) b.diffuse[0] = b.diffuse[1] = b.diffuse[2] = 0.5f;
+        float alpha = 0.1f;
+        c.number(obj, "alpha", alpha);
+        iorAndR0(b.iorIn, b.R0);
+        b.iorOut = 1.0f;
+        b.alpha = (float)std::sqrt(2.0f) * alpha;
+        material.bsdf = scene.addRoughPlasticBSDF(b);
+        material.hasBsdf = true;
+    } else if (type == "dielectric") {
+        gsb_smooth_dielectric_bsdf b = {1.5046f, 1.000277f};
+        c.number(obj, "int_ior", b.iorIn);
+        c.number(obj, "ext_ior", b.iorOut);
+        material.bsdf = scene.addSmoothDielectricBSDF(b);
+        material.hasBsdf = true;
+    } else if (type == "conductor") {
+        gsb_smooth_conductor_bsdf b = {0.0f, 1.0f};
+        c.number(obj, "eta", b.iorIn);
+        material.bsdf = scene.addSmoothConductorBSDF(b);
+        material.hasBsdf = true;
+    } else if (type == "plastic") {
+        gsb_smooth_plastic_bsdf b;
+        std::memset(&b, 0, sizeof(b));
+        if (!c.color(obj, "diffuse_reflectance", b.diffuse)) b.diffuse[0] = b.diffuse[1] = b.diffuse[2] = 0.5f;
+        iorAndR0(b.iorIn, b.R0);
+        b.iorOut = 1.0f;
+        material.bsdf = scene.addSmoothPlasticBSDF(b);
+        material.hasBsdf = true;
+    } else if (type == "roughconductor") {
+        gsb_rough_conductor_bsdf b;
+        std::memset(&b, 0, sizeof(b));
+        c.color(obj, "eta", b.eta);
+        c.color(obj, "k", b.k);
+        if (!c.color(obj, "specular_reflectance", b.reflectance)) b.reflectance[0] = b.reflectance[1] = b.reflectance[2] = 1.0f;
+        float alpha = 0.1f;
+        c.number(obj, "alpha", alpha);
+        b.alpha = (float)std::sqrt(2) * alpha;
+        material.bsdf = scene.addRoughConductorBSDF(b);
+        material.hasBsdf = true;
+    } else {
+        c.warn("bsdf plugin '" + type + "' is not supported by the reference loader");
+    }
+    for (auto& child : obj.children) {
+        if (child->attr("name")) continue;  // named children are properties, not nested bsdfs
+        const XmlNode* r = c.resolve(*child);
+        if (r && r->tag == "bsdf") loadMaterial(c, material, *r);
+    }
+}
+
+uint32_t meshFor(Ctx& c, const std::string& key) {
+    auto it = c.meshCache.find(key);
+    if (it != c.meshCache.end()) return it->second;
+    MeshData m;
+    if (key == "builtin:rectangle") m = makeRectangle();
+    else if (key == "builtin:cube") m = makeCube();
+    else m = loadObjMesh(key);
+    uint32_t id = c.scene->addMesh(std::move(m));
+    c.meshCache.emplace(key, id);
+    return id;
+}
+
+void collectIds(const XmlNode& n, std::map<std::string, const XmlNode*>& ids) {
+    if (n.tag != "ref")
+        if (const std::string* id = n.attr("id")) ids.emplace(*id, &n);
+    for (auto& c : n.children) collectIds(*c, ids);
+}
+
+Scene buildScene(const XmlNode& root, const std::string& baseDir) {
+    if (root.tag != "scene") throw std::runtime_error("mitsuba: root element is <" + root.tag + ">, expected <scene>");
+    Scene scene;
+    Ctx c;
+    c.scene = &scene;
+    c.baseDir = baseDir;
+    const std::string version = root.attrOr("version", "0.5.0");
+    c.camelCase = std::atoi(version.c_str()) < 2;
+    collectIds(root, c.ids);
+    for (auto& n : root.children)
+        if (n->tag == "default")
+            if (n->attr("name") && n->attr("value")) c.defaults.emplace(*n->attr("name"), *n->attr("value"));
+
+    for (auto& n : root.children) {
+        if (n->tag == "shape") {
+            const std::string type = n->attrOr("type", "");
+            std::string key;
+            if (type == "obj") key = baseDir + "/" + c.str(*n, "filename");
+            else if (type == "rectangle") key = "builtin:rectangle";
+            else if (type == "cube") key = "builtin:cube";
+            else {
+                c.warn("shape plugin '" + type + "' is not supported, skipped");
+                continue;
+            }
+            RenderObject obj;
+            obj.mesh = meshFor(c, key);
+            const XmlNode* tw = c.prop(*n, "to_world");
+            parseTransform(c, (tw && tw->tag == "transform") ? tw : nullptr, obj.transform);
+            if (const XmlNode* center = c.prop(*n, "center")) {
+                float p[3];
+                if (vec3Attr(c, *center, "value", 0.0f, p)) {
+                    obj.transform[12] = p[0]; obj.transform[13] = p[1]; obj.transform[14] = p[2]; obj.transform[15] = 1.0f;
+                }
+            }
+            Material material;
+            for (auto& child : n->children) {
+                if (child->attr("name")) continue;
+                const XmlNode* r = c.resolve(*child);
+                if (!r) continue;
+                if (r->tag == "bsdf") loadMaterial(c, material, *r);
+                else if (r->tag == "emitter" && r->attrOr("type", "") == "area") c.color(*r, "radiance", material.emission);
+            }
+            if (!material.hasBsdf) {
+                c.warn("shape without a supported bsdf: using diffuse 0.5");
+                material.bsdf = scene.addDiffuseBSDF({{0.5f, 0.5f, 0.5f}, 0});
+                material.hasBsdf = true;
+            }
+            material.facenormals = c.boolean(*n, "face_normals", false);
+            obj.material = scene.addMaterial(material);
+            scene.addRenderObject(obj);
+        } else if (n->tag == "sensor") {
+            float fov = 45.0f;
+            c.number(*n, "fov", fov);
+            scene.camera.fov = fov * kPiF / 180.f;
+            const XmlNode* tw = c.prop(*n, "to_world");
+            parseTransform(c, (tw && tw->tag == "transform") ? tw : nullptr, scene.camera.toWorld);
+            for (auto& child : n->children)
+                if (child->tag == "film") {
+                    float w = 0, h = 0;
+                    if (c.number(*child, "width", w)) scene.filmWidth = (uint32_t)w;
+                    if (c.number(*child, "height", h)) scene.filmHeight = (uint32_t)h;
+                }
+        } else if (n->tag == "emitter") {
+            c.warn("scene-level emitter '" + n->attrOr("type", "") + "' ignored (the reference has no environment light)");
+        }
+    }
+    return scene;
+}
+
+}  // namespace
+
+Scene loadMitsubaSceneFromString(const std::string& xml, const std::string& baseDir) {
+    auto root = parseXml(xml);
+    return buildScene(*root, baseDir);
+}
+
+Scene loadMitsubaScene(const std::string& xmlPath) {
+    return loadMitsubaSceneFromString(readFile(xmlPath), dirOf(xmlPath));
+}
+
+// Wavefront OBJ: v / vn / f (vt accepted and ignored).  Faces are fan-triangulated and
+// un-indexed.  Where a corner has no normal the geometric face normal is used.
+MeshData loadObjMesh(const std::string& objPath) {
+    std::ifstream f(objPath);
+    if (!f) throw std::runtime_error("cannot open " + objPath);
+    MeshData m;
+    m.name = objPath;
+    std::vector<float> V, N;
+    std::string line;
+    struct Corner { int v, n; };
+    std::vector<Corner> corners;
+    while (std::getline(f, line)) {
+        const char* p = line.c_str();
+        while (*p == ' ' || *p == '\t') p++;
+        if (p[0] == 'v' && (p[1] == ' ' || p[1] == '\t')) {
+            auto nums = parseNumbers(p + 2);
+            if (nums.size() >= 3) V.insert(V.end(), nums.begin(), nums.begin() + 3);
+        } else if (p[0] == 'v' && p[1] == 'n' && (p[2] == ' ' || p[2] == '\t')) {
+            auto nums = parseNumbers(p + 3);
+            if (nums.size() >= 3) N.insert(N.end(), nums.begin(), nums.begin() + 3);
+        } else if (p[0] == 'f' && (p[1] == ' ' || p[1] == '\t')) {
+            corners.clear();
+            p += 2;
+            while (*p) {
+                while (*p == ' ' || *p == '\t' || *p == '\r') p++;
+                if (!*p) break;
+                char* end = nullptr;
+                long vi = std::strtol(p, &end, 10);
+                if (end == p) break;
+                long ni = 0;
+                p = end;
+                if (*p == '/') {
+                    p++;
+                    if (*p != '/') { std::strtol(p, &end, 10); p = end; }  // vt
+                    if (*p == '/') {
+                        p++;
+                        ni = std::strtol(p, &end, 10);
+                        p = end;
+                    }
+                }
+                const int nv = (int)(V.size() / 3), nn = (int)(N.size() / 3);
+                Corner c;
+                c.v = vi > 0 ? (int)vi - 1 : nv + (int)vi;
+                c.n = ni > 0 ? (int)ni - 1 : (ni < 0 ? nn + (int)ni : -1);
+                if (c.v < 0 || c.v >= nv) throw std::runtime_error(objPath + ": face references a missing vertex");
+                if (c.n >= nn) c.n = -1;
+                corners.push_back(c);
+            }
+            for (size_t k = 1; k + 1 < corners.size(); k++) {
+                const Corner tri[3] = {corners[0], corners[k], corners[k + 1]};
+                const float* a = &V[3 * (size_t)tri[0].v];
+                const float* b = &V[3 * (size_t)tri[1].v];
+                const float* c3 = &V[3 * (size_t)tri[2].v];
+                float e1[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, e2[3] = {c3[0] - a[0], c3[1] - a[1], c3[2] - a[2]};
+                float fn[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+                float l = std::sqrt(fn[0] * fn[0] + fn[1] * fn[1] + fn[2] * fn[2]);
+                if (l > 0.0f) { fn[0] /= l; fn[1] /= l; fn[2] /= l; }
+                for (const Corner& cr : tri) {
+                    m.positions.insert(m.positions.end(), &V[3 * (size_t)cr.v], &V[3 * (size_t)cr.v] + 3);
+                    if (cr.n >= 0) m.normals.insert(m.normals.end(), &N[3 * (size_t)cr.n], &N[3 * (size_t)cr.n] + 3);
+                    else m.normals.insert(m.normals.end(), fn, fn + 3);
+                }
+            }
+        }
+    }
+    return m;
+}
+
+}  // namespace gsbhost

@@ -1,0 +1,64 @@
+// path_tracer.h — the host-side render pass, shaped like the reference's plugin.
+//
+// The reference registers `PathTracer : RenderPassCreator` with its Renderer
+// (renderer/Renderer.h:22-25, renderer/PathTracer.h:48-68); every frame the renderer calls
+// createRenderPass(frameGraph, scene), which rebuilds the TLAS, re-uploads the instance / BSDF /
+// light arrays and the RenderState UBO, records traceRays(w, h) for ONE sample per pixel and
+// bumps `timestamp` (renderer/PathTracer.cpp:9-93).
+//
+// This class keeps that shape — setup(), createRenderPass(scene), a running `timestamp` — but
+// talks to the CUDA core through the C ABI of include/gpuspectral_b200.h: the scene is uploaded
+// and its BVH built once (when the scene object changes), each createRenderPass adds one sample
+// per pixel, and render() batches many samples in one device-side wavefront run.
+#pragma once
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "scene.h"
+
+namespace gsbhost {
+
+class PathTracer {
+  public:
+    // device_ordinal: CUDA device of this process (one process per GPU).
+    explicit PathTracer(int device_ordinal = 0);
+    ~PathTracer();
+    PathTracer(const PathTracer&) = delete;
+    PathTracer& operator=(const PathTracer&) = delete;
+
+    // PathTracer::setup (PathTracer.cpp:5-7): fixes the frame size, clears the accumulation image.
+    void setup(uint32_t width, uint32_t height);
+    void setParams(const gsb_params& p);
+
+    // One frame of the reference: one sample per pixel with timestamp = this->timestamp++.
+    void createRenderPass(const Scene& scene);
+    // `spp` frames at once: timestamps timestamp, timestamp + stride, ... (stride > 1 = this GPU's
+    // share of a sample-sharded multi-GPU render).
+    void render(const Scene& scene, uint32_t spp, uint32_t stride = 1);
+
+    void uploadScene(const Scene& scene);  // explicit (re)upload + BVH build
+    void readHDR(std::vector<float>& rgba);
+    void readLDR(std::vector<uint8_t>& rgba8);
+    void synchronize();
+
+    gsb_context* context() const { return ctx; }
+    uint32_t width() const { return w; }
+    uint32_t height() const { return h; }
+    int timestamp = 0;  // PathTracer.h:65
+
+  private:
+    gsb_context* ctx = nullptr;
+    uint32_t w = 0, h = 0;
+    const Scene* uploaded = nullptr;
+    size_t uploadedObjects = 0;
+    std::vector<uint32_t> meshHandles;
+};
+
+// Image writers for the headless framebuffer.
+void writePFM(const std::string& path, const float* rgba, uint32_t width, uint32_t height);
+void writePPM(const std::string& path, const uint8_t* rgba8, uint32_t width, uint32_t height);
+void writePNG(const std::string& path, const uint8_t* rgba8, uint32_t width, uint32_t height);
+
+}  // namespace gsbhost

@@ -1,0 +1,220 @@
+/*
+ * gpuspectral_b200.h — C ABI of the B200-native path-tracing core.
+ *
+ * This library stands where the reference's ray-tracing driver operators and
+ * its PathTracer plugin glue stand (paths relative to the reference checkout):
+ *
+ *   HwDriver::createBLAS / createTLAS / destroyBLAS / destroyTLAS / traceRays
+ *       src/GPUSpectral/backend/Command.inc:83-87
+ *   RTInstance / RTSceneDescriptor / Ray / RayHit
+ *       src/GPUSpectral/backend/DriverTypes.h:253-276
+ *   PathTracer::setup / createRenderPass / prepareScene, RenderState
+ *       src/GPUSpectral/renderer/PathTracer.cpp:5-93, PathTracer.h:9-46
+ *   raygen.rgen / rayhit.rchit / miss.rmiss / shadowmiss.rmiss (the device code)
+ *       src/GPUSpectral/assets/shaders/
+ *
+ * Conventions
+ *   - plain C, no exceptions: every call returns a gsb_status; the message of
+ *     the last failure on the calling thread is gsb_last_error().
+ *   - the library copies every input during the call; the caller may free its
+ *     arrays as soon as the call returns.  Device memory belongs to the context.
+ *   - one context per GPU, externally synchronised (single-threaded use),
+ *     mirroring the reference's single-threaded frame loop.
+ *   - matrices are column-major float[16] (glm::mat4 memory order).
+ */
+#ifndef GPUSPECTRAL_B200_H
+#define GPUSPECTRAL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define GSB_API __attribute__((visibility("default")))
+#else
+#define GSB_API
+#endif
+
+typedef struct gsb_context gsb_context;
+
+typedef enum gsb_status {
+    GSB_OK = 0,
+    GSB_ERR_INVALID = 1, /* bad argument / handle / range */
+    GSB_ERR_CUDA = 2,    /* a CUDA runtime call or kernel failed */
+    GSB_ERR_STATE = 3,   /* call order violated (e.g. render before scene) */
+    GSB_ERR_OOM = 4
+} gsb_status;
+
+/* BSDF type ids = enum order of assets/shaders/BSDF.inc (rayhit.rchit:332-339). */
+enum {
+    GSB_BSDF_DIFFUSE = 0,
+    GSB_BSDF_SMOOTH_DIELECTRIC = 1,
+    GSB_BSDF_SMOOTH_CONDUCTOR = 2,
+    GSB_BSDF_SMOOTH_PLASTIC = 3,
+    GSB_BSDF_ROUGH_CONDUCTOR = 4,
+    GSB_BSDF_SMOOTH_FLOOR = 5,
+    GSB_BSDF_ROUGH_FLOOR = 6,
+    GSB_BSDF_ROUGH_PLASTIC = 7,
+    GSB_BSDF_TYPE_COUNT = 8
+};
+
+/* BSDF handle = type<<16 | index (renderer/Scene.h:84-97, pt_common.glsl:32-42). */
+#define GSB_BSDF_HANDLE(type, index) ((((uint32_t)(type)) << 16) | ((uint32_t)(index) & 0xffffu))
+
+/* Parameter records: byte-for-byte the host structs of renderer/Scene.h:29-82
+ * ("scalar" block layout on the shader side, rayhit.rchit:22-70). */
+typedef struct gsb_diffuse_bsdf { float reflectance[3]; int32_t hasTexture; } gsb_diffuse_bsdf;                 /* 16 B */
+typedef struct gsb_smooth_dielectric_bsdf { float iorIn; float iorOut; } gsb_smooth_dielectric_bsdf;           /*  8 B */
+typedef struct gsb_smooth_conductor_bsdf { float iorIn; float iorOut; } gsb_smooth_conductor_bsdf;             /*  8 B */
+typedef struct gsb_smooth_floor_bsdf { float diffuse[3]; float R0; } gsb_smooth_floor_bsdf;                    /* 16 B */
+typedef struct gsb_smooth_plastic_bsdf { float diffuse[3]; float iorIn; float iorOut; float R0; } gsb_smooth_plastic_bsdf; /* 24 B */
+typedef struct gsb_rough_conductor_bsdf {
+    float eta[3]; float k[3]; float reflectance[3]; float alpha; int32_t hasTexture;
+} gsb_rough_conductor_bsdf;                                                                                     /* 44 B */
+typedef struct gsb_rough_plastic_bsdf {
+    float diffuse[3]; float iorIn; float iorOut; float R0; float alpha; int32_t hasTexture;
+} gsb_rough_plastic_bsdf;                                                                                       /* 32 B */
+typedef struct gsb_rough_floor_bsdf { float diffuse[3]; float R0; float alpha; } gsb_rough_floor_bsdf;         /* 20 B */
+
+/* renderer/Scene.h:106-109: world-space triangle light, 64 B. radiance[3] unused. */
+typedef struct gsb_triangle_light { float positions[3][4]; float radiance[4]; } gsb_triangle_light;
+
+/* One render object: RTInstance{blas, transform} (DriverTypes.h:253-256) joined with
+ * RenderState::Instance (PathTracer.h:27-34).  `mesh` replaces both the BLAS handle and
+ * the position/normal device addresses; the inverse-transpose normal matrix
+ * (PathTracer.cpp:62) is derived inside the library.  Instance index = array order
+ * = gl_InstanceID. */
+typedef struct gsb_instance {
+    float transform[16]; /* object -> world, column-major */
+    uint32_t mesh;       /* handle from gsb_mesh_create */
+    float emission[3];
+    uint32_t bsdf;       /* GSB_BSDF_HANDLE */
+    uint32_t twofaced;
+} gsb_instance;          /* 88 B */
+
+/* DriverTypes.h:263-270 (32 B). */
+typedef struct gsb_ray { float origin[3]; float tmin; float dir[3]; float tmax; } gsb_ray;
+
+/* Result of one traced ray.  Closest hit: t, barycentrics (u = weight of vertex 1,
+ * v = weight of vertex 2: the hitAttributeEXT convention of rayhit.rchit:690),
+ * inst = gl_InstanceID, prim = gl_PrimitiveID.  Miss: inst = prim = GSB_NO_HIT, t = tmax.
+ * Any-hit mode: inst = 0 when occluded, GSB_NO_HIT when the segment is free. */
+typedef struct gsb_hit { float t; float u; float v; uint32_t inst; uint32_t prim; } gsb_hit;
+#define GSB_NO_HIT 0xffffffffu
+
+/* Integrator constants that are shader literals in the reference, with the
+ * reference's values as defaults (gsb_default_params):
+ *   max_depth 50 (raygen.rgen:27,73), rr_start 10 (:66), cutoff 20 (:60), nee 1 (rayhit.rchit:656). */
+typedef struct gsb_params { int32_t max_depth; int32_t rr_start; float cutoff; int32_t nee; } gsb_params;
+
+/* Device-side statistics since the last gsb_clear / gsb_reset_counters. */
+typedef struct gsb_counters {
+    uint64_t paths;           /* pixel-samples completed */
+    uint64_t extension_rays;  /* closest-hit rays traced */
+    uint64_t shadow_rays;     /* any-hit rays traced */
+    uint64_t iterations;      /* wavefront iterations launched */
+    /* filled only by instrumented traversal (gsb_trace_batch_stats) */
+    uint64_t nodes_visited;   /* 8-wide nodes fetched (80 B each) */
+    uint64_t tris_tested;     /* triangles fetched (48 B each) */
+    uint64_t inst_entered;    /* instance records fetched (64 B each) */
+    uint64_t rays_counted;
+} gsb_counters;
+
+/* Acceleration-structure statistics of the current scene. */
+typedef struct gsb_bvh_stats {
+    uint64_t num_meshes, num_instances;
+    uint64_t unique_triangles, instanced_triangles;
+    uint64_t blas_nodes, tlas_nodes;   /* 8-wide nodes */
+    uint64_t bvh_bytes;                /* nodes + packed triangles + instance records */
+    double   build_ms;                 /* device time of the last build (all BLAS + TLAS) */
+    double   sah_cost_before, sah_cost_after; /* binary-tree SAH before/after treelet refinement, summed over meshes */
+} gsb_bvh_stats;
+
+/* ---- context ------------------------------------------------------------------- */
+GSB_API gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx);
+GSB_API gsb_status gsb_destroy(gsb_context* ctx);
+GSB_API const char* gsb_last_error(void);
+GSB_API const char* gsb_version(void);
+
+/* ---- scene (replaces Mesh uploads + createBLAS/createTLAS + prepareScene) -------- */
+/* Non-indexed triangle soup, 3 consecutive vertices per triangle, tightly packed float3
+ * positions and normals (renderer/Mesh.cpp:7-22; VulkanRays.cpp:17-35).  nverts % 3 == 0.
+ * Builds the mesh's bottom-level BVH on the device. */
+GSB_API gsb_status gsb_mesh_create(gsb_context* ctx, const float* positions3, const float* normals3,
+                                   uint32_t nverts, uint32_t* out_mesh);
+GSB_API gsb_status gsb_mesh_destroy(gsb_context* ctx, uint32_t mesh);
+/* Replaces the instance list and builds the top-level BVH once (the reference rebuilds
+ * its TLAS every frame, PathTracer.cpp:10-19). */
+GSB_API gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instances, uint32_t count);
+/* type in [0, GSB_BSDF_TYPE_COUNT); params = array of the matching gsb_*_bsdf record. */
+GSB_API gsb_status gsb_scene_set_bsdfs(gsb_context* ctx, uint32_t type, const void* params, uint32_t count);
+GSB_API gsb_status gsb_scene_set_lights(gsb_context* ctx, const gsb_triangle_light* lights, uint32_t count);
+/* eye = toWorld[3].xyz in the reference (PathTracer.cpp:88-90); passed separately as there. */
+GSB_API gsb_status gsb_set_camera(gsb_context* ctx, const float eye[3], const float to_world[16], float fov_radians);
+GSB_API gsb_status gsb_default_params(gsb_params* out);
+GSB_API gsb_status gsb_set_params(gsb_context* ctx, const gsb_params* params);
+GSB_API gsb_status gsb_get_bvh_stats(gsb_context* ctx, gsb_bvh_stats* out);
+
+/* ---- render (replaces traceRays(pipeline, w, h), one launch = one sample/pixel) --- */
+/* Renders samples with timestamp = first_sample + k*sample_stride, k in [0, num_samples),
+ * for every pixel of a width x height frame and adds them to the context's accumulation
+ * buffer (allocated/cleared when the size changes).  Asynchronous on the context's stream. */
+GSB_API gsb_status gsb_render(gsb_context* ctx, uint32_t width, uint32_t height,
+                              uint32_t first_sample, uint32_t num_samples, uint32_t sample_stride);
+GSB_API gsb_status gsb_clear(gsb_context* ctx);       /* zero accumulation + counters */
+GSB_API gsb_status gsb_synchronize(gsb_context* ctx);
+/* Mean radiance, RGBA32F, row 0 = top (raygen.rgen:84-108); alpha = 1.  Synchronises. */
+GSB_API gsb_status gsb_read_hdr(gsb_context* ctx, float* out_rgba);
+/* 8-bit sRGB encode of the clamped mean, no tone map: what presenting the RGBA32F image
+ * to the B8G8R8A8_SRGB swapchain does (DrawTexture.frag:9-13).  RGBA byte order. */
+GSB_API gsb_status gsb_read_ldr(gsb_context* ctx, uint8_t* out_rgba8);
+/* Device pointer to the float4 accumulation buffer (rgb = sum of samples, a = number of
+ * samples added) for an external reduction across GPUs (NCCL), and its size in bytes. */
+GSB_API gsb_status gsb_device_sum_ptr(gsb_context* ctx, void** out_ptr, size_t* out_bytes);
+GSB_API gsb_status gsb_get_counters(gsb_context* ctx, gsb_counters* out);
+GSB_API gsb_status gsb_reset_counters(gsb_context* ctx);
+/* Device time (ms, CUDA events on the context's stream) of the last gsb_render, split by
+ * stage: [0] total, [1] extend traversal, [2] shade, [3] shadow traversal, [4] finish/regen.
+ * Stage times are only collected when profiling is enabled. */
+GSB_API gsb_status gsb_set_profiling(gsb_context* ctx, int enabled);
+GSB_API gsb_status gsb_last_render_ms(gsb_context* ctx, double out_ms[5]);
+
+/* ---- ray batches (the intersection-parity entry; Ray/RayHit of DriverTypes.h) ----- */
+/* Host arrays in, host arrays out.  any_hit = 0: closest hit; 1: occlusion only. */
+GSB_API gsb_status gsb_trace_batch(gsb_context* ctx, const gsb_ray* rays, uint32_t count,
+                                   gsb_hit* out_hits, int any_hit);
+/* Same rays through the instrumented traversal kernel: also accumulates nodes/tris/inst
+ * fetch counts into the context counters (algorithmic bytes per ray). */
+GSB_API gsb_status gsb_trace_batch_stats(gsb_context* ctx, const gsb_ray* rays, uint32_t count,
+                                         gsb_hit* out_hits, int any_hit);
+/* Device-resident variant for timing traversal alone: uploads once, then launches the
+ * traversal kernel `repeats` times and reports the mean kernel time in ms. */
+GSB_API gsb_status gsb_trace_batch_timed(gsb_context* ctx, const gsb_ray* rays, uint32_t count,
+                                         int any_hit, int repeats, double* out_ms_per_launch);
+
+/* ---- diagnostic entry points (unit parity against the oracle) ---------------------- */
+/* Seeds exactly as raygen.rgen:37 for pixel-linear index idx and frame `timestamp`, then
+ * draws n_draws values of randPcg(); out has n*(1+n_draws) words: seed, draws... */
+GSB_API gsb_status gsb_test_rng(gsb_context* ctx, const uint32_t* idx, const uint32_t* timestamp, uint32_t n,
+                                uint32_t n_draws, uint32_t* out);
+/* Primary rays of a width x height launch (raygen.rgen:20-35) for pixels px[i], py[i]. */
+GSB_API gsb_status gsb_test_camera_rays(gsb_context* ctx, uint32_t width, uint32_t height,
+                                        const uint32_t* px, const uint32_t* py, uint32_t n, gsb_ray* out);
+/* sampleBSDF / evalBSDF (rayhit.rchit:630-654) on the scene's BSDF tables.
+ * sample: in  wo[3n], seed[n];  out wi[3n], f[3n], pdf[n], is_delta[n], seed_out[n].
+ * eval:   in  wo[3n], wi[3n];   out f[3n], pdf[n], is_delta[n]. */
+GSB_API gsb_status gsb_test_bsdf_sample(gsb_context* ctx, uint32_t bsdf_handle, const float* wo, const uint32_t* seed,
+                                        uint32_t n, float* wi, float* f, float* pdf, uint32_t* is_delta, uint32_t* seed_out);
+GSB_API gsb_status gsb_test_bsdf_eval(gsb_context* ctx, uint32_t bsdf_handle, const float* wo, const float* wi,
+                                      uint32_t n, float* f, float* pdf, uint32_t* is_delta);
+/* sampleLight (rayhit.rchit:123-153): in pos[3n], seed[n]; out lpos[3n], emission[3n], pdf[n], seed_out[n]. */
+GSB_API gsb_status gsb_test_sample_light(gsb_context* ctx, const float* pos, const uint32_t* seed, uint32_t n,
+                                         float* lpos, float* emission, float* pdf, uint32_t* seed_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPUSPECTRAL_B200_H */

@@ -1,0 +1,221 @@
+"""ctypes binding of the CPU oracle (oracle/liboracle.so).  TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.  The product package (gpuspectral_b200/) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "liboracle.so")
+
+RAY_DTYPE = np.dtype([("origin", np.float32, 3), ("tmin", np.float32), ("dir", np.float32, 3), ("tmax", np.float32)])
+HIT_DTYPE = np.dtype([("t", np.float32), ("u", np.float32), ("v", np.float32), ("inst", np.uint32), ("prim", np.uint32)])
+BOUNCE_DTYPE = np.dtype([("inst", np.uint32), ("prim", np.uint32), ("t", np.float32), ("emitted", np.float32, 3),
+                         ("weight", np.float32, 3), ("seed", np.uint32), ("shadow_cast", np.uint32), ("shadow_visible", np.uint32)])
+NO_HIT = 0xFFFFFFFF
+
+
+class Params(C.Structure):
+    _fields_ = [("max_depth", C.c_int32), ("rr_start", C.c_int32), ("cutoff", C.c_float), ("nee", C.c_int32)]
+
+
+class Counters(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in ("paths", "extension_rays", "shadow_rays", "rng_draws")]
+
+
+def build(force=False):
+    """Compiles liboracle.so with oracle/Makefile when it is missing or older than its sources."""
+    srcs = [os.path.join(_HERE, f) for f in ("oracle.cpp", "oracle.h", "Makefile")]
+    srcs.append(os.path.join(_HERE, "..", "include", "gpuspectral_b200.h"))
+    stale = force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs)
+    if stale:
+        subprocess.run(["make", "-C", _HERE, "-B", "liboracle.so"], check=True, capture_output=True)
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        L = C.CDLL(_SO)
+        P, u32p, f32p = C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_float)
+        sig = {
+            "or_scene_create": (P, []),
+            "or_scene_destroy": (None, [P]),
+            "or_scene_add_mesh": (C.c_uint32, [P, f32p, f32p, C.c_uint32]),
+            "or_scene_set_instances": (C.c_int, [P, P, C.c_uint32]),
+            "or_scene_set_bsdfs": (C.c_int, [P, C.c_uint32, P, C.c_uint32]),
+            "or_scene_set_lights": (C.c_int, [P, P, C.c_uint32]),
+            "or_scene_set_camera": (None, [P, f32p, f32p, C.c_float]),
+            "or_scene_set_params": (None, [P, C.POINTER(Params)]),
+            "or_render": (C.c_int, [P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, f32p, C.c_int, C.c_int, C.POINTER(Counters)]),
+            "or_path_probe": (C.c_int, [P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, f32p, P, C.c_uint32]),
+            "or_trace_batch": (C.c_int, [P, P, C.c_uint32, P, C.c_int, C.c_int, C.c_int]),
+            "or_tea": (C.c_uint32, [C.c_uint32, C.c_uint32]),
+            "or_pcg_hash": (C.c_uint32, [C.c_uint32]),
+            "or_rng": (None, [u32p, u32p, C.c_uint32, C.c_uint32, u32p]),
+            "or_rand_to_float": (C.c_float, [C.c_uint32]),
+            "or_camera_rays": (None, [P, C.c_uint32, C.c_uint32, u32p, u32p, C.c_uint32, P]),
+            "or_bsdf_sample": (C.c_int, [P, C.c_uint32, f32p, u32p, C.c_uint32, f32p, f32p, f32p, u32p, u32p]),
+            "or_bsdf_eval": (C.c_int, [P, C.c_uint32, f32p, f32p, C.c_uint32, f32p, f32p, u32p]),
+            "or_sample_light": (C.c_int, [P, f32p, u32p, C.c_uint32, f32p, f32p, f32p, u32p]),
+            "or_encode_srgb8": (None, [f32p, C.c_uint32, C.POINTER(C.c_uint8)]),
+        }
+        for name, (res, args) in sig.items():
+            f = getattr(L, name)
+            f.restype, f.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+def _up(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint32))
+
+
+class OracleScene:
+    """The oracle's scene, fed with the same flat records as the product's C ABI."""
+
+    def __init__(self):
+        self._s = C.c_void_p(lib().or_scene_create())
+        self.set_params()
+
+    def __del__(self):
+        s, self._s = getattr(self, "_s", None), None
+        if s and _lib is not None:
+            _lib.or_scene_destroy(s)
+
+    @staticmethod
+    def from_host_scene(scene):
+        """scene: gpuspectral_b200.Scene (the host layer's flat arrays; no product compute involved)."""
+        o = OracleScene()
+        for i in range(scene.mesh_count):
+            o.add_mesh(*scene.mesh(i))
+        for t in range(8):
+            raw, n = scene.bsdfs(t)
+            o.set_bsdfs(t, raw, n)
+        lights, nl = scene.lights
+        o.set_lights(lights, nl)
+        inst, ni = scene.instances
+        o.set_instances(inst, ni)
+        o.set_camera(*scene.camera)
+        return o
+
+    def add_mesh(self, positions, normals):
+        p = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+        q = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+        return lib().or_scene_add_mesh(self._s, _fp(p), _fp(q), len(p))
+
+    def set_instances(self, instances, count):
+        if lib().or_scene_set_instances(self._s, C.cast(instances, C.c_void_p), count) != 0:
+            raise ValueError("oracle: instance references an unknown mesh")
+
+    def set_bsdfs(self, btype, raw, count):
+        buf = C.create_string_buffer(raw, max(1, len(raw)))
+        lib().or_scene_set_bsdfs(self._s, btype, C.cast(buf, C.c_void_p), count)
+
+    def set_lights(self, lights, count):
+        lib().or_scene_set_lights(self._s, C.cast(lights, C.c_void_p), count)
+
+    def set_camera(self, eye, to_world, fov):
+        eye = np.ascontiguousarray(eye, np.float32)
+        tw = np.ascontiguousarray(to_world, np.float32).reshape(16)
+        lib().or_scene_set_camera(self._s, _fp(eye), _fp(tw), fov)
+
+    def set_params(self, max_depth=50, rr_start=10, cutoff=20.0, nee=1):
+        p = Params(max_depth, rr_start, cutoff, nee)
+        lib().or_scene_set_params(self._s, C.byref(p))
+
+    def render(self, width, height, first=0, n=1, stride=1, image=None, sum_mode=False, threads=0):
+        """Returns (image[h,w,4] float32, counters dict, threads used). Running mean unless sum_mode."""
+        img = image if image is not None else np.zeros((height, width, 4), np.float32)
+        c = Counters()
+        used = lib().or_render(self._s, width, height, first, n, stride, _fp(img), int(sum_mode), threads, C.byref(c))
+        if used < 0:
+            raise ValueError("oracle: an instance references a BSDF record that was not set")
+        return img, {k: getattr(c, k) for k, _ in Counters._fields_}, used
+
+    def path_probe(self, width, height, x, y, timestamp, max_bounces=64):
+        rgb = np.zeros(3, np.float32)
+        b = np.zeros(max_bounces, BOUNCE_DTYPE)
+        n = lib().or_path_probe(self._s, width, height, x, y, timestamp, _fp(rgb), b.ctypes.data_as(C.c_void_p), max_bounces)
+        return rgb, b[:min(n, max_bounces)]
+
+    def trace_batch(self, rays, any_hit=False, mode=0, threads=0):
+        rays = np.ascontiguousarray(rays, RAY_DTYPE)
+        hits = np.zeros(len(rays), HIT_DTYPE)
+        lib().or_trace_batch(self._s, rays.ctypes.data_as(C.c_void_p), len(rays), hits.ctypes.data_as(C.c_void_p), int(any_hit), mode, threads)
+        return hits
+
+    def camera_rays(self, width, height, px, py):
+        px = np.ascontiguousarray(px, np.uint32)
+        py = np.ascontiguousarray(py, np.uint32)
+        out = np.zeros(len(px), RAY_DTYPE)
+        lib().or_camera_rays(self._s, width, height, _up(px), _up(py), len(px), out.ctypes.data_as(C.c_void_p))
+        return out
+
+    def bsdf_sample(self, handle, wo, seed):
+        wo = np.ascontiguousarray(wo, np.float32).reshape(-1, 3)
+        seed = np.ascontiguousarray(seed, np.uint32)
+        n = len(wo)
+        wi, f = np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+        pdf, delta, seed_out = np.zeros(n, np.float32), np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        if lib().or_bsdf_sample(self._s, handle, _fp(wo), _up(seed), n, _fp(wi), _fp(f), _fp(pdf), _up(delta), _up(seed_out)) != 0:
+            raise ValueError("oracle: BSDF handle out of range")
+        return wi, f, pdf, delta, seed_out
+
+    def bsdf_eval(self, handle, wo, wi):
+        wo = np.ascontiguousarray(wo, np.float32).reshape(-1, 3)
+        wi = np.ascontiguousarray(wi, np.float32).reshape(-1, 3)
+        n = len(wo)
+        f, pdf, delta = np.zeros((n, 3), np.float32), np.zeros(n, np.float32), np.zeros(n, np.uint32)
+        if lib().or_bsdf_eval(self._s, handle, _fp(wo), _fp(wi), n, _fp(f), _fp(pdf), _up(delta)) != 0:
+            raise ValueError("oracle: BSDF handle out of range")
+        return f, pdf, delta
+
+    def sample_light(self, pos, seed):
+        pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 3)
+        seed = np.ascontiguousarray(seed, np.uint32)
+        n = len(pos)
+        lpos, em = np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32)
+        pdf, seed_out = np.zeros(n, np.float32), np.zeros(n, np.uint32)
+        lib().or_sample_light(self._s, _fp(pos), _up(seed), n, _fp(lpos), _fp(em), _fp(pdf), _up(seed_out))
+        return lpos, em, pdf, seed_out
+
+
+def rng(idx, timestamp, n_draws):
+    idx = np.ascontiguousarray(idx, np.uint32)
+    ts = np.ascontiguousarray(timestamp, np.uint32)
+    out = np.zeros((len(idx), 1 + n_draws), np.uint32)
+    lib().or_rng(_up(idx), _up(ts), len(idx), n_draws, _up(out))
+    return out
+
+
+def tea(v0, v1):
+    return lib().or_tea(v0, v1)
+
+
+def pcg_hash(v):
+    return lib().or_pcg_hash(v)
+
+
+def rand_to_float(word):
+    return lib().or_rand_to_float(word)
+
+
+def encode_srgb8(rgba):
+    rgba = np.ascontiguousarray(rgba, np.float32)
+    out = np.zeros(rgba.shape, np.uint8)
+    lib().or_encode_srgb8(_fp(rgba), rgba.size // 4, out.ctypes.data_as(C.POINTER(C.c_uint8)))
+    return out
