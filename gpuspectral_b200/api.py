@@ -55,7 +55,7 @@ class Scene:
 
     def __del__(self):
         h, self._h = getattr(self, "_h", None), None
-        if h:
+        if h and N is not None and getattr(N, "host", None) is not None:
             N.host.gsbh_scene_free(h)
 
     @staticmethod
@@ -150,7 +150,7 @@ class Context:
 
     def close(self):
         c, self._c = getattr(self, "_c", None), None
-        if c and self._own:
+        if c and self._own and N is not None and getattr(N, "core", None) is not None:
             N.core.gsb_destroy(c)
 
     def __del__(self):
@@ -337,7 +337,7 @@ class PathTracer:
 
     def close(self):
         t, self._t = getattr(self, "_t", None), None
-        if t:
+        if t and N is not None and getattr(N, "host", None) is not None:
             N.host.gsbh_tracer_destroy(t)
 
     def __del__(self):
