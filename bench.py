@@ -1,0 +1,386 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the render path on B200 (one process per GPU).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+
+Workload (BASELINE.json configs[1]): Cornell box (Mitsuba scene rebuilt procedurally by the host layer, 36
+triangles / 8 instances / 2 triangle lights), 1920x1080, NEE + MIS, max depth 8.  One step = `--spp-per-step`
+(default 32) samples for every pixel on every GPU (32 steps = the 1024 spp of the config on one GPU).  With N GPUs
+the samples are sharded by index (GPU g renders timestamps base + g, base + g + N, ...): per-GPU work is fixed
+(weak scaling) and every step ends with one NCCL reduce of the float4 sum buffers to rank 0.
+
+Printed line: metric = Mpaths/s (pixel-samples per second, whole job), plus Mrays/s, `e2e` (same step driven through
+the reference-shaped per-frame API with host buffers: per-frame scene arrays up, HDR framebuffer down), `roofline` of
+the dominant kernel (closest-hit traversal, k_extend), `cpu_baseline` (the CPU oracle on the host cores).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "Mpaths/s"
+UNIT = "Mpaths/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--spp-per-step", type=int, default=32)
+    ap.add_argument("--max-depth", type=int, default=8)
+    ap.add_argument("--scene", default="cornell")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    return ap.parse_args()
+
+
+def workload_name(a, n):
+    return (f"{a.scene} box {a.width}x{a.height}, NEE+MIS, max_depth {a.max_depth}, {a.spp_per_step} spp per step per GPU"
+            f" (sample-index sharding over {n} GPU{'s' if n > 1 else ''})")
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (the recipe's clocks line)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(a, rank, world):
+    """The reference has no CPU implementation of this path and its Vulkan path is unavailable on this box, so the
+    reference arm is the CPU oracle (oracle/, a restatement of the shaders: kind "port") on all host cores.
+    Each step is a bounded sample of the workload: the full frame at 1 spp."""
+    if rank != 0:
+        return
+    import gpuspectral_b200 as g          # host layer only (scene arrays); no product compute on this arm
+    from oracle import oracle as orc
+    orc.build()
+    scene = g.Scene.builtin(a.scene)
+    o = orc.OracleScene.from_host_scene(scene)
+    o.set_params(max_depth=a.max_depth)
+    spp = 1
+    img = np.zeros((a.height, a.width, 4), np.float32)
+    paths = ext = sh = 0
+    threads = 0
+    for k in range(a.warmup):
+        o.render(a.width, a.height, k, spp, 1, image=img, sum_mode=True)
+    t0 = time.perf_counter()
+    for k in range(a.steps):
+        _, c, threads = o.render(a.width, a.height, a.warmup + k, spp, 1, image=img, sum_mode=True)
+        paths += c["paths"]; ext += c["extension_rays"]; sh += c["shadow_rays"]
+    dt = time.perf_counter() - t0
+    val = paths / dt / 1e6
+    sample = f"{a.width}x{a.height} x {spp} spp per step ({a.steps} steps), same scene/params"
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": dt / max(a.steps, 1) * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "mrays_per_s": (ext + sh) / dt / 1e6,
+            "config": {"workload": workload_name(a, a.gpus), "note": "CPU oracle (port of the shaders); reference's Vulkan path unavailable on this box"},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ ours
+class CudaBuffer:
+    """__cuda_array_interface__ view of the context's accumulation buffer (no copy)."""
+
+    def __init__(self, ptr, nfloats):
+        self.__cuda_array_interface__ = {"shape": (nfloats,), "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
+
+
+def scene_h2d_bytes(scene):
+    import gpuspectral_b200 as g
+    n = scene.instances[1] * 88 + scene.lights[1] * 64 + (3 + 16 + 1) * 4 + 16
+    for t in range(g.BSDF_TYPE_COUNT):
+        n += scene.bsdfs(t)[1] * g.BSDF_STRIDES[t]
+    return n
+
+
+def per_frame_upload(ctx, scene, mesh_map):
+    """What PathTracer::createRenderPass / prepareScene do every frame in the reference (PathTracer.cpp:9-93):
+    instance / BSDF / light arrays + camera from HOST memory, top-level structure rebuilt.  Meshes (BLAS) are cached,
+    as Renderer::getOrCreateBLAS does."""
+    import gpuspectral_b200 as g
+    for t in range(g.BSDF_TYPE_COUNT):
+        raw, n = scene.bsdfs(t)
+        ctx.set_bsdfs(t, raw, n)
+    lights, nl = scene.lights
+    ctx.set_lights(lights, nl)
+    inst, ni = scene.instances
+    for i in range(ni):
+        inst[i].mesh = mesh_map[inst[i].mesh]
+    ctx.set_instances(inst, ni)
+    ctx.set_camera(*scene.camera)
+
+
+def run_ours(a, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    import gpuspectral_b200 as g
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    W, H, S = a.width, a.height, a.spp_per_step
+    npix = W * H
+    scene = g.Scene.builtin(a.scene)
+    ctx = g.Context(local_rank)
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)
+    ctx.upload(scene)
+    ctx.set_params(max_depth=a.max_depth)
+    ctx.render(W, H, 0, 0)      # allocate the frame
+    ctx.clear()
+    ptr, nbytes = ctx.device_sum_ptr()
+    accum = torch.as_tensor(CudaBuffer(ptr, nbytes // 4), device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(k):
+        """S samples per pixel on this GPU, then the frame's single reduce."""
+        ctx.render(W, H, k * S * world + rank, S, world)
+        if world > 1:
+            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+            if rank != 0:
+                accum.zero_()       # rank 0 keeps the running global sum; the others restart their partial sums
+
+    # ---- instrumented pass (untimed): fetch counts of the rays this workload really traces ------------------
+    ctx.set_instrumented(1)
+    ctx.reset_counters()
+    ctx.render(W, H, 1 << 20, 2, 1)
+    ci = ctx.counters()
+    ctx.set_instrumented(2)
+    ctx.reset_counters()
+    ctx.render(W, H, 1 << 20, 2, 1)
+    cs = ctx.counters()
+    ctx.set_instrumented(0)
+    ext_fetch = {k: ci[k] / max(ci["rays_counted"], 1) for k in ("nodes_visited", "tris_tested", "inst_entered")}
+    sh_fetch = {k: cs[k] / max(cs["rays_counted"], 1) for k in ("nodes_visited", "tris_tested", "inst_entered")}
+    # 80 B per 8-wide node, 48 B per triangle, 64 B per instance record, + the wavefront streams of the
+    # ray (ray in 32 B; hit record out 20 B + 4 B queue entry)
+    ext_bytes_per_ray = 80 * ext_fetch["nodes_visited"] + 48 * ext_fetch["tris_tested"] + 64 * ext_fetch["inst_entered"] + 32 + 24
+    sh_bytes_per_ray = 80 * sh_fetch["nodes_visited"] + 48 * sh_fetch["tris_tested"] + 64 * sh_fetch["inst_entered"] + 32 + 4
+    ctx.clear()
+    accum.zero_()
+
+    # ---- timed region ------------------------------------------------------------------------------------------
+    for k in range(a.warmup):
+        step(k)
+    ctx.clear()
+    accum.zero_()
+    ctx.set_profiling(True)       # CUDA events around every stage of every wavefront iteration (same stream)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    stage = {"extend": 0.0, "shade": 0.0, "shadow": 0.0, "finish": 0.0}
+    iters = 0
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for k in range(a.steps):
+        step(a.warmup + k)
+        ms = ctx.last_render_ms()
+        for name in stage:
+            stage[name] += ms[name]
+        iters += ctx.launch_info()[1]
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    elapsed_ms = ev0.elapsed_time(ev1)
+    ctx.set_profiling(False)
+    c = ctx.counters()
+    launches = ctx.launch_info()[0]
+    t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
+    totals = torch.tensor([c["paths"], c["extension_rays"], c["shadow_rays"], launches], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(totals, op=dist.ReduceOp.SUM)
+    elapsed_ms = float(t.item())
+    paths, ext, sh, launches = [float(x) for x in totals.tolist()]
+    value = paths / (elapsed_ms * 1e-3) / 1e6
+    mrays = (ext + sh) / (elapsed_ms * 1e-3) / 1e6
+
+    # image sanity on rank 0: the running sum holds steps * S * world samples per pixel
+    if rank == 0:
+        img = ctx.read_hdr()
+        assert np.isfinite(img).all() and img[..., :3].mean() > 0.01, "bench image is empty"
+        samples = float(accum.view(-1, 4)[:, 3].mean().item())
+        assert abs(samples - a.steps * S * world) < 0.5, f"sum buffer holds {samples} samples per pixel"
+
+    # ---- roofline of the dominant kernel (k_extend: closest-hit traversal), from this rank's timed region -----------
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy)"
+    else:
+        peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+    ext_per_launch = c["extension_rays"] / max(iters, 1)
+    ext_ms_per_launch = stage["extend"] / max(iters, 1)
+    achieved = ext_bytes_per_ray * ext_per_launch / (ext_ms_per_launch * 1e-3) / 1e9 if ext_ms_per_launch > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "extend_traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+    stage_total = sum(stage.values())
+    roofline = {"kernel": "k_extend (closest-hit traversal)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "bytes_per_ray": ext_bytes_per_ray, "rays_per_launch": ext_per_launch, "ms_per_launch": ext_ms_per_launch,
+                "fetch_per_ray": ext_fetch, "launches": iters,
+                "share_of_step": {k: v / stage_total for k, v in stage.items()} if stage_total > 0 else None,
+                "shadow": {"bytes_per_ray": sh_bytes_per_ray, "fetch_per_ray": sh_fetch,
+                           "achieved": (sh_bytes_per_ray * c["shadow_rays"] / (stage["shadow"] * 1e-3) / 1e9) if stage["shadow"] > 0 else 0.0},
+                "note": "scene BVH is a few KB (L1/L2 resident): the HBM figure is the algorithmic-byte rate, not DRAM traffic"}
+
+    # ---- e2e: the per-frame API with host buffers ----------------------------------------------------------------------
+    e2e = None
+    if not a.no_e2e:
+        mesh_map = list(ctx._mesh_map)
+        host_img = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+        host_np = host_img.numpy()
+        h2d = scene_h2d_bytes(scene)
+        d2h = npix * 16 if rank == 0 else 0
+        ctx.clear()
+        accum.zero_()
+
+        def e2e_step(k):
+            per_frame_upload(ctx, scene, mesh_map)            # host arrays -> device, TLAS rebuilt (every frame, as the reference)
+            step(k)
+            if rank == 0:
+                ctx.read_hdr(out=host_np)                     # resolve + device -> pinned host
+
+        e2e_step(0)
+        ctx.reset_counters()
+        barrier()
+        t0 = time.perf_counter()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        for k in range(a.e2e_steps):
+            e2e_step(1 + k)
+        f1.record(stream)
+        barrier()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        dev_ms = f0.elapsed_time(f1)
+        tt = torch.tensor([max(wall_ms, dev_ms)], dtype=torch.float64, device=dev)
+        pp = torch.tensor([float(ctx.counters()["paths"])], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist.all_reduce(pp, op=dist.ReduceOp.SUM)
+        e2e = {"value": float(pp.item()) / (float(tt.item()) * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": npix * 16, "steps": a.e2e_steps, "ms_per_step": float(tt.item()) / a.e2e_steps,
+               "what": "per step: BSDF/light/instance arrays + camera from host memory, TLAS rebuild, render, NCCL reduce (N>1), "
+                       "HDR frame resolved and copied to pinned host memory on rank 0"}
+        if rank == 0:
+            assert np.isfinite(host_np).all() and host_np[..., :3].mean() > 0.01
+
+    # ---- CPU baseline (rank 0, N = 1 only) ---------------------------------------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        from oracle import oracle as orc
+        orc.build()
+        o = orc.OracleScene.from_host_scene(scene)
+        o.set_params(max_depth=a.max_depth)
+        o.render(W, H, 0, 1, sum_mode=True)
+        spp = 6
+        t0 = time.perf_counter()
+        _, oc, threads = o.render(W, H, 100, spp, sum_mode=True)
+        dt = time.perf_counter() - t0
+        cpu = {"value": oc["paths"] / dt / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
+               "mrays_per_s": (oc["extension_rays"] + oc["shadow_rays"]) / dt / 1e6,
+               "sample": f"{W}x{H} x {spp} spp of the same scene/params ({oc['paths']} paths, {dt:.1f} s)"}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": elapsed_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic", "mrays_per_s": mrays,
+                "rays_per_path": {"extension": ext / paths, "shadow": sh / paths},
+                "config": {"workload": workload_name(a, world), "width": W, "height": H, "spp_per_step": S, "max_depth": a.max_depth,
+                           "scene": a.scene, "parallelism": f"sample-index sharding x{world}" + (", 1 NCCL reduce per step" if world > 1 else ""),
+                           "l2": "path state streams of a step (2.07 M slots x ~230 B = 480 MB) exceed the 126 MB L2; scene data is meant to be cache resident"},
+                "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(launches),
+                "stage_ms_per_step": {k: v / a.steps for k, v in stage.items()}}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference":
+        run_reference(a, rank, world)
+        return
+    if world == 1 and a.gpus > 1:
+        # launched without torchrun: re-launch under it, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={a.gpus}", "--master-addr", "127.0.0.1",
+               "--master-port", "29533", os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    run_ours(a, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

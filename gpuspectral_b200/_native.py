@@ -84,6 +84,9 @@ CORE_API = {
     "gsb_reset_counters": (C.c_int, [_P]),
     "gsb_set_profiling": (C.c_int, [_P, C.c_int]),
     "gsb_last_render_ms": (C.c_int, [_P, C.POINTER(C.c_double)]),
+    "gsb_set_instrumented": (C.c_int, [_P, C.c_int]),
+    "gsb_set_stream": (C.c_int, [_P, _P]),
+    "gsb_get_launch_info": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "gsb_trace_batch": (C.c_int, [_P, C.POINTER(Ray), C.c_uint32, C.POINTER(Hit), C.c_int]),
     "gsb_trace_batch_stats": (C.c_int, [_P, C.POINTER(Ray), C.c_uint32, C.POINTER(Hit), C.c_int]),
     "gsb_trace_batch_timed": (C.c_int, [_P, C.POINTER(Ray), C.c_uint32, C.c_int, C.c_int, C.POINTER(C.c_double)]),

@@ -258,6 +258,19 @@ class Context:
     def set_profiling(self, enabled):
         _check(N.core.gsb_set_profiling(self._c, int(enabled)), "gsb_set_profiling")
 
+    def set_instrumented(self, mode):
+        """0 off, 1 extension rays, 2 shadow rays, 3 both."""
+        _check(N.core.gsb_set_instrumented(self._c, int(mode)), "gsb_set_instrumented")
+
+    def set_stream(self, cuda_stream):
+        """cuda_stream: integer value of a cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream); None = private stream."""
+        _check(N.core.gsb_set_stream(self._c, C.c_void_p(cuda_stream or 0)), "gsb_set_stream")
+
+    def launch_info(self):
+        a, b = C.c_uint64(), C.c_uint64()
+        _check(N.core.gsb_get_launch_info(self._c, C.byref(a), C.byref(b)), "gsb_get_launch_info")
+        return a.value, b.value
+
     def last_render_ms(self):
         ms = (C.c_double * 5)()
         _check(N.core.gsb_last_render_ms(self._c, ms), "gsb_last_render_ms")

@@ -294,7 +294,7 @@ gsb_status gsb_destroy(gsb_context* ctx) {
         cudaFree(ctx->dLights);
         cudaFree(ctx->dAccum);
         freeWavefront(ctx);
-        cudaStreamDestroy(ctx->stream);
+        if (ctx->ownStream) cudaStreamDestroy(ctx->stream);
         delete ctx;
         return GSB_OK;
     });
@@ -538,6 +538,7 @@ gsb_status gsb_clear(gsb_context* ctx) {
         Bind bind(ctx->device);
         if (ctx->dAccum) GSB_CUDA(cudaMemsetAsync(ctx->dAccum, 0, (size_t)ctx->width * ctx->height * sizeof(float4), ctx->stream));
         GSB_CUDA(cudaMemsetAsync(ctx->wf.stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
+        ctx->launches = 0;
         return GSB_OK;
     });
 }
@@ -603,6 +604,7 @@ gsb_status gsb_reset_counters(gsb_context* ctx) {
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
         GSB_CUDA(cudaMemsetAsync(ctx->wf.stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
+        ctx->launches = 0;
         return GSB_OK;
     });
 }
@@ -610,6 +612,36 @@ gsb_status gsb_reset_counters(gsb_context* ctx) {
 gsb_status gsb_set_profiling(gsb_context* ctx, int enabled) {
     if (!ctx) return fail(GSB_ERR_INVALID, "gsb_set_profiling: null context");
     ctx->profiling = enabled != 0;
+    return GSB_OK;
+}
+
+gsb_status gsb_set_instrumented(gsb_context* ctx, int mode) {
+    if (!ctx || mode < 0 || mode > 3) return fail(GSB_ERR_INVALID, "gsb_set_instrumented: bad argument");
+    ctx->instrumented = mode;
+    return GSB_OK;
+}
+
+gsb_status gsb_set_stream(gsb_context* ctx, void* cuda_stream) {
+    if (!ctx) return fail(GSB_ERR_INVALID, "gsb_set_stream: null context");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->ownStream) cudaStreamDestroy(ctx->stream);
+        if (cuda_stream) {
+            ctx->stream = (cudaStream_t)cuda_stream;
+            ctx->ownStream = false;
+        } else {
+            GSB_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+            ctx->ownStream = true;
+        }
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_get_launch_info(gsb_context* ctx, uint64_t* out_launches, uint64_t* out_last_render_iterations) {
+    if (!ctx) return fail(GSB_ERR_INVALID, "gsb_get_launch_info: null context");
+    if (out_launches) *out_launches = ctx->launches;
+    if (out_last_render_iterations) *out_last_render_iterations = ctx->lastRenderIters;
     return GSB_OK;
 }
 

@@ -73,6 +73,10 @@ struct gsb_context {
     float4* dAccum = nullptr;  // rgb = sum of samples, a = samples added
     gsb::WavefrontState wf;
     bool profiling = false;
+    int instrumented = 0;        // bit 0: count fetches of extension rays, bit 1: of shadow rays
+    bool ownStream = true;       // false after gsb_set_stream
+    uint64_t launches = 0;       // kernels launched by gsb_render since gsb_reset_counters
+    uint64_t lastRenderIters = 0;
     double lastRenderMs[5] = {0, 0, 0, 0, 0};
 
     gsb::SceneDev sceneDev() const;

@@ -86,15 +86,34 @@ __global__ void k_generate(SceneDev sc, WavefrontState wf, RenderArgs ra) {
 }
 
 // ---- extend ---------------------------------------------------------------------------------------
+// instrumented builds: fold one thread's fetch counts into the context counters
+GSB_D void flushTraceStats(unsigned long long* stats, TraceStats ts, uint32_t traced) {
+    uint32_t nn = ts.nodes, nt = ts.tris, ni = ts.insts, nr = traced;
+    for (int o = 16; o > 0; o >>= 1) {
+        nn += __shfl_xor_sync(0xffffffffu, nn, o);
+        nt += __shfl_xor_sync(0xffffffffu, nt, o);
+        ni += __shfl_xor_sync(0xffffffffu, ni, o);
+        nr += __shfl_xor_sync(0xffffffffu, nr, o);
+    }
+    if ((threadIdx.x & 31) == 0 && nr) {
+        atomicAdd(&stats[ST_NODES], (unsigned long long)nn);
+        atomicAdd(&stats[ST_TRIS], (unsigned long long)nt);
+        atomicAdd(&stats[ST_INSTS], (unsigned long long)ni);
+        atomicAdd(&stats[ST_RAYS], (unsigned long long)nr);
+    }
+}
+
+template <bool STATS>
 __global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState wf, uint32_t slots) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     bool live = slot < slots;
     if (live) live = wf.sampleK[slot] != kRetired;
     uint32_t key = 0;
+    TraceStats ts = {0u, 0u, 0u};
     if (live) {
         const float4 o = wf.rayO[slot], d = wf.rayD[slot];
         HitRecord hit;
-        traceRay<false, false>(sc, o.x, o.y, o.z, d.x, d.y, d.z, 0.0f, 1e10f, hit, nullptr, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+        traceRay<false, STATS>(sc, o.x, o.y, o.z, d.x, d.y, d.z, 0.0f, 1e10f, hit, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
         wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.prim));
         wf.hitInst[slot] = hit.inst;
         key = hit.inst == GSB_NO_HIT ? (uint32_t)Q_TERMINATED : (__ldg(sc.instBsdf + hit.inst) >> 16);
@@ -104,6 +123,7 @@ __global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState w
         if (key == Q_TERMINATED) wf.termQueue[pos] = slot;
         else wf.matQueue[(size_t)key * wf.capacity + pos] = slot;
     }
+    if (STATS) flushTraceStats(wf.stats, ts, live ? 1u : 0u);
 }
 
 // ---- shade ----------------------------------------------------------------------------------------
@@ -262,12 +282,16 @@ __global__ void __launch_bounds__(kBlock) k_shade(SceneDev sc, WavefrontState wf
 }
 
 // ---- shadow ---------------------------------------------------------------------------------------
+template <bool STATS>
 __global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState wf) {
     const uint32_t count = wf.qCount[Q_SHADOW];
+    TraceStats ts = {0u, 0u, 0u};
+    uint32_t traced = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
         const float4 o = wf.shadowO[i], d = wf.shadowD[i];
         HitRecord hit;
-        traceRay<true, false>(sc, o.x, o.y, o.z, d.x, d.y, d.z, 0.01f, o.w, hit, nullptr, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+        traceRay<true, STATS>(sc, o.x, o.y, o.z, d.x, d.y, d.z, 0.01f, o.w, hit, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+        traced++;
         const bool visible = hit.inst == GSB_NO_HIT;
         const uint32_t slot = __float_as_uint(d.w);
         const float4 base = wf.shadowBase[i];
@@ -285,6 +309,7 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState w
             wf.result[slot] = res;
         }
     }
+    if (STATS) flushTraceStats(wf.stats, ts, traced);
 }
 
 // ---- finish + regenerate ----------------------------------------------------------------------------
@@ -417,6 +442,10 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int queueGrid = std::min(fullGrid, sms * 16);
     k_generate<<<fullGrid, kBlock, 0, s>>>(sc, wf, ra);
+    ctx->launches += 1;
+    ctx->lastRenderIters = 0;
+    int typesUsed = 0;
+    for (bool u : ctx->typeUsed) typesUsed += u ? 1 : 0;
 
     // stage timing (profiling mode): events around every stage of every iteration
     const bool prof = ctx->profiling;
@@ -431,7 +460,8 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
 
     auto iteration = [&]() {
         mark();
-        k_extend<<<fullGrid, kBlock, 0, s>>>(sc, wf, slots);
+        if (ctx->instrumented & 1) k_extend<true><<<fullGrid, kBlock, 0, s>>>(sc, wf, slots);
+        else k_extend<false><<<fullGrid, kBlock, 0, s>>>(sc, wf, slots);
         mark();
         if (ctx->typeUsed[0]) launchShade<0>(ctx, sc, queueGrid);
         if (ctx->typeUsed[1]) launchShade<1>(ctx, sc, queueGrid);
@@ -442,11 +472,14 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         if (ctx->typeUsed[6]) launchShade<6>(ctx, sc, queueGrid);
         if (ctx->typeUsed[7]) launchShade<7>(ctx, sc, queueGrid);
         mark();
-        k_shadow<<<queueGrid, kBlock, 0, s>>>(sc, wf);
+        if (ctx->instrumented & 2) k_shadow<true><<<queueGrid, kBlock, 0, s>>>(sc, wf);
+        else k_shadow<false><<<queueGrid, kBlock, 0, s>>>(sc, wf);
         mark();
         k_finish<<<queueGrid, kBlock, 0, s>>>(sc, wf, ra);
         k_endIteration<<<1, 1, 0, s>>>(wf);
         mark();
+        ctx->launches += 4 + (uint64_t)typesUsed;
+        ctx->lastRenderIters++;
     };
 
     // Host loop: batches of iterations; the live-slot count of batch b is read back while batch
@@ -470,7 +503,10 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         b++;
         if (prof && pev.size() > 200000) break;
     }
-    if (lanes > 1) k_mergeLanes<<<(npix + 255) / 256, 256, 0, s>>>(wf.laneAccum, npix, lanes, ctx->dAccum);
+    if (lanes > 1) {
+        k_mergeLanes<<<(npix + 255) / 256, 256, 0, s>>>(wf.laneAccum, npix, lanes, ctx->dAccum);
+        ctx->launches += 1;
+    }
     GSB_CUDA(cudaEventRecord(evStop, s));
     GSB_CUDA(cudaEventSynchronize(evStop));
     GSB_CUDA(cudaGetLastError());

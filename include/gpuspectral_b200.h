@@ -181,6 +181,18 @@ GSB_API gsb_status gsb_reset_counters(gsb_context* ctx);
  * Stage times are only collected when profiling is enabled. */
 GSB_API gsb_status gsb_set_profiling(gsb_context* ctx, int enabled);
 GSB_API gsb_status gsb_last_render_ms(gsb_context* ctx, double out_ms[5]);
+/* Instrumented rendering: gsb_render runs the counting variants of the two traversal kernels and
+ * adds nodes / triangles / instance records fetched (and rays counted) to the counters, so the
+ * algorithmic bytes per ray are those of the rays the render really traced.
+ * mode: 0 off (default), 1 extension rays only, 2 shadow rays only, 3 both. */
+GSB_API gsb_status gsb_set_instrumented(gsb_context* ctx, int mode);
+/* Runs all of the context's work on a caller-owned CUDA stream (a cudaStream_t passed as void*;
+ * NULL = back to a private stream), so that a host framework's events and collectives (NCCL on
+ * the same stream) order with the render without extra synchronisation. */
+GSB_API gsb_status gsb_set_stream(gsb_context* ctx, void* cuda_stream);
+/* Kernels launched by gsb_render since gsb_reset_counters / gsb_clear, and the number of wavefront
+ * iterations of the last gsb_render (= launches of each stage kernel in it). */
+GSB_API gsb_status gsb_get_launch_info(gsb_context* ctx, uint64_t* out_launches, uint64_t* out_last_render_iterations);
 
 /* ---- ray batches (the intersection-parity entry; Ray/RayHit of DriverTypes.h) ----- */
 /* Host arrays in, host arrays out.  any_hit = 0: closest hit; 1: occlusion only. */
