@@ -81,9 +81,12 @@ def test_closest_hit_vs_float64(gsb, orc, ctx):
     # ids may differ only between candidates at the same distance (the boxes stand ON the floor: coplanar faces)
     same = hit & (got["inst"] == ref["inst"]) & (got["prim"] == ref["prim"])
     assert same.sum() > 0.99 * hit.sum()
-    ulp = np.spacing(np.maximum(np.abs(ref["t"][hit]), 1e-3).astype(np.float32))
-    # stated tolerance: 64 ulp of t (rays start up to ~5 scene units away: cancellation in v - o)
-    assert np.all(np.abs(got["t"][hit] - ref["t"][hit]) <= 64 * ulp)
+    # stated tolerance: 16 ulp at the magnitude max(t, |origin|_inf, 1): the float32 rule subtracts the ray origin from the
+    # vertices first, so its absolute error follows the coordinate magnitude, not t (a hit at t = 0.05 seen from 5 units away)
+    mag = np.maximum(np.maximum(np.abs(ref["t"][hit]), np.abs(rays["origin"][hit]).max(axis=1)), 1.0).astype(np.float32)
+    err = np.abs(got["t"][hit] - ref["t"][hit]) / np.spacing(mag)
+    # grazing incidence amplifies the error by 1 / cos: 99.9 % within 16 ulp, all within 512 ulp
+    assert np.percentile(err, 99.9) <= 16 and err.max() <= 512
     assert np.abs(got["u"][same] - ref["u"][same]).max() < 1e-4 and np.abs(got["v"][same] - ref["v"][same]).max() < 1e-4
 
 
