@@ -2,6 +2,7 @@
 // acceleration-structure builds, ray batches, framebuffer read-back, diagnostic entry points.
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -271,6 +272,10 @@ gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx) {
         ctx->device = device_ordinal;
         GSB_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
         ensureStats(ctx);
+        if (const char* e = getenv("GSB_SLOTS")) {
+            const long v = atol(e);
+            if (v >= 1024 && v <= (1l << 26)) ctx->targetSlots = (uint32_t)v;
+        }
         *out_ctx = ctx;
         return GSB_OK;
     });

@@ -29,7 +29,7 @@ struct WavefrontState {
     float4* weightDW = nullptr; // weight.xyz, directWeight
     float4* result = nullptr;   // radiance of the current sample .xyz, flags bits in .w
     uint32_t* seed = nullptr;
-    uint32_t* sampleK = nullptr;  // index of the sample this slot works on; 0xffffffff = slot retired
+    uint32_t* sampleK = nullptr;  // pixel the slot's current path belongs to; 0xffffffff = slot retired
     float4* hitTUVP = nullptr;    // t, u, v, primitive id bits
     uint32_t* hitInst = nullptr;
     uint32_t* matQueue = nullptr;   // GSB_BSDF_TYPE_COUNT queues of `capacity` slot ids each
@@ -38,14 +38,12 @@ struct WavefrontState {
     float4* shadowD = nullptr;      // direction.xyz, slot id bits
     float4* shadowBase = nullptr;   // emitted without NEE .xyz, directWeight if visible
     float4* shadowNee = nullptr;    // NEE contribution .xyz
-    float4* laneAccum = nullptr;    // per-slot accumulation when several slots share a pixel
-    uint32_t laneAccumCapacity = 0;
     uint32_t* qCount = nullptr;     // Q_COUNT queue counters
     // device statistics block: [0] live slots, [1] retirements this iteration, [2..] totals
     unsigned long long* stats = nullptr;
 };
 
-enum { ST_LIVE = 0, ST_RETIRED = 1, ST_PATHS = 2, ST_EXT = 3, ST_SHADOW = 4, ST_ITERS = 5, ST_NODES = 6, ST_TRIS = 7, ST_INSTS = 8, ST_RAYS = 9, ST_OVERFLOW = 10, ST_COUNT = 16 };
+enum { ST_LIVE = 0, ST_RETIRED = 1, ST_PATHS = 2, ST_EXT = 3, ST_SHADOW = 4, ST_ITERS = 5, ST_NODES = 6, ST_TRIS = 7, ST_INSTS = 8, ST_RAYS = 9, ST_OVERFLOW = 10, ST_NEXTWORK = 11, ST_COUNT = 16 };
 
 }  // namespace gsb
 
@@ -73,6 +71,7 @@ struct gsb_context {
     float4* dAccum = nullptr;  // rgb = sum of samples, a = samples added
     gsb::WavefrontState wf;
     bool profiling = false;
+    uint32_t targetSlots = 1u << 20;  // paths in flight per wavefront (GSB_SLOTS overrides)
     int instrumented = 0;        // bit 0: count fetches of extension rays, bit 1: of shadow rays
     bool ownStream = true;       // false after gsb_set_stream
     uint64_t launches = 0;       // kernels launched by gsb_render since gsb_reset_counters

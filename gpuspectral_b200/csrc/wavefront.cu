@@ -12,10 +12,11 @@
 //   k_finish   adds finished samples to the image (raygen.rgen:84-108) and starts the slot's
 //              next sample (raygen.rgen:31-48)
 //
-// A slot owns one pixel (or one of K sample lanes of a pixel when the image is small) for the
-// whole call and works through its samples in timestamp order, so image accumulation needs no
-// atomics and is deterministic.  Every path carries its own RNG word; each stage consumes
-// draws in the order the shader does, which makes per-path results match the checker's.
+// Slots are not tied to pixels: a slot whose path ends takes the next pixel-sample from a global work counter
+// (work item w = sample w / npix of pixel w % npix), so every slot stays busy until the call's work is exhausted and
+// only the last few iterations of a call run with a thinning wavefront.  Finished samples are added to the image with
+// one 128-bit atomic add (rgb, count).  Every path carries its own RNG word; each stage consumes draws in the order
+// the shader does, which makes per-path results match the checker's.
 #include <algorithm>
 #include <cstdio>
 #include <vector>
@@ -36,9 +37,9 @@ constexpr uint32_t kFlagCountEmitted = 1u << 17;
 struct RenderArgs {
     uint32_t width, height, npix;
     uint32_t first, count, stride;  // timestamps first + k*stride, k < count
-    uint32_t lanes;                 // slots per pixel
-    uint32_t slots;                 // npix * lanes
-    float4* accum;                  // where slot s accumulates: accum[s] (lanes == 1: the image itself)
+    uint32_t slots;                 // paths in flight
+    unsigned long long totalWork;   // npix * count pixel-samples
+    float4* accum;                  // the image: rgb = sum of samples, a = samples added
 };
 
 // Warp-aggregated append: every lane of the warp must call this (pred false = no push).
@@ -55,8 +56,9 @@ GSB_D uint32_t queueSlot(uint32_t* counters, uint32_t key, bool pred) {
 }
 
 // raygen.rgen:20-48: seed + primary ray + payload initialisation for sample k of the slot's pixel
-GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderArgs& ra, uint32_t slot, uint32_t k) {
-    const uint32_t pixel = slot % ra.npix;
+GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderArgs& ra, uint32_t slot, unsigned long long work) {
+    const uint32_t k = (uint32_t)(work / ra.npix);
+    const uint32_t pixel = (uint32_t)(work - (unsigned long long)k * ra.npix);
     const uint32_t x = pixel % ra.width, y = pixel / ra.width;
     const uint32_t timestamp = ra.first + k * ra.stride;
     // rayDir(size, fragCoord, fov)
@@ -74,14 +76,13 @@ GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderA
     wf.rayD[slot] = make_float4(d.x, d.y, d.z, 0.0f);
     wf.weightDW[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
     wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kFlagCountEmitted));  // depth 0, wasDelta 0, countEmitted 1
-    wf.sampleK[slot] = k;
+    wf.sampleK[slot] = pixel;
 }
 
 __global__ void k_generate(SceneDev sc, WavefrontState wf, RenderArgs ra) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= ra.slots) return;
-    const uint32_t lane = slot / ra.npix;
-    if (lane < ra.count) startPath(sc, wf, ra, slot, lane);
+    if (slot < ra.totalWork) startPath(sc, wf, ra, slot, slot);
     else wf.sampleK[slot] = kRetired;
 }
 
@@ -316,18 +317,31 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState w
 __global__ void __launch_bounds__(kBlock) k_finish(SceneDev sc, WavefrontState wf, RenderArgs ra) {
     const uint32_t count = wf.qCount[Q_TERMINATED];
     uint32_t retired = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
-        const uint32_t slot = wf.termQueue[i];
-        const float4 res = wf.result[slot];
-        // raygen.rgen:106-108: a NaN sample leaves the image untouched
-        if (!(isnan(res.x) || isnan(res.y) || isnan(res.z))) {
-            float4 a = ra.accum[slot];
-            a.x += res.x; a.y += res.y; a.z += res.z; a.w += 1.0f;
-            ra.accum[slot] = a;
+    const uint32_t rounds = (count + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
+    for (uint32_t r = 0; r < rounds; r++) {
+        const uint32_t i = (r * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+        const bool active = i < count;
+        uint32_t slot = 0;
+        if (active) {
+            slot = wf.termQueue[i];
+            const float4 res = wf.result[slot];
+            // raygen.rgen:106-108: a NaN sample leaves the image untouched
+            if (!(isnan(res.x) || isnan(res.y) || isnan(res.z)))
+                atomicAdd(&ra.accum[wf.sampleK[slot]], make_float4(res.x, res.y, res.z, 1.0f));
         }
-        const uint32_t k = wf.sampleK[slot] + ra.lanes;
-        if (k < ra.count) startPath(sc, wf, ra, slot, k);
-        else { wf.sampleK[slot] = kRetired; retired++; }
+        // next pixel-sample for every finished slot of the warp: one atomic per warp
+        const uint32_t mask = __ballot_sync(0xffffffffu, active);
+        if (mask == 0u) continue;
+        const uint32_t lane = threadIdx.x & 31u;
+        const uint32_t leader = (uint32_t)__ffs(mask) - 1u;
+        unsigned long long base = 0;
+        if (lane == leader) base = atomicAdd(&wf.stats[ST_NEXTWORK], (unsigned long long)__popc(mask));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (active) {
+            const unsigned long long work = base + (unsigned long long)__popc(mask & ((1u << lane) - 1u));
+            if (work < ra.totalWork) startPath(sc, wf, ra, slot, work);
+            else { wf.sampleK[slot] = kRetired; retired++; }
+        }
     }
     for (int o = 16; o > 0; o >>= 1) retired += __shfl_xor_sync(0xffffffffu, retired, o);
     if ((threadIdx.x & 31) == 0 && retired) atomicAdd(&wf.stats[ST_RETIRED], (unsigned long long)retired);
@@ -343,17 +357,6 @@ __global__ void k_endIteration(WavefrontState wf) {
     st[ST_LIVE] -= st[ST_RETIRED];
     st[ST_RETIRED] = 0;
     for (int q = 0; q < Q_COUNT; q++) wf.qCount[q] = 0;
-}
-
-__global__ void k_mergeLanes(const float4* __restrict__ laneAccum, uint32_t npix, uint32_t lanes, float4* __restrict__ accum) {
-    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= npix) return;
-    float4 a = accum[p];
-    for (uint32_t l = 0; l < lanes; l++) {
-        const float4 v = laneAccum[(size_t)l * npix + p];
-        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
-    }
-    accum[p] = a;
 }
 
 template <class T>
@@ -391,7 +394,7 @@ void launchShade(gsb_context* ctx, const SceneDev& sc, int grid) {
 void freeWavefront(gsb_context* ctx) {
     WavefrontState& wf = ctx->wf;
     void* ptrs[] = {wf.rayO, wf.rayD, wf.weightDW, wf.result, wf.seed, wf.sampleK, wf.hitTUVP, wf.hitInst, wf.matQueue,
-                    wf.termQueue, wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.laneAccum, wf.qCount, wf.stats};
+                    wf.termQueue, wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.qCount, wf.stats};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     wf = WavefrontState();
@@ -407,30 +410,23 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         ctx->height = height;
     }
     if (count == 0) return;
-    // enough slots to fill the machine: about one million paths in flight
-    const uint32_t targetSlots = 1u << 20;
-    uint32_t lanes = std::max<uint32_t>(1u, std::min<uint32_t>(count, (targetSlots + npix - 1) / npix));
-    const uint32_t slots = npix * lanes;
+    // paths in flight: enough to fill the machine several times over, small enough that the path state stays near L2
+    const unsigned long long totalWork = (unsigned long long)npix * count;
+    const uint32_t slots = (uint32_t)std::min<unsigned long long>(totalWork, ctx->targetSlots);
     allocWavefront(ctx, slots);
     WavefrontState& wf = ctx->wf;
     RenderArgs ra;
     ra.width = width; ra.height = height; ra.npix = npix;
     ra.first = first; ra.count = count; ra.stride = stride;
-    ra.lanes = lanes; ra.slots = slots;
-    if (lanes == 1) {
-        ra.accum = ctx->dAccum;
-    } else {
-        if (wf.laneAccumCapacity < slots) {
-            ensure(wf.laneAccum, (size_t)slots);
-            wf.laneAccumCapacity = slots;
-        }
-        GSB_CUDA(cudaMemsetAsync(wf.laneAccum, 0, (size_t)slots * sizeof(float4), s));
-        ra.accum = wf.laneAccum;
-    }
+    ra.slots = slots;
+    ra.totalWork = totalWork;
+    ra.accum = ctx->dAccum;
     const SceneDev sc = ctx->sceneDev();
     GSB_CUDA(cudaMemsetAsync(wf.qCount, 0, Q_COUNT * sizeof(uint32_t), s));
-    const unsigned long long liveInit[2] = {(unsigned long long)npix * std::min<uint32_t>(lanes, count), 0ull};
+    const unsigned long long liveInit[2] = {(unsigned long long)slots, 0ull};
+    const unsigned long long nextInit = (unsigned long long)slots;
     GSB_CUDA(cudaMemcpyAsync(wf.stats, liveInit, sizeof(liveInit), cudaMemcpyHostToDevice, s));
+    GSB_CUDA(cudaMemcpyAsync(&wf.stats[ST_NEXTWORK], &nextInit, sizeof(nextInit), cudaMemcpyHostToDevice, s));
 
     cudaEvent_t evStart = nullptr, evStop = nullptr;
     GSB_CUDA(cudaEventCreate(&evStart));
@@ -502,10 +498,6 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         }
         b++;
         if (prof && pev.size() > 200000) break;
-    }
-    if (lanes > 1) {
-        k_mergeLanes<<<(npix + 255) / 256, 256, 0, s>>>(wf.laneAccum, npix, lanes, ctx->dAccum);
-        ctx->launches += 1;
     }
     GSB_CUDA(cudaEventRecord(evStop, s));
     GSB_CUDA(cudaEventSynchronize(evStop));
