@@ -434,7 +434,8 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
             sh.twofaced = in.twofaced;
             sh.pad[0] = sh.pad[1] = 0;
             tr.blas = mesh.blas.buffer;
-            tr.triOffset16 = mesh.blas.leafOffset16;
+            // meshes of <= 4 triangles are traced without their (single) node: the TLAS box test already covered them
+            tr.triOffset16 = mesh.blas.leafOffset16 | ((mesh.ntris >= 1 && mesh.ntris <= 4) ? (mesh.ntris << kDirectShift) : 0u);
             tr.instId = i;
             handles[i] = in.bsdf;
             ctx->typeUsed[in.bsdf >> 16] = true;

@@ -17,8 +17,9 @@ struct MeshRec {
     DeviceBvh blas;
 };
 
-// Queue indices inside WavefrontState::qCount
-enum { Q_MATERIAL0 = 0, Q_TERMINATED = GSB_BSDF_TYPE_COUNT, Q_SHADOW = GSB_BSDF_TYPE_COUNT + 1, Q_COUNT = 12 };
+// Counter indices inside WavefrontState::qCount (two banks of Q_COUNT, selected by iteration parity):
+// one queue per BSDF type, the number of extension rays that missed, the shadow-ray queue.
+enum { Q_MATERIAL0 = 0, Q_MISS = GSB_BSDF_TYPE_COUNT, Q_SHADOW = GSB_BSDF_TYPE_COUNT + 1, Q_COUNT = 12 };
 
 // Per-slot path state, structure of arrays.  The 17-word HitPayload of pt_common.glsl:4-14
 // (+ pixel sample index and the hit record) spread over 16-byte and 4-byte streams.
@@ -29,17 +30,17 @@ struct WavefrontState {
     float4* weightDW = nullptr; // weight.xyz, directWeight
     float4* result = nullptr;   // radiance of the current sample .xyz, flags bits in .w
     uint32_t* seed = nullptr;
-    uint32_t* sampleK = nullptr;  // pixel the slot's current path belongs to; 0xffffffff = slot retired
+    uint32_t* sampleK = nullptr;  // pixel the slot's current path belongs to; bit 31: path finished, add it to the image;
+                                  // 0xffffffff = slot retired (no work left)
     float4* hitTUVP = nullptr;    // t, u, v, primitive id bits
     uint32_t* hitInst = nullptr;
     uint32_t* matQueue = nullptr;   // GSB_BSDF_TYPE_COUNT queues of `capacity` slot ids each
-    uint32_t* termQueue = nullptr;
     float4* shadowO = nullptr;      // origin.xyz, tmax
     float4* shadowD = nullptr;      // direction.xyz, slot id bits
     float4* shadowBase = nullptr;   // emitted without NEE .xyz, directWeight if visible
     float4* shadowNee = nullptr;    // NEE contribution .xyz
-    uint32_t* qCount = nullptr;     // Q_COUNT queue counters
-    // device statistics block: [0] live slots, [1] retirements this iteration, [2..] totals
+    uint32_t* qCount = nullptr;     // 2 x Q_COUNT queue counters
+    // device statistics block: [0] live slots, [2..] totals
     unsigned long long* stats = nullptr;
 };
 

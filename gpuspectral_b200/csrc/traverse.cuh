@@ -26,8 +26,10 @@
 
 namespace gsb {
 
-constexpr int kStackSize = 48;
-constexpr uint32_t kSentinel = 0u;  // stack entry with .y == 0 marks "leave the current instance"
+constexpr int kStackSize = 48;      // total traversal stack entries per ray
+constexpr int kSmemStack = 8;       // of which the first kSmemStack live in shared memory (the hot top of the stack)
+constexpr int kTraceBlock = 128;    // every kernel that calls traceRay runs with this block size
+constexpr uint32_t kDirectShift = 29;  // TraceInstance::triOffset16 bits 29..31: triangle count of a node-less mesh
 
 struct TraceStats { uint32_t nodes, tris, insts; };
 
@@ -67,7 +69,9 @@ GSB_D void makeObjRay(float ox, float oy, float oz, float dx, float dy, float dz
 }
 
 // Watertight ray/triangle test; every operation individually rounded (no FMA contraction).
-GSB_D bool woopTest(const ObjRay& r, float4 v0, float4 v1, float4 v2, float& t, float& bu, float& bv) {
+// Returns false when the ray misses; otherwise the scaled distance T, the barycentric numerators V, W and det,
+// so that callers pay for the divisions t = T/det, u = V/det, v = W/det only when they need them.
+GSB_D bool woopEdges(const ObjRay& r, float4 v0, float4 v1, float4 v2, float& T, float& V, float& W, float& det) {
     float Akx, Aky, Akz, Bkx, Bky, Bkz, Ckx, Cky, Ckz;
     permute(r.perm, v0.x, v0.y, v0.z, Akx, Aky, Akz);
     permute(r.perm, v1.x, v1.y, v1.z, Bkx, Bky, Bkz);
@@ -79,8 +83,8 @@ GSB_D bool woopTest(const ObjRay& r, float4 v0, float4 v1, float4 v2, float& t, 
     const float Bx = __fsub_rn(Bkx, __fmul_rn(r.Sx, Bkz)), By = __fsub_rn(Bky, __fmul_rn(r.Sy, Bkz));
     const float Cx = __fsub_rn(Ckx, __fmul_rn(r.Sx, Ckz)), Cy = __fsub_rn(Cky, __fmul_rn(r.Sy, Ckz));
     float U = __fsub_rn(__fmul_rn(Cx, By), __fmul_rn(Cy, Bx));
-    float V = __fsub_rn(__fmul_rn(Ax, Cy), __fmul_rn(Ay, Cx));
-    float W = __fsub_rn(__fmul_rn(Bx, Ay), __fmul_rn(By, Ax));
+    V = __fsub_rn(__fmul_rn(Ax, Cy), __fmul_rn(Ay, Cx));
+    W = __fsub_rn(__fmul_rn(Bx, Ay), __fmul_rn(By, Ax));
     if (U == 0.0f || V == 0.0f || W == 0.0f) {
         // products of two floats are exact in double; one rounding in the subtraction, one to float
         U = (float)__dsub_rn(__dmul_rn((double)Cx, (double)By), __dmul_rn((double)Cy, (double)Bx));
@@ -88,26 +92,40 @@ GSB_D bool woopTest(const ObjRay& r, float4 v0, float4 v1, float4 v2, float& t, 
         W = (float)__dsub_rn(__dmul_rn((double)Bx, (double)Ay), __dmul_rn((double)By, (double)Ax));
     }
     if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
-    const float det = __fadd_rn(__fadd_rn(U, V), W);
+    det = __fadd_rn(__fadd_rn(U, V), W);
     if (det == 0.0f) return false;
     const float Az = __fmul_rn(r.Sz, Akz), Bz = __fmul_rn(r.Sz, Bkz), Cz = __fmul_rn(r.Sz, Ckz);
-    const float T = __fadd_rn(__fadd_rn(__fmul_rn(U, Az), __fmul_rn(V, Bz)), __fmul_rn(W, Cz));
+    T = __fadd_rn(__fadd_rn(__fmul_rn(U, Az), __fmul_rn(V, Bz)), __fmul_rn(W, Cz));
+    return true;
+}
+
+// The full test with all three quotients (diagnostics; the checker's definition of a hit).
+GSB_D bool woopTest(const ObjRay& r, float4 v0, float4 v1, float4 v2, float& t, float& bu, float& bv) {
+    float T, V, W, det;
+    if (!woopEdges(r, v0, v1, v2, T, V, W, det)) return false;
     t = __fdiv_rn(T, det);
     bu = __fdiv_rn(V, det);
     bv = __fdiv_rn(W, det);
     return true;
 }
 
-GSB_D float safeInv(float d) {
-    // keeps 1/d finite for the box tests; 2^-80 as in the CWBVH paper
+// 1/d for the slab tests only (never for the triangle test): one MUFU.RCP.  |d| is clamped to 2^-80 as in the
+// CWBVH paper so the reciprocal stays finite; its 1-ulp error is far inside the box padding (bvh.h: kBoxPadRel).
+GSB_D float slabInv(float d) {
     const float eps = 8.271806125530277e-25f;
-    return 1.0f / (fabsf(d) > eps ? d : copysignf(eps, d));
+    const float c = fabsf(d) > eps ? d : copysignf(eps, d);
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(c));
+    return r;
 }
 
 GSB_D uint32_t byteOf(uint32_t w, int j) { return (w >> (8 * j)) & 0xffu; }
 
-// Intersects the 8 quantised child boxes of one node.  Returns the node group
+// Intersects the 8 quantised child boxes of one node, branch-free.  Returns the node group
 // (childBase, internal hit bits 24..31 | imask) and the leaf group (leafBase, hit bits 0..23).
+// Hit-bit position of a child comes from its meta byte, four children at a time (CWBVH paper, listing 2):
+// internal child in slot i has meta 0x20 | (24 + i) and lands on bit 24 + (i ^ oct7) so that a descending bit
+// scan visits children front to back; a leaf child has meta (unary count << 5) | first-primitive offset.
 GSB_D void intersectNode(const uint4* __restrict__ nodes, uint32_t nodeIndex, float ox, float oy, float oz, float idx,
                          float idy, float idz, float tmin, float tmax, uint32_t oct7, uint2& nodeGroup, uint2& leafGroup) {
     const uint4* n = nodes + (size_t)nodeIndex * 5;
@@ -126,10 +144,15 @@ GSB_D void intersectNode(const uint4* __restrict__ nodes, uint32_t nodeIndex, fl
     const float by = (__uint_as_float(w0.y) - oy) * idy;
     const float bz = (__uint_as_float(w0.z) - oz) * idz;
     const bool nx = idx < 0.0f, ny = idy < 0.0f, nz = idz < 0.0f;
+    const uint32_t oct4 = oct7 * 0x01010101u;
     uint32_t hits = 0;
 #pragma unroll
     for (int half = 0; half < 2; half++) {
         const uint32_t meta4 = half ? w1.w : w1.z;
+        const uint32_t isInner4 = (meta4 & (meta4 << 1)) & 0x10101010u;   // index field 24..31
+        const uint32_t innerMask4 = (isInner4 >> 4) * 0xffu;
+        const uint32_t bitIndex4 = (meta4 ^ (oct4 & innerMask4)) & 0x1f1f1f1fu;
+        const uint32_t childBits4 = (meta4 >> 5) & 0x07070707u;
         const uint32_t qlox = half ? w2.y : w2.x, qloy = half ? w2.w : w2.z, qloz = half ? w3.y : w3.x;
         const uint32_t qhix = half ? w3.w : w3.z, qhiy = half ? w4.y : w4.x, qhiz = half ? w4.w : w4.z;
         const uint32_t nearx = nx ? qhix : qlox, farx = nx ? qlox : qhix;
@@ -137,18 +160,13 @@ GSB_D void intersectNode(const uint4* __restrict__ nodes, uint32_t nodeIndex, fl
         const uint32_t nearz = nz ? qhiz : qloz, farz = nz ? qloz : qhiz;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const uint32_t m = byteOf(meta4, j);
-            if (m == 0) continue;
             const float t0x = fmaf((float)byteOf(nearx, j), sx, bx), t1x = fmaf((float)byteOf(farx, j), sx, bx);
             const float t0y = fmaf((float)byteOf(neary, j), sy, by), t1y = fmaf((float)byteOf(fary, j), sy, by);
             const float t0z = fmaf((float)byteOf(nearz, j), sz, bz), t1z = fmaf((float)byteOf(farz, j), sz, bz);
             const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, tmin));
             const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
-            if (tn <= tf) {
-                const int i = half * 4 + j;
-                if ((imask >> i) & 1u) hits |= 1u << (24 + ((uint32_t)i ^ oct7));
-                else hits |= (m >> 5) << (m & 31u);
-            }
+            const uint32_t bits = byteOf(childBits4, j) << byteOf(bitIndex4, j);  // 0 for an empty slot
+            hits |= (tn <= tf) ? bits : 0u;
         }
     }
     nodeGroup = make_uint2(w1.x, (hits & 0xff000000u) | imask);
@@ -157,15 +175,25 @@ GSB_D void intersectNode(const uint4* __restrict__ nodes, uint32_t nodeIndex, fl
 
 // Traces one ray.  ANYHIT: returns as soon as any triangle has tmin < t < tmax (hit.inst = 0).
 // STATS: counts fetched nodes / triangles / instance records.
+//
+// Loop shape: every pass runs the same three phases in the same order — (1) descend one node, (2) leaf work
+// (enter one instance at the top level / test the pending triangles at the bottom level), (3) pop — each under
+// its own predicate, so the lanes of a warp that are in the same phase execute it together and a lane can
+// advance through all three in one pass.  (A one-item-per-pass state machine ran at 9 of 32 lanes active on
+// the Cornell box: profiles/r1b_stage_kernels_ncu.md.)  The first kSmemStack stack entries live in shared
+// memory ([entry][thread]: conflict-free 64-bit accesses); deeper entries spill to local memory.
 template <bool ANYHIT, bool STATS>
 GSB_D void traceRay(const SceneDev& sc, float ox, float oy, float oz, float dx, float dy, float dz, float tmin, float tmax,
                     HitRecord& hit, TraceStats* stats, uint32_t* overflowFlag) {
     hit.t = tmax; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT;
-    uint2 stack[kStackSize];
+    __shared__ uint2 s_stack[kSmemStack][kTraceBlock];
+    uint2 lstack[kStackSize - kSmemStack];
+    const uint32_t tid = threadIdx.x;
     int sp = 0;
+    int spMark = -1;  // stack height at which the current instance was entered; -1 at the top level
 
     // world-space box-test constants
-    const float widx = safeInv(dx), widy = safeInv(dy), widz = safeInv(dz);
+    const float widx = slabInv(dx), widy = slabInv(dy), widz = slabInv(dz);
     const uint32_t woct = (dx < 0.0f ? 0u : 4u) | (dy < 0.0f ? 0u : 2u) | (dz < 0.0f ? 0u : 1u);
 
     // current level state (top level first)
@@ -173,92 +201,100 @@ GSB_D void traceRay(const SceneDev& sc, float ox, float oy, float oz, float dx, 
     const float4* tris = nullptr;
     float cox = ox, coy = oy, coz = oz, cidx = widx, cidy = widy, cidz = widz;
     uint32_t oct7 = woct;
-    bool inBlas = false;
     uint32_t curInst = 0;
     ObjRay oray;
 
     uint2 G = make_uint2(0u, 0x80000000u);  // root group: bit 31, imask 0 -> node childBase + 0
     uint2 T = make_uint2(0u, 0u);
 
-#define GSB_PUSH(entry)                                   \
-    do {                                                  \
-        if (sp < kStackSize) stack[sp++] = (entry);       \
-        else if (overflowFlag) *overflowFlag = 1u;        \
+#define GSB_PUSH(entry)                                                      \
+    do {                                                                     \
+        if (sp < kSmemStack) s_stack[sp++][tid] = (entry);                   \
+        else if (sp < kStackSize) lstack[sp++ - kSmemStack] = (entry);       \
+        else if (overflowFlag) *overflowFlag = 1u;                           \
     } while (0)
 
     for (;;) {
-        if (T.y) {
-            // leaf work first: it can only shrink the interval for the nodes still pending
-            const uint32_t bit = (uint32_t)__ffs(T.y) - 1u;
-            T.y &= ~(1u << bit);
-            if (inBlas) {
-                const float4* tp = tris + (size_t)(T.x + bit) * 3;
-                const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
-                if (STATS) stats->tris++;
-                float t, bu, bv;
-                if (woopTest(oray, v0, v1, v2, t, bu, bv)) {
-                    if (ANYHIT) {
-                        if (t > tmin && t < tmax) { hit.inst = 0u; hit.prim = 0u; hit.t = 0.0f; return; }
-                    } else if (t > tmin && t < tmax) {
-                        const uint32_t prim = __float_as_uint(v0.w);
-                        if (t < hit.t || (t == hit.t && (curInst < hit.inst || (curInst == hit.inst && prim < hit.prim)))) {
-                            hit.t = t; hit.u = bu; hit.v = bv; hit.inst = curInst; hit.prim = prim;
-                        }
-                    }
-                }
-            } else {
-                // enter an instance: park what is left of this top-level node, then a sentinel
-                const TraceInstance* ti = sc.tlasInst + (T.x + bit);
-                if (G.y & 0xff000000u) GSB_PUSH(G);
-                if (T.y) GSB_PUSH(T);
-                GSB_PUSH(make_uint2(0u, kSentinel));
-                const float4 r0 = __ldg(&ti->w2o[0]), r1 = __ldg(&ti->w2o[1]), r2 = __ldg(&ti->w2o[2]);
-                const uint4 tail = __ldg(reinterpret_cast<const uint4*>(ti) + 3);
-                if (STATS) stats->insts++;
-                // o' = M^-1 (o,1), d' = M^-1 (d,0); rounded op by op, same order as the checker
-                const float tox = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r0.x, ox), __fmul_rn(r0.y, oy)), __fmul_rn(r0.z, oz)), r0.w);
-                const float toy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r1.x, ox), __fmul_rn(r1.y, oy)), __fmul_rn(r1.z, oz)), r1.w);
-                const float toz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r2.x, ox), __fmul_rn(r2.y, oy)), __fmul_rn(r2.z, oz)), r2.w);
-                const float tdx = __fadd_rn(__fadd_rn(__fmul_rn(r0.x, dx), __fmul_rn(r0.y, dy)), __fmul_rn(r0.z, dz));
-                const float tdy = __fadd_rn(__fadd_rn(__fmul_rn(r1.x, dx), __fmul_rn(r1.y, dy)), __fmul_rn(r1.z, dz));
-                const float tdz = __fadd_rn(__fadd_rn(__fmul_rn(r2.x, dx), __fmul_rn(r2.y, dy)), __fmul_rn(r2.z, dz));
-                makeObjRay(tox, toy, toz, tdx, tdy, tdz, oray);
-                cox = tox; coy = toy; coz = toz;
-                cidx = safeInv(tdx); cidy = safeInv(tdy); cidz = safeInv(tdz);
-                oct7 = (tdx < 0.0f ? 0u : 4u) | (tdy < 0.0f ? 0u : 2u) | (tdz < 0.0f ? 0u : 1u);
-                const uint64_t base = ((uint64_t)tail.y << 32) | (uint64_t)tail.x;
-                nodes = reinterpret_cast<const uint4*>(base);
-                tris = reinterpret_cast<const float4*>(nodes + tail.z);
-                curInst = tail.w;
-                inBlas = true;
-                G = make_uint2(0u, 0x80000000u);
-                T = make_uint2(0u, 0u);
-            }
-        } else if (G.y & 0xff000000u) {
-            // descend into the pending internal child that comes first in octant order
+        // ---- phase 1: descend into the pending internal child that comes first in octant order
+        if (G.y & 0xff000000u) {
             const uint32_t bit = 31u - (uint32_t)__clz(G.y);
             G.y &= ~(1u << bit);
             const uint32_t slot = (bit - 24u) ^ oct7;
-            const uint32_t rel = __popc(G.y & 0xffu & ~(0xffffffffu << slot));
-            const uint32_t nodeIndex = G.x + rel;
+            const uint32_t nodeIndex = G.x + __popc(G.y & ((1u << slot) - 1u) & 0xffu);
             if (G.y & 0xff000000u) GSB_PUSH(G);
             if (STATS) stats->nodes++;
             intersectNode(nodes, nodeIndex, cox, coy, coz, cidx, cidy, cidz, tmin, hit.t, oct7, G, T);
-        } else {
-            if (sp == 0) break;
-            const uint2 e = stack[--sp];
-            if (e.y == kSentinel) {
-                inBlas = false;
+        }
+        // ---- phase 2a (top level): enter one instance, park the rest of this node
+        if (spMark < 0 && T.y) {
+            const uint32_t bit = (uint32_t)__ffs(T.y) - 1u;
+            T.y &= ~(1u << bit);
+            const TraceInstance* ti = sc.tlasInst + (T.x + bit);
+            if (G.y & 0xff000000u) GSB_PUSH(G);
+            if (T.y) GSB_PUSH(T);
+            spMark = sp;
+            const float4 r0 = __ldg(&ti->w2o[0]), r1 = __ldg(&ti->w2o[1]), r2 = __ldg(&ti->w2o[2]);
+            const uint4 tail = __ldg(reinterpret_cast<const uint4*>(ti) + 3);
+            if (STATS) stats->insts++;
+            // o' = M^-1 (o,1), d' = M^-1 (d,0); rounded op by op, same order as the checker
+            const float tox = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r0.x, ox), __fmul_rn(r0.y, oy)), __fmul_rn(r0.z, oz)), r0.w);
+            const float toy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r1.x, ox), __fmul_rn(r1.y, oy)), __fmul_rn(r1.z, oz)), r1.w);
+            const float toz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r2.x, ox), __fmul_rn(r2.y, oy)), __fmul_rn(r2.z, oz)), r2.w);
+            const float tdx = __fadd_rn(__fadd_rn(__fmul_rn(r0.x, dx), __fmul_rn(r0.y, dy)), __fmul_rn(r0.z, dz));
+            const float tdy = __fadd_rn(__fadd_rn(__fmul_rn(r1.x, dx), __fmul_rn(r1.y, dy)), __fmul_rn(r1.z, dz));
+            const float tdz = __fadd_rn(__fadd_rn(__fmul_rn(r2.x, dx), __fmul_rn(r2.y, dy)), __fmul_rn(r2.z, dz));
+            makeObjRay(tox, toy, toz, tdx, tdy, tdz, oray);
+            const uint64_t base = ((uint64_t)tail.y << 32) | (uint64_t)tail.x;
+            nodes = reinterpret_cast<const uint4*>(base);
+            tris = reinterpret_cast<const float4*>(nodes + (tail.z & ((1u << kDirectShift) - 1u)));
+            curInst = tail.w;
+            const uint32_t direct = tail.z >> kDirectShift;
+            if (direct) {
+                // node-less mesh (<= 7 triangles): its world box was already tested in the TLAS node
+                G = make_uint2(0u, 0u);
+                T = make_uint2(0u, (1u << direct) - 1u);
+            } else {
+                cox = tox; coy = toy; coz = toz;
+                cidx = slabInv(tdx); cidy = slabInv(tdy); cidz = slabInv(tdz);
+                oct7 = (tdx < 0.0f ? 0u : 4u) | (tdy < 0.0f ? 0u : 2u) | (tdz < 0.0f ? 0u : 1u);
+                G = make_uint2(0u, 0x80000000u);
+                T = make_uint2(0u, 0u);
+            }
+        }
+        // ---- phase 2b (bottom level): test the pending triangles; they can only shrink the interval
+        if (spMark >= 0) {
+            while (T.y) {
+                const uint32_t bit = (uint32_t)__ffs(T.y) - 1u;
+                T.y &= ~(1u << bit);
+                const float4* tp = tris + (size_t)(T.x + bit) * 3;
+                const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                if (STATS) stats->tris++;
+                float Tn, V, W, det;
+                if (woopEdges(oray, v0, v1, v2, Tn, V, W, det)) {
+                    const float t = __fdiv_rn(Tn, det);
+                    if (t > tmin && t < tmax) {
+                        if (ANYHIT) { hit.inst = 0u; hit.prim = 0u; hit.t = 0.0f; return; }
+                        const uint32_t prim = __float_as_uint(v0.w);
+                        if (t < hit.t || (t == hit.t && (curInst < hit.inst || (curInst == hit.inst && prim < hit.prim)))) {
+                            hit.t = t; hit.u = __fdiv_rn(V, det); hit.v = __fdiv_rn(W, det); hit.inst = curInst; hit.prim = prim;
+                        }
+                    }
+                }
+            }
+        }
+        // ---- phase 3: nothing pending in this node -> leave the instance if its stack is drained, then pop
+        if (!(G.y & 0xff000000u)) {
+            if (sp == spMark) {
+                spMark = -1;
                 nodes = sc.tlasNodes;
                 cox = ox; coy = oy; coz = oz; cidx = widx; cidy = widy; cidz = widz;
                 oct7 = woct;
-                G = make_uint2(0u, 0u);
-                T = make_uint2(0u, 0u);
-            } else if (e.y & 0xff000000u) {
-                G = e;
-            } else {
-                T = e;
             }
+            if (sp == 0) break;
+            --sp;
+            const uint2 e = sp < kSmemStack ? s_stack[sp][tid] : lstack[sp - kSmemStack];
+            if (e.y & 0xff000000u) { G = e; T = make_uint2(0u, 0u); }
+            else { T = e; G = make_uint2(0u, 0u); }
         }
     }
 #undef GSB_PUSH

@@ -4,13 +4,15 @@
 // rayhit.rchit:666-797 through traceRayEXT).  Here the same per-path state machine is cut
 // into stages that each run as one wide kernel over many paths:
 //
-//   k_extend   closest-hit traversal of every live path's ray  (raygen.rgen:54-58), bins the
-//              hits into one queue per BSDF type, misses (miss.rmiss) into the finish queue
+//   k_extend   first, for slots whose path has ended: adds the sample to the image (raygen.rgen:84-108) and
+//              starts the slot's next pixel-sample (raygen.rgen:31-48); then closest-hit traversal of every
+//              live path's ray (raygen.rgen:54-58), bins the hits into one queue per BSDF type; a miss
+//              (miss.rmiss) ends the path
 //   k_shade<T> material-sorted closest-hit shading             (rayhit.rchit:666-797) + the
 //              per-bounce bookkeeping of the raygen loop       (raygen.rgen:59-80)
 //   k_shadow   any-hit traversal of the NEE segments           (rayhit.rchit:737-757)
-//   k_finish   adds finished samples to the image (raygen.rgen:84-108) and starts the slot's
-//              next sample (raygen.rgen:31-48)
+// Three launches per wavefront iteration (for one BSDF type in use); queue counters are double-banked by
+// iteration parity so that no separate reset kernel is needed.
 //
 // Slots are not tied to pixels: a slot whose path ends takes the next pixel-sample from a global work counter
 // (work item w = sample w / npix of pixel w % npix), so every slot stays busy until the call's work is exhausted and
@@ -29,8 +31,9 @@ namespace gsb {
 
 namespace {
 
-constexpr int kBlock = 128;
+constexpr int kBlock = kTraceBlock;
 constexpr uint32_t kRetired = 0xffffffffu;
+constexpr uint32_t kFinished = 0x80000000u;  // sampleK bit: the path has ended, its sample waits to be added to the image
 constexpr uint32_t kFlagWasDelta = 1u << 16;
 constexpr uint32_t kFlagCountEmitted = 1u << 17;
 
@@ -38,6 +41,7 @@ struct RenderArgs {
     uint32_t width, height, npix;
     uint32_t first, count, stride;  // timestamps first + k*stride, k < count
     uint32_t slots;                 // paths in flight
+    float camZ;                     // (max(W,H)/2) / tan(fov/2) of rayDir(), raygen.rgen:20-25 (evaluated once on the host)
     unsigned long long totalWork;   // npix * count pixel-samples
     float4* accum;                  // the image: rgb = sum of samples, a = samples added
 };
@@ -55,8 +59,10 @@ GSB_D uint32_t queueSlot(uint32_t* counters, uint32_t key, bool pred) {
     return base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
 }
 
-// raygen.rgen:20-48: seed + primary ray + payload initialisation for sample k of the slot's pixel
-GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderArgs& ra, uint32_t slot, unsigned long long work) {
+// raygen.rgen:20-48: seed + primary ray + payload initialisation for work item `work` (sample work / npix of
+// pixel work % npix); the new ray is also returned in registers
+GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderArgs& ra, uint32_t slot, unsigned long long work,
+                     float4& o, float4& dOut, uint32_t& pixelOut) {
     const uint32_t k = (uint32_t)(work / ra.npix);
     const uint32_t pixel = (uint32_t)(work - (unsigned long long)k * ra.npix);
     const uint32_t x = pixel % ra.width, y = pixel / ra.width;
@@ -65,24 +71,28 @@ GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderA
     const float sx = (float)ra.width, sy = (float)ra.height;
     const float fx = (float)x - sx / 2.0f;
     const float fy = (float)y - sy / 2.0f;
-    const float z = (fmaxf(sx, sy) / 2.0f) / tanf(sc.fov / 2.0f);
-    const float3 dir = normalize(f3(-fx, fy, z));
+    const float3 dir = normalize(f3(-fx, fy, ra.camZ));
     const float* V = sc.view;
     float3 d = f3(V[0] * dir.x + V[4] * dir.y + V[8] * dir.z, V[1] * dir.x + V[5] * dir.y + V[9] * dir.z,
                   V[2] * dir.x + V[6] * dir.y + V[10] * dir.z);
     d.y *= -1.0f;
+    o = make_float4(sc.eye[0], sc.eye[1], sc.eye[2], 0.0f);
+    dOut = make_float4(d.x, d.y, d.z, 0.0f);
     wf.seed[slot] = pcgHash(tea(ra.width * y + x, timestamp));
-    wf.rayO[slot] = make_float4(sc.eye[0], sc.eye[1], sc.eye[2], 0.0f);
-    wf.rayD[slot] = make_float4(d.x, d.y, d.z, 0.0f);
+    wf.rayO[slot] = o;
+    wf.rayD[slot] = dOut;
     wf.weightDW[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
     wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kFlagCountEmitted));  // depth 0, wasDelta 0, countEmitted 1
     wf.sampleK[slot] = pixel;
+    pixelOut = pixel;
 }
 
 __global__ void k_generate(SceneDev sc, WavefrontState wf, RenderArgs ra) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= ra.slots) return;
-    if (slot < ra.totalWork) startPath(sc, wf, ra, slot, slot);
+    float4 o, d;
+    uint32_t pixel;
+    if (slot < ra.totalWork) startPath(sc, wf, ra, slot, slot, o, d, pixel);
     else wf.sampleK[slot] = kRetired;
 }
 
@@ -105,32 +115,76 @@ GSB_D void flushTraceStats(unsigned long long* stats, TraceStats ts, uint32_t tr
 }
 
 template <bool STATS>
-__global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState wf, uint32_t slots) {
+__global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState wf, RenderArgs ra, uint32_t parity) {
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
-    bool live = slot < slots;
-    if (live) live = wf.sampleK[slot] != kRetired;
+    uint32_t* qc = wf.qCount + parity * Q_COUNT;
+    if (slot == 0) {
+        // roll the previous iteration's queue sizes into the totals and clear that bank for the next iteration
+        uint32_t* prev = wf.qCount + (parity ^ 1u) * Q_COUNT;
+        unsigned long long ext = prev[Q_MISS];
+        for (int q = 0; q < GSB_BSDF_TYPE_COUNT; q++) ext += prev[q];
+        wf.stats[ST_EXT] += ext;
+        wf.stats[ST_SHADOW] += prev[Q_SHADOW];
+        wf.stats[ST_ITERS] += 1;
+        for (int q = 0; q < Q_COUNT; q++) prev[q] = 0;
+    }
+    uint32_t pix = kRetired;
+    if (slot < ra.slots) pix = wf.sampleK[slot];
+    float4 o, d;
+    bool live = pix != kRetired;
+    const bool finished = live && (pix & kFinished);
+
+    // ---- the raygen epilogue of paths that ended last iteration, and the prologue of the slot's next path
+    if (finished) {
+        const float4 res = wf.result[slot];
+        // raygen.rgen:106-108: a NaN sample leaves the image untouched
+        if (!(isnan(res.x) || isnan(res.y) || isnan(res.z)))
+            atomicAdd(&ra.accum[pix & ~kFinished], make_float4(res.x, res.y, res.z, 1.0f));
+    }
+    const uint32_t fmask = __ballot_sync(0xffffffffu, finished);
+    if (fmask) {
+        // next pixel-sample for every finished slot of the warp: one atomic per warp
+        const uint32_t lane = threadIdx.x & 31u;
+        const uint32_t leader = (uint32_t)__ffs(fmask) - 1u;
+        unsigned long long base = 0;
+        if (lane == leader) base = atomicAdd(&wf.stats[ST_NEXTWORK], (unsigned long long)__popc(fmask));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        bool retire = false;
+        if (finished) {
+            const unsigned long long work = base + (unsigned long long)__popc(fmask & ((1u << lane) - 1u));
+            if (work < ra.totalWork) startPath(sc, wf, ra, slot, work, o, d, pix);
+            else { wf.sampleK[slot] = kRetired; retire = true; live = false; }
+        }
+        const uint32_t rmask = __ballot_sync(0xffffffffu, retire);
+        if (rmask && lane == (uint32_t)__ffs(rmask) - 1u) atomicAdd(&wf.stats[ST_LIVE], (unsigned long long)(-(long long)__popc(rmask)));
+    }
+    if (live && !finished) { o = wf.rayO[slot]; d = wf.rayD[slot]; }
+
+    // ---- closest hit
     uint32_t key = 0;
     TraceStats ts = {0u, 0u, 0u};
     if (live) {
-        const float4 o = wf.rayO[slot], d = wf.rayD[slot];
         HitRecord hit;
         traceRay<false, STATS>(sc, o.x, o.y, o.z, d.x, d.y, d.z, 0.0f, 1e10f, hit, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
-        wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.prim));
-        wf.hitInst[slot] = hit.inst;
-        key = hit.inst == GSB_NO_HIT ? (uint32_t)Q_TERMINATED : (__ldg(sc.instBsdf + hit.inst) >> 16);
+        if (hit.inst == GSB_NO_HIT) {
+            key = Q_MISS;                                           // miss.rmiss: done = 1, nothing is added
+            wf.sampleK[slot] = pix | kFinished;
+        } else {
+            wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.prim));
+            wf.hitInst[slot] = hit.inst;
+            key = __ldg(sc.instBsdf + hit.inst) >> 16;
+        }
     }
-    const uint32_t pos = queueSlot(wf.qCount, key, live);
-    if (live) {
-        if (key == Q_TERMINATED) wf.termQueue[pos] = slot;
-        else wf.matQueue[(size_t)key * wf.capacity + pos] = slot;
-    }
+    const uint32_t pos = queueSlot(qc, key, live);
+    if (live && key != Q_MISS) wf.matQueue[(size_t)key * wf.capacity + pos] = slot;
     if (STATS) flushTraceStats(wf.stats, ts, live ? 1u : 0u);
 }
 
 // ---- shade ----------------------------------------------------------------------------------------
 template <int TYPE>
-__global__ void __launch_bounds__(kBlock) k_shade(SceneDev sc, WavefrontState wf) {
-    const uint32_t count = wf.qCount[TYPE];
+__global__ void __launch_bounds__(kBlock) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity) {
+    uint32_t* qc = wf.qCount + parity * Q_COUNT;
+    const uint32_t count = qc[TYPE];
     const uint32_t* queue = wf.matQueue + (size_t)TYPE * wf.capacity;
     const uint32_t rounds = (count + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
     for (uint32_t r = 0; r < rounds; r++) {
@@ -270,22 +324,21 @@ __global__ void __launch_bounds__(kBlock) k_shade(SceneDev sc, WavefrontState wf
                 wf.weightDW[slot] = make_float4(weight.x, weight.y, weight.z, 1.0f);  // directWeight 1 unless the shadow stage finds the light
             }
         }
-        const uint32_t sp = queueSlot(wf.qCount, Q_SHADOW, needShadow);
+        if (terminate) wf.sampleK[slot] |= kFinished;   // k_extend adds the sample to the image next iteration
+        const uint32_t sp = queueSlot(qc, Q_SHADOW, needShadow);
         if (needShadow) {
             wf.shadowO[sp] = shO;
             wf.shadowD[sp] = shD;
             wf.shadowBase[sp] = shBase;
             wf.shadowNee[sp] = shNee;
         }
-        const uint32_t tp = queueSlot(wf.qCount, Q_TERMINATED, terminate);
-        if (terminate) wf.termQueue[tp] = slot;
     }
 }
 
 // ---- shadow ---------------------------------------------------------------------------------------
 template <bool STATS>
-__global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState wf) {
-    const uint32_t count = wf.qCount[Q_SHADOW];
+__global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState wf, uint32_t parity) {
+    const uint32_t count = wf.qCount[parity * Q_COUNT + Q_SHADOW];
     TraceStats ts = {0u, 0u, 0u};
     uint32_t traced = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
@@ -313,50 +366,15 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState w
     if (STATS) flushTraceStats(wf.stats, ts, traced);
 }
 
-// ---- finish + regenerate ----------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBlock) k_finish(SceneDev sc, WavefrontState wf, RenderArgs ra) {
-    const uint32_t count = wf.qCount[Q_TERMINATED];
-    uint32_t retired = 0;
-    const uint32_t rounds = (count + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
-    for (uint32_t r = 0; r < rounds; r++) {
-        const uint32_t i = (r * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
-        const bool active = i < count;
-        uint32_t slot = 0;
-        if (active) {
-            slot = wf.termQueue[i];
-            const float4 res = wf.result[slot];
-            // raygen.rgen:106-108: a NaN sample leaves the image untouched
-            if (!(isnan(res.x) || isnan(res.y) || isnan(res.z)))
-                atomicAdd(&ra.accum[wf.sampleK[slot]], make_float4(res.x, res.y, res.z, 1.0f));
-        }
-        // next pixel-sample for every finished slot of the warp: one atomic per warp
-        const uint32_t mask = __ballot_sync(0xffffffffu, active);
-        if (mask == 0u) continue;
-        const uint32_t lane = threadIdx.x & 31u;
-        const uint32_t leader = (uint32_t)__ffs(mask) - 1u;
-        unsigned long long base = 0;
-        if (lane == leader) base = atomicAdd(&wf.stats[ST_NEXTWORK], (unsigned long long)__popc(mask));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (active) {
-            const unsigned long long work = base + (unsigned long long)__popc(mask & ((1u << lane) - 1u));
-            if (work < ra.totalWork) startPath(sc, wf, ra, slot, work);
-            else { wf.sampleK[slot] = kRetired; retired++; }
-        }
-    }
-    for (int o = 16; o > 0; o >>= 1) retired += __shfl_xor_sync(0xffffffffu, retired, o);
-    if ((threadIdx.x & 31) == 0 && retired) atomicAdd(&wf.stats[ST_RETIRED], (unsigned long long)retired);
-}
-
-// one thread: roll the iteration's queue sizes into the totals and clear the queues
-__global__ void k_endIteration(WavefrontState wf) {
-    unsigned long long* st = wf.stats;
-    st[ST_EXT] += st[ST_LIVE];
-    st[ST_SHADOW] += wf.qCount[Q_SHADOW];
-    st[ST_PATHS] += wf.qCount[Q_TERMINATED];
-    st[ST_ITERS] += 1;
-    st[ST_LIVE] -= st[ST_RETIRED];
-    st[ST_RETIRED] = 0;
-    for (int q = 0; q < Q_COUNT; q++) wf.qCount[q] = 0;
+// one thread, once per render call: roll the last iteration's queue sizes into the totals
+__global__ void k_foldCounters(WavefrontState wf, uint32_t parity, unsigned long long paths) {
+    uint32_t* bank = wf.qCount + parity * Q_COUNT;
+    unsigned long long ext = bank[Q_MISS];
+    for (int q = 0; q < GSB_BSDF_TYPE_COUNT; q++) ext += bank[q];
+    wf.stats[ST_EXT] += ext;
+    wf.stats[ST_SHADOW] += bank[Q_SHADOW];
+    wf.stats[ST_PATHS] += paths;
+    for (int q = 0; q < 2 * Q_COUNT; q++) wf.qCount[q] = 0;
 }
 
 template <class T>
@@ -374,9 +392,9 @@ void allocWavefront(gsb_context* ctx, uint32_t slots) {
     const size_t n = slots;
     ensure(wf.rayO, n); ensure(wf.rayD, n); ensure(wf.weightDW, n); ensure(wf.result, n);
     ensure(wf.seed, n); ensure(wf.sampleK, n); ensure(wf.hitTUVP, n); ensure(wf.hitInst, n);
-    ensure(wf.matQueue, n * GSB_BSDF_TYPE_COUNT); ensure(wf.termQueue, n);
+    ensure(wf.matQueue, n * GSB_BSDF_TYPE_COUNT);
     ensure(wf.shadowO, n); ensure(wf.shadowD, n); ensure(wf.shadowBase, n); ensure(wf.shadowNee, n);
-    if (!wf.qCount) ensure(wf.qCount, (size_t)Q_COUNT);
+    if (!wf.qCount) ensure(wf.qCount, (size_t)2 * Q_COUNT);
     if (!wf.stats) {
         ensure(wf.stats, (size_t)ST_COUNT);
         GSB_CUDA(cudaMemsetAsync(wf.stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
@@ -385,8 +403,8 @@ void allocWavefront(gsb_context* ctx, uint32_t slots) {
 }
 
 template <int TYPE>
-void launchShade(gsb_context* ctx, const SceneDev& sc, int grid) {
-    k_shade<TYPE><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf);
+void launchShade(gsb_context* ctx, const SceneDev& sc, int grid, uint32_t parity) {
+    k_shade<TYPE><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity);
 }
 
 }  // namespace
@@ -394,7 +412,7 @@ void launchShade(gsb_context* ctx, const SceneDev& sc, int grid) {
 void freeWavefront(gsb_context* ctx) {
     WavefrontState& wf = ctx->wf;
     void* ptrs[] = {wf.rayO, wf.rayD, wf.weightDW, wf.result, wf.seed, wf.sampleK, wf.hitTUVP, wf.hitInst, wf.matQueue,
-                    wf.termQueue, wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.qCount, wf.stats};
+                    wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.qCount, wf.stats};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     wf = WavefrontState();
@@ -421,8 +439,9 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     ra.slots = slots;
     ra.totalWork = totalWork;
     ra.accum = ctx->dAccum;
+    ra.camZ = (std::fmax((float)width, (float)height) / 2.0f) / std::tan(ctx->fov / 2.0f);
     const SceneDev sc = ctx->sceneDev();
-    GSB_CUDA(cudaMemsetAsync(wf.qCount, 0, Q_COUNT * sizeof(uint32_t), s));
+    GSB_CUDA(cudaMemsetAsync(wf.qCount, 0, 2 * Q_COUNT * sizeof(uint32_t), s));
     const unsigned long long liveInit[2] = {(unsigned long long)slots, 0ull};
     const unsigned long long nextInit = (unsigned long long)slots;
     GSB_CUDA(cudaMemcpyAsync(wf.stats, liveInit, sizeof(liveInit), cudaMemcpyHostToDevice, s));
@@ -454,27 +473,27 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         pev.push_back(e);
     };
 
+    uint32_t parity = 0;
     auto iteration = [&]() {
         mark();
-        if (ctx->instrumented & 1) k_extend<true><<<fullGrid, kBlock, 0, s>>>(sc, wf, slots);
-        else k_extend<false><<<fullGrid, kBlock, 0, s>>>(sc, wf, slots);
+        if (ctx->instrumented & 1) k_extend<true><<<fullGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
+        else k_extend<false><<<fullGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
         mark();
-        if (ctx->typeUsed[0]) launchShade<0>(ctx, sc, queueGrid);
-        if (ctx->typeUsed[1]) launchShade<1>(ctx, sc, queueGrid);
-        if (ctx->typeUsed[2]) launchShade<2>(ctx, sc, queueGrid);
-        if (ctx->typeUsed[3]) launchShade<3>(ctx, sc, queueGrid);
-        if (ctx->typeUsed[4]) launchShade<4>(ctx, sc, queueGrid);
-        if (ctx->typeUsed[5]) launchShade<5>(ctx, sc, queueGrid);
-        if (ctx->typeUsed[6]) launchShade<6>(ctx, sc, queueGrid);
-        if (ctx->typeUsed[7]) launchShade<7>(ctx, sc, queueGrid);
+        if (ctx->typeUsed[0]) launchShade<0>(ctx, sc, queueGrid, parity);
+        if (ctx->typeUsed[1]) launchShade<1>(ctx, sc, queueGrid, parity);
+        if (ctx->typeUsed[2]) launchShade<2>(ctx, sc, queueGrid, parity);
+        if (ctx->typeUsed[3]) launchShade<3>(ctx, sc, queueGrid, parity);
+        if (ctx->typeUsed[4]) launchShade<4>(ctx, sc, queueGrid, parity);
+        if (ctx->typeUsed[5]) launchShade<5>(ctx, sc, queueGrid, parity);
+        if (ctx->typeUsed[6]) launchShade<6>(ctx, sc, queueGrid, parity);
+        if (ctx->typeUsed[7]) launchShade<7>(ctx, sc, queueGrid, parity);
         mark();
-        if (ctx->instrumented & 2) k_shadow<true><<<queueGrid, kBlock, 0, s>>>(sc, wf);
-        else k_shadow<false><<<queueGrid, kBlock, 0, s>>>(sc, wf);
+        if (ctx->instrumented & 2) k_shadow<true><<<queueGrid, kBlock, 0, s>>>(sc, wf, parity);
+        else k_shadow<false><<<queueGrid, kBlock, 0, s>>>(sc, wf, parity);
         mark();
-        k_finish<<<queueGrid, kBlock, 0, s>>>(sc, wf, ra);
-        k_endIteration<<<1, 1, 0, s>>>(wf);
         mark();
-        ctx->launches += 4 + (uint64_t)typesUsed;
+        parity ^= 1u;
+        ctx->launches += 2 + (uint64_t)typesUsed;
         ctx->lastRenderIters++;
     };
 
@@ -499,6 +518,8 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         b++;
         if (prof && pev.size() > 200000) break;
     }
+    k_foldCounters<<<1, 1, 0, s>>>(wf, parity ^ 1u, totalWork);
+    ctx->launches += 1;
     GSB_CUDA(cudaEventRecord(evStop, s));
     GSB_CUDA(cudaEventSynchronize(evStop));
     GSB_CUDA(cudaGetLastError());
