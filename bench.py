@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--scene", default="cornell")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-instrumented", action="store_true", help="skip the untimed fetch-count pass (profiler runs)")
     ap.add_argument("--e2e-steps", type=int, default=3)
     return ap.parse_args()
 
@@ -185,7 +186,8 @@ def run_ours(a, rank, world, local_rank):
     npix = W * H
     scene = g.Scene.builtin(a.scene)
     ctx = g.Context(local_rank)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=dev)     # one stream for the render, the NCCL reduce and the timing events
+    torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
     ctx.upload(scene)
     ctx.set_params(max_depth=a.max_depth)
@@ -208,15 +210,17 @@ def run_ours(a, rank, world, local_rank):
                 accum.zero_()       # rank 0 keeps the running global sum; the others restart their partial sums
 
     # ---- instrumented pass (untimed): fetch counts of the rays this workload really traces ------------------
-    ctx.set_instrumented(1)
-    ctx.reset_counters()
-    ctx.render(W, H, 1 << 20, 2, 1)
-    ci = ctx.counters()
-    ctx.set_instrumented(2)
-    ctx.reset_counters()
-    ctx.render(W, H, 1 << 20, 2, 1)
-    cs = ctx.counters()
-    ctx.set_instrumented(0)
+    ci = cs = {"nodes_visited": 0, "tris_tested": 0, "inst_entered": 0, "rays_counted": 0}
+    if not a.no_instrumented:
+        ctx.set_instrumented(1)
+        ctx.reset_counters()
+        ctx.render(W, H, 1 << 20, 2, 1)
+        ci = ctx.counters()
+        ctx.set_instrumented(2)
+        ctx.reset_counters()
+        ctx.render(W, H, 1 << 20, 2, 1)
+        cs = ctx.counters()
+        ctx.set_instrumented(0)
     ext_fetch = {k: ci[k] / max(ci["rays_counted"], 1) for k in ("nodes_visited", "tris_tested", "inst_entered")}
     sh_fetch = {k: cs[k] / max(cs["rays_counted"], 1) for k in ("nodes_visited", "tris_tested", "inst_entered")}
     # 80 B per 8-wide node, 48 B per triangle, 64 B per instance record, + the wavefront streams of the
@@ -231,28 +235,38 @@ def run_ours(a, rank, world, local_rank):
         step(k)
     ctx.clear()
     accum.zero_()
-    ctx.set_profiling(True)       # CUDA events around every stage of every wavefront iteration (same stream)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    stage = {"extend": 0.0, "shade": 0.0, "shadow": 0.0, "finish": 0.0}
-    iters = 0
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
     for k in range(a.steps):
-        step(a.warmup + k)
+        step(a.warmup + k)      # asynchronous: the K steps queue up on the stream, the host never gates the device
+    ev1.record(stream)
+    barrier()
+    device_ms = ev0.elapsed_time(ev1)
+    c = ctx.counters()
+    launches = ctx.launch_info()[0]
+    # ---- stage breakdown: the same step with CUDA events around every stage of every wavefront iteration (events on
+    # the render stream; this mode drives the iterations from the host instead of the device-side graph loop)
+    ctx.set_profiling(True)
+    stage = {"extend": 0.0, "shade": 0.0, "shadow": 0.0, "finish": 0.0}
+    iters = 0
+    prof_steps = max(1, min(a.steps, 2))
+    prof_ext = 0
+    for k in range(prof_steps):
+        c0 = ctx.counters()
+        ctx.render(W, H, (a.warmup + a.steps + k) * S * world + rank, S, world)
         ms = ctx.last_render_ms()
         for name in stage:
             stage[name] += ms[name]
         iters += ctx.launch_info()[1]
-    ev1.record(stream)
+        prof_ext += ctx.counters()["extension_rays"] - c0["extension_rays"]
+    ctx.set_profiling(False)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     elapsed_ms = ev0.elapsed_time(ev1)
-    ctx.set_profiling(False)
-    c = ctx.counters()
-    launches = ctx.launch_info()[0]
     t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
     totals = torch.tensor([c["paths"], c["extension_rays"], c["shadow_rays"], launches], dtype=torch.float64, device=dev)
     if world > 1:
@@ -268,7 +282,7 @@ def run_ours(a, rank, world, local_rank):
         img = ctx.read_hdr()
         assert np.isfinite(img).all() and img[..., :3].mean() > 0.01, "bench image is empty"
         samples = float(accum.view(-1, 4)[:, 3].mean().item())
-        assert abs(samples - a.steps * S * world) < 0.5, f"sum buffer holds {samples} samples per pixel"
+        assert abs(samples - (a.steps * world + prof_steps) * S) < 0.5, f"sum buffer holds {samples} samples per pixel"
 
     # ---- roofline of the dominant kernel (k_extend: closest-hit traversal), from this rank's timed region -----------
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -276,7 +290,7 @@ def run_ours(a, rank, world, local_rank):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy)"
     else:
         peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
-    ext_per_launch = c["extension_rays"] / max(iters, 1)
+    ext_per_launch = prof_ext / max(iters, 1)
     ext_ms_per_launch = stage["extend"] / max(iters, 1)
     achieved = ext_bytes_per_ray * ext_per_launch / (ext_ms_per_launch * 1e-3) / 1e9 if ext_ms_per_launch > 0 else 0.0
     traffic = None
@@ -290,7 +304,7 @@ def run_ours(a, rank, world, local_rank):
                 "fetch_per_ray": ext_fetch, "launches": iters,
                 "share_of_step": {k: v / stage_total for k, v in stage.items()} if stage_total > 0 else None,
                 "shadow": {"bytes_per_ray": sh_bytes_per_ray, "fetch_per_ray": sh_fetch,
-                           "achieved": (sh_bytes_per_ray * c["shadow_rays"] / (stage["shadow"] * 1e-3) / 1e9) if stage["shadow"] > 0 else 0.0},
+                           "achieved": (sh_bytes_per_ray * c["shadow_rays"] * prof_steps / a.steps / (stage["shadow"] * 1e-3) / 1e9) if stage["shadow"] > 0 else 0.0},
                 "note": "scene BVH is a few KB (L1/L2 resident): the HBM figure is the algorithmic-byte rate, not DRAM traffic"}
 
     # ---- e2e: the per-frame API with host buffers ----------------------------------------------------------------------
@@ -359,7 +373,8 @@ def run_ours(a, rank, world, local_rank):
                            "scene": a.scene, "parallelism": f"sample-index sharding x{world}" + (", 1 NCCL reduce per step" if world > 1 else ""),
                            "l2": "path state streams of a step (2.07 M slots x ~230 B = 480 MB) exceed the 126 MB L2; scene data is meant to be cache resident"},
                 "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(launches),
-                "stage_ms_per_step": {k: v / a.steps for k, v in stage.items()}}
+                "stage_ms_per_step": {k: v / prof_steps for k, v in stage.items()},
+                "device_ms_per_step": device_ms / a.steps}
         print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:

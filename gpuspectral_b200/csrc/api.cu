@@ -1,5 +1,6 @@
 // api.cu — the extern "C" layer of include/gpuspectral_b200.h: context, scene upload,
 // acceleration-structure builds, ray batches, framebuffer read-back, diagnostic entry points.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -64,16 +65,30 @@ struct Bind {
 };
 
 // ---- kernels of this translation unit ----------------------------------------------------------------
-template <bool ANYHIT, bool STATS>
-__global__ void __launch_bounds__(128) k_traceBatch(SceneDev sc, const gsb_ray* __restrict__ rays, uint32_t n, gsb_hit* __restrict__ hits,
-                                                    unsigned long long* stats) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    TraceStats ts = {0u, 0u, 0u};
-    if (i < n) {
+// The ray stream of gsb_trace_batch: work index = position in the caller's ray array.
+template <bool ANYHIT>
+struct BatchSource {
+    const gsb_ray* rays;
+    gsb_hit* hits;
+    uint32_t n;
+    uint32_t* counter;
+    WorkRange range;
+    uint32_t traced = 0;
+
+    GSB_D bool drained() const { return range.exhausted; }
+    GSB_D bool fetch(bool want, RayJob& job) {
+        const uint32_t i = range.take(counter, n, want);
+        if (i == kNoTag) return false;
         const float4 a = __ldg(reinterpret_cast<const float4*>(rays) + 2 * (size_t)i);
         const float4 b = __ldg(reinterpret_cast<const float4*>(rays) + 2 * (size_t)i + 1);
-        HitRecord h;
-        traceRay<ANYHIT, STATS>(sc, a.x, a.y, a.z, b.x, b.y, b.z, a.w, b.w, h, &ts, (uint32_t*)&stats[ST_OVERFLOW]);
+        job.ox = a.x; job.oy = a.y; job.oz = a.z; job.tmin = a.w;
+        job.dx = b.x; job.dy = b.y; job.dz = b.z; job.tmax = b.w;
+        job.tag = i;
+        traced++;
+        return true;
+    }
+    GSB_D void commit(bool have, const HitRecord& h, uint32_t i) {
+        if (!have) return;
         gsb_hit o;
         if (ANYHIT) {
             o.t = 0.0f; o.u = 0.0f; o.v = 0.0f;
@@ -84,15 +99,25 @@ __global__ void __launch_bounds__(128) k_traceBatch(SceneDev sc, const gsb_ray* 
         }
         hits[i] = o;
     }
+};
+
+template <bool ANYHIT, bool STATS>
+__global__ void __launch_bounds__(kTraceBlock) k_traceBatch(SceneDev sc, const gsb_ray* __restrict__ rays, uint32_t n,
+                                                            gsb_hit* __restrict__ hits, unsigned long long* stats, uint32_t refillMin) {
+    BatchSource<ANYHIT> src;
+    src.rays = rays; src.hits = hits; src.n = n;
+    src.counter = reinterpret_cast<uint32_t*>(&stats[ST_BATCHNEXT]);
+    TraceStats ts = {0u, 0u, 0u};
+    traceStream<ANYHIT, STATS>(sc, src, refillMin, &ts, (uint32_t*)&stats[ST_OVERFLOW]);
     if (STATS) {
-        uint32_t nn = ts.nodes, nt = ts.tris, ni = ts.insts, nr = i < n ? 1u : 0u;
+        uint32_t nn = ts.nodes, nt = ts.tris, ni = ts.insts, nr = src.traced;
         for (int o = 16; o > 0; o >>= 1) {
             nn += __shfl_xor_sync(0xffffffffu, nn, o);
             nt += __shfl_xor_sync(0xffffffffu, nt, o);
             ni += __shfl_xor_sync(0xffffffffu, ni, o);
             nr += __shfl_xor_sync(0xffffffffu, nr, o);
         }
-        if ((threadIdx.x & 31) == 0) {
+        if ((threadIdx.x & 31) == 0 && nr) {
             atomicAdd(&stats[ST_NODES], (unsigned long long)nn);
             atomicAdd(&stats[ST_TRIS], (unsigned long long)nt);
             atomicAdd(&stats[ST_INSTS], (unsigned long long)ni);
@@ -230,6 +255,13 @@ void checkOverflow(gsb_context* ctx) {
     }
 }
 
+// Waits for asynchronous render calls and reports a traversal-stack overflow any of them hit.
+void drain(gsb_context* ctx) {
+    if (ctx->pending.empty()) return;
+    finishPending(ctx);
+    checkOverflow(ctx);
+}
+
 }  // namespace
 }  // namespace gsb
 
@@ -272,6 +304,11 @@ gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx) {
         ctx->device = device_ordinal;
         GSB_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
         ensureStats(ctx);
+        if (const char* e = getenv("GSB_GRAPH")) ctx->useGraphLoop = atoi(e) != 0;
+        if (const char* e = getenv("GSB_REFILL")) {
+            const long v = atol(e);
+            if (v >= 1 && v <= 32) ctx->refillMin = (uint32_t)v;
+        }
         if (const char* e = getenv("GSB_SLOTS")) {
             const long v = atol(e);
             if (v >= 1024 && v <= (1l << 26)) ctx->targetSlots = (uint32_t)v;
@@ -285,6 +322,7 @@ gsb_status gsb_destroy(gsb_context* ctx) {
     if (!ctx) return GSB_OK;
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         cudaStreamSynchronize(ctx->stream);
         for (MeshRec& m : ctx->meshes) {
             if (!m.alive) continue;
@@ -337,6 +375,7 @@ gsb_status gsb_mesh_destroy(gsb_context* ctx, uint32_t mesh) {
     if (!ctx || mesh >= ctx->meshes.size() || !ctx->meshes[mesh].alive) return fail(GSB_ERR_INVALID, "gsb_mesh_destroy: bad mesh handle");
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         for (const gsb_instance& in : ctx->instances)
             if (in.mesh == mesh) {
                 ctx->haveInstances = false;  // the scene referenced it: force a new gsb_scene_set_instances
@@ -358,6 +397,7 @@ gsb_status gsb_scene_set_bsdfs(gsb_context* ctx, uint32_t type, const void* para
     if (count > 65536) return fail(GSB_ERR_INVALID, "gsb_scene_set_bsdfs: more than 65536 records of one type (16-bit handle index)");
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
         cudaFree(ctx->dBsdf[type]);
         ctx->dBsdf[type] = uploadArray((const uint8_t*)params, (size_t)count * kBsdfStride[type], ctx->stream);
@@ -371,6 +411,7 @@ gsb_status gsb_scene_set_lights(gsb_context* ctx, const gsb_triangle_light* ligh
     if (!ctx || (count && !lights)) return fail(GSB_ERR_INVALID, "gsb_scene_set_lights: null argument");
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
         cudaFree(ctx->dLights);
         ctx->dLights = uploadArray(lights, count, ctx->stream);
@@ -390,6 +431,7 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
     }
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
         ctx->instances.assign(instances, instances + count);
         std::vector<ShadeInstance> shade(count);
@@ -533,7 +575,7 @@ gsb_status gsb_render(gsb_context* ctx, uint32_t width, uint32_t height, uint32_
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
         renderImpl(ctx, width, height, first_sample, num_samples, sample_stride);
-        checkOverflow(ctx);
+        if (ctx->pending.empty()) checkOverflow(ctx);   // host-driven loop: the call has completed
         return GSB_OK;
     });
 }
@@ -542,8 +584,10 @@ gsb_status gsb_clear(gsb_context* ctx) {
     if (!ctx) return fail(GSB_ERR_INVALID, "gsb_clear: null context");
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         if (ctx->dAccum) GSB_CUDA(cudaMemsetAsync(ctx->dAccum, 0, (size_t)ctx->width * ctx->height * sizeof(float4), ctx->stream));
         GSB_CUDA(cudaMemsetAsync(ctx->wf.stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
+        ctx->seenIters = 0;
         ctx->launches = 0;
         return GSB_OK;
     });
@@ -553,6 +597,7 @@ gsb_status gsb_synchronize(gsb_context* ctx) {
     if (!ctx) return fail(GSB_ERR_INVALID, "gsb_synchronize: null context");
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
         return GSB_OK;
     });
@@ -563,6 +608,7 @@ static gsb_status readImage(gsb_context* ctx, float* hdr, uint8_t* ldr) {
     if (!ctx->dAccum) return fail(GSB_ERR_STATE, "gsb_read: nothing rendered yet");
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         const uint32_t npix = ctx->width * ctx->height;
         Scratch sc;
         float4* dHdr = hdr ? sc.alloc<float4>(npix) : nullptr;
@@ -590,6 +636,7 @@ gsb_status gsb_get_counters(gsb_context* ctx, gsb_counters* out) {
     if (!ctx || !out) return fail(GSB_ERR_INVALID, "gsb_get_counters: null argument");
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         unsigned long long h[ST_COUNT];
         GSB_CUDA(cudaMemcpyAsync(h, ctx->wf.stats, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -609,7 +656,9 @@ gsb_status gsb_reset_counters(gsb_context* ctx) {
     if (!ctx) return fail(GSB_ERR_INVALID, "gsb_reset_counters: null context");
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         GSB_CUDA(cudaMemsetAsync(ctx->wf.stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
+        ctx->seenIters = 0;
         ctx->launches = 0;
         return GSB_OK;
     });
@@ -631,6 +680,7 @@ gsb_status gsb_set_stream(gsb_context* ctx, void* cuda_stream) {
     if (!ctx) return fail(GSB_ERR_INVALID, "gsb_set_stream: null context");
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
         if (ctx->ownStream) cudaStreamDestroy(ctx->stream);
         if (cuda_stream) {
@@ -646,6 +696,8 @@ gsb_status gsb_set_stream(gsb_context* ctx, void* cuda_stream) {
 
 gsb_status gsb_get_launch_info(gsb_context* ctx, uint64_t* out_launches, uint64_t* out_last_render_iterations) {
     if (!ctx) return fail(GSB_ERR_INVALID, "gsb_get_launch_info: null context");
+    const gsb_status st = guarded([&]() -> gsb_status { Bind bind(ctx->device); drain(ctx); return GSB_OK; });
+    if (st != GSB_OK) return st;
     if (out_launches) *out_launches = ctx->launches;
     if (out_last_render_iterations) *out_last_render_iterations = ctx->lastRenderIters;
     return GSB_OK;
@@ -653,6 +705,8 @@ gsb_status gsb_get_launch_info(gsb_context* ctx, uint64_t* out_launches, uint64_
 
 gsb_status gsb_last_render_ms(gsb_context* ctx, double out_ms[5]) {
     if (!ctx || !out_ms) return fail(GSB_ERR_INVALID, "gsb_last_render_ms: null argument");
+    const gsb_status st = guarded([&]() -> gsb_status { Bind bind(ctx->device); drain(ctx); return GSB_OK; });
+    if (st != GSB_OK) return st;
     for (int k = 0; k < 5; k++) out_ms[k] = ctx->lastRenderMs[k];
     return GSB_OK;
 }
@@ -663,11 +717,15 @@ static gsb_status traceBatch(gsb_context* ctx, const gsb_ray* rays, uint32_t cou
     if (!sceneReady(ctx)) return fail(GSB_ERR_STATE, "gsb_trace_batch: no scene (call gsb_scene_set_instances first)");
     return guarded([&]() -> gsb_status {
         Bind bind(ctx->device);
+        drain(ctx);
         Scratch scr;
         gsb_ray* dRays = scr.upload(rays, count, ctx->stream);
         gsb_hit* dHits = scr.alloc<gsb_hit>(count);
         const SceneDev sc = ctx->sceneDev();
-        const int grid = (int)((count + 127) / 128);
+        int sms = 148, perSm = 4;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_traceBatch<false, false>, kTraceBlock, 0);
+        const int grid = std::max(1, std::min((int)((count + kTraceBlock - 1) / kTraceBlock), sms * std::max(perSm, 1)));
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (out_ms) {
             GSB_CUDA(cudaEventCreate(&e0));
@@ -676,12 +734,13 @@ static gsb_status traceBatch(gsb_context* ctx, const gsb_ray* rays, uint32_t cou
         for (int r = 0; r < repeats + (out_ms ? 1 : 0); r++) {
             if (out_ms && r == 1) GSB_CUDA(cudaEventRecord(e0, ctx->stream));  // launch 0 is a warm-up
             if (count == 0) break;
+            GSB_CUDA(cudaMemsetAsync(&ctx->wf.stats[ST_BATCHNEXT], 0, sizeof(unsigned long long), ctx->stream));  // the stream's work counter
             if (stats) {
-                if (any_hit) k_traceBatch<true, true><<<grid, 128, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats);
-                else k_traceBatch<false, true><<<grid, 128, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats);
+                if (any_hit) k_traceBatch<true, true><<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, ctx->refillMin);
+                else k_traceBatch<false, true><<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, ctx->refillMin);
             } else {
-                if (any_hit) k_traceBatch<true, false><<<grid, 128, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats);
-                else k_traceBatch<false, false><<<grid, 128, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats);
+                if (any_hit) k_traceBatch<true, false><<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, ctx->refillMin);
+                else k_traceBatch<false, false><<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, ctx->refillMin);
             }
         }
         GSB_CUDA(cudaGetLastError());

@@ -19,7 +19,9 @@ struct MeshRec {
 
 // Counter indices inside WavefrontState::qCount (two banks of Q_COUNT, selected by iteration parity):
 // one queue per BSDF type, the number of extension rays that missed, the shadow-ray queue.
-enum { Q_MATERIAL0 = 0, Q_MISS = GSB_BSDF_TYPE_COUNT, Q_SHADOW = GSB_BSDF_TYPE_COUNT + 1, Q_COUNT = 12 };
+enum { Q_MATERIAL0 = 0, Q_MISS = GSB_BSDF_TYPE_COUNT, Q_SHADOW = GSB_BSDF_TYPE_COUNT + 1,
+       Q_NEXT_EXTEND = 10, Q_NEXT_SHADOW = 11,  // work counters of the persistent traversal kernels
+       Q_COUNT = 12 };
 
 // Per-slot path state, structure of arrays.  The 17-word HitPayload of pt_common.glsl:4-14
 // (+ pixel sample index and the hit record) spread over 16-byte and 4-byte streams.
@@ -44,7 +46,15 @@ struct WavefrontState {
     unsigned long long* stats = nullptr;
 };
 
-enum { ST_LIVE = 0, ST_RETIRED = 1, ST_PATHS = 2, ST_EXT = 3, ST_SHADOW = 4, ST_ITERS = 5, ST_NODES = 6, ST_TRIS = 7, ST_INSTS = 8, ST_RAYS = 9, ST_OVERFLOW = 10, ST_NEXTWORK = 11, ST_COUNT = 16 };
+enum { ST_LIVE = 0, ST_RETIRED = 1, ST_PATHS = 2, ST_EXT = 3, ST_SHADOW = 4, ST_ITERS = 5, ST_NODES = 6, ST_TRIS = 7, ST_INSTS = 8, ST_RAYS = 9, ST_OVERFLOW = 10, ST_NEXTWORK = 11, ST_BATCHNEXT = 12, ST_LOOPITERS = 13, ST_COUNT = 16 };
+
+// A render call that was launched as a device-side loop and has not been waited for yet.
+struct PendingRender {
+    cudaGraphExec_t exec = nullptr;
+    cudaGraph_t graph = nullptr;
+    cudaEvent_t start = nullptr, stop = nullptr;
+    uint32_t launchesPerIter = 0;
+};
 
 }  // namespace gsb
 
@@ -73,11 +83,15 @@ struct gsb_context {
     gsb::WavefrontState wf;
     bool profiling = false;
     uint32_t targetSlots = 1u << 20;  // paths in flight per wavefront (GSB_SLOTS overrides)
+    uint32_t refillMin = 24;     // idle lanes that trigger a refill in the persistent traversal kernels (GSB_REFILL overrides)
+    bool useGraphLoop = true;    // device-side render loop (conditional CUDA graph); GSB_GRAPH=0 or a failed build disables it
     int instrumented = 0;        // bit 0: count fetches of extension rays, bit 1: of shadow rays
     bool ownStream = true;       // false after gsb_set_stream
     uint64_t launches = 0;       // kernels launched by gsb_render since gsb_reset_counters
     uint64_t lastRenderIters = 0;
     double lastRenderMs[5] = {0, 0, 0, 0, 0};
+    std::vector<gsb::PendingRender> pending;   // asynchronous render calls in flight on `stream`
+    unsigned long long seenIters = 0;          // value of the device iteration counter already accounted for
 
     gsb::SceneDev sceneDev() const;
 };
@@ -86,4 +100,6 @@ namespace gsb {
 // wavefront.cu
 void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t first, uint32_t count, uint32_t stride);
 void freeWavefront(gsb_context* ctx);
+// Waits for the render calls in flight, releases their graphs and folds their iteration counts into the context.
+void finishPending(gsb_context* ctx);
 }  // namespace gsb

@@ -173,39 +173,99 @@ GSB_D void intersectNode(const uint4* __restrict__ nodes, uint32_t nodeIndex, fl
     leafGroup = make_uint2(w1.y, hits & 0x00ffffffu);
 }
 
-// Traces one ray.  ANYHIT: returns as soon as any triangle has tmin < t < tmax (hit.inst = 0).
-// STATS: counts fetched nodes / triangles / instance records.
+// One ray as the traversal loop sees it.  `tag` is the caller's handle (slot / queue index / batch index).
+struct RayJob {
+    float ox, oy, oz, dx, dy, dz, tmin, tmax;
+    uint32_t tag;
+};
+constexpr uint32_t kNoTag = 0xffffffffu;
+
+// Warp-private range of work indices [cur, end) carved out of a global counter in chunks, so that a refill costs
+// no atomic most of the time and consecutive lanes get consecutive indices (coalesced state loads).  The chunk after
+// the current one is reserved ahead of time (`next`), so the counter's round trip is off the critical path.
+struct WorkRange {
+    uint32_t cur = 0, end = 0;
+    uint32_t next = 0;         // base of the chunk reserved ahead; valid when haveNext
+    bool haveNext = false;
+    bool exhausted = false;    // the counter has passed `total`: nothing beyond [cur, end) will come
+    static constexpr uint32_t kChunk = 64;
+
+    GSB_D void reserve(uint32_t* counter, uint32_t total) {
+        if (haveNext || exhausted) return;
+        uint32_t base = 0;
+        if ((threadIdx.x & 31u) == 0) base = atomicAdd(counter, kChunk);
+        next = __shfl_sync(0xffffffffu, base, 0);
+        haveNext = true;
+    }
+    // Every lane of the warp calls this; lanes with `want` get distinct indices < total (or kNoTag when work ran out).
+    GSB_D uint32_t take(uint32_t* counter, uint32_t total, bool want) {
+        const uint32_t mask = __ballot_sync(0xffffffffu, want);
+        const uint32_t n = (uint32_t)__popc(mask);
+        const uint32_t lane = threadIdx.x & 31u;
+        const uint32_t rank = (uint32_t)__popc(mask & ((1u << lane) - 1u));
+        const uint32_t avail = end - cur;
+        uint32_t idx;
+        if (n <= avail) {
+            idx = cur + rank;
+            cur += n;
+        } else {
+            reserve(counter, total);
+            uint32_t base = total;
+            if (haveNext) { base = next; haveNext = false; }
+            if (base >= total) exhausted = true;     // the counter only grows: nothing later can be valid
+            idx = rank < avail ? cur + rank : base + (rank - avail);
+            cur = base + (n - avail);
+            end = base + kChunk;
+            if (exhausted) { cur = 0; end = 0; }
+        }
+        if (cur >= total) { cur = 0; end = 0; exhausted = true; }
+        reserve(counter, total);                     // issued now, consumed at a later refill
+        return (want && idx < total) ? idx : kNoTag;
+    }
+    // Index the lane would get at the next refill if all lanes asked (for prefetching); kNoTag when unknown.
+    GSB_D uint32_t peek(uint32_t total) const {
+        const uint32_t i = cur + (threadIdx.x & 31u);
+        return (i < end && i < total) ? i : kNoTag;
+    }
+};
+
+GSB_D void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
+// Traces a stream of rays with one persistent warp: the traversal loop never waits for the slowest ray of a
+// batch — a lane whose ray is finished hands its result to `src.commit` and gets the next ray from `src.fetch`
+// at the top of the next pass (dynamic ray fetch, Aila & Laine 2009), so all 32 lanes stay in flight until the
+// stream runs dry.
 //
-// Loop shape: every pass runs the same three phases in the same order — (1) descend one node, (2) leaf work
-// (enter one instance at the top level / test the pending triangles at the bottom level), (3) pop — each under
-// its own predicate, so the lanes of a warp that are in the same phase execute it together and a lane can
-// advance through all three in one pass.  (A one-item-per-pass state machine ran at 9 of 32 lanes active on
-// the Cornell box: profiles/r1b_stage_kernels_ncu.md.)  The first kSmemStack stack entries live in shared
-// memory ([entry][thread]: conflict-free 64-bit accesses); deeper entries spill to local memory.
-template <bool ANYHIT, bool STATS>
-GSB_D void traceRay(const SceneDev& sc, float ox, float oy, float oz, float dx, float dy, float dz, float tmin, float tmax,
-                    HitRecord& hit, TraceStats* stats, uint32_t* overflowFlag) {
-    hit.t = tmax; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT;
+// Source concept (all members are called by all 32 lanes together, warp-synchronously):
+//   void commit(bool have, const HitRecord& hit, uint32_t tag)   result of a finished ray (have = lane has one)
+//   bool fetch(bool want, RayJob& job)                           next ray for idle lanes; false = lane got none
+//   bool drained()                                               warp-uniform: no more rays will ever come
+//
+// Pass shape: every pass runs the same phases in the same order — (1) descend one node, (2a) enter one instance
+// at the top level, (2b) test the pending triangles at the bottom level, (3) pop — each under its own predicate,
+// so the lanes of a warp that are in the same phase execute it together and a lane can advance through all of
+// them in one pass.  ANYHIT: a ray ends at the first triangle with tmin < t < tmax (hit.inst = 0).
+// The first kSmemStack stack entries live in shared memory ([entry][thread]: conflict-free 64-bit accesses);
+// deeper entries spill to local memory.
+template <bool ANYHIT, bool STATS, class Source>
+GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t refillMin, TraceStats* stats, uint32_t* overflowFlag) {
     __shared__ uint2 s_stack[kSmemStack][kTraceBlock];
     uint2 lstack[kStackSize - kSmemStack];
     const uint32_t tid = threadIdx.x;
-    int sp = 0;
-    int spMark = -1;  // stack height at which the current instance was entered; -1 at the top level
 
-    // world-space box-test constants
-    const float widx = slabInv(dx), widy = slabInv(dy), widz = slabInv(dz);
-    const uint32_t woct = (dx < 0.0f ? 0u : 4u) | (dy < 0.0f ? 0u : 2u) | (dz < 0.0f ? 0u : 1u);
-
-    // current level state (top level first)
+    RayJob job;
+    job.tag = kNoTag;
+    HitRecord hit;
+    bool active = false;
+    int sp = 0, spMark = -1;
+    float widx = 0.0f, widy = 0.0f, widz = 0.0f;
+    uint32_t woct = 0;
     const uint4* nodes = sc.tlasNodes;
     const float4* tris = nullptr;
-    float cox = ox, coy = oy, coz = oz, cidx = widx, cidy = widy, cidz = widz;
-    uint32_t oct7 = woct;
-    uint32_t curInst = 0;
+    float cox = 0.0f, coy = 0.0f, coz = 0.0f, cidx = 0.0f, cidy = 0.0f, cidz = 0.0f;
+    uint32_t oct7 = 0, curInst = 0;
     ObjRay oray;
-
-    uint2 G = make_uint2(0u, 0x80000000u);  // root group: bit 31, imask 0 -> node childBase + 0
-    uint2 T = make_uint2(0u, 0u);
+    uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
 
 #define GSB_PUSH(entry)                                                      \
     do {                                                                     \
@@ -215,6 +275,33 @@ GSB_D void traceRay(const SceneDev& sc, float ox, float oy, float oz, float dx, 
     } while (0)
 
     for (;;) {
+        // ---- refill: hand in finished rays, take new ones (warp-uniform branch).  While the stream still has rays
+        // a refill waits until refillMin lanes are idle, so that its fixed cost (and the latency of the state
+        // loads) is shared by several rays.
+        const uint32_t idle = __ballot_sync(0xffffffffu, !active);
+        const uint32_t pending = __ballot_sync(0xffffffffu, !active && job.tag != kNoTag);
+        if (idle == 0xffffffffu || (src.drained() ? pending != 0u : (uint32_t)__popc(idle) >= refillMin)) {
+            src.commit(!active && job.tag != kNoTag, hit, job.tag);
+            if (!active) job.tag = kNoTag;
+            const bool got = src.fetch(!active, job);
+            if (got) {
+                active = true;
+                hit.t = job.tmax; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT;
+                widx = slabInv(job.dx); widy = slabInv(job.dy); widz = slabInv(job.dz);
+                woct = (job.dx < 0.0f ? 0u : 4u) | (job.dy < 0.0f ? 0u : 2u) | (job.dz < 0.0f ? 0u : 1u);
+                nodes = sc.tlasNodes;
+                cox = job.ox; coy = job.oy; coz = job.oz; cidx = widx; cidy = widy; cidz = widz;
+                oct7 = woct;
+                sp = 0; spMark = -1;
+                G = make_uint2(0u, 0x80000000u);  // root group: bit 31, imask 0 -> node childBase + 0
+                T = make_uint2(0u, 0u);
+            }
+            if (!__any_sync(0xffffffffu, active)) {
+                if (src.drained()) break;
+                continue;
+            }
+        }
+        if (active) {
         // ---- phase 1: descend into the pending internal child that comes first in octant order
         if (G.y & 0xff000000u) {
             const uint32_t bit = 31u - (uint32_t)__clz(G.y);
@@ -223,7 +310,7 @@ GSB_D void traceRay(const SceneDev& sc, float ox, float oy, float oz, float dx, 
             const uint32_t nodeIndex = G.x + __popc(G.y & ((1u << slot) - 1u) & 0xffu);
             if (G.y & 0xff000000u) GSB_PUSH(G);
             if (STATS) stats->nodes++;
-            intersectNode(nodes, nodeIndex, cox, coy, coz, cidx, cidy, cidz, tmin, hit.t, oct7, G, T);
+            intersectNode(nodes, nodeIndex, cox, coy, coz, cidx, cidy, cidz, job.tmin, hit.t, oct7, G, T);
         }
         // ---- phase 2a (top level): enter one instance, park the rest of this node
         if (spMark < 0 && T.y) {
@@ -237,6 +324,7 @@ GSB_D void traceRay(const SceneDev& sc, float ox, float oy, float oz, float dx, 
             const uint4 tail = __ldg(reinterpret_cast<const uint4*>(ti) + 3);
             if (STATS) stats->insts++;
             // o' = M^-1 (o,1), d' = M^-1 (d,0); rounded op by op, same order as the checker
+            const float ox = job.ox, oy = job.oy, oz = job.oz, dx = job.dx, dy = job.dy, dz = job.dz;
             const float tox = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r0.x, ox), __fmul_rn(r0.y, oy)), __fmul_rn(r0.z, oz)), r0.w);
             const float toy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r1.x, ox), __fmul_rn(r1.y, oy)), __fmul_rn(r1.z, oz)), r1.w);
             const float toz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r2.x, ox), __fmul_rn(r2.y, oy)), __fmul_rn(r2.z, oz)), r2.w);
@@ -250,7 +338,7 @@ GSB_D void traceRay(const SceneDev& sc, float ox, float oy, float oz, float dx, 
             curInst = tail.w;
             const uint32_t direct = tail.z >> kDirectShift;
             if (direct) {
-                // node-less mesh (<= 7 triangles): its world box was already tested in the TLAS node
+                // node-less mesh (<= 4 triangles): its world box was already tested in the TLAS node
                 G = make_uint2(0u, 0u);
                 T = make_uint2(0u, (1u << direct) - 1u);
             } else {
@@ -272,11 +360,16 @@ GSB_D void traceRay(const SceneDev& sc, float ox, float oy, float oz, float dx, 
                 float Tn, V, W, det;
                 if (woopEdges(oray, v0, v1, v2, Tn, V, W, det)) {
                     const float t = __fdiv_rn(Tn, det);
-                    if (t > tmin && t < tmax) {
-                        if (ANYHIT) { hit.inst = 0u; hit.prim = 0u; hit.t = 0.0f; return; }
-                        const uint32_t prim = __float_as_uint(v0.w);
-                        if (t < hit.t || (t == hit.t && (curInst < hit.inst || (curInst == hit.inst && prim < hit.prim)))) {
-                            hit.t = t; hit.u = __fdiv_rn(V, det); hit.v = __fdiv_rn(W, det); hit.inst = curInst; hit.prim = prim;
+                    if (t > job.tmin && t < job.tmax) {
+                        if (ANYHIT) {
+                            // occluded: drop everything still pending, phase 3 ends the ray
+                            hit.inst = 0u; hit.prim = 0u; hit.t = 0.0f;
+                            T.y = 0u; G.y = 0u; sp = 0;
+                        } else {
+                            const uint32_t prim = __float_as_uint(v0.w);
+                            if (t < hit.t || (t == hit.t && (curInst < hit.inst || (curInst == hit.inst && prim < hit.prim)))) {
+                                hit.t = t; hit.u = __fdiv_rn(V, det); hit.v = __fdiv_rn(W, det); hit.inst = curInst; hit.prim = prim;
+                            }
                         }
                     }
                 }
@@ -287,18 +380,21 @@ GSB_D void traceRay(const SceneDev& sc, float ox, float oy, float oz, float dx, 
             if (sp == spMark) {
                 spMark = -1;
                 nodes = sc.tlasNodes;
-                cox = ox; coy = oy; coz = oz; cidx = widx; cidy = widy; cidz = widz;
+                cox = job.ox; coy = job.oy; coz = job.oz; cidx = widx; cidy = widy; cidz = widz;
                 oct7 = woct;
             }
-            if (sp == 0) break;
-            --sp;
-            const uint2 e = sp < kSmemStack ? s_stack[sp][tid] : lstack[sp - kSmemStack];
-            if (e.y & 0xff000000u) { G = e; T = make_uint2(0u, 0u); }
-            else { T = e; G = make_uint2(0u, 0u); }
+            if (sp == 0) {
+                active = false;  // this ray is done; its result is handed in at the next refill
+            } else {
+                --sp;
+                const uint2 e = sp < kSmemStack ? s_stack[sp][tid] : lstack[sp - kSmemStack];
+                if (e.y & 0xff000000u) { G = e; T = make_uint2(0u, 0u); }
+                else { T = e; G = make_uint2(0u, 0u); }
+            }
         }
+        }  // active
     }
 #undef GSB_PUSH
-    if (ANYHIT) { hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT; }
 }
 
 }  // namespace gsb

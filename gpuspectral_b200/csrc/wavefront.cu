@@ -41,6 +41,8 @@ struct RenderArgs {
     uint32_t width, height, npix;
     uint32_t first, count, stride;  // timestamps first + k*stride, k < count
     uint32_t slots;                 // paths in flight
+    double invNpix;                 // 1 / npix
+    uint32_t refillMin;             // idle lanes that trigger a refill of a persistent traversal warp
     float camZ;                     // (max(W,H)/2) / tan(fov/2) of rayDir(), raygen.rgen:20-25 (evaluated once on the host)
     unsigned long long totalWork;   // npix * count pixel-samples
     float4* accum;                  // the image: rgb = sum of samples, a = samples added
@@ -63,8 +65,12 @@ GSB_D uint32_t queueSlot(uint32_t* counters, uint32_t key, bool pred) {
 // pixel work % npix); the new ray is also returned in registers
 GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderArgs& ra, uint32_t slot, unsigned long long work,
                      float4& o, float4& dOut, uint32_t& pixelOut) {
-    const uint32_t k = (uint32_t)(work / ra.npix);
-    const uint32_t pixel = (uint32_t)(work - (unsigned long long)k * ra.npix);
+    // k = work / npix without a 64-bit integer division: double quotient (exact to 2^53) and one correction step
+    uint32_t k = (uint32_t)__double2ull_rz(__ull2double_rn(work) * ra.invNpix);
+    long long rem = (long long)(work - (unsigned long long)k * ra.npix);
+    if (rem < 0) { k--; rem += ra.npix; }
+    else if (rem >= (long long)ra.npix) { k++; rem -= ra.npix; }
+    const uint32_t pixel = (uint32_t)rem;
     const uint32_t x = pixel % ra.width, y = pixel / ra.width;
     const uint32_t timestamp = ra.first + k * ra.stride;
     // rayDir(size, fragCoord, fov)
@@ -114,11 +120,96 @@ GSB_D void flushTraceStats(unsigned long long* stats, TraceStats ts, uint32_t tr
     }
 }
 
+// The ray stream of k_extend: work index = path slot.  A slot whose path ended last iteration is first given its
+// raygen epilogue (sample added to the image, raygen.rgen:84-108) and prologue (next pixel-sample, raygen.rgen:31-48).
+struct ExtendSource {
+    const SceneDev& sc;
+    const WavefrontState& wf;
+    const RenderArgs& ra;
+    uint32_t* qc;       // this iteration's counter bank
+    WorkRange range;
+    uint32_t pix = 0;   // pixel of the lane's current path
+    uint32_t traced = 0;
+
+    GSB_D ExtendSource(const SceneDev& s, const WavefrontState& w, const RenderArgs& r, uint32_t* q) : sc(s), wf(w), ra(r), qc(q) {}
+    GSB_D bool drained() const { return range.exhausted; }
+
+    GSB_D bool fetch(bool want, RayJob& job) {
+        const uint32_t slot = range.take(&qc[Q_NEXT_EXTEND], ra.slots, want);
+        // the slot's state words are loaded together (one memory latency, not a dependent chain); `result` is only
+        // needed when the path has ended
+        uint32_t p = kRetired;
+        float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = o, res = o;
+        if (slot != kNoTag) {
+            p = wf.sampleK[slot];
+            o = wf.rayO[slot];
+            d = wf.rayD[slot];
+            res = wf.result[slot];
+        }
+        bool live = p != kRetired;
+        const bool finished = live && (p & kFinished);
+        if (finished) {
+            // raygen.rgen:106-108: a NaN sample leaves the image untouched
+            if (!(isnan(res.x) || isnan(res.y) || isnan(res.z)))
+                atomicAdd(&ra.accum[p & ~kFinished], make_float4(res.x, res.y, res.z, 1.0f));
+        }
+        const uint32_t fmask = __ballot_sync(0xffffffffu, finished);
+        if (fmask) {
+            // next pixel-sample for every finished slot of the warp: one atomic per warp
+            const uint32_t lane = threadIdx.x & 31u;
+            const uint32_t leader = (uint32_t)__ffs(fmask) - 1u;
+            unsigned long long base = 0;
+            if (lane == leader) base = atomicAdd(&wf.stats[ST_NEXTWORK], (unsigned long long)__popc(fmask));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            bool retire = false;
+            if (finished) {
+                const unsigned long long work = base + (unsigned long long)__popc(fmask & ((1u << lane) - 1u));
+                if (work < ra.totalWork) startPath(sc, wf, ra, slot, work, o, d, p);
+                else { wf.sampleK[slot] = kRetired; retire = true; live = false; }
+            }
+            const uint32_t rmask = __ballot_sync(0xffffffffu, retire);
+            if (rmask && lane == (uint32_t)__ffs(rmask) - 1u)
+                atomicAdd(&wf.stats[ST_LIVE], (unsigned long long)(-(long long)__popc(rmask)));
+        }
+        // the state words of the slots this warp will take next: into L1 while the rays just fetched are traced
+        const uint32_t ahead = range.peek(ra.slots);
+        if (ahead != kNoTag) {
+            prefetchL1(wf.sampleK + ahead);
+            prefetchL1(wf.rayO + ahead);
+            prefetchL1(wf.rayD + ahead);
+            prefetchL1(wf.result + ahead);
+        }
+        if (!live) return false;
+        job.ox = o.x; job.oy = o.y; job.oz = o.z;
+        job.dx = d.x; job.dy = d.y; job.dz = d.z;
+        job.tmin = 0.0f; job.tmax = 1e10f;                              // raygen.rgen:54-58
+        job.tag = slot;
+        pix = p;
+        traced++;
+        return true;
+    }
+
+    GSB_D void commit(bool have, const HitRecord& hit, uint32_t slot) {
+        uint32_t key = 0;
+        if (have) {
+            if (hit.inst == GSB_NO_HIT) {
+                key = Q_MISS;                                           // miss.rmiss: done = 1, nothing is added
+                wf.sampleK[slot] = pix | kFinished;
+            } else {
+                wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.prim));
+                wf.hitInst[slot] = hit.inst;
+                key = __ldg(sc.instBsdf + hit.inst) >> 16;
+            }
+        }
+        const uint32_t pos = queueSlot(qc, key, have);
+        if (have && key != Q_MISS) wf.matQueue[(size_t)key * wf.capacity + pos] = slot;
+    }
+};
+
 template <bool STATS>
 __global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState wf, RenderArgs ra, uint32_t parity) {
-    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
-    if (slot == 0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
         // roll the previous iteration's queue sizes into the totals and clear that bank for the next iteration
         uint32_t* prev = wf.qCount + (parity ^ 1u) * Q_COUNT;
         unsigned long long ext = prev[Q_MISS];
@@ -128,56 +219,10 @@ __global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState w
         wf.stats[ST_ITERS] += 1;
         for (int q = 0; q < Q_COUNT; q++) prev[q] = 0;
     }
-    uint32_t pix = kRetired;
-    if (slot < ra.slots) pix = wf.sampleK[slot];
-    float4 o, d;
-    bool live = pix != kRetired;
-    const bool finished = live && (pix & kFinished);
-
-    // ---- the raygen epilogue of paths that ended last iteration, and the prologue of the slot's next path
-    if (finished) {
-        const float4 res = wf.result[slot];
-        // raygen.rgen:106-108: a NaN sample leaves the image untouched
-        if (!(isnan(res.x) || isnan(res.y) || isnan(res.z)))
-            atomicAdd(&ra.accum[pix & ~kFinished], make_float4(res.x, res.y, res.z, 1.0f));
-    }
-    const uint32_t fmask = __ballot_sync(0xffffffffu, finished);
-    if (fmask) {
-        // next pixel-sample for every finished slot of the warp: one atomic per warp
-        const uint32_t lane = threadIdx.x & 31u;
-        const uint32_t leader = (uint32_t)__ffs(fmask) - 1u;
-        unsigned long long base = 0;
-        if (lane == leader) base = atomicAdd(&wf.stats[ST_NEXTWORK], (unsigned long long)__popc(fmask));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        bool retire = false;
-        if (finished) {
-            const unsigned long long work = base + (unsigned long long)__popc(fmask & ((1u << lane) - 1u));
-            if (work < ra.totalWork) startPath(sc, wf, ra, slot, work, o, d, pix);
-            else { wf.sampleK[slot] = kRetired; retire = true; live = false; }
-        }
-        const uint32_t rmask = __ballot_sync(0xffffffffu, retire);
-        if (rmask && lane == (uint32_t)__ffs(rmask) - 1u) atomicAdd(&wf.stats[ST_LIVE], (unsigned long long)(-(long long)__popc(rmask)));
-    }
-    if (live && !finished) { o = wf.rayO[slot]; d = wf.rayD[slot]; }
-
-    // ---- closest hit
-    uint32_t key = 0;
+    ExtendSource src(sc, wf, ra, qc);
     TraceStats ts = {0u, 0u, 0u};
-    if (live) {
-        HitRecord hit;
-        traceRay<false, STATS>(sc, o.x, o.y, o.z, d.x, d.y, d.z, 0.0f, 1e10f, hit, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
-        if (hit.inst == GSB_NO_HIT) {
-            key = Q_MISS;                                           // miss.rmiss: done = 1, nothing is added
-            wf.sampleK[slot] = pix | kFinished;
-        } else {
-            wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.prim));
-            wf.hitInst[slot] = hit.inst;
-            key = __ldg(sc.instBsdf + hit.inst) >> 16;
-        }
-    }
-    const uint32_t pos = queueSlot(qc, key, live);
-    if (live && key != Q_MISS) wf.matQueue[(size_t)key * wf.capacity + pos] = slot;
-    if (STATS) flushTraceStats(wf.stats, ts, live ? 1u : 0u);
+    traceStream<false, STATS>(sc, src, ra.refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+    if (STATS) flushTraceStats(wf.stats, ts, src.traced);
 }
 
 // ---- shade ----------------------------------------------------------------------------------------
@@ -336,18 +381,40 @@ __global__ void __launch_bounds__(kBlock) k_shade(SceneDev sc, WavefrontState wf
 }
 
 // ---- shadow ---------------------------------------------------------------------------------------
-template <bool STATS>
-__global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState wf, uint32_t parity) {
-    const uint32_t count = wf.qCount[parity * Q_COUNT + Q_SHADOW];
-    TraceStats ts = {0u, 0u, 0u};
+// The ray stream of k_shadow: work index = entry of the shadow queue written by k_shade.
+struct ShadowSource {
+    const SceneDev& sc;
+    const WavefrontState& wf;
+    uint32_t* qc;
+    uint32_t count;
+    WorkRange range;
+    uint32_t slot = 0;
     uint32_t traced = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+
+    GSB_D ShadowSource(const SceneDev& s, const WavefrontState& w, uint32_t* q) : sc(s), wf(w), qc(q), count(q[Q_SHADOW]) {}
+    GSB_D bool drained() const { return range.exhausted; }
+
+    GSB_D bool fetch(bool want, RayJob& job) {
+        const uint32_t i = range.take(&qc[Q_NEXT_SHADOW], count, want);
+        const uint32_t ahead = range.peek(count);
+        if (ahead != kNoTag) {
+            prefetchL1(wf.shadowO + ahead);
+            prefetchL1(wf.shadowD + ahead);
+        }
+        if (i == kNoTag) return false;
         const float4 o = wf.shadowO[i], d = wf.shadowD[i];
-        HitRecord hit;
-        traceRay<true, STATS>(sc, o.x, o.y, o.z, d.x, d.y, d.z, 0.01f, o.w, hit, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+        job.ox = o.x; job.oy = o.y; job.oz = o.z;
+        job.dx = d.x; job.dy = d.y; job.dz = d.z;
+        job.tmin = 0.01f; job.tmax = o.w;                                            // rayhit.rchit:737-748
+        job.tag = i;
+        slot = __float_as_uint(d.w);
         traced++;
+        return true;
+    }
+
+    GSB_D void commit(bool have, const HitRecord& hit, uint32_t i) {
+        if (!have) return;
         const bool visible = hit.inst == GSB_NO_HIT;
-        const uint32_t slot = __float_as_uint(d.w);
         const float4 base = wf.shadowBase[i];
         float3 emitted = f3(0.0f);
         if (visible) {
@@ -363,7 +430,22 @@ __global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState w
             wf.result[slot] = res;
         }
     }
-    if (STATS) flushTraceStats(wf.stats, ts, traced);
+};
+
+template <bool STATS>
+__global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t refillMin) {
+    ShadowSource src(sc, wf, wf.qCount + parity * Q_COUNT);
+    TraceStats ts = {0u, 0u, 0u};
+    traceStream<true, STATS>(sc, src, refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+    if (STATS) flushTraceStats(wf.stats, ts, src.traced);
+}
+
+// one thread, end of the body of the device-side render loop: keep looping while slots are live (and, as a safety net
+// against a hung device, while the iteration bound of the call is not reached)
+__global__ void k_loopCondition(cudaGraphConditionalHandle handle, WavefrontState wf, unsigned long long maxIters) {
+    const bool more = wf.stats[ST_LIVE] != 0ull && wf.stats[ST_LOOPITERS] + 2ull <= maxIters;
+    wf.stats[ST_LOOPITERS] += 2ull;
+    cudaGraphSetConditional(handle, more ? 1u : 0u);
 }
 
 // one thread, once per render call: roll the last iteration's queue sizes into the totals
@@ -418,9 +500,35 @@ void freeWavefront(gsb_context* ctx) {
     wf = WavefrontState();
 }
 
+void finishPending(gsb_context* ctx) {
+    if (ctx->pending.empty()) return;
+    cudaStream_t s = ctx->stream;
+    unsigned long long iters = 0;
+    GSB_CUDA(cudaMemcpyAsync(&iters, &ctx->wf.stats[ST_ITERS], sizeof(iters), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA(cudaStreamSynchronize(s));
+    GSB_CUDA(cudaGetLastError());
+    const PendingRender& last = ctx->pending.back();
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, last.start, last.stop);
+    ctx->lastRenderMs[0] = ms;
+    for (int k = 1; k < 5; k++) ctx->lastRenderMs[k] = 0.0;
+    const unsigned long long ran = iters - ctx->seenIters;   // wavefront iterations of all pending calls together
+    ctx->launches += ran * last.launchesPerIter + ran / 2;    // stage kernels + one loop condition per two iterations
+    ctx->lastRenderIters = ctx->pending.size() == 1 ? ran : ran / ctx->pending.size();
+    ctx->seenIters = iters;
+    for (PendingRender& pr : ctx->pending) {
+        cudaGraphExecDestroy(pr.exec);
+        cudaGraphDestroy(pr.graph);
+        cudaEventDestroy(pr.start);
+        cudaEventDestroy(pr.stop);
+    }
+    ctx->pending.clear();
+}
+
 void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t first, uint32_t count, uint32_t stride) {
     cudaStream_t s = ctx->stream;
     const uint32_t npix = width * height;
+    if (ctx->profiling || !ctx->useGraphLoop || ctx->pending.size() >= 64) finishPending(ctx);
     if (ctx->width != width || ctx->height != height || !ctx->dAccum) {
         ensure(ctx->dAccum, (size_t)npix);
         GSB_CUDA(cudaMemsetAsync(ctx->dAccum, 0, (size_t)npix * sizeof(float4), s));
@@ -439,6 +547,8 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     ra.slots = slots;
     ra.totalWork = totalWork;
     ra.accum = ctx->dAccum;
+    ra.invNpix = 1.0 / (double)npix;
+    ra.refillMin = ctx->refillMin;
     ra.camZ = (std::fmax((float)width, (float)height) / 2.0f) / std::tan(ctx->fov / 2.0f);
     const SceneDev sc = ctx->sceneDev();
     GSB_CUDA(cudaMemsetAsync(wf.qCount, 0, 2 * Q_COUNT * sizeof(uint32_t), s));
@@ -456,6 +566,14 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     int dev = ctx->device, sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int queueGrid = std::min(fullGrid, sms * 16);
+    // persistent traversal kernels: exactly as many blocks as the machine holds at once
+    auto residentGrid = [&](const void* kernel) {
+        int perSm = 1;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, kBlock, 0);
+        return std::max(1, std::min(fullGrid, sms * std::max(perSm, 1)));
+    };
+    const int extendGrid = residentGrid((ctx->instrumented & 1) ? (const void*)k_extend<true> : (const void*)k_extend<false>);
+    const int shadowGrid = residentGrid((ctx->instrumented & 2) ? (const void*)k_shadow<true> : (const void*)k_shadow<false>);
     k_generate<<<fullGrid, kBlock, 0, s>>>(sc, wf, ra);
     ctx->launches += 1;
     ctx->lastRenderIters = 0;
@@ -476,8 +594,8 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     uint32_t parity = 0;
     auto iteration = [&]() {
         mark();
-        if (ctx->instrumented & 1) k_extend<true><<<fullGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
-        else k_extend<false><<<fullGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
+        if (ctx->instrumented & 1) k_extend<true><<<extendGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
+        else k_extend<false><<<extendGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
         mark();
         if (ctx->typeUsed[0]) launchShade<0>(ctx, sc, queueGrid, parity);
         if (ctx->typeUsed[1]) launchShade<1>(ctx, sc, queueGrid, parity);
@@ -488,8 +606,8 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         if (ctx->typeUsed[6]) launchShade<6>(ctx, sc, queueGrid, parity);
         if (ctx->typeUsed[7]) launchShade<7>(ctx, sc, queueGrid, parity);
         mark();
-        if (ctx->instrumented & 2) k_shadow<true><<<queueGrid, kBlock, 0, s>>>(sc, wf, parity);
-        else k_shadow<false><<<queueGrid, kBlock, 0, s>>>(sc, wf, parity);
+        if (ctx->instrumented & 2) k_shadow<true><<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ra.refillMin);
+        else k_shadow<false><<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ra.refillMin);
         mark();
         mark();
         parity ^= 1u;
@@ -497,8 +615,64 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         ctx->lastRenderIters++;
     };
 
-    // Host loop: batches of iterations; the live-slot count of batch b is read back while batch
-    // b+1 is already queued, so the device never waits for the host.
+    // An upper bound on the iterations of this call: every iteration advances every live slot's path by one bounce.
+    const unsigned long long pathsPerSlot = (totalWork + slots - 1) / slots;
+    const unsigned long long maxIters = (pathsPerSlot + 1ull) * (unsigned long long)(ctx->params.max_depth + 4) + 16ull;
+
+    bool looped = false;
+    if (!prof && ctx->useGraphLoop) {
+        // Device-side loop: ONE graph launch per render call.  A WHILE conditional node whose body is two wavefront
+        // iterations (one per counter bank) plus the loop condition; the host is not involved until the frame is done,
+        // so there are no launch gaps and no sensitivity to host scheduling.
+        cudaGraph_t graph = nullptr;
+        cudaGraphExec_t exec = nullptr;
+        do {
+            if (cudaGraphCreate(&graph, 0) != cudaSuccess) break;
+            cudaGraphConditionalHandle handle;
+            if (cudaGraphConditionalHandleCreate(&handle, graph, 1, cudaGraphCondAssignDefault) != cudaSuccess) break;
+            cudaGraphNodeParams np = {};
+            np.type = cudaGraphNodeTypeConditional;
+            np.conditional.handle = handle;
+            np.conditional.type = cudaGraphCondTypeWhile;
+            np.conditional.size = 1;
+            cudaGraphNode_t node;
+            if (cudaGraphAddNode(&node, graph, nullptr, 0, &np) != cudaSuccess) break;
+            cudaGraph_t body = np.conditional.phGraph_out[0];
+            if (cudaStreamBeginCaptureToGraph(s, body, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed) != cudaSuccess) break;
+            iteration();
+            iteration();
+            k_loopCondition<<<1, 1, 0, s>>>(handle, wf, maxIters);
+            cudaGraph_t captured = nullptr;
+            if (cudaStreamEndCapture(s, &captured) != cudaSuccess) break;
+            if (cudaGraphInstantiate(&exec, graph, 0) != cudaSuccess) break;
+            GSB_CUDA(cudaMemsetAsync(&wf.stats[ST_LOOPITERS], 0, sizeof(unsigned long long), s));
+            if (cudaGraphLaunch(exec, s) != cudaSuccess) break;
+            looped = true;
+        } while (false);
+        if (!looped) {
+            cudaGetLastError();  // clear; fall back to the host-driven loop below
+            ctx->useGraphLoop = false;
+            parity = 0;
+        }
+        if (looped) {
+            // asynchronous from here on: the graph, its executable and the timing events are released by
+            // finishPending() once the stream has drained (gsb_synchronize, read-back, counters, ...)
+            k_foldCounters<<<1, 1, 0, s>>>(wf, 1u, totalWork);   // an even number of iterations ran: the last bank is 1
+            GSB_CUDA(cudaEventRecord(evStop, s));
+            PendingRender pr;
+            pr.exec = exec; pr.graph = graph; pr.start = evStart; pr.stop = evStop;
+            pr.launchesPerIter = 2u + (uint32_t)typesUsed;
+            ctx->pending.push_back(pr);
+            ctx->launches -= 2ull * (2 + (uint64_t)typesUsed);   // iteration() ran twice on the host during capture
+            ctx->launches += 1;
+            return;
+        }
+        if (exec) cudaGraphExecDestroy(exec);
+        if (graph) cudaGraphDestroy(graph);
+    }
+
+    // Host loop (profiling mode, or no conditional graph nodes): batches of iterations; the live-slot count of
+    // batch b is read back while batch b+1 is already queued, so the device rarely waits for the host.
     const int batch = 8;
     unsigned long long* hLive = nullptr;
     GSB_CUDA(cudaMallocHost(&hLive, 2 * sizeof(unsigned long long)));
@@ -516,7 +690,7 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
             if (hLive[(b - 1) & 1] == 0) finished = true;
         }
         b++;
-        if (prof && pev.size() > 200000) break;
+        if ((unsigned long long)b * batch > maxIters + 2 * batch) break;
     }
     k_foldCounters<<<1, 1, 0, s>>>(wf, parity ^ 1u, totalWork);
     ctx->launches += 1;
@@ -525,6 +699,7 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     GSB_CUDA(cudaGetLastError());
     float ms = 0.0f;
     GSB_CUDA(cudaEventElapsedTime(&ms, evStart, evStop));
+    ctx->seenIters += ctx->lastRenderIters;
     ctx->lastRenderMs[0] = ms;
     for (int k = 1; k < 5; k++) ctx->lastRenderMs[k] = 0.0;
     if (prof) {

@@ -161,7 +161,9 @@ GSB_API gsb_status gsb_get_bvh_stats(gsb_context* ctx, gsb_bvh_stats* out);
 /* ---- render (replaces traceRays(pipeline, w, h), one launch = one sample/pixel) --- */
 /* Renders samples with timestamp = first_sample + k*sample_stride, k in [0, num_samples),
  * for every pixel of a width x height frame and adds them to the context's accumulation
- * buffer (allocated/cleared when the size changes).  Asynchronous on the context's stream. */
+ * buffer (allocated/cleared when the size changes).  Asynchronous on the context's stream: the whole call is one
+ * device-side loop (a conditional CUDA graph); gsb_synchronize, the read-back and counter calls wait for it, and
+ * an error raised inside the loop (traversal stack overflow) is reported by the first of those calls. */
 GSB_API gsb_status gsb_render(gsb_context* ctx, uint32_t width, uint32_t height,
                               uint32_t first_sample, uint32_t num_samples, uint32_t sample_stride);
 GSB_API gsb_status gsb_clear(gsb_context* ctx);       /* zero accumulation + counters */
