@@ -6,7 +6,7 @@
 
 Workload (BASELINE.json configs[1]): Cornell box (Mitsuba scene rebuilt procedurally by the host layer, 36
 triangles / 8 instances / 2 triangle lights), 1920x1080, NEE + MIS, max depth 8.  One step = `--spp-per-step`
-(default 32) samples for every pixel on every GPU (32 steps = the 1024 spp of the config on one GPU).  With N GPUs
+(default 128) samples for every pixel on every GPU (8 steps = the 1024 spp of the config on one GPU).  With N GPUs
 the samples are sharded by index (GPU g renders timestamps base + g, base + g + N, ...): per-GPU work is fixed
 (weak scaling) and every step ends with one NCCL reduce of the float4 sum buffers to rank 0.
 
@@ -40,7 +40,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
-    ap.add_argument("--spp-per-step", type=int, default=32)
+    ap.add_argument("--spp-per-step", type=int, default=128)
     ap.add_argument("--max-depth", type=int, default=8)
     ap.add_argument("--scene", default="cornell")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -371,7 +371,7 @@ def run_ours(a, rank, world, local_rank):
                 "rays_per_path": {"extension": ext / paths, "shadow": sh / paths},
                 "config": {"workload": workload_name(a, world), "width": W, "height": H, "spp_per_step": S, "max_depth": a.max_depth,
                            "scene": a.scene, "parallelism": f"sample-index sharding x{world}" + (", 1 NCCL reduce per step" if world > 1 else ""),
-                           "l2": "path state streams of a step (2.07 M slots x ~230 B = 480 MB) exceed the 126 MB L2; scene data is meant to be cache resident"},
+                           "l2": "path state streams of a step (up to 4.2 M slots x ~230 B) exceed the 126 MB L2; scene data is meant to be cache resident"},
                 "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(launches),
                 "stage_ms_per_step": {k: v / prof_steps for k, v in stage.items()},
                 "device_ms_per_step": device_ms / a.steps}

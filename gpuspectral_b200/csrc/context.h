@@ -18,8 +18,8 @@ struct MeshRec {
 };
 
 // Counter indices inside WavefrontState::qCount (two banks of Q_COUNT, selected by iteration parity):
-// one queue per BSDF type, the number of extension rays that missed, the shadow-ray queue.
-enum { Q_MATERIAL0 = 0, Q_MISS = GSB_BSDF_TYPE_COUNT, Q_SHADOW = GSB_BSDF_TYPE_COUNT + 1,
+// [0..7] unused (material sorting happens inside k_shade), extension rays traced, the shadow-ray queue.
+enum { Q_MATERIAL0 = 0, Q_TRACED = GSB_BSDF_TYPE_COUNT, Q_SHADOW = GSB_BSDF_TYPE_COUNT + 1,
        Q_NEXT_EXTEND = 10, Q_NEXT_SHADOW = 11,  // work counters of the persistent traversal kernels
        Q_COUNT = 12 };
 
@@ -36,7 +36,6 @@ struct WavefrontState {
                                   // 0xffffffff = slot retired (no work left)
     float4* hitTUVP = nullptr;    // t, u, v, primitive id bits
     uint32_t* hitInst = nullptr;
-    uint32_t* matQueue = nullptr;   // GSB_BSDF_TYPE_COUNT queues of `capacity` slot ids each
     float4* shadowO = nullptr;      // origin.xyz, tmax
     float4* shadowD = nullptr;      // direction.xyz, slot id bits
     float4* shadowBase = nullptr;   // emitted without NEE .xyz, directWeight if visible
@@ -82,7 +81,7 @@ struct gsb_context {
     float4* dAccum = nullptr;  // rgb = sum of samples, a = samples added
     gsb::WavefrontState wf;
     bool profiling = false;
-    uint32_t targetSlots = 1u << 20;  // paths in flight per wavefront (GSB_SLOTS overrides)
+    uint32_t targetSlots = 1u << 22;  // paths in flight per wavefront (GSB_SLOTS overrides)
     uint32_t refillMin = 24;     // idle lanes that trigger a refill in the persistent traversal kernels (GSB_REFILL overrides)
     bool useGraphLoop = true;    // device-side render loop (conditional CUDA graph); GSB_GRAPH=0 or a failed build disables it
     int instrumented = 0;        // bit 0: count fetches of extension rays, bit 1: of shadow rays

@@ -99,7 +99,7 @@ __global__ void k_generate(SceneDev sc, WavefrontState wf, RenderArgs ra) {
     float4 o, d;
     uint32_t pixel;
     if (slot < ra.totalWork) startPath(sc, wf, ra, slot, slot, o, d, pixel);
-    else wf.sampleK[slot] = kRetired;
+    else { wf.sampleK[slot] = kRetired; wf.hitInst[slot] = GSB_NO_HIT; }
 }
 
 // ---- extend ---------------------------------------------------------------------------------------
@@ -165,7 +165,7 @@ struct ExtendSource {
             if (finished) {
                 const unsigned long long work = base + (unsigned long long)__popc(fmask & ((1u << lane) - 1u));
                 if (work < ra.totalWork) startPath(sc, wf, ra, slot, work, o, d, p);
-                else { wf.sampleK[slot] = kRetired; retire = true; live = false; }
+                else { wf.sampleK[slot] = kRetired; wf.hitInst[slot] = GSB_NO_HIT; retire = true; live = false; }
             }
             const uint32_t rmask = __ballot_sync(0xffffffffu, retire);
             if (rmask && lane == (uint32_t)__ffs(rmask) - 1u)
@@ -189,20 +189,12 @@ struct ExtendSource {
         return true;
     }
 
+    // stores only: k_shade finds its work by scanning hitInst in slot order
     GSB_D void commit(bool have, const HitRecord& hit, uint32_t slot) {
-        uint32_t key = 0;
-        if (have) {
-            if (hit.inst == GSB_NO_HIT) {
-                key = Q_MISS;                                           // miss.rmiss: done = 1, nothing is added
-                wf.sampleK[slot] = pix | kFinished;
-            } else {
-                wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.prim));
-                wf.hitInst[slot] = hit.inst;
-                key = __ldg(sc.instBsdf + hit.inst) >> 16;
-            }
-        }
-        const uint32_t pos = queueSlot(qc, key, have);
-        if (have && key != Q_MISS) wf.matQueue[(size_t)key * wf.capacity + pos] = slot;
+        if (!have) return;
+        wf.hitInst[slot] = hit.inst;
+        if (hit.inst == GSB_NO_HIT) wf.sampleK[slot] = pix | kFinished;   // miss.rmiss: done = 1, nothing is added
+        else wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.prim));
     }
 };
 
@@ -212,7 +204,7 @@ __global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState w
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         // roll the previous iteration's queue sizes into the totals and clear that bank for the next iteration
         uint32_t* prev = wf.qCount + (parity ^ 1u) * Q_COUNT;
-        unsigned long long ext = prev[Q_MISS];
+        unsigned long long ext = prev[Q_TRACED];
         for (int q = 0; q < GSB_BSDF_TYPE_COUNT; q++) ext += prev[q];
         wf.stats[ST_EXT] += ext;
         wf.stats[ST_SHADOW] += prev[Q_SHADOW];
@@ -222,24 +214,60 @@ __global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState w
     ExtendSource src(sc, wf, ra, qc);
     TraceStats ts = {0u, 0u, 0u};
     traceStream<false, STATS>(sc, src, ra.refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+    // extension rays traced by this warp -> this iteration's counter bank
+    uint32_t traced = src.traced;
+    for (int o = 16; o > 0; o >>= 1) traced += __shfl_xor_sync(0xffffffffu, traced, o);
+    if ((threadIdx.x & 31u) == 0u && traced) atomicAdd(&qc[Q_TRACED], traced);
     if (STATS) flushTraceStats(wf.stats, ts, src.traced);
 }
 
 // ---- shade ----------------------------------------------------------------------------------------
+// Material sorting without a global queue: every warp scans the slots 32 at a time in slot order and keeps those whose
+// hit carries a BSDF of this kernel's TYPE.  A tile that matches completely (always, in a single-material scene) is
+// shaded as it is — the path-state streams are then read and written fully coalesced; partial tiles are compacted
+// through a 64-entry per-warp buffer in shared memory and shaded 32 at a time.
 template <int TYPE>
-__global__ void __launch_bounds__(kBlock) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity) {
+__global__ void __launch_bounds__(kBlock) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t slots) {
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
-    const uint32_t count = qc[TYPE];
-    const uint32_t* queue = wf.matQueue + (size_t)TYPE * wf.capacity;
-    const uint32_t rounds = (count + gridDim.x * blockDim.x - 1) / (gridDim.x * blockDim.x);
-    for (uint32_t r = 0; r < rounds; r++) {
-        const uint32_t i = (r * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
-        const bool active = i < count;
-        bool terminate = false, needShadow = false;
+    __shared__ uint32_t s_buf[kBlock / 32][64];
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t* buf = s_buf[threadIdx.x >> 5];
+    const uint32_t warpsTotal = gridDim.x * (kBlock / 32), warpId = blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5);
+    const uint32_t tiles = (slots + 31u) / 32u;
+    uint32_t pendingCount = 0;
+    for (uint32_t tile = warpId;; tile += warpsTotal) {
+        const bool scanning = tile < tiles;
+        const uint32_t cand = tile * 32u + lane;
+        bool match = false;
+        if (scanning && cand < slots) {
+            const uint32_t hi = wf.hitInst[cand];
+            match = hi != GSB_NO_HIT && (__ldg(sc.instBsdf + hi) >> 16) == (uint32_t)TYPE;
+        }
+        const uint32_t mm = __ballot_sync(0xffffffffu, match);
+        bool active;
         uint32_t slot = 0;
+        if (mm == 0xffffffffu && pendingCount == 0u) {
+            active = true;
+            slot = cand;
+        } else {
+            if (match) buf[pendingCount + (uint32_t)__popc(mm & ((1u << lane) - 1u))] = cand;
+            pendingCount += (uint32_t)__popc(mm);
+            __syncwarp();
+            if (pendingCount >= 32u || (!scanning && pendingCount > 0u)) {
+                const uint32_t n = pendingCount < 32u ? pendingCount : 32u;
+                active = lane < n;
+                if (active) slot = buf[pendingCount - n + lane];
+                pendingCount -= n;
+                __syncwarp();
+            } else if (!scanning) {
+                break;
+            } else {
+                continue;
+            }
+        }
+        bool terminate = false, needShadow = false;
         float4 shO, shD, shBase, shNee;
         if (active) {
-            slot = queue[i];
             const float4 ro = wf.rayO[slot], rd = wf.rayD[slot];
             const float4 hit = wf.hitTUVP[slot];
             const uint32_t inst = wf.hitInst[slot];
@@ -377,6 +405,7 @@ __global__ void __launch_bounds__(kBlock) k_shade(SceneDev sc, WavefrontState wf
             wf.shadowBase[sp] = shBase;
             wf.shadowNee[sp] = shNee;
         }
+        if (!scanning && pendingCount == 0u) break;
     }
 }
 
@@ -451,7 +480,7 @@ __global__ void k_loopCondition(cudaGraphConditionalHandle handle, WavefrontStat
 // one thread, once per render call: roll the last iteration's queue sizes into the totals
 __global__ void k_foldCounters(WavefrontState wf, uint32_t parity, unsigned long long paths) {
     uint32_t* bank = wf.qCount + parity * Q_COUNT;
-    unsigned long long ext = bank[Q_MISS];
+    unsigned long long ext = bank[Q_TRACED];
     for (int q = 0; q < GSB_BSDF_TYPE_COUNT; q++) ext += bank[q];
     wf.stats[ST_EXT] += ext;
     wf.stats[ST_SHADOW] += bank[Q_SHADOW];
@@ -474,7 +503,7 @@ void allocWavefront(gsb_context* ctx, uint32_t slots) {
     const size_t n = slots;
     ensure(wf.rayO, n); ensure(wf.rayD, n); ensure(wf.weightDW, n); ensure(wf.result, n);
     ensure(wf.seed, n); ensure(wf.sampleK, n); ensure(wf.hitTUVP, n); ensure(wf.hitInst, n);
-    ensure(wf.matQueue, n * GSB_BSDF_TYPE_COUNT);
+
     ensure(wf.shadowO, n); ensure(wf.shadowD, n); ensure(wf.shadowBase, n); ensure(wf.shadowNee, n);
     if (!wf.qCount) ensure(wf.qCount, (size_t)2 * Q_COUNT);
     if (!wf.stats) {
@@ -485,15 +514,15 @@ void allocWavefront(gsb_context* ctx, uint32_t slots) {
 }
 
 template <int TYPE>
-void launchShade(gsb_context* ctx, const SceneDev& sc, int grid, uint32_t parity) {
-    k_shade<TYPE><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity);
+void launchShade(gsb_context* ctx, const SceneDev& sc, int grid, uint32_t parity, uint32_t slots) {
+    k_shade<TYPE><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots);
 }
 
 }  // namespace
 
 void freeWavefront(gsb_context* ctx) {
     WavefrontState& wf = ctx->wf;
-    void* ptrs[] = {wf.rayO, wf.rayD, wf.weightDW, wf.result, wf.seed, wf.sampleK, wf.hitTUVP, wf.hitInst, wf.matQueue,
+    void* ptrs[] = {wf.rayO, wf.rayD, wf.weightDW, wf.result, wf.seed, wf.sampleK, wf.hitTUVP, wf.hitInst,
                     wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.qCount, wf.stats};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -597,14 +626,14 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         if (ctx->instrumented & 1) k_extend<true><<<extendGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
         else k_extend<false><<<extendGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
         mark();
-        if (ctx->typeUsed[0]) launchShade<0>(ctx, sc, queueGrid, parity);
-        if (ctx->typeUsed[1]) launchShade<1>(ctx, sc, queueGrid, parity);
-        if (ctx->typeUsed[2]) launchShade<2>(ctx, sc, queueGrid, parity);
-        if (ctx->typeUsed[3]) launchShade<3>(ctx, sc, queueGrid, parity);
-        if (ctx->typeUsed[4]) launchShade<4>(ctx, sc, queueGrid, parity);
-        if (ctx->typeUsed[5]) launchShade<5>(ctx, sc, queueGrid, parity);
-        if (ctx->typeUsed[6]) launchShade<6>(ctx, sc, queueGrid, parity);
-        if (ctx->typeUsed[7]) launchShade<7>(ctx, sc, queueGrid, parity);
+        if (ctx->typeUsed[0]) launchShade<0>(ctx, sc, queueGrid, parity, slots);
+        if (ctx->typeUsed[1]) launchShade<1>(ctx, sc, queueGrid, parity, slots);
+        if (ctx->typeUsed[2]) launchShade<2>(ctx, sc, queueGrid, parity, slots);
+        if (ctx->typeUsed[3]) launchShade<3>(ctx, sc, queueGrid, parity, slots);
+        if (ctx->typeUsed[4]) launchShade<4>(ctx, sc, queueGrid, parity, slots);
+        if (ctx->typeUsed[5]) launchShade<5>(ctx, sc, queueGrid, parity, slots);
+        if (ctx->typeUsed[6]) launchShade<6>(ctx, sc, queueGrid, parity, slots);
+        if (ctx->typeUsed[7]) launchShade<7>(ctx, sc, queueGrid, parity, slots);
         mark();
         if (ctx->instrumented & 2) k_shadow<true><<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ra.refillMin);
         else k_shadow<false><<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ra.refillMin);

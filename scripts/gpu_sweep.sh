@@ -1,9 +1,9 @@
 #!/bin/bash
 # parity tests + sweep of one environment knob:  VAR=GSB_REFILL VALUES="1 4 8" bash scripts/gpu_sweep.sh
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+[ -n "$NOTEST" ] || timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
 for v in $VALUES; do
-  env $VAR=$v timeout 300 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-e2e 2>&1 | python -c "
+  env $VAR=$v timeout 300 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-e2e $EXTRA 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):
