@@ -32,6 +32,9 @@ namespace gsb {
 namespace {
 
 constexpr int kBlock = kTraceBlock;
+#ifndef GSB_SHADE_MIN_BLOCKS
+#define GSB_SHADE_MIN_BLOCKS 6   // resident blocks per SM the shading kernels are compiled for (register cap 80)
+#endif
 constexpr uint32_t kRetired = 0xffffffffu;
 constexpr uint32_t kFinished = 0x80000000u;  // sampleK bit: the path has ended, its sample waits to be added to the image
 constexpr uint32_t kFlagWasDelta = 1u << 16;
@@ -227,7 +230,7 @@ __global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState w
 // shaded as it is — the path-state streams are then read and written fully coalesced; partial tiles are compacted
 // through a 64-entry per-warp buffer in shared memory and shaded 32 at a time.
 template <int TYPE>
-__global__ void __launch_bounds__(kBlock) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t slots) {
+__global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t slots) {
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
     __shared__ uint32_t s_buf[kBlock / 32][64];
     const uint32_t lane = threadIdx.x & 31u;
