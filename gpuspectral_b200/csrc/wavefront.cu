@@ -32,8 +32,11 @@ namespace gsb {
 namespace {
 
 constexpr int kBlock = kTraceBlock;
+#ifndef GSB_TRACE_MIN_BLOCKS
+#define GSB_TRACE_MIN_BLOCKS 8   // resident blocks per SM the traversal kernels are compiled for
+#endif
 #ifndef GSB_SHADE_MIN_BLOCKS
-#define GSB_SHADE_MIN_BLOCKS 6   // resident blocks per SM the shading kernels are compiled for (register cap 80)
+#define GSB_SHADE_MIN_BLOCKS 8   // resident blocks per SM the shading kernels are compiled for (register cap 80)
 #endif
 constexpr uint32_t kRetired = 0xffffffffu;
 constexpr uint32_t kFinished = 0x80000000u;  // sampleK bit: the path has ended, its sample waits to be added to the image
@@ -202,7 +205,7 @@ struct ExtendSource {
 };
 
 template <bool STATS>
-__global__ void __launch_bounds__(kBlock) k_extend(SceneDev sc, WavefrontState wf, RenderArgs ra, uint32_t parity) {
+__global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_extend(SceneDev sc, WavefrontState wf, RenderArgs ra, uint32_t parity) {
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         // roll the previous iteration's queue sizes into the totals and clear that bank for the next iteration
@@ -465,7 +468,7 @@ struct ShadowSource {
 };
 
 template <bool STATS>
-__global__ void __launch_bounds__(kBlock) k_shadow(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t refillMin) {
+__global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_shadow(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t refillMin) {
     ShadowSource src(sc, wf, wf.qCount + parity * Q_COUNT);
     TraceStats ts = {0u, 0u, 0u};
     traceStream<true, STATS>(sc, src, refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
