@@ -42,7 +42,8 @@ def parse():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--spp-per-step", type=int, default=128)
     ap.add_argument("--max-depth", type=int, default=8)
-    ap.add_argument("--scene", default="cornell")
+    ap.add_argument("--scene", default="cornell", help="cornell (configs[1]) | gallery (configs[2]) | field (configs[3])")
+    ap.add_argument("--scene-params", default="", help="comma-separated integers for the built-in scene (field: seed,meshes,subdiv,grid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-instrumented", action="store_true", help="skip the untimed fetch-count pass (profiler runs)")
@@ -51,7 +52,7 @@ def parse():
 
 
 def workload_name(a, n):
-    return (f"{a.scene} box {a.width}x{a.height}, NEE+MIS, max_depth {a.max_depth}, {a.spp_per_step} spp per step per GPU"
+    return (f"{a.scene}{' box' if a.scene == 'cornell' else ' scene'} {a.width}x{a.height}, NEE+MIS, max_depth {a.max_depth}, {a.spp_per_step} spp per step per GPU"
             f" (sample-index sharding over {n} GPU{'s' if n > 1 else ''})")
 
 
@@ -112,7 +113,7 @@ def run_reference(a, rank, world):
     import gpuspectral_b200 as g          # host layer only (scene arrays); no product compute on this arm
     from oracle import oracle as orc
     orc.build()
-    scene = g.Scene.builtin(a.scene)
+    scene = g.Scene.builtin(a.scene, *scene_params(a))
     o = orc.OracleScene.from_host_scene(scene)
     o.set_params(max_depth=a.max_depth)
     spp = 1
@@ -143,6 +144,10 @@ class CudaBuffer:
 
     def __init__(self, ptr, nfloats):
         self.__cuda_array_interface__ = {"shape": (nfloats,), "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
+
+
+def scene_params(a):
+    return [int(x) for x in a.scene_params.split(",") if x.strip()]
 
 
 def scene_h2d_bytes(scene):
@@ -184,13 +189,14 @@ def run_ours(a, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=dev)
     W, H, S = a.width, a.height, a.spp_per_step
     npix = W * H
-    scene = g.Scene.builtin(a.scene)
+    scene = g.Scene.builtin(a.scene, *scene_params(a))
     ctx = g.Context(local_rank)
     stream = torch.cuda.Stream(device=dev)     # one stream for the render, the NCCL reduce and the timing events
     torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
     ctx.upload(scene)
     ctx.set_params(max_depth=a.max_depth)
+    bvh = ctx.bvh_stats()       # device time of the BLAS + TLAS builds, node / triangle counts, SAH before / after refinement
     ctx.render(W, H, 0, 0)      # allocate the frame
     ctx.clear()
     ptr, nbytes = ctx.device_sum_ptr()
@@ -374,7 +380,7 @@ def run_ours(a, rank, world, local_rank):
                            "l2": "path state streams of a step (up to 4.2 M slots x ~230 B) exceed the 126 MB L2; scene data is meant to be cache resident"},
                 "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(launches),
                 "stage_ms_per_step": {k: v / prof_steps for k, v in stage.items()},
-                "device_ms_per_step": device_ms / a.steps}
+                "device_ms_per_step": device_ms / a.steps, "bvh": bvh}
         print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:

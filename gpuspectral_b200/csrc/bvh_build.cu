@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "bvh.h"
@@ -482,8 +483,12 @@ GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi,
     GSB_CUDA(cudaMemsetAsync(dCost, 0, 2 * sizeof(double), s));
     const int costBlocks = (int)std::min<uint32_t>((n + B - 1) / B, 1024u);
     k_sahCost<<<costBlocks, B, 0, s>>>(t, plo, phi, (int)n, dCost);
-    if (g_treelets && n >= 16) {
-        refineTreelets(pool.s, t, plo, phi, sorted, (int)n, [&](size_t bytes) { return (void*)pool.get<uint8_t>(bytes); });
+    int passes = g_treelets ? 2 : 0;
+    if (const char* e = getenv("GSB_TREELET_PASSES")) passes = atoi(e);
+    const bool refine = passes > 0 && n >= 16;
+    if (refine) {
+        refineTreelets(pool.s, t, plo, phi, sorted, (int)n, passes, [&](size_t bytes) { return (void*)pool.get<uint8_t>(bytes); });
+        ca.sorted = sorted;  // the refinement re-derives the leaf order
         k_sahCost<<<costBlocks, B, 0, s>>>(t, plo, phi, (int)n, dCost + 1);
     }
 
@@ -510,7 +515,7 @@ GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi,
     GSB_CUDA(cudaMemcpyAsync(hostCost, dCost, sizeof(hostCost), cudaMemcpyDeviceToHost, s));
     GSB_CUDA(cudaStreamSynchronize(s));
     out.sahBefore = hostCost[0];
-    out.sahAfter = (g_treelets && n >= 16) ? hostCost[1] : hostCost[0];
+    out.sahAfter = refine ? hostCost[1] : hostCost[0];
     return r;
 }
 
