@@ -307,7 +307,15 @@ gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx) {
         if (const char* e = getenv("GSB_GRAPH")) ctx->useGraphLoop = atoi(e) != 0;
         if (const char* e = getenv("GSB_REFILL")) {
             const long v = atol(e);
-            if (v >= 1 && v <= 32) ctx->refillMin = (uint32_t)v;
+            if (v >= 1 && v <= 32) ctx->refillMin = (ctx->refillMin & ~0xffu) | (uint32_t)v;
+        }
+        if (const char* e = getenv("GSB_VOTE")) {
+            const long v = atol(e);
+            if (v >= 0 && v <= 32) ctx->refillMin = (ctx->refillMin & ~0xff00u) | ((uint32_t)v << 8);
+        }
+        if (const char* e = getenv("GSB_TRIMIN")) {
+            const long v = atol(e);
+            if (v >= 0 && v <= 32) ctx->refillMin = (ctx->refillMin & ~0xff0000u) | ((uint32_t)v << 16);
         }
         if (const char* e = getenv("GSB_SLOTS")) {
             const long v = atol(e);

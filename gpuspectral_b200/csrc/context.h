@@ -82,7 +82,10 @@ struct gsb_context {
     gsb::WavefrontState wf;
     bool profiling = false;
     uint32_t targetSlots = 1u << 22;  // paths in flight per wavefront (GSB_SLOTS overrides)
-    uint32_t refillMin = 24;     // idle lanes that trigger a refill in the persistent traversal kernels (GSB_REFILL overrides)
+    // control word of the persistent traversal kernels (traverse.cuh: traceStream): idle lanes that trigger a refill
+    // (bits 0..7, GSB_REFILL), lanes that make a quorum for a traversal phase (8..15, GSB_VOTE; closest-hit kernel only,
+    // the any-hit kernel measured best without a quorum), lanes that keep the triangle loop spinning (16..23, GSB_TRIMIN)
+    uint32_t refillMin = 24u | (4u << 8) | (2u << 16);
     bool useGraphLoop = true;    // device-side render loop (conditional CUDA graph); GSB_GRAPH=0 or a failed build disables it
     int instrumented = 0;        // bit 0: count fetches of extension rays, bit 1: of shadow rays
     bool ownStream = true;       // false after gsb_set_stream

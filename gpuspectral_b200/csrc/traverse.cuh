@@ -40,26 +40,24 @@ struct HitRecord {
 
 // object-space ray with the Woop shear constants
 struct ObjRay {
-    float ox, oy, oz;     // origin, permuted so that z is the dominant axis
+    float ox, oy, oz;     // origin, rotated so that z is the dominant axis
     float Sx, Sy, Sz;
-    uint32_t perm;        // kz | swap << 2
+    uint32_t perm;        // kz
 };
 
-GSB_D void permute(uint32_t perm, float x, float y, float z, float& px, float& py, float& pz) {
-    const uint32_t kz = perm & 3u;
+// Cyclic rotation that brings axis kz to z.  The checker additionally swaps x and y when d[kz] < 0 (to keep the
+// winding); that swap negates U, V, W, det and T together (round-to-nearest is symmetric in sign), so the accept /
+// reject decisions and the quotients t = T/det, u = V/det, v = W/det keep their bits without it — it is left out.
+GSB_D void permute(uint32_t kz, float x, float y, float z, float& px, float& py, float& pz) {
     pz = kz == 0 ? x : (kz == 1 ? y : z);
-    float a = kz == 0 ? y : (kz == 1 ? z : x);
-    float b = kz == 0 ? z : (kz == 1 ? x : y);
-    const bool swap = (perm >> 2) != 0;
-    px = swap ? b : a;
-    py = swap ? a : b;
+    px = kz == 0 ? y : (kz == 1 ? z : x);
+    py = kz == 0 ? z : (kz == 1 ? x : y);
 }
 
 GSB_D void makeObjRay(float ox, float oy, float oz, float dx, float dy, float dz, ObjRay& r) {
     const float ax = fabsf(dx), ay = fabsf(dy), az = fabsf(dz);
     const uint32_t kz = (ax > ay) ? ((ax > az) ? 0u : 2u) : ((ay > az) ? 1u : 2u);
-    const float dkz = kz == 0 ? dx : (kz == 1 ? dy : dz);
-    r.perm = kz | ((dkz < 0.0f) ? 4u : 0u);
+    r.perm = kz;
     float pdx, pdy, pdz;
     permute(r.perm, dx, dy, dz, pdx, pdy, pdz);
     r.Sx = __fdiv_rn(pdx, pdz);
@@ -241,14 +239,24 @@ GSB_D void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :
 //   bool fetch(bool want, RayJob& job)                           next ray for idle lanes; false = lane got none
 //   bool drained()                                               warp-uniform: no more rays will ever come
 //
-// Pass shape: every pass runs the same phases in the same order — (1) descend one node, (2a) enter one instance
-// at the top level, (2b) test the pending triangles at the bottom level, (3) pop — each under its own predicate,
-// so the lanes of a warp that are in the same phase execute it together and a lane can advance through all of
-// them in one pass.  ANYHIT: a ray ends at the first triangle with tmin < t < tmax (hit.inst = 0).
-// The first kSmemStack stack entries live in shared memory ([entry][thread]: conflict-free 64-bit accesses);
-// deeper entries spill to local memory.
+// Pass shape: the lanes of a persistent warp drift apart (different rays, different depths), so at any moment some
+// want to (1) descend one node, some to (2a) enter an instance at the top level, some to (2b) test pending triangles
+// at the bottom level, and the rest have nothing pending and (3) pop.  Running every phase in every pass under its
+// own predicate would issue each phase for a handful of lanes.  Instead the warp votes: a phase runs in this pass only
+// if at least `vote` lanes are waiting for it (if no phase has a quorum, the one with the most lanes runs, so every
+// pass makes progress); a lane whose phase sits the pass out simply keeps its state.  Lanes that arrive at a phase
+// while it runs (phase 1 hands triangles to 2b, 2a hands direct triangles to 2b) ride along.  Per-lane operation
+// order is unchanged, so results and fetch counts do not depend on the vote threshold.
+// `control` packs refillMin (bits 0..7), vote (8..15) and triMin (16..23: lanes needed to keep the triangle loop of
+// phase 2b spinning after its first round).  ANYHIT: a ray ends at the first triangle with tmin < t < tmax
+// (hit.inst = 0).  The first kSmemStack stack entries live in shared memory ([entry][thread]: conflict-free 64-bit
+// accesses); deeper entries spill to local memory.  Closest hit: u and v are kept as numerators (hit.u = V,
+// hit.v = W, with `hitDet`) while the ray is in flight and divided once when it is handed in.
 template <bool ANYHIT, bool STATS, class Source>
-GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t refillMin, TraceStats* stats, uint32_t* overflowFlag) {
+GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceStats* stats, uint32_t* overflowFlag) {
+    const uint32_t refillMin = control & 0xffu;
+    const int vote = (int)((control >> 8) & 0xffu);
+    const int triMin = (int)((control >> 16) & 0xffu);
     __shared__ uint2 s_stack[kSmemStack][kTraceBlock];
     uint2 lstack[kStackSize - kSmemStack];
     const uint32_t tid = threadIdx.x;
@@ -256,6 +264,7 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t refillMin, Trac
     RayJob job;
     job.tag = kNoTag;
     HitRecord hit;
+    float hitDet = 1.0f;
     bool active = false;
     int sp = 0, spMark = -1;
     float widx = 0.0f, widy = 0.0f, widz = 0.0f;
@@ -281,6 +290,10 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t refillMin, Trac
         const uint32_t idle = __ballot_sync(0xffffffffu, !active);
         const uint32_t pending = __ballot_sync(0xffffffffu, !active && job.tag != kNoTag);
         if (idle == 0xffffffffu || (src.drained() ? pending != 0u : (uint32_t)__popc(idle) >= refillMin)) {
+            if (!ANYHIT && !active && job.tag != kNoTag && hit.inst != GSB_NO_HIT) {
+                hit.u = __fdiv_rn(hit.u, hitDet);
+                hit.v = __fdiv_rn(hit.v, hitDet);
+            }
             src.commit(!active && job.tag != kNoTag, hit, job.tag);
             if (!active) job.tag = kNoTag;
             const bool got = src.fetch(!active, job);
@@ -301,9 +314,22 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t refillMin, Trac
                 continue;
             }
         }
-        if (active) {
+        // ---- vote: which phases run in this pass
+        bool run1, run2a, run2b;
+        {
+            const bool hasT = active && T.y != 0u;
+            const int n1 = __popc(__ballot_sync(0xffffffffu, active && !hasT && (G.y & 0xff000000u) != 0u));
+            const int n2a = __popc(__ballot_sync(0xffffffffu, hasT && spMark < 0));
+            const int n2b = __popc(__ballot_sync(0xffffffffu, hasT && spMark >= 0));
+            run1 = n1 >= vote; run2a = n2a >= vote; run2b = n2b >= vote;
+            if (!(run1 || run2a || run2b)) {
+                if (n1 >= n2a && n1 >= n2b) run1 = true;
+                else if (n2a >= n2b) run2a = true;
+                else run2b = true;
+            }
+        }
         // ---- phase 1: descend into the pending internal child that comes first in octant order
-        if (G.y & 0xff000000u) {
+        if (run1 && active && !T.y && (G.y & 0xff000000u)) {
             const uint32_t bit = 31u - (uint32_t)__clz(G.y);
             G.y &= ~(1u << bit);
             const uint32_t slot = (bit - 24u) ^ oct7;
@@ -313,7 +339,7 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t refillMin, Trac
             intersectNode(nodes, nodeIndex, cox, coy, coz, cidx, cidy, cidz, job.tmin, hit.t, oct7, G, T);
         }
         // ---- phase 2a (top level): enter one instance, park the rest of this node
-        if (spMark < 0 && T.y) {
+        if (run2a && active && spMark < 0 && T.y) {
             const uint32_t bit = (uint32_t)__ffs(T.y) - 1u;
             T.y &= ~(1u << bit);
             const TraceInstance* ti = sc.tlasInst + (T.x + bit);
@@ -349,26 +375,32 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t refillMin, Trac
                 T = make_uint2(0u, 0u);
             }
         }
-        // ---- phase 2b (bottom level): test the pending triangles; they can only shrink the interval
-        if (spMark >= 0) {
-            while (T.y) {
-                const uint32_t bit = (uint32_t)__ffs(T.y) - 1u;
-                T.y &= ~(1u << bit);
-                const float4* tp = tris + (size_t)(T.x + bit) * 3;
-                const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
-                if (STATS) stats->tris++;
-                float Tn, V, W, det;
-                if (woopEdges(oray, v0, v1, v2, Tn, V, W, det)) {
-                    const float t = __fdiv_rn(Tn, det);
-                    if (t > job.tmin && t < job.tmax) {
-                        if (ANYHIT) {
-                            // occluded: drop everything still pending, phase 3 ends the ray
-                            hit.inst = 0u; hit.prim = 0u; hit.t = 0.0f;
-                            T.y = 0u; G.y = 0u; sp = 0;
-                        } else {
-                            const uint32_t prim = __float_as_uint(v0.w);
-                            if (t < hit.t || (t == hit.t && (curInst < hit.inst || (curInst == hit.inst && prim < hit.prim)))) {
-                                hit.t = t; hit.u = __fdiv_rn(V, det); hit.v = __fdiv_rn(W, det); hit.inst = curInst; hit.prim = prim;
+        // ---- phase 2b (bottom level): test the pending triangles, one per lane per round; they can only shrink
+        // the interval.  The loop keeps spinning while at least triMin lanes still have triangles.
+        if (run2b) {
+            for (bool first = true;; first = false) {
+                const bool w = active && spMark >= 0 && T.y != 0u;
+                const uint32_t m = __ballot_sync(0xffffffffu, w);
+                if (!m || (!first && __popc(m) < triMin)) break;
+                if (w) {
+                    const uint32_t bit = (uint32_t)__ffs(T.y) - 1u;
+                    T.y &= ~(1u << bit);
+                    const float4* tp = tris + (size_t)(T.x + bit) * 3;
+                    const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                    if (STATS) stats->tris++;
+                    float Tn, V, W, det;
+                    if (woopEdges(oray, v0, v1, v2, Tn, V, W, det)) {
+                        const float t = __fdiv_rn(Tn, det);
+                        if (t > job.tmin && t < job.tmax) {
+                            if (ANYHIT) {
+                                // occluded: drop everything still pending, phase 3 ends the ray
+                                hit.inst = 0u; hit.prim = 0u; hit.t = 0.0f;
+                                T.y = 0u; G.y = 0u; sp = 0;
+                            } else {
+                                const uint32_t prim = __float_as_uint(v0.w);
+                                if (t < hit.t || (t == hit.t && (curInst < hit.inst || (curInst == hit.inst && prim < hit.prim)))) {
+                                    hit.t = t; hit.u = V; hit.v = W; hitDet = det; hit.inst = curInst; hit.prim = prim;
+                                }
                             }
                         }
                     }
@@ -376,7 +408,7 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t refillMin, Trac
             }
         }
         // ---- phase 3: nothing pending in this node -> leave the instance if its stack is drained, then pop
-        if (!(G.y & 0xff000000u)) {
+        if (active && !T.y && !(G.y & 0xff000000u)) {
             if (sp == spMark) {
                 spMark = -1;
                 nodes = sc.tlasNodes;
@@ -392,7 +424,6 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t refillMin, Trac
                 else { T = e; G = make_uint2(0u, 0u); }
             }
         }
-        }  // active
     }
 #undef GSB_PUSH
 }

@@ -48,7 +48,8 @@ for (f, l), a in agg.items():
     byfile[f] += a[0]
 print("by file:", {f: f"{100 * v / totI:.1f}%" for f, v in byfile.most_common()})
 print(f"{'file:line':24s} {'%inst':>6s} {'thr/inst':>8s} {'%samples':>8s} {'%long_sb':>8s}  source")
-for (f, l), a in sorted(agg.items(), key=lambda kv: -kv[1][0])[:top]:
+key = 2 if "--by-samples" in sys.argv else 0
+for (f, l), a in sorted(agg.items(), key=lambda kv: -kv[1][key])[:top]:
     print(f"{f + ':' + str(l):24s} {100 * a[0] / totI:6.2f} {a[1] / max(a[0], 1):8.1f} {100 * a[2] / max(totS, 1):8.2f} {100 * a[3] / max(totS, 1):8.2f}  {a[4]}")
 if "--ranges" in sys.argv:
     # cumulative per file in source order, for section totals
