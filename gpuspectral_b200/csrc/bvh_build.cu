@@ -424,7 +424,7 @@ struct GenericResult {
 };
 
 GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi, uint32_t n, const float cmin[3], const float cmax[3],
-                           cudaStream_t s, DeviceBvh& out) {
+                           cudaStream_t s, DeviceBvh& out, bool topLevel) {
     GenericResult r;
     r.nodes = pool.get<uint4>((size_t)std::max<uint32_t>(n, 1) * 5);
     r.leafPrim = pool.get<uint32_t>(n);
@@ -483,8 +483,11 @@ GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi,
     GSB_CUDA(cudaMemsetAsync(dCost, 0, 2 * sizeof(double), s));
     const int costBlocks = (int)std::min<uint32_t>((n + B - 1) / B, 1024u);
     k_sahCost<<<costBlocks, B, 0, s>>>(t, plo, phi, (int)n, dCost);
-    int passes = g_treelets ? 2 : 0;
-    if (const char* e = getenv("GSB_TREELET_PASSES")) passes = atoi(e);
+    // Bottom level: two passes.  Top level: off by default — on the instanced test scene the refined TLAS lowered the SAH
+    // cost but raised the instances entered per ray (4.7 -> 6.1): the Morton order of the instance centroids gives a
+    // better front-to-back visiting order than the SAH-optimal grouping (profiles/README.md, r1g).
+    int passes = (g_treelets && !topLevel) ? 2 : 0;
+    if (const char* e = getenv(topLevel ? "GSB_TREELET_PASSES_TLAS" : "GSB_TREELET_PASSES")) passes = atoi(e);
     const bool refine = passes > 0 && n >= 16;
     if (refine) {
         refineTreelets(pool.s, t, plo, phi, sorted, (int)n, passes, [&](size_t bytes) { return (void*)pool.get<uint8_t>(bytes); });
@@ -569,7 +572,7 @@ void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBv
             pad = scale * kBoxPadRel;
             k_triBoxes<<<(ntris + B - 1) / B, B, 0, s>>>(dVertices, ntris, pad, plo, phi);
         }
-        GenericResult r = buildGeneric(pool, plo, phi, ntris, lo, hi, s, out);
+        GenericResult r = buildGeneric(pool, plo, phi, ntris, lo, hi, s, out, false);
         finishBuffer(r, ntris, 48, s, out);
         if (ntris > 0)
             k_packTriangles<<<(ntris + B - 1) / B, B, 0, s>>>(r.leafPrim, ntris, dVertices,
@@ -612,7 +615,7 @@ void buildTlas(const float* hostLo, const float* hostHi, const TraceInstance* ho
             GSB_CUDA(cudaMemcpyAsync(phi, hi4.data(), (size_t)n * sizeof(float4), cudaMemcpyHostToDevice, s));
             GSB_CUDA(cudaMemcpyAsync(rec, hostRecords, (size_t)n * sizeof(TraceInstance), cudaMemcpyHostToDevice, s));
         }
-        GenericResult r = buildGeneric(pool, plo, phi, n, clo, chi, s, out);
+        GenericResult r = buildGeneric(pool, plo, phi, n, clo, chi, s, out, true);
         finishBuffer(r, n, sizeof(TraceInstance), s, out);
         if (n > 0) k_packInstances<<<(n + 255) / 256, 256, 0, s>>>(r.leafPrim, n, rec, out.buffer + out.leafOffset16);
         GSB_CUDA(cudaGetLastError());

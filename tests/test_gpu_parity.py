@@ -68,6 +68,32 @@ def test_closest_hit_ids_exact(gsb, orc, ctx, name, n):
     assert (got["inst"] != gsb.NO_HIT).mean() > 0.3
 
 
+def test_treelet_refinement_keeps_hits_and_lowers_sah(gsb, orc, monkeypatch):
+    """The SAH treelet refinement only re-shapes the BVH: hits (ids, t, barycentrics) are bit-identical with it off,
+    with one, two and three passes, at both levels, and the binary-tree SAH cost never goes up."""
+    s = host_scene("field_medium")
+    rays = random_rays(s, 30000, seed=11)
+    results, stats = [], []
+    for blas, tlas in [(0, 0), (1, 0), (2, 0), (3, 2)]:
+        monkeypatch.setenv("GSB_TREELET_PASSES", str(blas))
+        monkeypatch.setenv("GSB_TREELET_PASSES_TLAS", str(tlas))
+        with gsb.Context(0) as c:
+            c.upload(s)
+            stats.append(c.bvh_stats())
+            results.append(c.trace_batch(rays))
+            occl = c.trace_batch(rays, any_hit=True)
+            assert np.array_equal(occl["inst"] != gsb.NO_HIT, results[-1]["inst"] != gsb.NO_HIT)
+    for r in results[1:]:
+        for k in ("inst", "prim", "t", "u", "v"):
+            assert np.array_equal(r[k], results[0][k]), k
+    assert stats[0]["sah_cost_after"] == stats[0]["sah_cost_before"]
+    assert stats[1]["sah_cost_after"] < 0.97 * stats[1]["sah_cost_before"]
+    assert stats[2]["sah_cost_after"] <= stats[1]["sah_cost_after"] * 1.0001
+    assert stats[3]["sah_cost_after"] <= stats[2]["sah_cost_after"] * 1.0001
+    for st in stats:
+        assert st["unique_triangles"] == stats[0]["unique_triangles"] and st["num_instances"] == stats[0]["num_instances"]
+
+
 def test_closest_hit_vs_float64(gsb, orc, ctx):
     """Independent check of the rule itself: float64 Moeller-Trumbore brute force. ids may differ only
     where two candidates are within rounding distance; t within 16 ulp of float32 at the hit distance."""
