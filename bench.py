@@ -303,9 +303,16 @@ def run_ours(a, rank, world, local_rank):
     tpath = os.path.join(ROOT, "profiles", "extend_traffic.json")
     if os.path.exists(tpath):
         traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+    # L2 / FP32 denominators measured on a B200 of this pool by lib/gsb_peaks (not in MEASURED_PEAKS.json)
+    l2_peak = fp32_peak = None
+    ppath = os.path.join(ROOT, "profiles", "peaks_b200.json")
+    if os.path.exists(ppath):
+        pk = json.load(open(ppath))
+        l2_peak, fp32_peak = pk.get("l2_read_gbs"), pk.get("fp32_fma_tflops")
     stage_total = sum(stage.values())
     roofline = {"kernel": "k_extend (closest-hit traversal)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "l2_peak": l2_peak, "frac_of_l2_peak": (achieved / l2_peak) if l2_peak else None, "fp32_peak_tflops": fp32_peak,
                 "bytes_per_ray": ext_bytes_per_ray, "rays_per_launch": ext_per_launch, "ms_per_launch": ext_ms_per_launch,
                 "fetch_per_ray": ext_fetch, "launches": iters,
                 "share_of_step": {k: v / stage_total for k, v in stage.items()} if stage_total > 0 else None,
