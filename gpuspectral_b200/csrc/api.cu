@@ -317,6 +317,10 @@ gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx) {
             const long v = atol(e);
             if (v >= 0 && v <= 32) ctx->refillMin = (ctx->refillMin & ~0xff0000u) | ((uint32_t)v << 16);
         }
+        if (const char* e = getenv("GSB_SHADE_DIRECT")) {
+            const long v = atol(e);
+            if (v >= 1 && v <= 33) ctx->shadeDirectMin = (uint32_t)v;
+        }
         if (const char* e = getenv("GSB_SLOTS")) {
             const long v = atol(e);
             if (v >= 1024 && v <= (1l << 26)) ctx->targetSlots = (uint32_t)v;

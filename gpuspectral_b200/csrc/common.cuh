@@ -33,7 +33,8 @@ GSB_HD float3 operator-(float3 a) { return f3(-a.x, -a.y, -a.z); }
 GSB_HD float3 operator*(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
 GSB_HD float3 operator*(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
 GSB_HD float3 operator*(float s, float3 a) { return f3(s * a.x, s * a.y, s * a.z); }
-GSB_HD float3 operator/(float3 a, float s) { return f3(a.x / s, a.y / s, a.z / s); }
+// one IEEE reciprocal + three products (<= 1 ulp from three divisions; GLSL does not promise correctly rounded division)
+GSB_HD float3 operator/(float3 a, float s) { const float r = 1.0f / s; return f3(a.x * r, a.y * r, a.z * r); }
 GSB_HD float3 operator/(float3 a, float3 b) { return f3(a.x / b.x, a.y / b.y, a.z / b.z); }
 GSB_HD float3 operator+(float3 a, float s) { return f3(a.x + s, a.y + s, a.z + s); }
 GSB_HD float3 operator-(float3 a, float s) { return f3(a.x - s, a.y - s, a.z - s); }

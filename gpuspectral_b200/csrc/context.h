@@ -86,6 +86,7 @@ struct gsb_context {
     // (bits 0..7, GSB_REFILL), lanes that make a quorum for a traversal phase (8..15, GSB_VOTE; closest-hit kernel only,
     // the any-hit kernel measured best without a quorum), lanes that keep the triangle loop spinning (16..23, GSB_TRIMIN)
     uint32_t refillMin = 24u | (4u << 8) | (2u << 16);
+    uint32_t shadeDirectMin = 32;  // k_shade: matching lanes from which a tile is shaded in place (GSB_SHADE_DIRECT; measured flat from 12 to 32)
     bool useGraphLoop = true;    // device-side render loop (conditional CUDA graph); GSB_GRAPH=0 or a failed build disables it
     int instrumented = 0;        // bit 0: count fetches of extension rays, bit 1: of shadow rays
     bool ownStream = true;       // false after gsb_set_stream

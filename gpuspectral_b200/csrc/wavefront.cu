@@ -229,11 +229,11 @@ __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_extend(SceneDe
 
 // ---- shade ----------------------------------------------------------------------------------------
 // Material sorting without a global queue: every warp scans the slots 32 at a time in slot order and keeps those whose
-// hit carries a BSDF of this kernel's TYPE.  A tile that matches completely (always, in a single-material scene) is
-// shaded as it is — the path-state streams are then read and written fully coalesced; partial tiles are compacted
-// through a 64-entry per-warp buffer in shared memory and shaded 32 at a time.
+// hit carries a BSDF of this kernel's TYPE.  A tile with at least directMin matching lanes is shaded as it is — the
+// path-state streams are then read and written coalesced; sparser tiles are compacted through a 64-entry per-warp
+// buffer in shared memory and shaded 32 at a time (entries wait there across in-place tiles).
 template <int TYPE>
-__global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t slots) {
+__global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t slots, uint32_t directMin) {
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
     __shared__ uint32_t s_buf[kBlock / 32][64];
     const uint32_t lane = threadIdx.x & 31u;
@@ -252,8 +252,10 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
         const uint32_t mm = __ballot_sync(0xffffffffu, match);
         bool active;
         uint32_t slot = 0;
-        if (mm == 0xffffffffu && pendingCount == 0u) {
-            active = true;
+        if ((uint32_t)__popc(mm) >= directMin) {
+            // a tile that matches (almost) completely is shaded in place: coalesced state streams and no trip through
+            // the compaction buffer, at the price of its few non-matching lanes idling
+            active = match;
             slot = cand;
         } else {
             if (match) buf[pendingCount + (uint32_t)__popc(mm & ((1u << lane) - 1u))] = cand;
@@ -521,7 +523,7 @@ void allocWavefront(gsb_context* ctx, uint32_t slots) {
 
 template <int TYPE>
 void launchShade(gsb_context* ctx, const SceneDev& sc, int grid, uint32_t parity, uint32_t slots) {
-    k_shade<TYPE><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots);
+    k_shade<TYPE><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots, ctx->shadeDirectMin);
 }
 
 }  // namespace
