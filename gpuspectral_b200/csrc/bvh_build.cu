@@ -372,17 +372,19 @@ __global__ void k_emptyRoot(uint4* nodes) {
     nodes[2] = nodes[3] = nodes[4] = make_uint4(0u, 0u, 0u, 0u);
 }
 
+// Leaf record of a triangle: three copies, one per dominant ray axis kz, each rotated so that kz comes last
+// (traverse.cuh: permute) — the traversal fetches the copy that matches its ray and needs no per-vertex selects.
+// Copy kz of leaf position k sits at float4 index 9 k + 3 kz; v0.w carries the primitive id in every copy.
 __global__ void k_packTriangles(const uint32_t* __restrict__ leafPrim, uint32_t n, const float4* __restrict__ v, float4* __restrict__ out) {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     const uint32_t p = leafPrim[k];
-    float4 a = __ldg(v + 3 * (size_t)p), b = __ldg(v + 3 * (size_t)p + 1), c = __ldg(v + 3 * (size_t)p + 2);
-    a.w = __uint_as_float(p);
-    b.w = 0.0f;
-    c.w = 0.0f;
-    out[3 * (size_t)k] = a;
-    out[3 * (size_t)k + 1] = b;
-    out[3 * (size_t)k + 2] = c;
+    const float4 a = __ldg(v + 3 * (size_t)p), b = __ldg(v + 3 * (size_t)p + 1), c = __ldg(v + 3 * (size_t)p + 2);
+    const float pw = __uint_as_float(p);
+    float4* o = out + 9 * (size_t)k;
+    o[0] = make_float4(a.y, a.z, a.x, pw); o[1] = make_float4(b.y, b.z, b.x, 0.0f); o[2] = make_float4(c.y, c.z, c.x, 0.0f);   // kz = 0
+    o[3] = make_float4(a.z, a.x, a.y, pw); o[4] = make_float4(b.z, b.x, b.y, 0.0f); o[5] = make_float4(c.z, c.x, c.y, 0.0f);   // kz = 1
+    o[6] = make_float4(a.x, a.y, a.z, pw); o[7] = make_float4(b.x, b.y, b.z, 0.0f); o[8] = make_float4(c.x, c.y, c.z, 0.0f);   // kz = 2
 }
 
 __global__ void k_packInstances(const uint32_t* __restrict__ leafPrim, uint32_t n, const uint4* __restrict__ rec, uint4* __restrict__ out) {
@@ -573,7 +575,7 @@ void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBv
             k_triBoxes<<<(ntris + B - 1) / B, B, 0, s>>>(dVertices, ntris, pad, plo, phi);
         }
         GenericResult r = buildGeneric(pool, plo, phi, ntris, lo, hi, s, out, false);
-        finishBuffer(r, ntris, 48, s, out);
+        finishBuffer(r, ntris, 144, s, out);
         if (ntris > 0)
             k_packTriangles<<<(ntris + B - 1) / B, B, 0, s>>>(r.leafPrim, ntris, dVertices,
                                                               reinterpret_cast<float4*>(out.buffer + out.leafOffset16));

@@ -12,7 +12,8 @@
 //   w2: qlo.x[8], qlo.y[8]      w3: qlo.z[8], qhi.x[8]      w4: qhi.y[8], qhi.z[8]
 // child i box = origin + q * 2^(e - 127).  meta[i] = 0: empty; internal child: 0x20 | (24 + i);
 // leaf child: (unary count 1/3/7) << 5 | offset of its first primitive inside the node's leaf range.
-// Bottom level primitive = triangle (3 x float4: v0.xyz|primId, v1.xyz, v2.xyz), 48 B.
+// Bottom level primitive = triangle (3 x float4: v0.xyz|primId, v1.xyz, v2.xyz), 48 B fetched per test; stored three
+// times (144 B), once per dominant ray axis, pre-rotated so that the test needs no per-vertex selects.
 // Top level primitive = TraceInstance (64 B).
 //
 // Intersection rule (shared with the checker; the reference has no source for it):
@@ -69,11 +70,9 @@ GSB_D void makeObjRay(float ox, float oy, float oz, float dx, float dy, float dz
 // Watertight ray/triangle test; every operation individually rounded (no FMA contraction).
 // Returns false when the ray misses; otherwise the scaled distance T, the barycentric numerators V, W and det,
 // so that callers pay for the divisions t = T/det, u = V/det, v = W/det only when they need them.
+// v0, v1, v2: the triangle copy already rotated for the ray's dominant axis (bvh_build.cu: k_packTriangles).
 GSB_D bool woopEdges(const ObjRay& r, float4 v0, float4 v1, float4 v2, float& T, float& V, float& W, float& det) {
-    float Akx, Aky, Akz, Bkx, Bky, Bkz, Ckx, Cky, Ckz;
-    permute(r.perm, v0.x, v0.y, v0.z, Akx, Aky, Akz);
-    permute(r.perm, v1.x, v1.y, v1.z, Bkx, Bky, Bkz);
-    permute(r.perm, v2.x, v2.y, v2.z, Ckx, Cky, Ckz);
+    float Akx = v0.x, Aky = v0.y, Akz = v0.z, Bkx = v1.x, Bky = v1.y, Bkz = v1.z, Ckx = v2.x, Cky = v2.y, Ckz = v2.z;
     Akx = __fsub_rn(Akx, r.ox); Aky = __fsub_rn(Aky, r.oy); Akz = __fsub_rn(Akz, r.oz);
     Bkx = __fsub_rn(Bkx, r.ox); Bky = __fsub_rn(Bky, r.oy); Bkz = __fsub_rn(Bkz, r.oz);
     Ckx = __fsub_rn(Ckx, r.ox); Cky = __fsub_rn(Cky, r.oy); Ckz = __fsub_rn(Ckz, r.oz);
@@ -385,7 +384,7 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
                 if (w) {
                     const uint32_t bit = (uint32_t)__ffs(T.y) - 1u;
                     T.y &= ~(1u << bit);
-                    const float4* tp = tris + (size_t)(T.x + bit) * 3;
+                    const float4* tp = tris + ((size_t)(T.x + bit) * 9 + oray.perm * 3u);
                     const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                     if (STATS) stats->tris++;
                     float Tn, V, W, det;
