@@ -12,14 +12,14 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIBDIR = os.path.join(_HERE, "lib")
 
-BSDF_TYPE_COUNT = 8
+BSDF_TYPE_COUNT = 9
 NO_HIT = 0xFFFFFFFF
 (BSDF_DIFFUSE, BSDF_SMOOTH_DIELECTRIC, BSDF_SMOOTH_CONDUCTOR, BSDF_SMOOTH_PLASTIC,
- BSDF_ROUGH_CONDUCTOR, BSDF_SMOOTH_FLOOR, BSDF_ROUGH_FLOOR, BSDF_ROUGH_PLASTIC) = range(8)
+ BSDF_ROUGH_CONDUCTOR, BSDF_SMOOTH_FLOOR, BSDF_ROUGH_FLOOR, BSDF_ROUGH_PLASTIC, BSDF_ROUGH_DIELECTRIC) = range(9)
 BSDF_NAMES = ("diffuse", "smooth_dielectric", "smooth_conductor", "smooth_plastic",
-              "rough_conductor", "smooth_floor", "rough_floor", "rough_plastic")
+              "rough_conductor", "smooth_floor", "rough_floor", "rough_plastic", "rough_dielectric")
 # sizeof of the parameter records, renderer/Scene.h:29-82 of the reference
-BSDF_STRIDES = (16, 8, 8, 24, 44, 16, 20, 32)
+BSDF_STRIDES = (16, 8, 8, 24, 44, 16, 20, 32, 16)   # last: the rough dielectric extension
 
 
 class Instance(C.Structure):

@@ -45,7 +45,8 @@ gsb_status fail(gsb_status st, const std::string& msg) {
 
 const uint32_t kBsdfStride[GSB_BSDF_TYPE_COUNT] = {
     sizeof(gsb_diffuse_bsdf), sizeof(gsb_smooth_dielectric_bsdf), sizeof(gsb_smooth_conductor_bsdf), sizeof(gsb_smooth_plastic_bsdf),
-    sizeof(gsb_rough_conductor_bsdf), sizeof(gsb_smooth_floor_bsdf), sizeof(gsb_rough_floor_bsdf), sizeof(gsb_rough_plastic_bsdf)};
+    sizeof(gsb_rough_conductor_bsdf), sizeof(gsb_smooth_floor_bsdf), sizeof(gsb_rough_floor_bsdf), sizeof(gsb_rough_plastic_bsdf),
+    sizeof(gsb_rough_dielectric_bsdf)};
 
 template <class T>
 T* uploadArray(const T* host, size_t count, cudaStream_t s) {

@@ -392,8 +392,85 @@ GSB_D void roughFloorEval(const gsb_rough_floor_bsdf& b, float3 wo, float3 wi, B
     res.isDelta = false;
 }
 
+// RoughDielectric — extension, no counterpart in rayhit.rchit (include/gpuspectral_b200.h: GSB_BSDF_ROUGH_DIELECTRIC).
+// GGX microfacet reflection + refraction after Walter, Marschner, Li & Torrance, "Microfacet Models for Refraction
+// through Rough Surfaces" (EGSR 2007), in this shader's conventions: f excludes the cosine, wo points back along the
+// path, light arrives along wi; the transmitted lobe carries the (no/nt)^2 radiance scaling of the smooth dielectric
+// (:362-404) and converges to it for alpha -> 0.  Draw order: two uniforms for the half vector, one for the lobe.
+GSB_D float3 sampleHalfGGX(uint32_t& rng, float alpha) {
+    const float ux = randUniform(rng);
+    const float uy = randUniform(rng);
+    const float phi = 2.0f * GSB_PI * ux;
+    const float tan2 = alpha * alpha * uy / (1.0f - uy);   // uy = 1 -> inf -> grazing half vector, D = 0
+    const float cost = 1.0f / sqrtf(1.0f + tan2);
+    const float sint = sqrtf(fmaxf(0.0f, 1.0f - cost * cost));
+    return f3(cosf(phi) * sint, sinf(phi) * sint, cost);
+}
+GSB_D void roughDielectricInvalid(float3 wo, float3& wi, BSDFOutput& res) {
+    wi = mirrorZ(wo);
+    res.bsdf = f3(0.0f);
+    res.pdf = 0.0f;
+    res.isDelta = false;
+}
+GSB_D void roughDielectricSample(const gsb_rough_dielectric_bsdf& b, uint32_t& rng, float3 wo, float3& wi, BSDFOutput& res) {
+    const bool entering = wo.z > 0.0f;
+    const float no = entering ? b.iorOut : b.iorIn;
+    const float nt = entering ? b.iorIn : b.iorOut;
+    float3 wh = sampleHalfGGX(rng, b.alpha);
+    if (!entering) wh = wh * -1.0f;                        // half vector on wo's side
+    const float u = randUniform(rng);
+    const float cosI = dot(wo, wh);
+    const float D = ggxD(wh, b.alpha);
+    if (!(cosI > 0.0f) || !(D > 0.0f)) { roughDielectricInvalid(wo, wi, res); return; }
+    const float Fr = fresnelC(cosI, no, nt);
+    res.isDelta = false;
+    if (u < Fr) {
+        wi = normalize(-wo + 2.0f * cosI * wh);
+        if (!(wi.z * wo.z > 0.0f)) { roughDielectricInvalid(wo, wi, res); return; }
+        res.bsdf = f3(Fr * D * ggxMask(wo, wi, b.alpha) / (4.0f * fabsf(wi.z) * fabsf(wo.z)));
+        res.pdf = Fr * D * fabsf(wh.z) / (4.0f * cosI);
+    } else {
+        const float eta = no / nt;
+        const float cosT2 = 1.0f - eta * eta * (1.0f - cosI * cosI);   // > 0 here: Fr = 1 under total internal reflection
+        wi = normalize(-eta * wo + (eta * cosI - sqrtf(fmaxf(cosT2, 0.0f))) * wh);
+        const float cosO = dot(wi, wh);
+        if (!(wi.z * wo.z < 0.0f) || !(cosO < 0.0f)) { roughDielectricInvalid(wo, wi, res); return; }
+        const float denom = no * cosI + nt * cosO;
+        const float jac = fabsf(cosO) / (denom * denom);
+        res.bsdf = f3((1.0f - Fr) * D * ggxMask(wo, wi, b.alpha) * cosI * no * no * jac / (fabsf(wi.z) * fabsf(wo.z)));
+        res.pdf = (1.0f - Fr) * D * fabsf(wh.z) * nt * nt * jac;
+    }
+}
+GSB_D void roughDielectricEval(const gsb_rough_dielectric_bsdf& b, float3 wo, float3 wi, BSDFOutput& res) {
+    const bool entering = wo.z > 0.0f;
+    const float no = entering ? b.iorOut : b.iorIn;
+    const float nt = entering ? b.iorIn : b.iorOut;
+    res.isDelta = false;
+    res.bsdf = f3(0.0f);
+    res.pdf = 0.0f;
+    const bool reflect = wi.z * wo.z > 0.0f;
+    float3 wh = reflect ? normalize(wo + wi) : normalize(no * wo + nt * wi);
+    if (dot(wo, wh) < 0.0f) wh = wh * -1.0f;
+    const float cosI = dot(wo, wh), cosO = dot(wi, wh);
+    const float D = ggxD(wh, b.alpha);
+    if (!(cosI > 0.0f) || !(D > 0.0f) || wi.z == 0.0f || wo.z == 0.0f) return;
+    if (entering ? wh.z <= 0.0f : wh.z >= 0.0f) return;     // the sampler only produces half vectors on wo's side
+    const float Fr = fresnelC(cosI, no, nt);
+    if (reflect) {
+        res.bsdf = f3(Fr * D * ggxMask(wo, wi, b.alpha) / (4.0f * fabsf(wi.z) * fabsf(wo.z)));
+        res.pdf = Fr * D * fabsf(wh.z) / (4.0f * cosI);
+    } else {
+        if (!(cosO < 0.0f)) return;
+        const float denom = no * cosI + nt * cosO;
+        if (denom == 0.0f) return;
+        const float jac = fabsf(cosO) / (denom * denom);
+        res.bsdf = f3((1.0f - Fr) * D * ggxMask(wo, wi, b.alpha) * cosI * no * no * jac / (fabsf(wi.z) * fabsf(wo.z)));
+        res.pdf = (1.0f - Fr) * D * fabsf(wh.z) * nt * nt * jac;
+    }
+}
+
 // :620-627
-GSB_D bool isTransmissionBSDF(uint32_t type) { return type == GSB_BSDF_SMOOTH_DIELECTRIC; }
+GSB_D bool isTransmissionBSDF(uint32_t type) { return type == GSB_BSDF_SMOOTH_DIELECTRIC || type == GSB_BSDF_ROUGH_DIELECTRIC; }
 
 // Compile-time dispatch used by the material-sorted shade kernel (TYPE is uniform per block);
 // the runtime switch of :630-654 survives only in the diagnostic entry points.
@@ -407,6 +484,7 @@ GSB_D void sampleBSDFT(const SceneDev& sc, uint32_t index, uint32_t& rng, float3
     else if (TYPE == GSB_BSDF_SMOOTH_FLOOR) smoothFloorSample(((const gsb_smooth_floor_bsdf*)sc.bsdf[TYPE])[index], rng, wo, wi, res);
     else if (TYPE == GSB_BSDF_ROUGH_FLOOR) roughFloorSample(((const gsb_rough_floor_bsdf*)sc.bsdf[TYPE])[index], rng, wo, wi, res);
     else if (TYPE == GSB_BSDF_ROUGH_PLASTIC) roughPlasticSample(((const gsb_rough_plastic_bsdf*)sc.bsdf[TYPE])[index], rng, wo, wi, res);
+    else if (TYPE == GSB_BSDF_ROUGH_DIELECTRIC) roughDielectricSample(((const gsb_rough_dielectric_bsdf*)sc.bsdf[TYPE])[index], rng, wo, wi, res);
 }
 template <int TYPE>
 GSB_D void evalBSDFT(const SceneDev& sc, uint32_t index, float3 wo, float3 wi, BSDFOutput& res) {
@@ -418,6 +496,7 @@ GSB_D void evalBSDFT(const SceneDev& sc, uint32_t index, float3 wo, float3 wi, B
     else if (TYPE == GSB_BSDF_SMOOTH_FLOOR) smoothFloorEval(((const gsb_smooth_floor_bsdf*)sc.bsdf[TYPE])[index], wo, wi, res);
     else if (TYPE == GSB_BSDF_ROUGH_FLOOR) roughFloorEval(((const gsb_rough_floor_bsdf*)sc.bsdf[TYPE])[index], wo, wi, res);
     else if (TYPE == GSB_BSDF_ROUGH_PLASTIC) roughPlasticEval(((const gsb_rough_plastic_bsdf*)sc.bsdf[TYPE])[index], wo, wi, res);
+    else if (TYPE == GSB_BSDF_ROUGH_DIELECTRIC) roughDielectricEval(((const gsb_rough_dielectric_bsdf*)sc.bsdf[TYPE])[index], wo, wi, res);
 }
 
 // runtime dispatch :630-654 (diagnostics only)
@@ -432,6 +511,7 @@ GSB_D void sampleBSDF(const SceneDev& sc, uint32_t handle, uint32_t& rng, float3
         case 5: sampleBSDFT<5>(sc, i, rng, wo, wi, res); break;
         case 6: sampleBSDFT<6>(sc, i, rng, wo, wi, res); break;
         case 7: sampleBSDFT<7>(sc, i, rng, wo, wi, res); break;
+        case 8: sampleBSDFT<8>(sc, i, rng, wo, wi, res); break;
     }
 }
 GSB_D void evalBSDF(const SceneDev& sc, uint32_t handle, float3 wo, float3 wi, BSDFOutput& res) {
@@ -445,6 +525,7 @@ GSB_D void evalBSDF(const SceneDev& sc, uint32_t handle, float3 wo, float3 wi, B
         case 5: evalBSDFT<5>(sc, i, wo, wi, res); break;
         case 6: evalBSDFT<6>(sc, i, wo, wi, res); break;
         case 7: evalBSDFT<7>(sc, i, wo, wi, res); break;
+        case 8: evalBSDFT<8>(sc, i, wo, wi, res); break;
     }
 }
 

@@ -18,10 +18,10 @@ struct MeshRec {
 };
 
 // Counter indices inside WavefrontState::qCount (two banks of Q_COUNT, selected by iteration parity):
-// [0..7] unused (material sorting happens inside k_shade), extension rays traced, the shadow-ray queue.
+// [0..TYPE_COUNT) unused (material sorting happens inside k_shade), extension rays traced, the shadow-ray queue.
 enum { Q_MATERIAL0 = 0, Q_TRACED = GSB_BSDF_TYPE_COUNT, Q_SHADOW = GSB_BSDF_TYPE_COUNT + 1,
-       Q_NEXT_EXTEND = 10, Q_NEXT_SHADOW = 11,  // work counters of the persistent traversal kernels
-       Q_COUNT = 12 };
+       Q_NEXT_EXTEND = GSB_BSDF_TYPE_COUNT + 2, Q_NEXT_SHADOW = GSB_BSDF_TYPE_COUNT + 3,  // work counters of the persistent traversal kernels
+       Q_COUNT = GSB_BSDF_TYPE_COUNT + 4 };
 
 // Per-slot path state, structure of arrays.  The 17-word HitPayload of pt_common.glsl:4-14
 // (+ pixel sample index and the hit record) spread over 16-byte and 4-byte streams.

@@ -642,6 +642,7 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         if (ctx->typeUsed[5]) launchShade<5>(ctx, sc, queueGrid, parity, slots);
         if (ctx->typeUsed[6]) launchShade<6>(ctx, sc, queueGrid, parity, slots);
         if (ctx->typeUsed[7]) launchShade<7>(ctx, sc, queueGrid, parity, slots);
+        if (ctx->typeUsed[8]) launchShade<8>(ctx, sc, queueGrid, parity, slots);
         mark();
         if (ctx->instrumented & 2) k_shadow<true><<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ra.refillMin & 0xffu);
         else k_shadow<false><<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ra.refillMin & 0xffu);

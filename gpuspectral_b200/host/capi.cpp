@@ -81,7 +81,8 @@ const void* gsbh_scene_bsdf_data(const gsbh_scene* s, uint32_t type) {
 uint32_t gsbh_scene_bsdf_stride(uint32_t type) {
     static const uint32_t strides[GSB_BSDF_TYPE_COUNT] = {
         sizeof(gsb_diffuse_bsdf), sizeof(gsb_smooth_dielectric_bsdf), sizeof(gsb_smooth_conductor_bsdf), sizeof(gsb_smooth_plastic_bsdf),
-        sizeof(gsb_rough_conductor_bsdf), sizeof(gsb_smooth_floor_bsdf), sizeof(gsb_rough_floor_bsdf), sizeof(gsb_rough_plastic_bsdf)};
+        sizeof(gsb_rough_conductor_bsdf), sizeof(gsb_smooth_floor_bsdf), sizeof(gsb_rough_floor_bsdf), sizeof(gsb_rough_plastic_bsdf),
+        sizeof(gsb_rough_dielectric_bsdf)};
     return type < GSB_BSDF_TYPE_COUNT ? strides[type] : 0;
 }
 uint32_t gsbh_scene_light_count(const gsbh_scene* s) { return (uint32_t)s->scene.triangleLights.size(); }

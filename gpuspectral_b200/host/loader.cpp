@@ -227,6 +227,14 @@ void loadMaterial(Ctx& c, Material& material, const XmlNode& obj) {
         b.alpha = (float)std::sqrt(2.0f) * alpha;
         material.bsdf = scene.addRoughPlasticBSDF(b);
         material.hasBsdf = true;
+    } else if (type == "roughdielectric") {
+        // extension: the reference's loader has no such branch (Loader.cpp:145-234); Mitsuba semantics, GGX alpha as given
+        gsb_rough_dielectric_bsdf b = {1.5046f, 1.000277f, 0.1f, 0};
+        c.number(obj, "int_ior", b.iorIn);
+        c.number(obj, "ext_ior", b.iorOut);
+        c.number(obj, "alpha", b.alpha);
+        material.bsdf = scene.addRoughDielectricBSDF(b);
+        material.hasBsdf = true;
     } else if (type == "dielectric") {
         gsb_smooth_dielectric_bsdf b = {1.5046f, 1.000277f};
         c.number(obj, "int_ior", b.iorIn);

@@ -128,6 +128,7 @@ const void* Scene::bsdfData(uint32_t type, uint32_t* count, uint32_t* stride) co
         GSBH_CASE(GSB_BSDF_SMOOTH_FLOOR, smoothFloorBSDFs)
         GSBH_CASE(GSB_BSDF_ROUGH_FLOOR, roughFloorBSDFs)
         GSBH_CASE(GSB_BSDF_ROUGH_PLASTIC, roughPlasticBSDFs)
+        GSBH_CASE(GSB_BSDF_ROUGH_DIELECTRIC, roughDielectricBSDFs)
     }
 #undef GSBH_CASE
     *count = 0;
@@ -346,8 +347,9 @@ static const char* kCornellXml = R"XML(<?xml version="1.0" encoding="utf-8"?>
 
 Scene makeCornellBox() { return loadMitsubaSceneFromString(kCornellXml, "."); }
 
-// BSDF gallery (BASELINE.json config 3): the Cornell shell without its boxes + six spheres, one
-// per non-diffuse material the reference's loader can produce (Loader.cpp:162-227).  Material
+// BSDF gallery (BASELINE.json config 3): the Cornell shell without its boxes + seven spheres, one
+// per non-diffuse material the reference's loader can produce (Loader.cpp:162-227) and one frosted-glass
+// sphere for the rough dielectric extension.  Material
 // constants follow assets/scenes/test3/scene.xml:57-95 where it has them.
 Scene makeBsdfGallery() {
     Scene base = makeCornellBox();
@@ -376,7 +378,7 @@ Scene makeBsdfGallery() {
     gsb_smooth_dielectric_bsdf glass = {1.5f, 1.0f};
     gsb_smooth_plastic_bsdf plastic = {{1.0f, 0.378676f, 0.0134734f}, ior, 1.0f, R0};
     gsb_rough_plastic_bsdf rplastic1 = {{0.434734f, 0.578676f, 1.0f}, ior, 1.0f, R0, s2 * 0.05f, 0};
-    gsb_rough_plastic_bsdf rplastic2 = {{1.0f, 0.578676f, 0.134734f}, ior, 1.0f, R0, s2 * 0.3f, 0};
+    gsb_rough_dielectric_bsdf frosted = {1.5f, 1.0f, 0.15f, 0};
     const Ball balls[7] = {
         {-0.62f, 0.27f, 0.35f, 0.27f, s.addRoughConductorBSDF(gold)},
         {0.0f, 0.27f, 0.45f, 0.27f, s.addSmoothDielectricBSDF(glass)},
@@ -384,13 +386,13 @@ Scene makeBsdfGallery() {
         {-0.62f, 0.95f, -0.45f, 0.27f, s.addSmoothConductorBSDF(mirror)},
         {0.0f, 1.05f, -0.5f, 0.27f, s.addRoughPlasticBSDF(rplastic1)},
         {0.62f, 0.95f, -0.45f, 0.27f, s.addRoughConductorBSDF(alu)},
-        {0.0f, 0.3f, -0.45f, 0.3f, s.addRoughPlasticBSDF(rplastic2)},
+        {0.0f, 0.3f, -0.45f, 0.3f, s.addRoughDielectricBSDF(frosted)},
     };
     for (const Ball& b : balls) {
         Material m;
         m.bsdf = b.bsdf;
         m.hasBsdf = true;
-        m.twofaced = (b.bsdf >> 16) != GSB_BSDF_SMOOTH_DIELECTRIC;
+        m.twofaced = (b.bsdf >> 16) != GSB_BSDF_SMOOTH_DIELECTRIC && (b.bsdf >> 16) != GSB_BSDF_ROUGH_DIELECTRIC;
         RenderObject o;
         float T[16], S[16];
         matTranslate(b.x, b.y, b.z, T);

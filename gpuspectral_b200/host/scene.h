@@ -58,6 +58,7 @@ struct Scene {
     std::vector<gsb_smooth_floor_bsdf> smoothFloorBSDFs;
     std::vector<gsb_rough_floor_bsdf> roughFloorBSDFs;
     std::vector<gsb_rough_plastic_bsdf> roughPlasticBSDFs;
+    std::vector<gsb_rough_dielectric_bsdf> roughDielectricBSDFs;   // extension (no reference counterpart)
     std::vector<std::string> warnings;
 
     int addMaterial(const Material& m) { materials.push_back(m); return (int)materials.size() - 1; }
@@ -71,6 +72,8 @@ struct Scene {
     uint32_t addSmoothFloorBSDF(const gsb_smooth_floor_bsdf& b) { smoothFloorBSDFs.push_back(b); return GSB_BSDF_HANDLE(GSB_BSDF_SMOOTH_FLOOR, smoothFloorBSDFs.size() - 1); }
     uint32_t addRoughFloorBSDF(const gsb_rough_floor_bsdf& b) { roughFloorBSDFs.push_back(b); return GSB_BSDF_HANDLE(GSB_BSDF_ROUGH_FLOOR, roughFloorBSDFs.size() - 1); }
     uint32_t addRoughPlasticBSDF(const gsb_rough_plastic_bsdf& b) { roughPlasticBSDFs.push_back(b); return GSB_BSDF_HANDLE(GSB_BSDF_ROUGH_PLASTIC, roughPlasticBSDFs.size() - 1); }
+
+    uint32_t addRoughDielectricBSDF(const gsb_rough_dielectric_bsdf& b) { roughDielectricBSDFs.push_back(b); return GSB_BSDF_HANDLE(GSB_BSDF_ROUGH_DIELECTRIC, roughDielectricBSDFs.size() - 1); }
 
     // Adds the object and, when its material emits, one world-space TriangleLight per mesh
     // triangle (Loader.cpp:310-330).

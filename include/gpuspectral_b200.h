@@ -58,7 +58,11 @@ enum {
     GSB_BSDF_SMOOTH_FLOOR = 5,
     GSB_BSDF_ROUGH_FLOOR = 6,
     GSB_BSDF_ROUGH_PLASTIC = 7,
-    GSB_BSDF_TYPE_COUNT = 8
+    /* Extension: not in BSDF.inc.  The reference only has the dead include of a rough dielectric (engine/Loader.cpp:88-143
+     * never instantiates one); north_star lists it, so it is built against Mitsuba's `roughdielectric` semantics
+     * (GGX microfacet reflection + refraction, Walter et al. 2007) with the checker's own restatement as the oracle. */
+    GSB_BSDF_ROUGH_DIELECTRIC = 8,
+    GSB_BSDF_TYPE_COUNT = 9
 };
 
 /* BSDF handle = type<<16 | index (renderer/Scene.h:84-97, pt_common.glsl:32-42). */
@@ -78,6 +82,8 @@ typedef struct gsb_rough_plastic_bsdf {
     float diffuse[3]; float iorIn; float iorOut; float R0; float alpha; int32_t hasTexture;
 } gsb_rough_plastic_bsdf;                                                                                       /* 32 B */
 typedef struct gsb_rough_floor_bsdf { float diffuse[3]; float R0; float alpha; } gsb_rough_floor_bsdf;         /* 20 B */
+/* extension (no reference struct): GGX roughness alpha as in Mitsuba, no sqrt(2) rescale */
+typedef struct gsb_rough_dielectric_bsdf { float iorIn; float iorOut; float alpha; int32_t pad; } gsb_rough_dielectric_bsdf; /* 16 B */
 
 /* renderer/Scene.h:106-109: world-space triangle light, 64 B. radiance[3] unused. */
 typedef struct gsb_triangle_light { float positions[3][4]; float radiance[4]; } gsb_triangle_light;

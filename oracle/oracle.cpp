@@ -167,6 +167,7 @@ struct or_scene {
     std::vector<gsb_smooth_floor_bsdf> smoothFloor;
     std::vector<gsb_rough_floor_bsdf> roughFloor;
     std::vector<gsb_rough_plastic_bsdf> roughPlastic;
+    std::vector<gsb_rough_dielectric_bsdf> roughDielectric;   // extension, see roughDielectricSample
     std::vector<gsb_triangle_light> lights;
     float eye[3] = {0, 0, 0};
     float view[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
@@ -830,8 +831,87 @@ void roughFloorEval(const gsb_rough_floor_bsdf& b, vec3 wo, vec3 wi, BSDFOutput&
     res.isDelta = false;
 }
 
-// isTransimissionBSDF, :620-627
-inline bool isTransmission(uint32_t type) { return type == GSB_BSDF_SMOOTH_DIELECTRIC; }
+// RoughDielectric — extension with no counterpart in rayhit.rchit (the reference only carries a dead include,
+// engine/Loader.cpp:88-143).  Restates Walter, Marschner, Li & Torrance, "Microfacet Models for Refraction through
+// Rough Surfaces" (EGSR 2007): GGX D (eq. 33), the reference shader's ggxMask as G, reflection term eq. 20,
+// transmission term eq. 21 with the half-vector Jacobian of eq. 17, written for a path that walks against the light
+// (wo back along the path, light arriving along wi), hence the (no/nt)^2 factor of the smooth dielectric (:362-404).
+// Draw order: two uniforms for the half vector (eq. 35-36), then one for the lobe.  Parity for this type is
+// unpinned by construction: this restatement is the only oracle.
+vec3 sampleHalfGGX(Rng& rng, float alpha) {
+    float ux = rng.randUniform();
+    float uy = rng.randUniform();
+    float phi = 2.0f * kPi * ux;
+    float tan2 = alpha * alpha * uy / (1.0f - uy);
+    float cost = 1.0f / std::sqrt(1.0f + tan2);
+    float sint = std::sqrt(std::fmax(0.0f, 1.0f - cost * cost));
+    return vec3(std::cos(phi) * sint, std::sin(phi) * sint, cost);
+}
+void roughDielectricInvalid(vec3 wo, vec3& wi, BSDFOutput& res) {
+    wi = vec3(-wo.x, -wo.y, wo.z);
+    res.bsdf = vec3(0.0f);
+    res.pdf = 0.0f;
+    res.isDelta = false;
+}
+void roughDielectricSample(const gsb_rough_dielectric_bsdf& b, Rng& rng, vec3 wo, vec3& wi, BSDFOutput& res) {
+    const bool entering = wo.z > 0.0f;
+    const float no = entering ? b.iorOut : b.iorIn;
+    const float nt = entering ? b.iorIn : b.iorOut;
+    vec3 wh = sampleHalfGGX(rng, b.alpha);
+    if (!entering) wh = wh * -1.0f;
+    const float u = rng.randUniform();
+    const float cosI = dot(wo, wh);
+    const float D = ggxD(wh, b.alpha);
+    if (!(cosI > 0.0f) || !(D > 0.0f)) { roughDielectricInvalid(wo, wi, res); return; }
+    const float Fr = fresnelC(cosI, no, nt);
+    res.isDelta = false;
+    if (u < Fr) {
+        wi = normalize(-wo + 2.0f * cosI * wh);
+        if (!(wi.z * wo.z > 0.0f)) { roughDielectricInvalid(wo, wi, res); return; }
+        res.bsdf = vec3(Fr * D * ggxMask(wo, wi, b.alpha) / (4.0f * std::fabs(wi.z) * std::fabs(wo.z)));
+        res.pdf = Fr * D * std::fabs(wh.z) / (4.0f * cosI);
+    } else {
+        const float eta = no / nt;
+        const float cosT2 = 1.0f - eta * eta * (1.0f - cosI * cosI);
+        wi = normalize(-eta * wo + (eta * cosI - std::sqrt(std::fmax(cosT2, 0.0f))) * wh);
+        const float cosO = dot(wi, wh);
+        if (!(wi.z * wo.z < 0.0f) || !(cosO < 0.0f)) { roughDielectricInvalid(wo, wi, res); return; }
+        const float denom = no * cosI + nt * cosO;
+        const float jac = std::fabs(cosO) / (denom * denom);
+        res.bsdf = vec3((1.0f - Fr) * D * ggxMask(wo, wi, b.alpha) * cosI * no * no * jac / (std::fabs(wi.z) * std::fabs(wo.z)));
+        res.pdf = (1.0f - Fr) * D * std::fabs(wh.z) * nt * nt * jac;
+    }
+}
+void roughDielectricEval(const gsb_rough_dielectric_bsdf& b, vec3 wo, vec3 wi, BSDFOutput& res) {
+    const bool entering = wo.z > 0.0f;
+    const float no = entering ? b.iorOut : b.iorIn;
+    const float nt = entering ? b.iorIn : b.iorOut;
+    res.isDelta = false;
+    res.bsdf = vec3(0.0f);
+    res.pdf = 0.0f;
+    const bool reflect = wi.z * wo.z > 0.0f;
+    vec3 wh = reflect ? normalize(wo + wi) : normalize(no * wo + nt * wi);
+    if (dot(wo, wh) < 0.0f) wh = wh * -1.0f;
+    const float cosI = dot(wo, wh), cosO = dot(wi, wh);
+    const float D = ggxD(wh, b.alpha);
+    if (!(cosI > 0.0f) || !(D > 0.0f) || wi.z == 0.0f || wo.z == 0.0f) return;
+    if (entering ? wh.z <= 0.0f : wh.z >= 0.0f) return;
+    const float Fr = fresnelC(cosI, no, nt);
+    if (reflect) {
+        res.bsdf = vec3(Fr * D * ggxMask(wo, wi, b.alpha) / (4.0f * std::fabs(wi.z) * std::fabs(wo.z)));
+        res.pdf = Fr * D * std::fabs(wh.z) / (4.0f * cosI);
+    } else {
+        if (!(cosO < 0.0f)) return;
+        const float denom = no * cosI + nt * cosO;
+        if (denom == 0.0f) return;
+        const float jac = std::fabs(cosO) / (denom * denom);
+        res.bsdf = vec3((1.0f - Fr) * D * ggxMask(wo, wi, b.alpha) * cosI * no * no * jac / (std::fabs(wi.z) * std::fabs(wo.z)));
+        res.pdf = (1.0f - Fr) * D * std::fabs(wh.z) * nt * nt * jac;
+    }
+}
+
+// isTransimissionBSDF, :620-627 (+ the rough dielectric extension)
+inline bool isTransmission(uint32_t type) { return type == GSB_BSDF_SMOOTH_DIELECTRIC || type == GSB_BSDF_ROUGH_DIELECTRIC; }
 
 // sampleBSDF dispatch, :630-641
 void sampleBSDF(const or_scene& s, uint32_t handle, Rng& rng, vec3 wo, vec3& wi, BSDFOutput& res) {
@@ -845,6 +925,7 @@ void sampleBSDF(const or_scene& s, uint32_t handle, Rng& rng, vec3 wo, vec3& wi,
         case GSB_BSDF_SMOOTH_FLOOR: smoothFloorSample(s.smoothFloor[idx], rng, wo, wi, res); break;
         case GSB_BSDF_ROUGH_FLOOR: roughFloorSample(s.roughFloor[idx], rng, wo, wi, res); break;
         case GSB_BSDF_ROUGH_PLASTIC: roughPlasticSample(s.roughPlastic[idx], rng, wo, wi, res); break;
+        case GSB_BSDF_ROUGH_DIELECTRIC: roughDielectricSample(s.roughDielectric[idx], rng, wo, wi, res); break;
     }
 }
 
@@ -860,6 +941,7 @@ void evalBSDF(const or_scene& s, uint32_t handle, vec3 wo, vec3 wi, BSDFOutput& 
         case GSB_BSDF_SMOOTH_FLOOR: smoothFloorEval(s.smoothFloor[idx], wo, wi, res); break;
         case GSB_BSDF_ROUGH_FLOOR: roughFloorEval(s.roughFloor[idx], wo, wi, res); break;
         case GSB_BSDF_ROUGH_PLASTIC: roughPlasticEval(s.roughPlastic[idx], wo, wi, res); break;
+        case GSB_BSDF_ROUGH_DIELECTRIC: roughDielectricEval(s.roughDielectric[idx], wo, wi, res); break;
     }
 }
 
@@ -873,6 +955,7 @@ size_t bsdfCount(const or_scene& s, uint32_t type) {
         case GSB_BSDF_SMOOTH_FLOOR: return s.smoothFloor.size();
         case GSB_BSDF_ROUGH_FLOOR: return s.roughFloor.size();
         case GSB_BSDF_ROUGH_PLASTIC: return s.roughPlastic.size();
+        case GSB_BSDF_ROUGH_DIELECTRIC: return s.roughDielectric.size();
     }
     return 0;
 }
@@ -1192,6 +1275,7 @@ int or_scene_set_bsdfs(or_scene* s, uint32_t type, const void* params, uint32_t 
         case GSB_BSDF_SMOOTH_FLOOR: OR_ASSIGN(smoothFloor, gsb_smooth_floor_bsdf)
         case GSB_BSDF_ROUGH_FLOOR: OR_ASSIGN(roughFloor, gsb_rough_floor_bsdf)
         case GSB_BSDF_ROUGH_PLASTIC: OR_ASSIGN(roughPlastic, gsb_rough_plastic_bsdf)
+        case GSB_BSDF_ROUGH_DIELECTRIC: OR_ASSIGN(roughDielectric, gsb_rough_dielectric_bsdf)
     }
 #undef OR_ASSIGN
     return 1;

@@ -102,7 +102,7 @@ class OracleScene:
         o = OracleScene()
         for i in range(scene.mesh_count):
             o.add_mesh(*scene.mesh(i))
-        for t in range(8):
+        for t in range(9):   # 8 reference types + the rough dielectric extension
             raw, n = scene.bsdfs(t)
             o.set_bsdfs(t, raw, n)
         lights, nl = scene.lights

@@ -36,7 +36,8 @@ def test_host_exports_every_declared_symbol(gsb):
 
 def test_record_layouts_match_reference(gsb):
     # renderer/Scene.h:29-82 sizes (scalar block layout), TriangleLight 64 B, Ray 32 B
-    assert gsb.BSDF_STRIDES == (16, 8, 8, 24, 44, 16, 20, 32)
+    assert gsb.BSDF_STRIDES[:8] == (16, 8, 8, 24, 44, 16, 20, 32)
+    assert gsb.BSDF_STRIDES[8] == 16 and gsb.BSDF_TYPE_COUNT == 9      # the rough dielectric extension
     from gpuspectral_b200 import _native as N
     assert C.sizeof(N.TriangleLight) == 64 and C.sizeof(N.Ray) == 32 and C.sizeof(N.Instance) == 88
     assert C.sizeof(N.Params) == 16 and C.sizeof(N.Counters) == 64
@@ -99,7 +100,7 @@ def test_xml_scene_equals_builtin(gsb):
     for i in range(na):
         assert np.allclose(list(ia[i].transform), list(ib[i].transform), atol=1e-6)
         assert (ia[i].mesh, ia[i].bsdf, ia[i].twofaced, list(ia[i].emission)) == (ib[i].mesh, ib[i].bsdf, ib[i].twofaced, list(ib[i].emission))
-    for t in range(8):
+    for t in range(9):
         assert a.bsdfs(t) == b.bsdfs(t)
     for m in range(a.mesh_count):
         assert np.array_equal(a.mesh(m)[0], b.mesh(m)[0]) and np.array_equal(a.mesh(m)[1], b.mesh(m)[1])

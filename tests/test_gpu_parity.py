@@ -158,7 +158,7 @@ def _close(a, b, rtol=2e-4, atol=1e-6):
     return ok
 
 
-@pytest.mark.parametrize("btype", range(8))
+@pytest.mark.parametrize("btype", range(9))
 def test_bsdf_sample_and_eval(gsb, orc, ctx, btype):
     import ctypes as C
     import struct
@@ -173,6 +173,7 @@ def test_bsdf_sample_and_eval(gsb, orc, ctx, btype):
         5: [struct.pack("4f", 0.5, 0.5, 0.5, 0.04)],
         6: [struct.pack("5f", 0.5, 0.3, 0.2, 0.04, 0.2)],
         7: [struct.pack("7fi", 1.0, 0.58, 0.13, 1.3, 1.0, 0.017, 0.0707, 0), struct.pack("7fi", 0.43, 0.58, 1.0, 1.5, 1.0, 0.04, 0.4243, 0)],
+        8: [struct.pack("3fi", 1.5, 1.0, 0.15, 0), struct.pack("3fi", 1.33, 1.0, 0.4, 0)],    # rough dielectric (extension)
     }[btype]
     raw = b"".join(recs)
     ctx.set_bsdfs(btype, raw, len(recs))
@@ -294,6 +295,38 @@ def test_progressive_and_stride_equivalence(gsb, orc, ctx):
     ctx.set_params()
     assert np.allclose(a, b, rtol=1e-5, atol=1e-6)
     assert np.allclose(a, c, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ["cornell", "gallery"])
+def test_full_size_properties(gsb, orc, ctx, name):
+    """BASELINE.json's frame size (1920x1080, depth 8), where the oracle would take minutes: size-independent
+    properties instead.  Every pixel receives exactly spp samples; one call, two progressive calls and the two strided
+    shards of a 2-GPU run give the same image; more slots than pixels (work stealing across samples) changes nothing;
+    the frame mean agrees with a small oracle render of the same scene within its sampling error."""
+    s, o = upload_pair(gsb, orc, ctx, name)
+    w, h, spp = 1920, 1080, 8
+    ctx.set_params(max_depth=8)
+    o.set_params(max_depth=8)
+    ctx.render(w, h, 0, 0); ctx.clear(); ctx.reset_counters()
+    ctx.render(w, h, 0, spp)
+    a = ctx.read_hdr().copy()
+    c = ctx.counters()
+    assert c["paths"] == w * h * spp
+    assert 1.0 <= c["extension_rays"] / c["paths"] <= 9.0
+    ptr, nbytes = ctx.device_sum_ptr()
+    assert nbytes == w * h * 16
+    assert np.isfinite(a).all() and np.all(a[..., 3] == 1.0) and a[..., :3].min() >= 0.0
+    ctx.clear(); ctx.render(w, h, 0, spp // 2); ctx.render(w, h, spp // 2, spp // 2); b = ctx.read_hdr().copy()
+    ctx.clear(); ctx.render(w, h, 0, spp // 2, 2); ctx.render(w, h, 1, spp // 2, 2); d = ctx.read_hdr().copy()
+    ctx.set_params()
+    # float addition order differs (atomics): a few ulp of the per-pixel sum
+    assert np.allclose(a, b, rtol=2e-5, atol=1e-6)
+    assert np.allclose(a, d, rtol=2e-5, atol=1e-6)
+    # frame mean against the oracle at 1/100 of the pixels (same camera, so the same image up to resolution)
+    ref, _, _ = o.render(192, 108, 0, spp)
+    o.set_params()
+    m_gpu, m_ref = a[..., :3].mean(), ref[..., :3].mean()
+    assert abs(m_gpu - m_ref) < 0.03 * m_ref + 1e-4, (m_gpu, m_ref)
 
 
 def test_ldr_encode(gsb, orc, ctx):
