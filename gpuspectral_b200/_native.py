@@ -101,6 +101,7 @@ HOST_API = {
     "gsbh_last_error": (C.c_char_p, []),
     "gsbh_scene_load_xml": (_P, [C.c_char_p]),
     "gsbh_scene_load_xml_string": (_P, [C.c_char_p, C.c_char_p]),
+    "gsbh_scene_load_gltf": (_P, [C.c_char_p]),
     "gsbh_scene_builtin": (_P, [C.c_char_p, C.POINTER(C.c_int), C.c_int]),
     "gsbh_scene_free": (None, [_P]),
     "gsbh_scene_mesh_count": (C.c_uint32, [_P]),

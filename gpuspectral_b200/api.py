@@ -63,6 +63,15 @@ class Scene:
         return Scene(N.host.gsbh_scene_load_xml(str(path).encode()))
 
     @staticmethod
+    def load_gltf(path):
+        return Scene(N.host.gsbh_scene_load_gltf(str(path).encode()))
+
+    @staticmethod
+    def load(path):
+        """Mitsuba XML or glTF (.gltf / .glb), by extension."""
+        return Scene.load_gltf(path) if str(path).lower().endswith((".gltf", ".glb")) else Scene.load_xml(path)
+
+    @staticmethod
     def from_xml_string(xml, base_dir="."):
         return Scene(N.host.gsbh_scene_load_xml_string(xml.encode(), str(base_dir).encode()))
 

@@ -38,6 +38,12 @@ gsbh_scene* gsbh_scene_load_xml(const char* path) {
     return s;
 }
 
+gsbh_scene* gsbh_scene_load_gltf(const char* path) {
+    gsbh_scene* s = nullptr;
+    guarded([&] { s = new gsbh_scene{gsbhost::loadGltfScene(path)}; });
+    return s;
+}
+
 gsbh_scene* gsbh_scene_load_xml_string(const char* xml, const char* base_dir) {
     gsbh_scene* s = nullptr;
     guarded([&] { s = new gsbh_scene{gsbhost::loadMitsubaSceneFromString(xml, base_dir ? base_dir : ".")}; });

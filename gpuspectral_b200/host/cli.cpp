@@ -14,7 +14,7 @@ using namespace gsbhost;
 
 static void usage() {
     std::fprintf(stderr,
-                 "usage: gsb_render (<scene.xml> | --builtin cornell|gallery|field) [--size WxH] [--spp N]\n"
+                 "usage: gsb_render (<scene.xml | scene.gltf | scene.glb> | --builtin cornell|gallery|field) [--size WxH] [--spp N]\n"
                  "                  [--max-depth D] [--device I] [--hdr out.pfm] [--ldr out.png]\n");
 }
 
@@ -37,7 +37,7 @@ int main(int argc, char** argv) {
     }
     if (xml.empty() && builtin.empty()) { usage(); return 2; }
     try {
-        Scene scene = !xml.empty() ? loadMitsubaScene(xml)
+        Scene scene = !xml.empty() ? ((xml.size() > 4 && (xml.rfind(".gltf") == xml.size() - 5 || xml.rfind(".glb") == xml.size() - 4)) ? loadGltfScene(xml) : loadMitsubaScene(xml))
                       : builtin == "gallery" ? makeBsdfGallery()
                       : builtin == "field" ? makeInstancedField(1234, 16, 7, 13)
                                            : makeCornellBox();

@@ -91,6 +91,8 @@ struct Scene {
 // Throws std::runtime_error on unreadable input.
 Scene loadMitsubaScene(const std::string& xmlPath);
 MeshData loadObjMesh(const std::string& objPath);
+// glTF 2.0 (.gltf / .glb), see gltf.cpp.  Throws std::runtime_error on unreadable input.
+Scene loadGltfScene(const std::string& path);
 
 MeshData makeRectangle();                       // assets/rect.obj equivalent (2 triangles, z = 0, normal +z)
 MeshData makeCube();                            // assets/box.obj equivalent (12 triangles, [-1,1]^3)

@@ -24,6 +24,9 @@ GSB_API const char* gsbh_last_error(void);
 /* Mitsuba XML (0.5 / 2 dialects) with obj / rectangle / cube shapes. NULL on failure. */
 GSB_API gsbh_scene* gsbh_scene_load_xml(const char* path);
 GSB_API gsbh_scene* gsbh_scene_load_xml_string(const char* xml, const char* base_dir);
+/* glTF 2.0 (.gltf with external or data-URI buffers, .glb): triangle meshes, node transforms, the first perspective
+ * camera, pbrMetallicRoughness factors mapped onto the shader's BSDFs (host/gltf.cpp). NULL on failure. */
+GSB_API gsbh_scene* gsbh_scene_load_gltf(const char* path);
 /* Built-in scenes: "cornell" | "gallery" | "field" (params: seed, unique meshes, subdiv, grid n;
  * missing trailing params take defaults 1234, 16, 7, 13). NULL on failure. */
 GSB_API gsbh_scene* gsbh_scene_builtin(const char* name, const int* params, int nparams);

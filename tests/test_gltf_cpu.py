@@ -1,0 +1,134 @@
+"""glTF 2.0 input (host/gltf.cpp) — CPU only: a hand-built scene written as .gltf (external .bin + data URI) and as .glb
+must come out as the same host Scene: meshes un-indexed, node hierarchy composed, materials mapped, emissive triangles
+turned into lights, the camera upright in the reference's ray-generation formula (checked through the oracle)."""
+import base64
+import json
+import struct
+
+import numpy as np
+import pytest
+
+
+def _build(tmp_path, glb):
+    # buffer 0: floor quad (4 vertices + normals, u16 indices); buffer 1: light triangle (positions only) + tetrahedron (u32 indices)
+    quad_p = np.float32([[-2, 0, -2], [2, 0, -2], [2, 0, 2], [-2, 0, 2]])
+    quad_n = np.float32([[0, 1, 0]] * 4)
+    quad_i = np.uint16([0, 2, 1, 0, 3, 2])
+    b0 = quad_p.tobytes() + quad_n.tobytes() + quad_i.tobytes()
+    tri_p = np.float32([[-0.5, 0, -0.5], [0, 0, 0.5], [0.5, 0, -0.5]])        # normal +y; the node turns it to face down
+    tet_p = np.float32([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1]])
+    tet_i = np.uint32([0, 2, 1, 0, 1, 3, 0, 3, 2, 1, 2, 3])
+    b1 = tri_p.tobytes() + tet_p.tobytes() + tet_i.tobytes()
+    views = [
+        {"buffer": 0, "byteOffset": 0, "byteLength": 48}, {"buffer": 0, "byteOffset": 48, "byteLength": 48},
+        {"buffer": 0, "byteOffset": 96, "byteLength": 12},
+        {"buffer": 1, "byteOffset": 0, "byteLength": 36}, {"buffer": 1, "byteOffset": 36, "byteLength": 48},
+        {"buffer": 1, "byteOffset": 84, "byteLength": 48},
+    ]
+    acc = [
+        {"bufferView": 0, "componentType": 5126, "count": 4, "type": "VEC3"},
+        {"bufferView": 1, "componentType": 5126, "count": 4, "type": "VEC3"},
+        {"bufferView": 2, "componentType": 5123, "count": 6, "type": "SCALAR"},
+        {"bufferView": 3, "componentType": 5126, "count": 3, "type": "VEC3"},
+        {"bufferView": 4, "componentType": 5126, "count": 4, "type": "VEC3"},
+        {"bufferView": 5, "componentType": 5125, "count": 12, "type": "SCALAR"},
+    ]
+    doc = {
+        "asset": {"version": "2.0"}, "scene": 0, "scenes": [{"nodes": [0, 1, 4]}],
+        "nodes": [
+            {"name": "floor", "mesh": 0},
+            {"name": "rig", "translation": [0, 3, 0], "children": [2, 3]},
+            {"name": "light", "mesh": 1, "rotation": [1, 0, 0, 0]},                         # 180 deg about x: faces down
+            {"name": "glass", "mesh": 2, "translation": [1, -2.5, 0], "scale": [0.5, 0.5, 0.5]},
+            {"name": "cam", "camera": 0, "translation": [0, 1, 5]},
+        ],
+        "cameras": [{"type": "perspective", "perspective": {"yfov": 0.6, "aspectRatio": 16 / 9, "znear": 0.1}}],
+        "meshes": [
+            {"name": "quad", "primitives": [{"attributes": {"POSITION": 0, "NORMAL": 1}, "indices": 2, "material": 0}]},
+            {"name": "tri", "primitives": [{"attributes": {"POSITION": 3}, "material": 1}]},
+            {"name": "tet", "primitives": [{"attributes": {"POSITION": 4}, "indices": 5, "material": 2},
+                                           {"attributes": {"POSITION": 4}, "indices": 5, "material": 3, "mode": 1}]},
+        ],
+        "materials": [
+            {"pbrMetallicRoughness": {"baseColorFactor": [0.8, 0.2, 0.2, 1], "metallicFactor": 0, "roughnessFactor": 1}},
+            {"emissiveFactor": [1, 1, 0.5], "extensions": {"KHR_materials_emissive_strength": {"emissiveStrength": 10}},
+             "pbrMetallicRoughness": {"metallicFactor": 0}},
+            {"pbrMetallicRoughness": {"metallicFactor": 0, "roughnessFactor": 0.5},
+             "extensions": {"KHR_materials_transmission": {"transmissionFactor": 1}, "KHR_materials_ior": {"ior": 1.33}}},
+            {"pbrMetallicRoughness": {"roughnessFactor": 0.2}},
+        ],
+        "bufferViews": views, "accessors": acc,
+    }
+    if glb:
+        for v in views:
+            if v["buffer"] == 1:
+                v["byteOffset"] += len(b0)
+            v["buffer"] = 0
+        blob = b0 + b1
+        doc["buffers"] = [{"byteLength": len(blob)}]
+        js = json.dumps(doc).encode()
+        js += b" " * (-len(js) % 4)
+        blob += b"\0" * (-len(blob) % 4)
+        path = tmp_path / "scene.glb"
+        body = struct.pack("<II", len(js), 0x4E4F534A) + js + struct.pack("<II", len(blob), 0x004E4942) + blob
+        path.write_bytes(b"glTF" + struct.pack("<II", 2, 12 + len(body)) + body)
+    else:
+        (tmp_path / "floor.bin").write_bytes(b0)
+        doc["buffers"] = [{"uri": "floor.bin", "byteLength": len(b0)},
+                          {"uri": "data:application/octet-stream;base64," + base64.b64encode(b1).decode(), "byteLength": len(b1)}]
+        path = tmp_path / "scene.gltf"
+        path.write_text(json.dumps(doc, indent=1))
+    return path
+
+
+@pytest.mark.parametrize("glb", [False, True])
+def test_gltf_scene_maps_onto_the_host_scene(gsb, orc, tmp_path, glb):
+    s = gsb.Scene.load(_build(tmp_path, glb))
+    assert s.mesh_count == 3
+    pos, nrm = s.mesh(0)
+    assert pos.shape == (6, 3) and np.allclose(nrm, [0, 1, 0])                    # indexed quad -> 2 un-indexed triangles
+    assert np.array_equal(pos[1], [2, 0, 2])                                       # index order kept
+    pos, nrm = s.mesh(1)
+    assert pos.shape == (3, 3) and np.allclose(np.abs(nrm), [0, 1, 0])             # no NORMAL: face normal
+    assert s.mesh(2)[0].shape == (12, 3)
+    inst, n = s.instances
+    assert n == 3                                                                  # the mode-1 primitive is skipped
+    assert any("mode 1" in w for w in s.warnings)
+    T = [np.array(inst[i].transform, np.float32).reshape(4, 4).T for i in range(n)]
+    assert np.allclose(T[0], np.eye(4))
+    assert np.allclose(T[1], [[1, 0, 0, 0], [0, -1, 0, 3], [0, 0, -1, 0], [0, 0, 0, 1]], atol=1e-6)      # parent T * child R
+    assert np.allclose(T[2], [[0.5, 0, 0, 1], [0, 0.5, 0, 0.5], [0, 0, 0.5, 0], [0, 0, 0, 1]], atol=1e-6)
+    # materials: diffuse floor (+ the light's black-ish default), rough dielectric for the transmissive tetrahedron
+    assert [inst[i].bsdf >> 16 for i in range(n)] == [gsb.BSDF_DIFFUSE, gsb.BSDF_DIFFUSE, 8]
+    raw, cnt = s.bsdfs(8)
+    assert cnt == 1 and np.allclose(struct.unpack("3fi", bytes(raw)[:16])[:3], [1.33, 1.0, 0.25])
+    raw, cnt = s.bsdfs(gsb.BSDF_DIFFUSE)
+    assert np.allclose(struct.unpack("3f", bytes(raw)[:12]), [0.8, 0.2, 0.2])
+    assert list(inst[1].emission) == [10.0, 10.0, 5.0] and inst[2].twofaced == 0
+    lights, nl = s.lights
+    assert nl == 1
+    lp = np.array(lights[0].positions, np.float32)[:, :3]
+    assert np.allclose(lp[:, 1], 3.0) and np.allclose(sorted(lp[:, 0]), [-0.5, 0, 0.5])
+    # camera: at (0, 1, 5) looking down -Z, upright, fov on the larger axis
+    w, h = s.film
+    assert (w, h) == (1920, 1080)
+    o = orc.OracleScene.from_host_scene(s)
+    r = o.camera_rays(w, h, np.uint32([w // 2, w // 2, w - 1]), np.uint32([h // 2, 0, h // 2]))
+    assert np.allclose(r["origin"], [0, 1, 5])
+    assert np.allclose(r["dir"][0], [0, 0, -1], atol=2e-3)
+    assert r["dir"][1][1] > 0.25 and abs(r["dir"][1][0]) < 2e-3                    # top row looks up
+    assert r["dir"][2][0] > 0.4                                                    # right column looks right
+    assert np.isclose(np.arctan2(r["dir"][1][1], -r["dir"][1][2]), 0.3, atol=2e-3)  # yfov / 2
+    # and it renders: the floor is lit by the triangle light
+    o.set_params(max_depth=4)
+    img, counters, _ = o.render(64, 36, 0, 4)
+    assert np.isfinite(img).all() and img[..., :3].mean() > 1e-3 and counters["shadow_rays"] > 0
+
+
+def test_gltf_errors_are_reported(gsb, tmp_path):
+    p = tmp_path / "broken.gltf"
+    p.write_text('{"asset": {"version": "2.0"}, "scenes": [{"nodes": [0]}], "nodes": [{"mesh": 3}]}')
+    with pytest.raises(gsb.GsbError):
+        gsb.Scene.load(p)
+    with pytest.raises(gsb.GsbError):
+        gsb.Scene.load(tmp_path / "missing.glb")
