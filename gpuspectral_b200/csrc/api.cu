@@ -216,12 +216,19 @@ __global__ void k_testSampleLight(SceneDev sc, const float* pos, const uint32_t*
 }
 
 // device scratch that frees itself
+// Temporary device buffers of one API call.  With a stream they come from the stream-ordered pool (no device-wide
+// synchronisation in cudaFree, and the pool keeps the memory: see the release threshold set in gsb_create).
 struct Scratch {
     std::vector<void*> ptrs;
+    cudaStream_t stream = nullptr;
+    bool ordered = false;
+    Scratch() {}
+    explicit Scratch(cudaStream_t s) : stream(s), ordered(true) {}
     template <class T>
     T* alloc(size_t count) {
         void* p = nullptr;
-        GSB_CUDA(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
+        if (ordered) GSB_CUDA(cudaMallocAsync(&p, std::max<size_t>(count, 1) * sizeof(T), stream));
+        else GSB_CUDA(cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T)));
         ptrs.push_back(p);
         return (T*)p;
     }
@@ -232,7 +239,10 @@ struct Scratch {
         return p;
     }
     ~Scratch() {
-        for (void* p : ptrs) cudaFree(p);
+        for (void* p : ptrs) {
+            if (ordered) cudaFreeAsync(p, stream);
+            else cudaFree(p);
+        }
     }
 };
 
@@ -304,6 +314,16 @@ gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx) {
         gsb_context* ctx = new gsb_context();
         ctx->device = device_ordinal;
         GSB_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        {
+            // keep freed stream-ordered allocations (BVH build temporaries, read-back staging) in the pool instead of
+            // handing them back to the driver at every synchronisation
+            cudaMemPool_t pool = nullptr;
+            if (cudaDeviceGetDefaultMemPool(&pool, device_ordinal) == cudaSuccess) {
+                unsigned long long keep = ~0ull;
+                cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+            }
+            cudaGetLastError();
+        }
         ensureStats(ctx);
         if (const char* e = getenv("GSB_GRAPH")) ctx->useGraphLoop = atoi(e) != 0;
         if (const char* e = getenv("GSB_REFILL")) {
@@ -623,7 +643,7 @@ static gsb_status readImage(gsb_context* ctx, float* hdr, uint8_t* ldr) {
         Bind bind(ctx->device);
         drain(ctx);
         const uint32_t npix = ctx->width * ctx->height;
-        Scratch sc;
+        Scratch sc(ctx->stream);
         float4* dHdr = hdr ? sc.alloc<float4>(npix) : nullptr;
         uchar4* dLdr = ldr ? sc.alloc<uchar4>(npix) : nullptr;
         k_resolve<<<(npix + 255) / 256, 256, 0, ctx->stream>>>(ctx->dAccum, npix, dHdr, dLdr);

@@ -1,5 +1,5 @@
 #!/bin/bash
-# r1h pass: parity tests, smoke, benches of the three scenes (+ TLAS refinement A/B on the field), launch list,
+# r1h / r1i pass: parity tests, smoke, benches of the three scenes (+ TLAS refinement A/B on the field), launch list,
 # full ncu of the stage kernels (cornell and field)
 mkdir -p gpurun_out
 timeout 300 python -m pytest tests -m gpu -q -x 2>&1 | tail -15 > gpurun_out/pytest_gpu.log; tail -4 gpurun_out/pytest_gpu.log
