@@ -81,7 +81,8 @@ struct gsb_context {
     float4* dAccum = nullptr;  // rgb = sum of samples, a = samples added
     gsb::WavefrontState wf;
     bool profiling = false;
-    uint32_t targetSlots = 1u << 22;  // paths in flight per wavefront (GSB_SLOTS overrides)
+    uint32_t targetSlots = 1u << 23;  // paths in flight per wavefront (GSB_SLOTS overrides); 8 M x ~230 B = 1.9 GB of state.
+                                      // Measured: 4 M -> 8 M +3..4 % on all three scenes (shorter relative tail of the persistent launches), 16 M flat
     // control word of the persistent traversal kernels (traverse.cuh: traceStream): idle lanes that trigger a refill
     // (bits 0..7, GSB_REFILL), lanes that make a quorum for a traversal phase (8..15, GSB_VOTE; closest-hit kernel only,
     // the any-hit kernel measured best without a quorum), lanes that keep the triangle loop spinning (16..23, GSB_TRIMIN)

@@ -28,7 +28,10 @@
 namespace gsb {
 
 constexpr int kStackSize = 48;      // total traversal stack entries per ray
-constexpr int kSmemStack = 8;       // of which the first kSmemStack live in shared memory (the hot top of the stack)
+#ifndef GSB_SMEM_STACK
+#define GSB_SMEM_STACK 8
+#endif
+constexpr int kSmemStack = GSB_SMEM_STACK;   // of which the first kSmemStack live in shared memory (the hot bottom of the stack)
 constexpr int kTraceBlock = 128;    // every kernel that calls traceRay runs with this block size
 constexpr uint32_t kDirectShift = 29;  // TraceInstance::triOffset16 bits 29..31: triangle count of a node-less mesh
 
@@ -185,7 +188,10 @@ struct WorkRange {
     uint32_t next = 0;         // base of the chunk reserved ahead; valid when haveNext
     bool haveNext = false;
     bool exhausted = false;    // the counter has passed `total`: nothing beyond [cur, end) will come
-    static constexpr uint32_t kChunk = 64;
+#ifndef GSB_WORK_CHUNK
+#define GSB_WORK_CHUNK 64
+#endif
+    static constexpr uint32_t kChunk = GSB_WORK_CHUNK;
 
     GSB_D void reserve(uint32_t* counter, uint32_t total) {
         if (haveNext || exhausted) return;

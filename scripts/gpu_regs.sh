@@ -4,7 +4,8 @@ mkdir -p gpurun_out
 for v in $VARIANTS; do
   k=${v%%=*}; n=${v##*=}
   make -C gpuspectral_b200 clean > /dev/null
-  make -C gpuspectral_b200 EXTRA_DEFS=-DGSB_${k}_MIN_BLOCKS=$n > /dev/null 2>&1 || { echo "$v: build failed"; continue; }
+  if [ $k = SMEM_STACK ]; then D=-DGSB_SMEM_STACK=$n; elif [ $k = WORK_CHUNK ]; then D=-DGSB_WORK_CHUNK=$n; else D=-DGSB_${k}_MIN_BLOCKS=$n; fi
+  make -C gpuspectral_b200 EXTRA_DEFS=$D > /dev/null 2>&1 || { echo "$v: build failed"; continue; }
   grep -A3 "k_extendILb0\|k_shadeILi0" gpuspectral_b200/build/wavefront.ptxas.log | grep "Used\|spill" | tr '\n' ' '; echo
   for sc in cornell ${SCENES}; do
     if [ $sc = field ]; then A="--steps 3 --spp-per-step 16"; elif [ $sc = gallery ]; then A="--steps 3 --spp-per-step 32"; else A="--steps 3 --spp-per-step 64"; fi
