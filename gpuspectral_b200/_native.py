@@ -80,6 +80,8 @@ CORE_API = {
     "gsb_read_hdr": (C.c_int, [_P, _f32p]),
     "gsb_read_ldr": (C.c_int, [_P, C.POINTER(C.c_uint8)]),
     "gsb_device_sum_ptr": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_size_t)]),
+    "gsb_read_sum": (C.c_int, [_P, C.POINTER(C.c_float)]),
+    "gsb_write_sum": (C.c_int, [_P, C.c_uint32, C.c_uint32, C.POINTER(C.c_float)]),
     "gsb_get_counters": (C.c_int, [_P, C.POINTER(Counters)]),
     "gsb_reset_counters": (C.c_int, [_P]),
     "gsb_set_profiling": (C.c_int, [_P, C.c_int]),

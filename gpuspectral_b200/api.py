@@ -156,6 +156,7 @@ class Context:
             _check(N.core.gsb_create(device, C.byref(h)), "gsb_create")
             self._c = h
         self._mesh_map = []
+        self._size = None
 
     def close(self):
         c, self._c = getattr(self, "_c", None), None
@@ -236,20 +237,39 @@ class Context:
     def clear(self):
         _check(N.core.gsb_clear(self._c), "gsb_clear")
 
+    def _film(self, what):
+        if self._size is None:
+            raise GsbError(f"{what}: nothing rendered yet")
+        return self._size
+
     def synchronize(self):
         _check(N.core.gsb_synchronize(self._c), "gsb_synchronize")
 
     def read_hdr(self, out=None):
-        w, h = self._size
+        w, h = self._film("gsb_read_hdr")
         img = out if out is not None else np.empty((h, w, 4), np.float32)
         _check(N.core.gsb_read_hdr(self._c, _fp(img)), "gsb_read_hdr")
         return img
 
     def read_ldr(self):
-        w, h = self._size
+        w, h = self._film("gsb_read_ldr")
         img = np.empty((h, w, 4), np.uint8)
         _check(N.core.gsb_read_ldr(self._c, img.ctypes.data_as(C.POINTER(C.c_uint8))), "gsb_read_ldr")
         return img
+
+    def read_sum(self):
+        """Checkpoint: the raw accumulation buffer (H, W, 4) = rgb sums + sample counts."""
+        w, h = self._film("gsb_read_sum")
+        out = np.empty((h, w, 4), np.float32)
+        _check(N.core.gsb_read_sum(self._c, _fp(out)), "gsb_read_sum")
+        return out
+
+    def write_sum(self, sums):
+        """Resume: replaces the accumulation buffer by a checkpoint taken with read_sum (any context, any GPU)."""
+        sums = np.ascontiguousarray(sums, np.float32)
+        h, w = sums.shape[:2]
+        _check(N.core.gsb_write_sum(self._c, w, h, _fp(sums)), "gsb_write_sum")
+        self._size = (w, h)
 
     def device_sum_ptr(self):
         p, n = C.c_void_p(), C.c_size_t()

@@ -657,6 +657,31 @@ static gsb_status readImage(gsb_context* ctx, float* hdr, uint8_t* ldr) {
 gsb_status gsb_read_hdr(gsb_context* ctx, float* out_rgba) { return readImage(ctx, out_rgba, nullptr); }
 gsb_status gsb_read_ldr(gsb_context* ctx, uint8_t* out_rgba8) { return readImage(ctx, nullptr, out_rgba8); }
 
+gsb_status gsb_read_sum(gsb_context* ctx, float* out_rgba_sum) {
+    if (!ctx || !out_rgba_sum) return fail(GSB_ERR_INVALID, "gsb_read_sum: null argument");
+    if (!ctx->dAccum) return fail(GSB_ERR_STATE, "gsb_read_sum: nothing rendered yet");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        drain(ctx);
+        GSB_CUDA(cudaMemcpyAsync(out_rgba_sum, ctx->dAccum, (size_t)ctx->width * ctx->height * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_write_sum(gsb_context* ctx, uint32_t width, uint32_t height, const float* rgba_sum) {
+    if (!ctx || !rgba_sum) return fail(GSB_ERR_INVALID, "gsb_write_sum: null argument");
+    if (width == 0 || height == 0 || (uint64_t)width * height > (1ull << 28)) return fail(GSB_ERR_INVALID, "gsb_write_sum: bad frame size");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        drain(ctx);
+        renderImpl(ctx, width, height, 0, 0, 1);   // count 0: (re)allocates the frame, renders nothing
+        GSB_CUDA(cudaMemcpyAsync(ctx->dAccum, rgba_sum, (size_t)width * height * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        return GSB_OK;
+    });
+}
+
 gsb_status gsb_device_sum_ptr(gsb_context* ctx, void** out_ptr, size_t* out_bytes) {
     if (!ctx || !out_ptr || !out_bytes) return fail(GSB_ERR_INVALID, "gsb_device_sum_ptr: null argument");
     if (!ctx->dAccum) return fail(GSB_ERR_STATE, "gsb_device_sum_ptr: nothing rendered yet");

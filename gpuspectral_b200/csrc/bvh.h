@@ -30,7 +30,7 @@ struct DeviceBvh {
 constexpr float kBoxPadRel = 1.0f / 32768.0f;
 
 // Bottom level over a triangle soup (3 float4 per triangle, object space).  Leaf record =
-// 3 x float4 (v0.xyz | primId bits, v1.xyz, v2.xyz).
+// 3 copies (one per dominant ray axis, pre-rotated) of 3 x float4 (v0.xyz | primId bits, v1.xyz, v2.xyz) = 144 B.
 void buildBlas(const float4* dVertices, uint32_t numTriangles, cudaStream_t stream, DeviceBvh& out);
 
 // Top level over instances.  hostLo/hostHi: padded world bounds (3 floats each) per instance;

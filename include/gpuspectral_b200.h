@@ -182,6 +182,13 @@ GSB_API gsb_status gsb_read_ldr(gsb_context* ctx, uint8_t* out_rgba8);
 /* Device pointer to the float4 accumulation buffer (rgb = sum of samples, a = number of
  * samples added) for an external reduction across GPUs (NCCL), and its size in bytes. */
 GSB_API gsb_status gsb_device_sum_ptr(gsb_context* ctx, void** out_ptr, size_t* out_bytes);
+/* Checkpoint / resume of a progressive render: the raw accumulation buffer (width x height float4: rgb = sum of samples,
+ * a = samples added) out to and in from host memory.  gsb_write_sum (re)sizes the frame like gsb_render does and replaces
+ * its contents; continuing with gsb_render(first_sample = samples already in the checkpoint) gives the image an
+ * uninterrupted render would have given.  The reference keeps its running mean in the RGBA32F image of
+ * PathTracer.cpp:5-7 and has no way to save it. */
+GSB_API gsb_status gsb_read_sum(gsb_context* ctx, float* out_rgba_sum);
+GSB_API gsb_status gsb_write_sum(gsb_context* ctx, uint32_t width, uint32_t height, const float* rgba_sum);
 GSB_API gsb_status gsb_get_counters(gsb_context* ctx, gsb_counters* out);
 GSB_API gsb_status gsb_reset_counters(gsb_context* ctx);
 /* Device time (ms, CUDA events on the context's stream) of the last gsb_render, split by

@@ -365,3 +365,27 @@ def test_errors_are_status_codes(gsb, ctx):
     with pytest.raises(gsb.GsbError):
         c2.mesh_create(np.zeros((4, 3), np.float32), np.zeros((4, 3), np.float32))   # not a multiple of 3
     c2.close()
+
+
+def test_checkpoint_and_resume(gsb, orc, ctx):
+    """gsb_read_sum / gsb_write_sum: 4 samples, checkpoint, a fresh context resumes with 4 more -> the image of an
+    uninterrupted 8-sample render (sum buffers equal up to float addition order, counts exact)."""
+    s, o = upload_pair(gsb, orc, ctx, "cornell")
+    w, h = 200, 120
+    ctx.set_params(max_depth=8)
+    ctx.render(w, h, 0, 0); ctx.clear(); ctx.render(w, h, 0, 8)
+    full = ctx.read_sum()
+    ctx.clear(); ctx.render(w, h, 0, 4)
+    half = ctx.read_sum()
+    ctx.set_params()
+    assert np.all(half[..., 3] == 4.0) and np.all(full[..., 3] == 8.0)
+    with gsb.Context(0) as other:
+        other.upload(s)
+        other.set_params(max_depth=8)
+        other.write_sum(half)
+        other.render(w, h, 4, 4)
+        resumed = other.read_sum()
+        assert np.allclose(resumed, full, rtol=1e-5, atol=1e-6)
+        assert np.allclose(other.read_hdr(), full / full[..., 3:4] * [1, 1, 1, 0] + [0, 0, 0, 1], rtol=1e-5, atol=1e-6)
+    with pytest.raises(gsb.GsbError):
+        gsb.Context(0).read_sum()
