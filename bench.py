@@ -104,6 +104,14 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
+def host_threads():
+    """Every host core this process may run on; torchrun exports OMP_NUM_THREADS=1, which the CPU arm must not inherit."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def run_reference(a, rank, world):
     """The reference has no CPU implementation of this path and its Vulkan path is unavailable on this box, so the
     reference arm is the CPU oracle (oracle/, a restatement of the shaders: kind "port") on all host cores.
@@ -119,12 +127,13 @@ def run_reference(a, rank, world):
     spp = 1
     img = np.zeros((a.height, a.width, 4), np.float32)
     paths = ext = sh = 0
+    ncpu = host_threads()
     threads = 0
     for k in range(a.warmup):
-        o.render(a.width, a.height, k, spp, 1, image=img, sum_mode=True)
+        o.render(a.width, a.height, k, spp, 1, image=img, sum_mode=True, threads=ncpu)
     t0 = time.perf_counter()
     for k in range(a.steps):
-        _, c, threads = o.render(a.width, a.height, a.warmup + k, spp, 1, image=img, sum_mode=True)
+        _, c, threads = o.render(a.width, a.height, a.warmup + k, spp, 1, image=img, sum_mode=True, threads=ncpu)
         paths += c["paths"]; ext += c["extension_rays"]; sh += c["shadow_rays"]
     dt = time.perf_counter() - t0
     val = paths / dt / 1e6
@@ -371,7 +380,7 @@ def run_ours(a, rank, world, local_rank):
         o.render(W, H, 0, 1, sum_mode=True)
         spp = 6
         t0 = time.perf_counter()
-        _, oc, threads = o.render(W, H, 100, spp, sum_mode=True)
+        _, oc, threads = o.render(W, H, 100, spp, sum_mode=True, threads=host_threads())
         dt = time.perf_counter() - t0
         cpu = {"value": oc["paths"] / dt / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
                "mrays_per_s": (oc["extension_rays"] + oc["shadow_rays"]) / dt / 1e6,
