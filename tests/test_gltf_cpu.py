@@ -158,3 +158,56 @@ def test_gltf_scene_renders_like_the_oracle(gsb, orc, tmp_path):
         diff = np.abs(img[..., :3] - want[..., :3]).max(axis=2)
         close = diff <= 2e-3 * np.maximum(want[..., :3].max(axis=2), 0.05)
         assert close.mean() > 0.98 and img[..., :3].mean() > 1e-3
+
+
+def _one_triangle(tmp_path, emissive):
+    """The smallest scene the loaders accept: one triangle facing the camera, lit by nothing or by itself."""
+    p = np.float32([[-1, -1, 0], [1, -1, 0], [0, 1, 0]])
+    mat = {"pbrMetallicRoughness": {"baseColorFactor": [0.5, 0.5, 0.5, 1], "metallicFactor": 0}}
+    if emissive:
+        mat["emissiveFactor"] = [1, 1, 1]
+    doc = {
+        "asset": {"version": "2.0"}, "scene": 0, "scenes": [{"nodes": [0, 1]}],
+        "nodes": [{"mesh": 0}, {"camera": 0, "translation": [0, 0, 4]}],
+        "cameras": [{"type": "perspective", "perspective": {"yfov": 0.8, "aspectRatio": 1.0, "znear": 0.1}}],
+        "meshes": [{"primitives": [{"attributes": {"POSITION": 0}, "material": 0}]}],
+        "materials": [mat],
+        "buffers": [{"uri": "data:application/octet-stream;base64," + base64.b64encode(p.tobytes()).decode(), "byteLength": 36}],
+        "bufferViews": [{"buffer": 0, "byteOffset": 0, "byteLength": 36}],
+        "accessors": [{"bufferView": 0, "componentType": 5126, "count": 3, "type": "VEC3"}],
+    }
+    path = tmp_path / ("lit.gltf" if emissive else "dark.gltf")
+    path.write_text(json.dumps(doc))
+    return path
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("emissive", [False, True])
+def test_smallest_scenes_match_the_oracle(gsb, orc, tmp_path, emissive):
+    """Edge cases of SURVEY 8(a) A9: a scene without any light (numLights == 0, a modulo by zero in the shader; both sides
+    still make the three draws and add nothing) and a one-triangle scene whose only surface is its only light. One mesh,
+    one instance, a node-less BVH: hits exact, ray counts exact, images equal."""
+    s = gsb.Scene.load(_one_triangle(tmp_path, emissive))
+    assert s.lights[1] == (1 if emissive else 0) and s.instances[1] == 1 and s.instanced_triangles == 1
+    o = orc.OracleScene.from_host_scene(s)
+    w = h = 96
+    with gsb.Context(0) as ctx:
+        ctx.upload(s)
+        ys, xs = np.mgrid[0:h, 0:w]
+        rays = o.camera_rays(w, h, xs.ravel(), ys.ravel())
+        got, ref = ctx.trace_batch(rays), o.trace_batch(rays, mode=1)
+        for k in ("inst", "prim", "t", "u", "v"):
+            assert np.array_equal(got[k], ref[k]), k
+        assert 0.05 < (got["inst"] != gsb.NO_HIT).mean() < 0.5
+        ctx.set_params(max_depth=5)
+        o.set_params(max_depth=5)
+        ctx.render(w, h, 0, 0); ctx.clear(); ctx.render(w, h, 0, 8)
+        img, gc = ctx.read_hdr(), ctx.counters()
+        want, oc, _ = o.render(w, h, 0, 8)
+        for k in ("paths", "extension_rays", "shadow_rays"):
+            assert gc[k] == oc[k], k
+        assert np.isfinite(img).all() and np.allclose(img, want, rtol=1e-5, atol=1e-6)
+        if emissive:
+            assert img[..., :3].max() == pytest.approx(1.0, rel=1e-5)      # the triangle shows its own radiance
+        else:
+            assert not img[..., :3].any() and gc["shadow_rays"] == 0
