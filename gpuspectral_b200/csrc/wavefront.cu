@@ -42,6 +42,7 @@ constexpr uint32_t kRetired = 0xffffffffu;
 constexpr uint32_t kFinished = 0x80000000u;  // sampleK bit: the path has ended, its sample waits to be added to the image
 constexpr uint32_t kFlagWasDelta = 1u << 16;
 constexpr uint32_t kFlagCountEmitted = 1u << 17;
+constexpr uint32_t kShadowHasBase = 1u << 31;   // shadowD.w = path slot | this bit when shadowBase holds surface emission
 
 struct RenderArgs {
     uint32_t width, height, npix;
@@ -89,12 +90,12 @@ GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderA
                   V[2] * dir.x + V[6] * dir.y + V[10] * dir.z);
     d.y *= -1.0f;
     o = make_float4(sc.eye[0], sc.eye[1], sc.eye[2], 0.0f);
-    dOut = make_float4(d.x, d.y, d.z, 0.0f);
+    dOut = make_float4(d.x, d.y, d.z, __uint_as_float(kFlagCountEmitted));   // .w: depth 0, wasDelta 0, countEmitted 1
     wf.seed[slot] = pcgHash(tea(ra.width * y + x, timestamp));
     wf.rayO[slot] = o;
     wf.rayD[slot] = dOut;
     wf.weightDW[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
-    wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kFlagCountEmitted));  // depth 0, wasDelta 0, countEmitted 1
+    wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     wf.sampleK[slot] = pixel;
     pixelOut = pixel;
 }
@@ -273,7 +274,7 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
                 continue;
             }
         }
-        bool terminate = false, needShadow = false;
+        bool terminate = false, needShadow = false, hasBase = false;
         float4 shO, shD, shBase, shNee;
         if (active) {
             const float4 ro = wf.rayO[slot], rd = wf.rayD[slot];
@@ -281,8 +282,7 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
             const uint32_t inst = wf.hitInst[slot];
             uint32_t rng = wf.seed[slot];                                         // rayhit.rchit:668
             float4 wdw = wf.weightDW[slot];
-            float4 res = wf.result[slot];
-            uint32_t flags = __float_as_uint(res.w);
+            uint32_t flags = __float_as_uint(rd.w);
             float3 weight = xyz(wdw);
             const float directWeight = wdw.w;
             const uint32_t prim = __float_as_uint(hit.w);
@@ -387,21 +387,24 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
 
             if (needShadow) {
                 shO = make_float4(position.x, position.y, position.z, Ldist - 0.01f);
-                shD = make_float4(L.x, L.y, L.z, __uint_as_float(slot));
-                shBase = make_float4(emitted.x, emitted.y, emitted.z, dwVisible);
-                shNee = make_float4(nee.x, nee.y, nee.z, 0.0f);
-            } else {
+                // surface emission rides along only when there is some (bit 31 of the slot word says so)
+                hasBase = emitted.x != 0.0f || emitted.y != 0.0f || emitted.z != 0.0f;
+                shD = make_float4(L.x, L.y, L.z, __uint_as_float(slot | (hasBase ? kShadowHasBase : 0u)));
+                shBase = make_float4(emitted.x, emitted.y, emitted.z, 0.0f);
+                shNee = make_float4(nee.x, nee.y, nee.z, dwVisible);
+            } else if (emitted.x != 0.0f || emitted.y != 0.0f || emitted.z != 0.0f) {
+                // the running radiance of the sample is touched only by vertices that add to it
                 const float cutoff = sc.params.cutoff;                               // raygen.rgen:60-63
                 if (emitted.x < cutoff && emitted.y < cutoff && emitted.z < cutoff) {
+                    float4 res = wf.result[slot];
                     res.x += emitted.x; res.y += emitted.y; res.z += emitted.z;
+                    wf.result[slot] = res;
                 }
             }
-            res.w = __uint_as_float(flags);
-            wf.result[slot] = res;
             wf.seed[slot] = rng;                                                     // rayhit.rchit:759
             if (!terminate) {
                 wf.rayO[slot] = make_float4(newO.x, newO.y, newO.z, 0.0f);
-                wf.rayD[slot] = make_float4(newD.x, newD.y, newD.z, 0.0f);
+                wf.rayD[slot] = make_float4(newD.x, newD.y, newD.z, __uint_as_float(flags));
                 wf.weightDW[slot] = make_float4(weight.x, weight.y, weight.z, 1.0f);  // directWeight 1 unless the shadow stage finds the light
             }
         }
@@ -410,7 +413,7 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
         if (needShadow) {
             wf.shadowO[sp] = shO;
             wf.shadowD[sp] = shD;
-            wf.shadowBase[sp] = shBase;
+            if (hasBase) wf.shadowBase[sp] = shBase;
             wf.shadowNee[sp] = shNee;
         }
         if (!scanning && pendingCount == 0u) break;
@@ -444,7 +447,7 @@ struct ShadowSource {
         job.dx = d.x; job.dy = d.y; job.dz = d.z;
         job.tmin = 0.01f; job.tmax = o.w;                                            // rayhit.rchit:737-748
         job.tag = i;
-        slot = __float_as_uint(d.w);
+        slot = __float_as_uint(d.w);      // bit 31 (kShadowHasBase) stays in until commit
         traced++;
         return true;
     }
@@ -452,16 +455,18 @@ struct ShadowSource {
     GSB_D void commit(bool have, const HitRecord& hit, uint32_t i) {
         if (!have) return;
         const bool visible = hit.inst == GSB_NO_HIT;
-        const float4 base = wf.shadowBase[i];
+        const bool hasBase = (slot & kShadowHasBase) != 0u;
+        slot &= ~kShadowHasBase;
         float3 emitted = f3(0.0f);
         if (visible) {
             const float4 nee = wf.shadowNee[i];
             emitted = emitted + xyz(nee);                                            // rayhit.rchit:752
-            wf.weightDW[slot].w = base.w;                                            // :786 (neeDone)
+            wf.weightDW[slot].w = nee.w;                                             // :786 (neeDone)
         }
-        emitted = emitted + xyz(base);                                               // :763-768
+        if (hasBase) emitted = emitted + xyz(wf.shadowBase[i]);                      // :763-768
         const float cutoff = sc.params.cutoff;                                       // raygen.rgen:60-63
-        if (emitted.x < cutoff && emitted.y < cutoff && emitted.z < cutoff) {
+        if ((emitted.x != 0.0f || emitted.y != 0.0f || emitted.z != 0.0f) &&
+            emitted.x < cutoff && emitted.y < cutoff && emitted.z < cutoff) {
             float4 res = wf.result[slot];
             res.x += emitted.x; res.y += emitted.y; res.z += emitted.z;
             wf.result[slot] = res;
