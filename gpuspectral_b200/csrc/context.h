@@ -27,11 +27,10 @@ enum { Q_MATERIAL0 = 0, Q_TRACED = GSB_BSDF_TYPE_COUNT, Q_SHADOW = GSB_BSDF_TYPE
 // (+ pixel sample index and the hit record) spread over 16-byte and 4-byte streams.
 struct WavefrontState {
     uint32_t capacity = 0;      // slots allocated
-    float4* rayO = nullptr;     // origin.xyz
-    float4* rayD = nullptr;     // direction.xyz
+    float4* rayO = nullptr;     // origin.xyz, RNG state of the path (payload `seed`) in .w
+    float4* rayD = nullptr;     // direction.xyz, path flags in .w: depth (bits 0-15), wasDelta, countEmitted
     float4* weightDW = nullptr; // weight.xyz, directWeight
-    float4* result = nullptr;   // radiance of the current sample .xyz, flags bits in .w
-    uint32_t* seed = nullptr;
+    float4* result = nullptr;   // radiance of the current sample .xyz; only touched by vertices that add light
     uint32_t* sampleK = nullptr;  // pixel the slot's current path belongs to; bit 31: path finished, add it to the image;
                                   // 0xffffffff = slot retired (no work left)
     float4* hitTUVP = nullptr;    // t, u, v, primitive id bits

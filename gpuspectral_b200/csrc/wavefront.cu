@@ -40,6 +40,9 @@ constexpr int kBlock = kTraceBlock;
 #endif
 constexpr uint32_t kRetired = 0xffffffffu;
 constexpr uint32_t kFinished = 0x80000000u;  // sampleK bit: the path has ended, its sample waits to be added to the image
+#ifndef GSB_LAZY_RESULT
+#define GSB_LAZY_RESULT 0     // 1: k_extend loads a slot's radiance only when its path has ended (a dependent load)
+#endif
 constexpr uint32_t kFlagWasDelta = 1u << 16;
 constexpr uint32_t kFlagCountEmitted = 1u << 17;
 constexpr uint32_t kShadowHasBase = 1u << 31;   // shadowD.w = path slot | this bit when shadowBase holds surface emission
@@ -89,9 +92,9 @@ GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderA
     float3 d = f3(V[0] * dir.x + V[4] * dir.y + V[8] * dir.z, V[1] * dir.x + V[5] * dir.y + V[9] * dir.z,
                   V[2] * dir.x + V[6] * dir.y + V[10] * dir.z);
     d.y *= -1.0f;
-    o = make_float4(sc.eye[0], sc.eye[1], sc.eye[2], 0.0f);
+    // .w: the path's RNG state (raygen.rgen:37)
+    o = make_float4(sc.eye[0], sc.eye[1], sc.eye[2], __uint_as_float(pcgHash(tea(ra.width * y + x, timestamp))));
     dOut = make_float4(d.x, d.y, d.z, __uint_as_float(kFlagCountEmitted));   // .w: depth 0, wasDelta 0, countEmitted 1
-    wf.seed[slot] = pcgHash(tea(ra.width * y + x, timestamp));
     wf.rayO[slot] = o;
     wf.rayD[slot] = dOut;
     wf.weightDW[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
@@ -146,16 +149,24 @@ struct ExtendSource {
         // the slot's state words are loaded together (one memory latency, not a dependent chain); `result` is only
         // needed when the path has ended
         uint32_t p = kRetired;
-        float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = o, res = o;
+        float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = o;
+#if !GSB_LAZY_RESULT
+        float4 res = o;
+#endif
         if (slot != kNoTag) {
             p = wf.sampleK[slot];
             o = wf.rayO[slot];
             d = wf.rayD[slot];
+#if !GSB_LAZY_RESULT
             res = wf.result[slot];
+#endif
         }
         bool live = p != kRetired;
         const bool finished = live && (p & kFinished);
         if (finished) {
+#if GSB_LAZY_RESULT
+            const float4 res = wf.result[slot];
+#endif
             // raygen.rgen:106-108: a NaN sample leaves the image untouched
             if (!(isnan(res.x) || isnan(res.y) || isnan(res.z)))
                 atomicAdd(&ra.accum[p & ~kFinished], make_float4(res.x, res.y, res.z, 1.0f));
@@ -184,7 +195,9 @@ struct ExtendSource {
             prefetchL1(wf.sampleK + ahead);
             prefetchL1(wf.rayO + ahead);
             prefetchL1(wf.rayD + ahead);
+#if !GSB_LAZY_RESULT
             prefetchL1(wf.result + ahead);
+#endif
         }
         if (!live) return false;
         job.ox = o.x; job.oy = o.y; job.oz = o.z;
@@ -280,7 +293,7 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
             const float4 ro = wf.rayO[slot], rd = wf.rayD[slot];
             const float4 hit = wf.hitTUVP[slot];
             const uint32_t inst = wf.hitInst[slot];
-            uint32_t rng = wf.seed[slot];                                         // rayhit.rchit:668
+            uint32_t rng = __float_as_uint(ro.w);                                 // rayhit.rchit:668
             float4 wdw = wf.weightDW[slot];
             uint32_t flags = __float_as_uint(rd.w);
             float3 weight = xyz(wdw);
@@ -401,9 +414,8 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
                     wf.result[slot] = res;
                 }
             }
-            wf.seed[slot] = rng;                                                     // rayhit.rchit:759
             if (!terminate) {
-                wf.rayO[slot] = make_float4(newO.x, newO.y, newO.z, 0.0f);
+                wf.rayO[slot] = make_float4(newO.x, newO.y, newO.z, __uint_as_float(rng));   // rayhit.rchit:759
                 wf.rayD[slot] = make_float4(newD.x, newD.y, newD.z, __uint_as_float(flags));
                 wf.weightDW[slot] = make_float4(weight.x, weight.y, weight.z, 1.0f);  // directWeight 1 unless the shadow stage finds the light
             }
@@ -515,7 +527,7 @@ void allocWavefront(gsb_context* ctx, uint32_t slots) {
     if (wf.capacity >= slots && wf.qCount) return;
     const size_t n = slots;
     ensure(wf.rayO, n); ensure(wf.rayD, n); ensure(wf.weightDW, n); ensure(wf.result, n);
-    ensure(wf.seed, n); ensure(wf.sampleK, n); ensure(wf.hitTUVP, n); ensure(wf.hitInst, n);
+    ensure(wf.sampleK, n); ensure(wf.hitTUVP, n); ensure(wf.hitInst, n);
 
     ensure(wf.shadowO, n); ensure(wf.shadowD, n); ensure(wf.shadowBase, n); ensure(wf.shadowNee, n);
     if (!wf.qCount) ensure(wf.qCount, (size_t)2 * Q_COUNT);
@@ -535,7 +547,7 @@ void launchShade(gsb_context* ctx, const SceneDev& sc, int grid, uint32_t parity
 
 void freeWavefront(gsb_context* ctx) {
     WavefrontState& wf = ctx->wf;
-    void* ptrs[] = {wf.rayO, wf.rayD, wf.weightDW, wf.result, wf.seed, wf.sampleK, wf.hitTUVP, wf.hitInst,
+    void* ptrs[] = {wf.rayO, wf.rayD, wf.weightDW, wf.result, wf.sampleK, wf.hitTUVP, wf.hitInst,
                     wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.qCount, wf.stats};
     for (void* p : ptrs)
         if (p) cudaFree(p);
