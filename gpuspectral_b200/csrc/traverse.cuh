@@ -233,6 +233,7 @@ struct WorkRange {
 };
 
 GSB_D void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+GSB_D void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // Traces a stream of rays with one persistent warp: the traversal loop never waits for the slowest ray of a
 // batch — a lane whose ray is finished hands its result to `src.commit` and gets the next ray from `src.fetch`

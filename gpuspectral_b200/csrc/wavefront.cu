@@ -40,6 +40,12 @@ constexpr int kBlock = kTraceBlock;
 #endif
 constexpr uint32_t kRetired = 0xffffffffu;
 constexpr uint32_t kFinished = 0x80000000u;  // sampleK bit: the path has ended, its sample waits to be added to the image
+#ifndef GSB_SHADE_PREFETCH
+#define GSB_SHADE_PREFETCH 0  // k_shade prefetches its next tile's state: 1 into L1, 2 into L2
+#endif
+#ifndef GSB_SHADE_STREAM
+#define GSB_SHADE_STREAM 0    // 1: k_shade reads the per-slot state with ld.global.cs
+#endif
 #ifndef GSB_LAZY_RESULT
 #define GSB_LAZY_RESULT 0     // 1: k_extend loads a slot's radiance only when its path has ended (a dependent load)
 #endif
@@ -264,6 +270,26 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
             match = hi != GSB_NO_HIT && (__ldg(sc.instBsdf + hi) >> 16) == (uint32_t)TYPE;
         }
         const uint32_t mm = __ballot_sync(0xffffffffu, match);
+#if GSB_SHADE_PREFETCH
+        {
+            // the tile this warp scans next is known (static stride): its state streams start their trip from DRAM
+            // while this tile is shaded
+            const uint32_t nxt = cand + warpsTotal * 32u;
+            if (nxt < slots) {
+#if GSB_SHADE_PREFETCH == 1
+#define GSB_PF prefetchL1
+#else
+#define GSB_PF prefetchL2
+#endif
+                GSB_PF(wf.hitInst + nxt);
+                GSB_PF(wf.rayO + nxt);
+                GSB_PF(wf.rayD + nxt);
+                GSB_PF(wf.hitTUVP + nxt);
+                GSB_PF(wf.weightDW + nxt);
+#undef GSB_PF
+            }
+        }
+#endif
         bool active;
         uint32_t slot = 0;
         if ((uint32_t)__popc(mm) >= directMin) {
@@ -290,11 +316,21 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
         bool terminate = false, needShadow = false, hasBase = false;
         float4 shO, shD, shBase, shNee;
         if (active) {
+#if GSB_SHADE_STREAM
+            // read-once state streams go past L1 (evict-first), which then keeps the scene records the hit points to
+            const float4 ro = __ldcs(wf.rayO + slot), rd = __ldcs(wf.rayD + slot);
+            const float4 hit = __ldcs(wf.hitTUVP + slot);
+#else
             const float4 ro = wf.rayO[slot], rd = wf.rayD[slot];
             const float4 hit = wf.hitTUVP[slot];
+#endif
             const uint32_t inst = wf.hitInst[slot];
             uint32_t rng = __float_as_uint(ro.w);                                 // rayhit.rchit:668
+#if GSB_SHADE_STREAM
+            float4 wdw = __ldcs(wf.weightDW + slot);
+#else
             float4 wdw = wf.weightDW[slot];
+#endif
             uint32_t flags = __float_as_uint(rd.w);
             float3 weight = xyz(wdw);
             const float directWeight = wdw.w;
