@@ -389,3 +389,31 @@ def test_checkpoint_and_resume(gsb, orc, ctx):
         assert np.allclose(other.read_hdr(), full / full[..., 3:4] * [1, 1, 1, 0] + [0, 0, 0, 1], rtol=1e-5, atol=1e-6)
     with pytest.raises(gsb.GsbError):
         gsb.Context(0).read_sum()
+
+
+def test_cli_writes_both_framebuffers(gsb, ctx, tmp_path):
+    """The headless stand-in for the reference's main.cpp: `gsb_render` renders a scene and writes the HDR (PFM) and the
+    LDR (PNG) framebuffer; the HDR file equals what the library returns for the same samples."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "gpuspectral_b200", "lib", "gsb_render")
+    hdr, ldr = tmp_path / "out.pfm", tmp_path / "out.png"
+    r = subprocess.run([exe, "--builtin", "cornell", "--size", "96x64", "--spp", "8", "--max-depth", "6",
+                        "--hdr", str(hdr), "--ldr", str(ldr)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    assert "Mpaths/s" in r.stdout + r.stderr
+    raw = hdr.read_bytes()
+    head = raw.split(b"\n", 3)
+    assert head[0] == b"PF" and head[1].split() == [b"96", b"64"] and float(head[2]) < 0      # little-endian RGB
+    img = np.frombuffer(head[3], "<f4").reshape(64, 96, 3)[::-1]                               # PFM rows run bottom-up
+    assert ldr.read_bytes()[:8] == b"\x89PNG\r\n\x1a\n"
+    ctx.upload(host_scene("cornell"))
+    ctx.set_params(max_depth=6)
+    ctx.render(96, 64, 0, 0); ctx.clear(); ctx.render(96, 64, 0, 8)
+    want = ctx.read_hdr()[..., :3]
+    ctx.set_params()
+    assert np.isfinite(img).all() and img.mean() > 1e-3
+    assert np.allclose(img, want, rtol=1e-4, atol=1e-5)
+    r = subprocess.run([exe, str(tmp_path / "missing.xml")], capture_output=True, text=True, timeout=60)
+    assert r.returncode != 0 and "error" in (r.stdout + r.stderr).lower()
