@@ -21,6 +21,14 @@
 // All shading arithmetic is float32 like the shaders.  RNG draws are sequenced explicitly
 // left to right (GLSL evaluates constructor/call arguments in order; C++ does not).
 //
+// PINNED (everything except the intersection rule above): oracle/_ref/libgsref.so is the reference's own shader text
+// compiled as C++ against the reference's glm (oracle/Makefile, oracle/ref/); tests/test_oracle_vs_reference_cpu.py
+// requires this file to equal it BIT FOR BIT — RNG, every BSDF sample / eval through the reference's own switch, light
+// sampling, camera rays, per-bounce payloads and whole frames (running mean included) — live on >= 1e5 inputs per
+// function, and against frozen outputs of that library (tests/golden/ref_vectors.npz) where the reference is absent.
+// Vector helpers therefore use glm's formulas (normalize = v * (1 / sqrt(dot(v, v))), min / max as GLSL defines them,
+// the cofactor 4x4 inverse for transformInvT).
+//
 // Build: see oracle/Makefile (-O2 -ffp-contract=off: nothing here may be fused).
 
 #include "oracle.h"
@@ -63,11 +71,18 @@ inline vec3 cross(vec3 a, vec3 b) {
     return vec3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y);
 }
 inline float length(vec3 a) { return std::sqrt(dot(a, a)); }
-inline vec3 normalize(vec3 a) { return a / length(a); }
+// glm::normalize (external/glm/glm/detail/func_geometric.inl:82-90): v * inversesqrt(dot(v, v)), inversesqrt = 1 / sqrt
+// (func_exponential.inl:134-139) — the formula the reference's host math library uses, one division and three products
+inline vec3 normalize(vec3 a) { return a * (1.0f / std::sqrt(dot(a, a))); }
 inline vec3 vsqrt(vec3 a) { return vec3(std::sqrt(a.x), std::sqrt(a.y), std::sqrt(a.z)); }
 // GLSL faceforward(N, I, Nref): dot(Nref, I) < 0 ? N : -N
 inline vec3 faceforward(vec3 N, vec3 I, vec3 Nref) { return dot(Nref, I) < 0.0f ? N : -N; }
-inline float clampf(float v, float lo, float hi) { return std::fmin(std::fmax(v, lo), hi); }
+// GLSL 4.60 section 8.3: max(x, y) "returns y if x < y, otherwise x", min(x, y) "returns y if y < x, otherwise x",
+// clamp = min(max(x, lo), hi) — also glm's definitions (func_common.inl:17-30,505-509).  They differ from fmax / fmin
+// only when an operand is NaN (the first operand then wins), which the shader text reaches at grazing directions.
+inline float gmax(float x, float y) { return (x < y) ? y : x; }
+inline float gmin(float x, float y) { return (y < x) ? y : x; }
+inline float clampf(float v, float lo, float hi) { return gmin(gmax(v, lo), hi); }
 
 // GLSL "#define M_PI 3.14159265358979323846" is a 32-bit float literal in the shaders.
 constexpr float kPi = 3.14159265358979323846f;
@@ -464,12 +479,12 @@ inline vec2 sampleConcentric(Rng& rng) {
 // randCosineHemisphere, rayhit.rchit:107-111
 inline vec3 randCosineHemisphere(Rng& rng) {
     vec2 u = sampleConcentric(rng);
-    float z = std::sqrt(std::fmax(0.0f, 1.0f - u.x * u.x - u.y * u.y));
+    float z = std::sqrt(gmax(0.0f, 1.0f - u.x * u.x - u.y * u.y));
     return vec3(u.x, u.y, z);
 }
 
 // cosineHemispherePdf, rayhit.rchit:113-115
-inline float cosineHemispherePdf(vec3 w) { return std::fmax(std::fabs(w.z) / kPi, 0.000001f); }
+inline float cosineHemispherePdf(vec3 w) { return gmax(std::fabs(w.z) / kPi, 0.000001f); }
 
 // sampleHalf, rayhit.rchit:155-166
 inline vec3 sampleHalf(Rng& rng, float alpha) {
@@ -480,7 +495,7 @@ inline vec3 sampleHalf(Rng& rng, float alpha) {
     if (std::isinf(logSample)) logSample = 0.0f;
     float tan2 = -alpha * alpha * logSample;
     float cost = 1.0f / std::sqrt(1.0f + tan2);
-    float sint = std::sqrt(std::fmax(0.0f, 1.0f - cost * cost));
+    float sint = std::sqrt(gmax(0.0f, 1.0f - cost * cost));
     return vec3(std::cos(phi) * sint, std::sin(phi) * sint, cost);
 }
 
@@ -537,7 +552,7 @@ inline float fresnel4(float no, float cosTho, float nt, float cosTht) {
 
 // fresnel(vec3 wo, no, nt), rayhit.rchit:228-237
 inline float fresnelW(vec3 wo, float no, float nt) {
-    float sinTho = std::sqrt(std::fmax(wo.x * wo.x + wo.y * wo.y, 0.0f));
+    float sinTho = std::sqrt(gmax(wo.x * wo.x + wo.y * wo.y, 0.0f));
     float sqrtTerm = 1.0f - ((no * no) / (nt * nt)) * (sinTho * sinTho);
     if (sqrtTerm <= 0.0f) return 1.0f;
     float cosTht = std::sqrt(sqrtTerm);
@@ -547,7 +562,7 @@ inline float fresnelW(vec3 wo, float no, float nt) {
 
 // fresnel(float cosTho, no, nt), rayhit.rchit:239-247
 inline float fresnelC(float cosTho, float no, float nt) {
-    float sinTho = std::sqrt(std::fmax(1.0f - cosTho * cosTho, 0.0f));
+    float sinTho = std::sqrt(gmax(1.0f - cosTho * cosTho, 0.0f));
     float sqrtTerm = 1.0f - ((no * no) / (nt * nt)) * (sinTho * sinTho);
     if (sqrtTerm <= 0.0f) return 1.0f;
     float cosTht = std::sqrt(sqrtTerm);
@@ -574,7 +589,7 @@ inline vec3 FresnelDieletricConductor(vec3 Eta, vec3 Etak, float CosTheta) {
 
 // refractRay, rayhit.rchit:290-299
 inline bool refractRay(vec3 wo, vec3 n, float no, float nt, vec3& wt) {
-    float sinTho = std::sqrt(std::fmax(wo.x * wo.x + wo.y * wo.y, 0.0f));
+    float sinTho = std::sqrt(gmax(wo.x * wo.x + wo.y * wo.y, 0.0f));
     float sqrtTerm = 1.0f - ((no * no) / (nt * nt)) * (sinTho * sinTho);
     if (sqrtTerm <= 0.0f) return false;
     float cosTht = std::sqrt(sqrtTerm);
@@ -797,7 +812,7 @@ void roughPlasticEval(const gsb_rough_plastic_bsdf& b, vec3 wo, vec3 wi, BSDFOut
     vec3 kD = v3(b.diffuse);
     vec3 specular = vec3(Fri) * ggxD(wh, b.alpha) * ggxMask(wo, wi, b.alpha) / (4.0f * std::fabs(wo.z) * std::fabs(wi.z));
     vec3 d = kD * (1.0f - Fri) * (1.0f - Fro) * eta * eta / (kPi * (1.0f - kD * Ri));
-    res.pdf = 0.5f * std::fmax(beckmannD(wh, b.alpha) * std::fabs(wh.z), 0.01f) / (4.0f * std::fabs(dot(wo, wh))) + 0.5f * cosineHemispherePdf(wi);
+    res.pdf = 0.5f * gmax(beckmannD(wh, b.alpha) * std::fabs(wh.z), 0.01f) / (4.0f * std::fabs(dot(wo, wh))) + 0.5f * cosineHemispherePdf(wi);
     res.bsdf = d + specular;
     res.isDelta = false;
 }
@@ -815,7 +830,7 @@ void roughFloorSample(const gsb_rough_floor_bsdf& b, Rng& rng, vec3 wo, vec3& wi
     vec3 wh = normalize(wi + wo);
     float Fr = schlickFresnel(b.R0, std::fabs(dot(wo, wh)));
     vec3 d = v3(b.diffuse) * fresnelBlendDiffuseTerm(b.R0, std::fabs(wo.z), std::fabs(wi.z));
-    vec3 specular = vec3(Fr) * ggxD(wh, b.alpha) / (4.0f * std::fabs(dot(wo, wh)) * std::fmax(std::fabs(wo.z), std::fabs(wi.z)));
+    vec3 specular = vec3(Fr) * ggxD(wh, b.alpha) / (4.0f * std::fabs(dot(wo, wh)) * gmax(std::fabs(wo.z), std::fabs(wi.z)));
     res.pdf = 0.5f * beckmannD(wh, b.alpha) * std::fabs(wh.z) / (4.0f * std::fabs(dot(wo, wh))) + 0.5f * cosineHemispherePdf(wi);
     res.bsdf = d + specular;
     res.isDelta = false;
@@ -825,7 +840,7 @@ void roughFloorEval(const gsb_rough_floor_bsdf& b, vec3 wo, vec3 wi, BSDFOutput&
     float Fr = schlickFresnel(b.R0, std::fabs(dot(wo, wh)));
     vec3 d = v3(b.diffuse) * fresnelBlendDiffuseTerm(b.R0, std::fabs(wo.z), std::fabs(wi.z));
     float ggx = ggxD(wh, b.alpha);
-    vec3 specular = vec3(Fr) * ggx / (4.0f * std::fabs(dot(wo, wh)) * std::fmax(std::fabs(wo.z), std::fabs(wi.z)));
+    vec3 specular = vec3(Fr) * ggx / (4.0f * std::fabs(dot(wo, wh)) * gmax(std::fabs(wo.z), std::fabs(wi.z)));
     res.pdf = 0.5f * beckmannD(wh, b.alpha) * std::fabs(wh.z) / (4.0f * std::fabs(dot(wo, wh))) + 0.5f * cosineHemispherePdf(wi);
     res.bsdf = d + specular;
     res.isDelta = false;
@@ -844,7 +859,7 @@ vec3 sampleHalfGGX(Rng& rng, float alpha) {
     float phi = 2.0f * kPi * ux;
     float tan2 = alpha * alpha * uy / (1.0f - uy);
     float cost = 1.0f / std::sqrt(1.0f + tan2);
-    float sint = std::sqrt(std::fmax(0.0f, 1.0f - cost * cost));
+    float sint = std::sqrt(gmax(0.0f, 1.0f - cost * cost));
     return vec3(std::cos(phi) * sint, std::sin(phi) * sint, cost);
 }
 void roughDielectricInvalid(vec3 wo, vec3& wi, BSDFOutput& res) {
@@ -873,7 +888,7 @@ void roughDielectricSample(const gsb_rough_dielectric_bsdf& b, Rng& rng, vec3 wo
     } else {
         const float eta = no / nt;
         const float cosT2 = 1.0f - eta * eta * (1.0f - cosI * cosI);
-        wi = normalize(-eta * wo + (eta * cosI - std::sqrt(std::fmax(cosT2, 0.0f))) * wh);
+        wi = normalize(-eta * wo + (eta * cosI - std::sqrt(gmax(cosT2, 0.0f))) * wh);
         const float cosO = dot(wi, wh);
         if (!(wi.z * wo.z < 0.0f) || !(cosO < 0.0f)) { roughDielectricInvalid(wo, wi, res); return; }
         const float denom = no * cosI + nt * cosO;
@@ -1123,7 +1138,7 @@ void primaryRay(const or_scene& s, uint32_t W, uint32_t H, uint32_t x, uint32_t 
     const float sx = (float)W, sy = (float)H;
     const float fx = (float)x - sx / 2.0f;
     const float fy = (float)y - sy / 2.0f;
-    const float z = (std::fmax(sx, sy) / 2.0f) / std::tan(s.fov / 2.0f);
+    const float z = (gmax(sx, sy) / 2.0f) / std::tan(s.fov / 2.0f);
     vec3 dir = normalize(vec3(-fx, fy, z));
     const float* V = s.view;  // column-major
     direction = vec3(V[0] * dir.x + V[4] * dir.y + V[8] * dir.z,
@@ -1171,7 +1186,7 @@ vec3 pathSample(const or_scene& s, uint32_t W, uint32_t H, uint32_t x, uint32_t 
         const float cutoff = s.params.cutoff;
         if (prd.emitted.x < cutoff && prd.emitted.y < cutoff && prd.emitted.z < cutoff) result = result + prd.emitted;  // :60-63
         if (depth > s.params.rr_start) {                               // :66-71
-            float q = clampf(std::fmax(std::fmax(prd.weight.x, prd.weight.y), prd.weight.z), 0.05f, 1.0f);
+            float q = clampf(gmax(gmax(prd.weight.x, prd.weight.y), prd.weight.z), 0.05f, 1.0f);
             if (rr.randUniform() > q) break;
             prd.weight = prd.weight / q;
         }
@@ -1202,9 +1217,37 @@ void deriveInstance(Instance& in) {
         for (int k = 0; k < 3; k++) in.w2o[r * 4 + k] = (float)inv[r][k];
         in.w2o[r * 4 + 3] = (float)(-(inv[r][0] * M[0][3] + inv[r][1] * M[1][3] + inv[r][2] * M[2][3]));
     }
-    // inverse(transpose(M)) upper-left 3x3 = inverse(A)^T
-    for (int r = 0; r < 3; r++)
-        for (int k = 0; k < 3; k++) in.nrmM[r * 3 + k] = (float)inv[k][r];
+    // transformInvT = glm::inverse(glm::transpose(M)) in float32, PathTracer.cpp:62.  glm's 4x4 inverse is the cofactor
+    // expansion of external/glm/glm/detail/func_matrix.inl:294-352, restated here operation for operation so that the
+    // normal matrix carries the same bits as the reference's host code computes; rows 0..2 of its 3x3 part are kept.
+    {
+        float m[4][4];   // m[c][r] = transpose(M)[c][r] = M[r][c] = T[r*4 + c]
+        for (int c = 0; c < 4; c++)
+            for (int r = 0; r < 4; r++) m[c][r] = T[r * 4 + c];
+        const float c00 = m[2][2] * m[3][3] - m[3][2] * m[2][3], c02 = m[1][2] * m[3][3] - m[3][2] * m[1][3], c03 = m[1][2] * m[2][3] - m[2][2] * m[1][3];
+        const float c04 = m[2][1] * m[3][3] - m[3][1] * m[2][3], c06 = m[1][1] * m[3][3] - m[3][1] * m[1][3], c07 = m[1][1] * m[2][3] - m[2][1] * m[1][3];
+        const float c08 = m[2][1] * m[3][2] - m[3][1] * m[2][2], c10 = m[1][1] * m[3][2] - m[3][1] * m[1][2], c11 = m[1][1] * m[2][2] - m[2][1] * m[1][2];
+        const float c12 = m[2][0] * m[3][3] - m[3][0] * m[2][3], c14 = m[1][0] * m[3][3] - m[3][0] * m[1][3], c15 = m[1][0] * m[2][3] - m[2][0] * m[1][3];
+        const float c16 = m[2][0] * m[3][2] - m[3][0] * m[2][2], c18 = m[1][0] * m[3][2] - m[3][0] * m[1][2], c19 = m[1][0] * m[2][2] - m[2][0] * m[1][2];
+        const float c20 = m[2][0] * m[3][1] - m[3][0] * m[2][1], c22 = m[1][0] * m[3][1] - m[3][0] * m[1][1], c23 = m[1][0] * m[2][1] - m[2][0] * m[1][1];
+        const float f0[4] = {c00, c00, c02, c03}, f1[4] = {c04, c04, c06, c07}, f2[4] = {c08, c08, c10, c11};
+        const float f3[4] = {c12, c12, c14, c15}, f4[4] = {c16, c16, c18, c19}, f5[4] = {c20, c20, c22, c23};
+        const float v0[4] = {m[1][0], m[0][0], m[0][0], m[0][0]}, v1[4] = {m[1][1], m[0][1], m[0][1], m[0][1]};
+        const float v2[4] = {m[1][2], m[0][2], m[0][2], m[0][2]}, v3[4] = {m[1][3], m[0][3], m[0][3], m[0][3]};
+        const float sa[4] = {1.0f, -1.0f, 1.0f, -1.0f}, sb[4] = {-1.0f, 1.0f, -1.0f, 1.0f};
+        float inv4[4][4];   // inv4[c][r]
+        for (int k = 0; k < 4; k++) {
+            inv4[0][k] = ((v1[k] * f0[k] - v2[k] * f1[k]) + v3[k] * f2[k]) * sa[k];
+            inv4[1][k] = ((v0[k] * f0[k] - v2[k] * f3[k]) + v3[k] * f4[k]) * sb[k];
+            inv4[2][k] = ((v0[k] * f1[k] - v1[k] * f3[k]) + v3[k] * f5[k]) * sa[k];
+            inv4[3][k] = ((v0[k] * f2[k] - v1[k] * f4[k]) + v2[k] * f5[k]) * sb[k];
+        }
+        const float d0 = m[0][0] * inv4[0][0], d1 = m[0][1] * inv4[1][0], d2 = m[0][2] * inv4[2][0], d3 = m[0][3] * inv4[3][0];
+        const float oneOverDet = 1.0f / ((d0 + d1) + (d2 + d3));
+        // normal' = transformInvT * vec4(n, 0): row r of the 3x3 part is (inv4[0][r], inv4[1][r], inv4[2][r])
+        for (int r = 0; r < 3; r++)
+            for (int k = 0; k < 3; k++) in.nrmM[r * 3 + k] = inv4[k][r] * oneOverDet;
+    }
 }
 
 void instanceBounds(const or_scene& s, Instance& in) {
@@ -1348,6 +1391,15 @@ int or_path_probe(or_scene* s, uint32_t width, uint32_t height, uint32_t x, uint
     vec3 c = pathSample(*s, width, height, x, y, timestamp, st, bounces, max_bounces, &nb);
     out_rgb[0] = c.x; out_rgb[1] = c.y; out_rgb[2] = c.z;
     return (int)nb;
+}
+
+// One ray query in the shape oracle/ref/ref_glue.cpp's traceRayEXT takes as its callback (the ray/triangle search has no
+// source in the reference; the compiled reference shaders therefore run on top of this intersector).
+int or_intersect(void* scene, const float* origin, const float* dir, float tmin, float tmax, int any_hit, gsb_hit* out) {
+    const or_scene* s = static_cast<const or_scene*>(scene);
+    Hit h = traceF32(*s, origin, dir, tmin, tmax, any_hit != 0, true);
+    out->t = h.t; out->u = h.u; out->v = h.v; out->inst = h.inst; out->prim = h.prim;
+    return h.inst != GSB_NO_HIT ? 1 : 0;
 }
 
 int or_trace_batch(or_scene* s, const gsb_ray* rays, uint32_t count, gsb_hit* hits, int any_hit, int mode, int threads) {

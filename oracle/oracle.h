@@ -66,6 +66,9 @@ int or_path_probe(or_scene* s, uint32_t width, uint32_t height, uint32_t x, uint
  * mode 2: float64 Moeller-Trumbore brute force in world space (independent cross-check) */
 int or_trace_batch(or_scene* s, const gsb_ray* rays, uint32_t count, gsb_hit* hits, int any_hit, int mode, int threads);
 
+/* One ray query, callable as the `ref_intersect_fn` of oracle/ref/ref_glue.cpp (scene = or_scene*).  Returns 1 on a hit. */
+int or_intersect(void* scene, const float* origin, const float* dir, float tmin, float tmax, int any_hit, gsb_hit* out);
+
 /* unit-level functions */
 uint32_t or_tea(uint32_t v0, uint32_t v1);
 uint32_t or_pcg_hash(uint32_t v);

@@ -59,6 +59,7 @@ def lib():
             "or_render": (C.c_int, [P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, f32p, C.c_int, C.c_int, C.POINTER(Counters)]),
             "or_path_probe": (C.c_int, [P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, f32p, P, C.c_uint32]),
             "or_trace_batch": (C.c_int, [P, P, C.c_uint32, P, C.c_int, C.c_int, C.c_int]),
+            "or_intersect": (C.c_int, [P, f32p, f32p, C.c_float, C.c_float, C.c_int, P]),
             "or_tea": (C.c_uint32, [C.c_uint32, C.c_uint32]),
             "or_pcg_hash": (C.c_uint32, [C.c_uint32]),
             "or_rng": (None, [u32p, u32p, C.c_uint32, C.c_uint32, u32p]),
