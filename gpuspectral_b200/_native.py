@@ -51,7 +51,8 @@ class Counters(C.Structure):
 class BvhStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("num_meshes", "num_instances", "unique_triangles", "instanced_triangles",
                                           "blas_nodes", "tlas_nodes", "bvh_bytes")] + \
-               [("build_ms", C.c_double), ("sah_cost_before", C.c_double), ("sah_cost_after", C.c_double)]
+               [("build_ms", C.c_double), ("sah_cost_before", C.c_double), ("sah_cost_after", C.c_double)] + \
+               [(n, C.c_uint64) for n in ("baked_instances", "baked_triangles", "world_nodes")]
 
 
 assert C.sizeof(Instance) == 88 and C.sizeof(TriangleLight) == 64 and C.sizeof(Ray) == 32 and C.sizeof(Hit) == 20

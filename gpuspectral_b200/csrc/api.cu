@@ -58,11 +58,14 @@ T* uploadArray(const T* host, size_t count, cudaStream_t s) {
 
 struct Bind {
     int prev = -1;
-    explicit Bind(int dev) {
+    explicit Bind(int dev) : dev_(dev) {
         cudaGetDevice(&prev);
         if (prev != dev) cudaSetDevice(dev);
     }
-    ~Bind() {}
+    ~Bind() {
+        if (prev >= 0 && prev != dev_) cudaSetDevice(prev);   // the caller's current device is not ours to change
+    }
+    int dev_ = 0;
 };
 
 // ---- kernels of this translation unit ----------------------------------------------------------------
@@ -102,14 +105,14 @@ struct BatchSource {
     }
 };
 
-template <bool ANYHIT, bool STATS>
+template <bool ANYHIT, bool STATS, bool HASINST>
 __global__ void __launch_bounds__(kTraceBlock) k_traceBatch(SceneDev sc, const gsb_ray* __restrict__ rays, uint32_t n,
                                                             gsb_hit* __restrict__ hits, unsigned long long* stats, uint32_t refillMin) {
     BatchSource<ANYHIT> src;
     src.rays = rays; src.hits = hits; src.n = n;
     src.counter = reinterpret_cast<uint32_t*>(&stats[ST_BATCHNEXT]);
     TraceStats ts = {0u, 0u, 0u};
-    traceStream<ANYHIT, STATS>(sc, src, refillMin, &ts, (uint32_t*)&stats[ST_OVERFLOW]);
+    traceStream<ANYHIT, STATS, HASINST>(sc, src, refillMin, &ts, (uint32_t*)&stats[ST_OVERFLOW]);
     if (STATS) {
         uint32_t nn = ts.nodes, nt = ts.tris, ni = ts.insts, nr = src.traced;
         for (int o = 16; o > 0; o >>= 1) {
@@ -124,6 +127,23 @@ __global__ void __launch_bounds__(kTraceBlock) k_traceBatch(SceneDev sc, const g
             atomicAdd(&stats[ST_INSTS], (unsigned long long)ni);
             atomicAdd(&stats[ST_RAYS], (unsigned long long)nr);
         }
+    }
+}
+
+// Bake rule, device side: vertex k of triangle t of instance `inst` in world space, x' = ((m0*x + m1*y) + m2*z) + m3 per
+// row, every operation rounded on its own (no FMA) — the order of gl_ObjectToWorldEXT * vec4(p, 1) (rayhit.rchit:679-681)
+// and of the checker.  .w carries the ids the world level reports: v0.w = gl_PrimitiveID, v1.w = gl_InstanceID.
+__global__ void k_bakeInstance(const float4* __restrict__ vpos, uint32_t ntris, float4 m0, float4 m1, float4 m2, uint32_t inst,
+                               float4* __restrict__ out) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntris) return;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const float4 p = __ldg(vpos + 3 * (size_t)t + k);
+        const float x = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m0.x, p.x), __fmul_rn(m0.y, p.y)), __fmul_rn(m0.z, p.z)), m0.w);
+        const float y = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m1.x, p.x), __fmul_rn(m1.y, p.y)), __fmul_rn(m1.z, p.z)), m1.w);
+        const float z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m2.x, p.x), __fmul_rn(m2.y, p.y)), __fmul_rn(m2.z, p.z)), m2.w);
+        out[3 * (size_t)t + k] = make_float4(x, y, z, __uint_as_float(k == 0 ? t : (k == 1 ? inst : 0u)));
     }
 }
 
@@ -278,9 +298,42 @@ void drain(gsb_context* ctx) {
 
 using namespace gsb;
 
+// transformInvT = glm::inverse(glm::transpose(M)) (PathTracer.cpp:62) in float32: glm's 4x4 inverse is the cofactor
+// expansion of external/glm/glm/detail/func_matrix.inl:294-352; restated operation for operation so that the normal
+// matrix carries the bits the reference's host code computes.  T: column-major object->world; out: rows of the 3x3 part.
+static void normalMatrixGlm(const float* T, float out[3][3]) {
+    float m[4][4];   // m[c][r] = transpose(M)[c][r] = M[r][c] = T[r*4 + c]
+    for (int c = 0; c < 4; c++)
+        for (int r = 0; r < 4; r++) m[c][r] = T[r * 4 + c];
+    const float c00 = m[2][2] * m[3][3] - m[3][2] * m[2][3], c02 = m[1][2] * m[3][3] - m[3][2] * m[1][3], c03 = m[1][2] * m[2][3] - m[2][2] * m[1][3];
+    const float c04 = m[2][1] * m[3][3] - m[3][1] * m[2][3], c06 = m[1][1] * m[3][3] - m[3][1] * m[1][3], c07 = m[1][1] * m[2][3] - m[2][1] * m[1][3];
+    const float c08 = m[2][1] * m[3][2] - m[3][1] * m[2][2], c10 = m[1][1] * m[3][2] - m[3][1] * m[1][2], c11 = m[1][1] * m[2][2] - m[2][1] * m[1][2];
+    const float c12 = m[2][0] * m[3][3] - m[3][0] * m[2][3], c14 = m[1][0] * m[3][3] - m[3][0] * m[1][3], c15 = m[1][0] * m[2][3] - m[2][0] * m[1][3];
+    const float c16 = m[2][0] * m[3][2] - m[3][0] * m[2][2], c18 = m[1][0] * m[3][2] - m[3][0] * m[1][2], c19 = m[1][0] * m[2][2] - m[2][0] * m[1][2];
+    const float c20 = m[2][0] * m[3][1] - m[3][0] * m[2][1], c22 = m[1][0] * m[3][1] - m[3][0] * m[1][1], c23 = m[1][0] * m[2][1] - m[2][0] * m[1][1];
+    const float f0[4] = {c00, c00, c02, c03}, f1[4] = {c04, c04, c06, c07}, f2[4] = {c08, c08, c10, c11};
+    const float f3[4] = {c12, c12, c14, c15}, f4[4] = {c16, c16, c18, c19}, f5[4] = {c20, c20, c22, c23};
+    const float v0[4] = {m[1][0], m[0][0], m[0][0], m[0][0]}, v1[4] = {m[1][1], m[0][1], m[0][1], m[0][1]};
+    const float v2[4] = {m[1][2], m[0][2], m[0][2], m[0][2]}, v3[4] = {m[1][3], m[0][3], m[0][3], m[0][3]};
+    const float sa[4] = {1.0f, -1.0f, 1.0f, -1.0f}, sb[4] = {-1.0f, 1.0f, -1.0f, 1.0f};
+    volatile float inv4[4][4];   // volatile: keeps the host compiler from contracting a*b - c*d into fused operations
+    for (int k = 0; k < 4; k++) {
+        inv4[0][k] = ((v1[k] * f0[k] - v2[k] * f1[k]) + v3[k] * f2[k]) * sa[k];
+        inv4[1][k] = ((v0[k] * f0[k] - v2[k] * f3[k]) + v3[k] * f4[k]) * sb[k];
+        inv4[2][k] = ((v0[k] * f1[k] - v1[k] * f3[k]) + v3[k] * f5[k]) * sa[k];
+        inv4[3][k] = ((v0[k] * f2[k] - v1[k] * f4[k]) + v2[k] * f5[k]) * sb[k];
+    }
+    const float d0 = m[0][0] * inv4[0][0], d1 = m[0][1] * inv4[1][0], d2 = m[0][2] * inv4[2][0], d3 = m[0][3] * inv4[3][0];
+    const float oneOverDet = 1.0f / ((d0 + d1) + (d2 + d3));
+    for (int r = 0; r < 3; r++)
+        for (int k = 0; k < 3; k++) out[r][k] = inv4[k][r] * oneOverDet;
+}
+
 SceneDev gsb_context::sceneDev() const {
     SceneDev sc;
     memset(&sc, 0, sizeof(sc));
+    sc.worldNodes = world.buffer;
+    sc.worldTris = reinterpret_cast<const float4*>(world.buffer + world.leafOffset16);
     sc.tlasNodes = tlas.buffer;
     sc.tlasInst = reinterpret_cast<const TraceInstance*>(tlas.buffer + tlas.leafOffset16);
     sc.shadeInst = dShade;
@@ -364,6 +417,8 @@ gsb_status gsb_destroy(gsb_context* ctx) {
             freeBvh(m.blas);
         }
         freeBvh(ctx->tlas);
+        freeBvh(ctx->world);
+        cudaFree(ctx->dWorldVerts);
         cudaFree(ctx->dShade);
         cudaFree(ctx->dInstBsdf);
         for (void* p : ctx->dBsdf) cudaFree(p);
@@ -468,9 +523,24 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
         ctx->instances.assign(instances, instances + count);
         std::vector<ShadeInstance> shade(count);
-        std::vector<TraceInstance> trace(count);
+        std::vector<TraceInstance> trace;
         std::vector<uint32_t> handles(count);
-        std::vector<float> wlo(3 * (size_t)count), whi(3 * (size_t)count);
+        std::vector<float> wlo, whi;
+        // Bake rule (shared with the checker, oracle.cpp: kBakeMaxTris / kBakeBudget): in gl_InstanceID order, an instance
+        // whose mesh has at most kBakeMaxTris triangles goes to the world level while the baked total fits the budget.
+        std::vector<uint64_t> bakeOffset(count, ~0ull);   // first world-level triangle of a baked instance
+        uint64_t baked = 0;
+        for (uint32_t i = 0; i < count; i++) {
+            const uint32_t nt = ctx->meshes[instances[i].mesh].ntris;
+            if (nt > 0 && nt <= kBakeMaxTris && baked + nt <= kBakeBudget) { bakeOffset[i] = baked; baked += nt; }
+        }
+        cudaFree(ctx->dWorldVerts);
+        ctx->dWorldVerts = nullptr;
+        if (baked) {
+            void* q = nullptr;
+            GSB_CUDA(cudaMalloc(&q, (size_t)baked * 3 * sizeof(float4)));
+            ctx->dWorldVerts = (float4*)q;
+        }
         for (bool& u : ctx->typeUsed) u = false;
         for (uint32_t i = 0; i < count; i++) {
             const gsb_instance& in = instances[i];
@@ -494,26 +564,36 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
             inv[0][2] = (M[0][1] * M[1][2] - M[0][2] * M[1][1]) * id;
             inv[1][2] = (M[0][2] * M[1][0] - M[0][0] * M[1][2]) * id;
             inv[2][2] = (M[0][0] * M[1][1] - M[0][1] * M[1][0]) * id;
+            // transformInvT = glm::inverse(glm::transpose(M)) in float32 as the reference's host computes it (PathTracer.cpp:62)
+            float nrm[3][3];
+            normalMatrixGlm(T, nrm);
             ShadeInstance& sh = shade[i];
-            TraceInstance& tr = trace[i];
             for (int r = 0; r < 3; r++) {
                 sh.o2w[r] = make_float4((float)M[r][0], (float)M[r][1], (float)M[r][2], (float)M[r][3]);
-                // rows of inverse(transpose(M))'s 3x3 = columns of inv
-                sh.nrm[r] = make_float4((float)inv[0][r], (float)inv[1][r], (float)inv[2][r], in.emission[r]);
-                const double tw = -(inv[r][0] * M[0][3] + inv[r][1] * M[1][3] + inv[r][2] * M[2][3]);
-                tr.w2o[r] = make_float4((float)inv[r][0], (float)inv[r][1], (float)inv[r][2], (float)tw);
+                sh.nrm[r] = make_float4(nrm[r][0], nrm[r][1], nrm[r][2], in.emission[r]);
             }
             sh.vpos = mesh.vpos;
             sh.vnrm = mesh.vnrm;
             sh.bsdf = in.bsdf;
             sh.twofaced = in.twofaced;
             sh.pad[0] = sh.pad[1] = 0;
+            handles[i] = in.bsdf;
+            ctx->typeUsed[in.bsdf >> 16] = true;
+            if (bakeOffset[i] != ~0ull) {
+                k_bakeInstance<<<(mesh.ntris + 127) / 128, 128, 0, ctx->stream>>>(mesh.vpos, mesh.ntris, sh.o2w[0], sh.o2w[1], sh.o2w[2], i,
+                                                                                  ctx->dWorldVerts + 3 * bakeOffset[i]);
+                continue;
+            }
+            TraceInstance tr;
+            for (int r = 0; r < 3; r++) {
+                const double tw = -(inv[r][0] * M[0][3] + inv[r][1] * M[1][3] + inv[r][2] * M[2][3]);
+                tr.w2o[r] = make_float4((float)inv[r][0], (float)inv[r][1], (float)inv[r][2], (float)tw);
+            }
             tr.blas = mesh.blas.buffer;
             // meshes of <= 4 triangles are traced without their (single) node: the TLAS box test already covered them
             tr.triOffset16 = mesh.blas.leafOffset16 | ((mesh.ntris >= 1 && mesh.ntris <= 4) ? (mesh.ntris << kDirectShift) : 0u);
             tr.instId = i;
-            handles[i] = in.bsdf;
-            ctx->typeUsed[in.bsdf >> 16] = true;
+            trace.push_back(tr);
             // padded world bounds of the padded object box
             double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
             for (int corner = 0; corner < 8; corner++) {
@@ -529,22 +609,27 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
             for (int a = 0; a < 3; a++) scale = std::fmax(scale, std::fmax(std::fabs(lo[a]), std::fabs(hi[a])));
             const double pad = scale * (double)kBoxPadRel;
             for (int a = 0; a < 3; a++) {
-                wlo[3 * (size_t)i + a] = std::nextafter((float)(lo[a] - pad), -INFINITY);
-                whi[3 * (size_t)i + a] = std::nextafter((float)(hi[a] + pad), INFINITY);
+                wlo.push_back(std::nextafter((float)(lo[a] - pad), -INFINITY));
+                whi.push_back(std::nextafter((float)(hi[a] + pad), INFINITY));
             }
         }
+        GSB_CUDA(cudaGetLastError());
         cudaFree(ctx->dShade);
         cudaFree(ctx->dInstBsdf);
         ctx->dShade = uploadArray(shade.data(), count, ctx->stream);
         ctx->dInstBsdf = uploadArray(handles.data(), count, ctx->stream);
+        freeBvh(ctx->world);
+        buildBlas(ctx->dWorldVerts, (uint32_t)baked, ctx->stream, ctx->world, true);
         freeBvh(ctx->tlas);
-        buildTlas(wlo.data(), whi.data(), trace.data(), count, ctx->stream, ctx->tlas);
+        ctx->numTraceInstances = (uint32_t)trace.size();
+        ctx->numBakedTriangles = (uint32_t)baked;
+        buildTlas(wlo.data(), whi.data(), trace.data(), (uint32_t)trace.size(), ctx->stream, ctx->tlas);
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
         ctx->haveInstances = true;
-        double ms = ctx->tlas.buildMs;
+        double ms = ctx->tlas.buildMs + ctx->world.buildMs;
         std::vector<bool> seen(ctx->meshes.size(), false);
         for (uint32_t i = 0; i < count; i++)
-            if (!seen[instances[i].mesh]) { seen[instances[i].mesh] = true; ms += ctx->meshes[instances[i].mesh].blas.buildMs; }
+            if (bakeOffset[i] == ~0ull && !seen[instances[i].mesh]) { seen[instances[i].mesh] = true; ms += ctx->meshes[instances[i].mesh].blas.buildMs; }
         ctx->lastBuildMs = ms;
         return GSB_OK;
     });
@@ -577,22 +662,35 @@ gsb_status gsb_set_params(gsb_context* ctx, const gsb_params* params) {
 gsb_status gsb_get_bvh_stats(gsb_context* ctx, gsb_bvh_stats* out) {
     if (!ctx || !out) return fail(GSB_ERR_INVALID, "gsb_get_bvh_stats: null argument");
     memset(out, 0, sizeof(*out));
-    std::vector<bool> seen(ctx->meshes.size(), false);
+    std::vector<bool> seen(ctx->meshes.size(), false), blasUsed(ctx->meshes.size(), false);
+    uint64_t baked = 0;
     for (const gsb_instance& in : ctx->instances) {
         const MeshRec& m = ctx->meshes[in.mesh];
         out->instanced_triangles += m.ntris;
-        if (seen[in.mesh]) continue;
-        seen[in.mesh] = true;
-        out->num_meshes++;
-        out->unique_triangles += m.ntris;
-        out->blas_nodes += m.blas.numNodes;
-        out->bvh_bytes += m.blas.bytes;
-        out->sah_cost_before += m.blas.sahBefore;
-        out->sah_cost_after += m.blas.sahAfter;
+        if (!seen[in.mesh]) {
+            seen[in.mesh] = true;
+            out->num_meshes++;
+            out->unique_triangles += m.ntris;
+        }
+        // the bake rule of gsb_scene_set_instances: a baked instance does not go through its mesh's own BLAS
+        if (m.ntris > 0 && m.ntris <= kBakeMaxTris && baked + m.ntris <= kBakeBudget) {
+            baked += m.ntris;
+            out->baked_instances++;
+        } else if (!blasUsed[in.mesh]) {
+            blasUsed[in.mesh] = true;
+            out->blas_nodes += m.blas.numNodes;
+            out->bvh_bytes += m.blas.bytes;
+            out->sah_cost_before += m.blas.sahBefore;
+            out->sah_cost_after += m.blas.sahAfter;
+        }
     }
     out->num_instances = ctx->instances.size();
     out->tlas_nodes = ctx->tlas.numNodes;
-    out->bvh_bytes += ctx->tlas.bytes;
+    out->bvh_bytes += ctx->tlas.bytes + ctx->world.bytes;
+    out->baked_triangles = ctx->numBakedTriangles;
+    out->world_nodes = ctx->world.numNodes;
+    out->sah_cost_before += ctx->world.sahBefore;
+    out->sah_cost_after += ctx->world.sahAfter;
     out->build_ms = ctx->lastBuildMs;
     return GSB_OK;
 }
@@ -782,24 +880,24 @@ static gsb_status traceBatch(gsb_context* ctx, const gsb_ray* rays, uint32_t cou
         const SceneDev sc = ctx->sceneDev();
         int sms = 148, perSm = 4;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_traceBatch<false, false>, kTraceBlock, 0);
+        const bool hasInst = ctx->numTraceInstances > 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, hasInst ? (const void*)k_traceBatch<false, false, true> : (const void*)k_traceBatch<false, false, false>, kTraceBlock, 0);
         const int grid = std::max(1, std::min((int)((count + kTraceBlock - 1) / kTraceBlock), sms * std::max(perSm, 1)));
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (out_ms) {
             GSB_CUDA(cudaEventCreate(&e0));
             GSB_CUDA(cudaEventCreate(&e1));
         }
+        using BatchKernel = void (*)(SceneDev, const gsb_ray*, uint32_t, gsb_hit*, unsigned long long*, uint32_t);
+        static const BatchKernel kernels[8] = {
+            k_traceBatch<false, false, false>, k_traceBatch<false, false, true>, k_traceBatch<false, true, false>, k_traceBatch<false, true, true>,
+            k_traceBatch<true, false, false>,  k_traceBatch<true, false, true>,  k_traceBatch<true, true, false>,  k_traceBatch<true, true, true>};
+        const BatchKernel kernel = kernels[(any_hit ? 4 : 0) | (stats ? 2 : 0) | (hasInst ? 1 : 0)];
         for (int r = 0; r < repeats + (out_ms ? 1 : 0); r++) {
             if (out_ms && r == 1) GSB_CUDA(cudaEventRecord(e0, ctx->stream));  // launch 0 is a warm-up
             if (count == 0) break;
             GSB_CUDA(cudaMemsetAsync(&ctx->wf.stats[ST_BATCHNEXT], 0, sizeof(unsigned long long), ctx->stream));  // the stream's work counter
-            if (stats) {
-                if (any_hit) k_traceBatch<true, true><<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, ctx->refillMin);
-                else k_traceBatch<false, true><<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, ctx->refillMin);
-            } else {
-                if (any_hit) k_traceBatch<true, false><<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, ctx->refillMin);
-                else k_traceBatch<false, false><<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, ctx->refillMin);
-            }
+            kernel<<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, ctx->refillMin);
         }
         GSB_CUDA(cudaGetLastError());
         if (out_ms) {

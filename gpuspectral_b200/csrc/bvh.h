@@ -31,7 +31,14 @@ constexpr float kBoxPadRel = 1.0f / 32768.0f;
 
 // Bottom level over a triangle soup (3 float4 per triangle, object space).  Leaf record =
 // 3 copies (one per dominant ray axis, pre-rotated) of 3 x float4 (v0.xyz | primId bits, v1.xyz, v2.xyz) = 144 B.
-void buildBlas(const float4* dVertices, uint32_t numTriangles, cudaStream_t stream, DeviceBvh& out);
+// idsInVertices: the leaf records take v0.w / v1.w from the input vertices (world level: primitive and instance id of
+// every baked triangle) instead of the position of the triangle in the soup.
+void buildBlas(const float4* dVertices, uint32_t numTriangles, cudaStream_t stream, DeviceBvh& out, bool idsInVertices = false);
+
+// Bake rule (shared with the checker, oracle/oracle.cpp): in gl_InstanceID order an instance whose mesh has at most
+// kBakeMaxTris triangles is stored in world space at the world level, while the baked total stays within kBakeBudget.
+constexpr uint32_t kBakeMaxTris = 16384;
+constexpr uint64_t kBakeBudget = 1ull << 22;
 
 // Top level over instances.  hostLo/hostHi: padded world bounds (3 floats each) per instance;
 // hostRecords: TraceInstance per instance in gl_InstanceID order.  Leaf record = TraceInstance.

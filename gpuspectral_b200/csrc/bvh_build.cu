@@ -228,6 +228,7 @@ struct CollapseArgs {
     uint4* nodes;          // output nodes, 5 x uint4 each
     uint32_t* leafPrim;    // output: primitive index per leaf position
     uint32_t* counters;    // [0] nodes allocated, [1] leaf positions allocated, [2] next-level item count
+    uint32_t maxLeaf;      // primitives per leaf child (one box per leaf child): 1..3
 };
 
 __device__ inline uint32_t refCount(const BinTree& t, int ref) { return ref >= 0 ? t.last[ref] - t.first[ref] + 1u : 1u; }
@@ -240,7 +241,7 @@ __device__ void emitNode(const CollapseArgs& a, uint32_t outNode, float4 nlo, fl
     bool internal[8];
     for (int k = 0; k < nc; k++) {
         refBox(a.t, a.plo, a.phi, a.sorted, child[k], clo[k], chi[k]);
-        internal[k] = refCount(a.t, child[k]) > 3u;
+        internal[k] = refCount(a.t, child[k]) > a.maxLeaf;
     }
     // octant slot assignment: slot s (bits x,y,z = 4,2,1) should hold the child lying furthest
     // towards (+ if bit set, - if clear) on each axis; traversal visits slot^octant in descending order.
@@ -375,16 +376,18 @@ __global__ void k_emptyRoot(uint4* nodes) {
 // Leaf record of a triangle: three copies, one per dominant ray axis kz, each rotated so that kz comes last
 // (traverse.cuh: permute) — the traversal fetches the copy that matches its ray and needs no per-vertex selects.
 // Copy kz of leaf position k sits at float4 index 9 k + 3 kz; v0.w carries the primitive id in every copy.
-__global__ void k_packTriangles(const uint32_t* __restrict__ leafPrim, uint32_t n, const float4* __restrict__ v, float4* __restrict__ out) {
+// idsInVertices (world level): v0.w / v1.w are copied from the input (primitive id, instance id of a baked triangle).
+__global__ void k_packTriangles(const uint32_t* __restrict__ leafPrim, uint32_t n, const float4* __restrict__ v, float4* __restrict__ out,
+                                bool idsInVertices) {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     const uint32_t p = leafPrim[k];
     const float4 a = __ldg(v + 3 * (size_t)p), b = __ldg(v + 3 * (size_t)p + 1), c = __ldg(v + 3 * (size_t)p + 2);
-    const float pw = __uint_as_float(p);
+    const float pw = idsInVertices ? a.w : __uint_as_float(p), iw = idsInVertices ? b.w : 0.0f;
     float4* o = out + 9 * (size_t)k;
-    o[0] = make_float4(a.y, a.z, a.x, pw); o[1] = make_float4(b.y, b.z, b.x, 0.0f); o[2] = make_float4(c.y, c.z, c.x, 0.0f);   // kz = 0
-    o[3] = make_float4(a.z, a.x, a.y, pw); o[4] = make_float4(b.z, b.x, b.y, 0.0f); o[5] = make_float4(c.z, c.x, c.y, 0.0f);   // kz = 1
-    o[6] = make_float4(a.x, a.y, a.z, pw); o[7] = make_float4(b.x, b.y, b.z, 0.0f); o[8] = make_float4(c.x, c.y, c.z, 0.0f);   // kz = 2
+    o[0] = make_float4(a.y, a.z, a.x, pw); o[1] = make_float4(b.y, b.z, b.x, iw); o[2] = make_float4(c.y, c.z, c.x, 0.0f);   // kz = 0
+    o[3] = make_float4(a.z, a.x, a.y, pw); o[4] = make_float4(b.z, b.x, b.y, iw); o[5] = make_float4(c.z, c.x, c.y, 0.0f);   // kz = 1
+    o[6] = make_float4(a.x, a.y, a.z, pw); o[7] = make_float4(b.x, b.y, b.z, iw); o[8] = make_float4(c.x, c.y, c.z, 0.0f);   // kz = 2
 }
 
 __global__ void k_packInstances(const uint32_t* __restrict__ leafPrim, uint32_t n, const uint4* __restrict__ rec, uint4* __restrict__ out) {
@@ -460,6 +463,11 @@ GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi,
     ca.nodes = r.nodes;
     ca.leafPrim = r.leafPrim;
     ca.counters = counters;
+    // Top level: one instance per leaf child, so that every instance is culled by a box of its own before the ray pays
+    // for its transform and root fetch (with 3 per leaf the gallery entered 5.8 and the field 4.7 - 6.9 instances per ray).
+    // Bottom level: up to GSB_MAX_LEAF (default 3) triangles share a leaf box.
+    ca.maxLeaf = topLevel ? 1u : 3u;
+    if (const char* e = getenv(topLevel ? "GSB_MAX_LEAF_TLAS" : "GSB_MAX_LEAF")) ca.maxLeaf = (uint32_t)std::min(3, std::max(1, atoi(e)));
     if (n == 1) {
         memset(&ca.t, 0, sizeof(ca.t));
         k_singleLeafRoot<<<1, 1, 0, s>>>(ca);
@@ -545,7 +553,7 @@ void freeBvh(DeviceBvh& bvh) {
     bvh = DeviceBvh();
 }
 
-void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out) {
+void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out, bool idsInVertices) {
     cudaEvent_t e0, e1;
     GSB_CUDA(cudaEventCreate(&e0));
     GSB_CUDA(cudaEventCreate(&e1));
@@ -578,7 +586,7 @@ void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBv
         finishBuffer(r, ntris, 144, s, out);
         if (ntris > 0)
             k_packTriangles<<<(ntris + B - 1) / B, B, 0, s>>>(r.leafPrim, ntris, dVertices,
-                                                              reinterpret_cast<float4*>(out.buffer + out.leafOffset16));
+                                                              reinterpret_cast<float4*>(out.buffer + out.leafOffset16), idsInVertices);
         GSB_CUDA(cudaGetLastError());
         for (int a = 0; a < 3; a++) { out.lo[a] = lo[a] - pad; out.hi[a] = hi[a] + pad; }
     }

@@ -104,7 +104,9 @@ static_assert(sizeof(TraceInstance) == 64, "TraceInstance must stay 64 bytes");
 
 // Everything the kernels need to know about the scene; passed by value as a kernel parameter.
 struct SceneDev {
-    const uint4* tlasNodes;          // 8-wide nodes of the top level (5 x uint4 each)
+    const uint4* worldNodes;         // world level: 8-wide nodes over the triangles of all baked instances (world space)
+    const float4* worldTris;         //   their leaf records (3 rotated copies of 3 float4; v0.w = primitive, v1.w = instance)
+    const uint4* tlasNodes;          // 8-wide nodes of the top level over the instances that are not baked
     const TraceInstance* tlasInst;   // instance records in TLAS leaf order
     const ShadeInstance* shadeInst;  // instance records in gl_InstanceID order
     const uint32_t* instBsdf;        // bsdf handle per instance (compact copy for queue binning)

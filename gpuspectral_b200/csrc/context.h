@@ -61,7 +61,11 @@ struct gsb_context {
     cudaStream_t stream = nullptr;
     std::vector<gsb::MeshRec> meshes;
     std::vector<gsb_instance> instances;
-    gsb::DeviceBvh tlas;
+    gsb::DeviceBvh world;              // world level: BVH over the triangles of all baked instances, in world space
+    float4* dWorldVerts = nullptr;     //   their vertices (3 float4 per triangle; v0.w = primitive id, v1.w = instance id)
+    uint32_t numBakedTriangles = 0;
+    gsb::DeviceBvh tlas;               // top level over the instances that are not baked
+    uint32_t numTraceInstances = 0;
     gsb::ShadeInstance* dShade = nullptr;
     uint32_t* dInstBsdf = nullptr;
     void* dBsdf[GSB_BSDF_TYPE_COUNT] = {};

@@ -27,7 +27,8 @@
 
 namespace gsb {
 
-constexpr int kStackSize = 48;      // total traversal stack entries per ray
+constexpr int kStackSize = 48;      // total traversal stack entries per ray (world level, then TLAS + BLAS)
+constexpr int kWorldStackSize = 32; // ... when the scene has the world level only (at most 2^22 baked triangles)
 #ifndef GSB_SMEM_STACK
 #define GSB_SMEM_STACK 8
 #endif
@@ -245,9 +246,17 @@ GSB_D void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :
 //   bool fetch(bool want, RayJob& job)                           next ray for idle lanes; false = lane got none
 //   bool drained()                                               warp-uniform: no more rays will ever come
 //
+// Levels.  Every ray first walks the WORLD level: one BVH over the triangles of all baked instances, stored in world
+// space (api.cu: the bake rule; v0.w = gl_PrimitiveID, v1.w = gl_InstanceID per triangle), which the ray meets as it
+// is — no transform, no instance record.  HASINST = false (every instance of the scene is baked: the Cornell box, the
+// BSDF gallery): the ray is done when that stack drains, and none of the two-level state below exists in the kernel.
+// HASINST = true: the ray then walks the TLAS over the remaining (large, instanced) meshes; on an instance leaf it is
+// taken to object space (unnormalised direction, so t is shared between levels) and walks that mesh's BLAS; a stack mark
+// returns it to the top level.
+//
 // Pass shape: the lanes of a persistent warp drift apart (different rays, different depths), so at any moment some
-// want to (1) descend one node, some to (2a) enter an instance at the top level, some to (2b) test pending triangles
-// at the bottom level, and the rest have nothing pending and (3) pop.  Running every phase in every pass under its
+// want to (1) descend one node, some to (2a) enter an instance at the top level, some to (2b) test pending triangles,
+// and the rest have nothing pending and (3) pop.  Running every phase in every pass under its
 // own predicate would issue each phase for a handful of lanes.  Instead the warp votes: a phase runs in this pass only
 // if at least `vote` lanes are waiting for it (if no phase has a quorum, the one with the most lanes runs, so every
 // pass makes progress); a lane whose phase sits the pass out simply keeps its state.  Lanes that arrive at a phase
@@ -258,13 +267,14 @@ GSB_D void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :
 // (hit.inst = 0).  The first kSmemStack stack entries live in shared memory ([entry][thread]: conflict-free 64-bit
 // accesses); deeper entries spill to local memory.  Closest hit: u and v are kept as numerators (hit.u = V,
 // hit.v = W, with `hitDet`) while the ray is in flight and divided once when it is handed in.
-template <bool ANYHIT, bool STATS, class Source>
+template <bool ANYHIT, bool STATS, bool HASINST, class Source>
 GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceStats* stats, uint32_t* overflowFlag) {
     const uint32_t refillMin = control & 0xffu;
     const int vote = (int)((control >> 8) & 0xffu);
     const int triMin = (int)((control >> 16) & 0xffu);
+    constexpr int kLocalStack = HASINST ? kStackSize - kSmemStack : kWorldStackSize - kSmemStack;
     __shared__ uint2 s_stack[kSmemStack][kTraceBlock];
-    uint2 lstack[kStackSize - kSmemStack];
+    uint2 lstack[kLocalStack];
     const uint32_t tid = threadIdx.x;
 
     RayJob job;
@@ -272,21 +282,24 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
     HitRecord hit;
     float hitDet = 1.0f;
     bool active = false;
-    int sp = 0, spMark = -1;
-    float widx = 0.0f, widy = 0.0f, widz = 0.0f;
-    uint32_t woct = 0;
-    const uint4* nodes = sc.tlasNodes;
-    const float4* tris = nullptr;
+    int sp = 0;
+    // current level: origin, reciprocal direction and octant used by the node tests; shear constants used by the triangle tests
     float cox = 0.0f, coy = 0.0f, coz = 0.0f, cidx = 0.0f, cidy = 0.0f, cidz = 0.0f;
-    uint32_t oct7 = 0, curInst = 0;
+    uint32_t oct7 = 0;
     ObjRay oray;
     uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
+    // two-level state (HASINST only)
+    int spMark = 0;            // >= 0: inside a bottom-level structure whose stack starts here; -1: at the top level
+    bool inWorld = true;       // the bottom-level structure is the world level
+    uint32_t curInst = 0;
+    const uint4* nodes = sc.worldNodes;
+    const float4* tris = sc.worldTris;
 
-#define GSB_PUSH(entry)                                                      \
-    do {                                                                     \
-        if (sp < kSmemStack) s_stack[sp++][tid] = (entry);                   \
-        else if (sp < kStackSize) lstack[sp++ - kSmemStack] = (entry);       \
-        else if (overflowFlag) *overflowFlag = 1u;                           \
+#define GSB_PUSH(entry)                                                          \
+    do {                                                                         \
+        if (sp < kSmemStack) s_stack[sp++][tid] = (entry);                       \
+        else if (sp < kSmemStack + kLocalStack) lstack[sp++ - kSmemStack] = (entry); \
+        else if (overflowFlag) *overflowFlag = 1u;                               \
     } while (0)
 
     for (;;) {
@@ -306,12 +319,13 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
             if (got) {
                 active = true;
                 hit.t = job.tmax; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT;
-                widx = slabInv(job.dx); widy = slabInv(job.dy); widz = slabInv(job.dz);
-                woct = (job.dx < 0.0f ? 0u : 4u) | (job.dy < 0.0f ? 0u : 2u) | (job.dz < 0.0f ? 0u : 1u);
-                nodes = sc.tlasNodes;
-                cox = job.ox; coy = job.oy; coz = job.oz; cidx = widx; cidy = widy; cidz = widz;
-                oct7 = woct;
-                sp = 0; spMark = -1;
+                // the world level: the ray as it is
+                cox = job.ox; coy = job.oy; coz = job.oz;
+                cidx = slabInv(job.dx); cidy = slabInv(job.dy); cidz = slabInv(job.dz);
+                oct7 = (job.dx < 0.0f ? 0u : 4u) | (job.dy < 0.0f ? 0u : 2u) | (job.dz < 0.0f ? 0u : 1u);
+                makeObjRay(job.ox, job.oy, job.oz, job.dx, job.dy, job.dz, oray);
+                sp = 0;
+                if (HASINST) { spMark = 0; inWorld = true; nodes = sc.worldNodes; tris = sc.worldTris; }
                 G = make_uint2(0u, 0x80000000u);  // root group: bit 31, imask 0 -> node childBase + 0
                 T = make_uint2(0u, 0u);
             }
@@ -321,13 +335,14 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
             }
         }
         // ---- vote: which phases run in this pass
-        bool run1, run2a, run2b;
+        bool run1, run2a = false, run2b;
         {
             const bool hasT = active && T.y != 0u;
             const int n1 = __popc(__ballot_sync(0xffffffffu, active && !hasT && (G.y & 0xff000000u) != 0u));
-            const int n2a = __popc(__ballot_sync(0xffffffffu, hasT && spMark < 0));
-            const int n2b = __popc(__ballot_sync(0xffffffffu, hasT && spMark >= 0));
-            run1 = n1 >= vote; run2a = n2a >= vote; run2b = n2b >= vote;
+            const int n2a = HASINST ? __popc(__ballot_sync(0xffffffffu, hasT && spMark < 0)) : 0;
+            const int n2b = __popc(__ballot_sync(0xffffffffu, hasT && (!HASINST || spMark >= 0)));
+            run1 = n1 >= vote; run2b = n2b >= vote;
+            if (HASINST) run2a = n2a >= vote;
             if (!(run1 || run2a || run2b)) {
                 if (n1 >= n2a && n1 >= n2b) run1 = true;
                 else if (n2a >= n2b) run2a = true;
@@ -342,10 +357,10 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
             const uint32_t nodeIndex = G.x + __popc(G.y & ((1u << slot) - 1u) & 0xffu);
             if (G.y & 0xff000000u) GSB_PUSH(G);
             if (STATS) stats->nodes++;
-            intersectNode(nodes, nodeIndex, cox, coy, coz, cidx, cidy, cidz, job.tmin, hit.t, oct7, G, T);
+            intersectNode(HASINST ? nodes : sc.worldNodes, nodeIndex, cox, coy, coz, cidx, cidy, cidz, job.tmin, hit.t, oct7, G, T);
         }
         // ---- phase 2a (top level): enter one instance, park the rest of this node
-        if (run2a && active && spMark < 0 && T.y) {
+        if (HASINST && run2a && active && spMark < 0 && T.y) {
             const uint32_t bit = (uint32_t)__ffs(T.y) - 1u;
             T.y &= ~(1u << bit);
             const TraceInstance* ti = sc.tlasInst + (T.x + bit);
@@ -385,13 +400,13 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
         // the interval.  The loop keeps spinning while at least triMin lanes still have triangles.
         if (run2b) {
             for (bool first = true;; first = false) {
-                const bool w = active && spMark >= 0 && T.y != 0u;
+                const bool w = active && (!HASINST || spMark >= 0) && T.y != 0u;
                 const uint32_t m = __ballot_sync(0xffffffffu, w);
                 if (!m || (!first && __popc(m) < triMin)) break;
                 if (w) {
                     const uint32_t bit = (uint32_t)__ffs(T.y) - 1u;
                     T.y &= ~(1u << bit);
-                    const float4* tp = tris + ((size_t)(T.x + bit) * 9 + oray.perm * 3u);
+                    const float4* tp = (HASINST ? tris : sc.worldTris) + ((size_t)(T.x + bit) * 9 + oray.perm * 3u);
                     const float4 v0 = __ldg(tp), v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
                     if (STATS) stats->tris++;
                     float Tn, V, W, det;
@@ -402,10 +417,12 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
                                 // occluded: drop everything still pending, phase 3 ends the ray
                                 hit.inst = 0u; hit.prim = 0u; hit.t = 0.0f;
                                 T.y = 0u; G.y = 0u; sp = 0;
+                                if (HASINST) spMark = -1;
                             } else {
                                 const uint32_t prim = __float_as_uint(v0.w);
-                                if (t < hit.t || (t == hit.t && (curInst < hit.inst || (curInst == hit.inst && prim < hit.prim)))) {
-                                    hit.t = t; hit.u = V; hit.v = W; hitDet = det; hit.inst = curInst; hit.prim = prim;
+                                const uint32_t inst = (!HASINST || inWorld) ? __float_as_uint(v1.w) : curInst;
+                                if (t < hit.t || (t == hit.t && (inst < hit.inst || (inst == hit.inst && prim < hit.prim)))) {
+                                    hit.t = t; hit.u = V; hit.v = W; hitDet = det; hit.inst = inst; hit.prim = prim;
                                 }
                             }
                         }
@@ -413,21 +430,32 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
                 }
             }
         }
-        // ---- phase 3: nothing pending in this node -> leave the instance if its stack is drained, then pop
+        // ---- phase 3: nothing pending in this node -> leave the level if its stack is drained, then pop
         if (active && !T.y && !(G.y & 0xff000000u)) {
-            if (sp == spMark) {
+            bool pop = true;
+            if (HASINST && sp == spMark) {
+                // back to the top level: the world ray again
                 spMark = -1;
                 nodes = sc.tlasNodes;
-                cox = job.ox; coy = job.oy; coz = job.oz; cidx = widx; cidy = widy; cidz = widz;
-                oct7 = woct;
+                cox = job.ox; coy = job.oy; coz = job.oz;
+                cidx = slabInv(job.dx); cidy = slabInv(job.dy); cidz = slabInv(job.dz);
+                oct7 = (job.dx < 0.0f ? 0u : 4u) | (job.dy < 0.0f ? 0u : 2u) | (job.dz < 0.0f ? 0u : 1u);
+                if (inWorld) {
+                    // the world level is done: start the top level at its root
+                    inWorld = false;
+                    G = make_uint2(0u, 0x80000000u);
+                    pop = false;
+                }
             }
-            if (sp == 0) {
-                active = false;  // this ray is done; its result is handed in at the next refill
-            } else {
-                --sp;
-                const uint2 e = sp < kSmemStack ? s_stack[sp][tid] : lstack[sp - kSmemStack];
-                if (e.y & 0xff000000u) { G = e; T = make_uint2(0u, 0u); }
-                else { T = e; G = make_uint2(0u, 0u); }
+            if (pop) {
+                if (sp == 0) {
+                    active = false;  // this ray is done; its result is handed in at the next refill
+                } else {
+                    --sp;
+                    const uint2 e = sp < kSmemStack ? s_stack[sp][tid] : lstack[sp - kSmemStack];
+                    if (e.y & 0xff000000u) { G = e; T = make_uint2(0u, 0u); }
+                    else { T = e; G = make_uint2(0u, 0u); }
+                }
             }
         }
     }

@@ -224,7 +224,7 @@ struct ExtendSource {
     }
 };
 
-template <bool STATS>
+template <bool STATS, bool HASINST>
 __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_extend(SceneDev sc, WavefrontState wf, RenderArgs ra, uint32_t parity) {
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_extend(SceneDe
     }
     ExtendSource src(sc, wf, ra, qc);
     TraceStats ts = {0u, 0u, 0u};
-    traceStream<false, STATS>(sc, src, ra.refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+    traceStream<false, STATS, HASINST>(sc, src, ra.refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
     // extension rays traced by this warp -> this iteration's counter bank
     uint32_t traced = src.traced;
     for (int o = 16; o > 0; o >>= 1) traced += __shfl_xor_sync(0xffffffffu, traced, o);
@@ -522,11 +522,11 @@ struct ShadowSource {
     }
 };
 
-template <bool STATS>
+template <bool STATS, bool HASINST>
 __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_shadow(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t refillMin) {
     ShadowSource src(sc, wf, wf.qCount + parity * Q_COUNT);
     TraceStats ts = {0u, 0u, 0u};
-    traceStream<true, STATS>(sc, src, refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+    traceStream<true, STATS, HASINST>(sc, src, refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
     if (STATS) flushTraceStats(wf.stats, ts, src.traced);
 }
 
@@ -662,8 +662,16 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, kBlock, 0);
         return std::max(1, std::min(fullGrid, sms * std::max(perSm, 1)));
     };
-    const int extendGrid = residentGrid((ctx->instrumented & 1) ? (const void*)k_extend<true> : (const void*)k_extend<false>);
-    const int shadowGrid = residentGrid((ctx->instrumented & 2) ? (const void*)k_shadow<true> : (const void*)k_shadow<false>);
+    // the traversal kernels exist per (instrumented, scene has instances that are not baked)
+    using ExtendKernel = void (*)(SceneDev, WavefrontState, RenderArgs, uint32_t);
+    using ShadowKernel = void (*)(SceneDev, WavefrontState, uint32_t, uint32_t);
+    static const ExtendKernel extendKernels[4] = {k_extend<false, false>, k_extend<false, true>, k_extend<true, false>, k_extend<true, true>};
+    static const ShadowKernel shadowKernels[4] = {k_shadow<false, false>, k_shadow<false, true>, k_shadow<true, false>, k_shadow<true, true>};
+    const int hasInst = ctx->numTraceInstances > 0 ? 1 : 0;
+    const ExtendKernel extendKernel = extendKernels[((ctx->instrumented & 1) ? 2 : 0) | hasInst];
+    const ShadowKernel shadowKernel = shadowKernels[((ctx->instrumented & 2) ? 2 : 0) | hasInst];
+    const int extendGrid = residentGrid((const void*)extendKernel);
+    const int shadowGrid = residentGrid((const void*)shadowKernel);
     k_generate<<<fullGrid, kBlock, 0, s>>>(sc, wf, ra);
     ctx->launches += 1;
     ctx->lastRenderIters = 0;
@@ -684,8 +692,7 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     uint32_t parity = 0;
     auto iteration = [&]() {
         mark();
-        if (ctx->instrumented & 1) k_extend<true><<<extendGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
-        else k_extend<false><<<extendGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
+        extendKernel<<<extendGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
         mark();
         if (ctx->typeUsed[0]) launchShade<0>(ctx, sc, queueGrid, parity, slots);
         if (ctx->typeUsed[1]) launchShade<1>(ctx, sc, queueGrid, parity, slots);
@@ -697,8 +704,7 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         if (ctx->typeUsed[7]) launchShade<7>(ctx, sc, queueGrid, parity, slots);
         if (ctx->typeUsed[8]) launchShade<8>(ctx, sc, queueGrid, parity, slots);
         mark();
-        if (ctx->instrumented & 2) k_shadow<true><<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ra.refillMin & 0xffu);
-        else k_shadow<false><<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ra.refillMin & 0xffu);
+        shadowKernel<<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ra.refillMin & 0xffu);
         mark();
         mark();
         parity ^= 1u;

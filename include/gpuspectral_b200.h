@@ -137,6 +137,9 @@ typedef struct gsb_bvh_stats {
     uint64_t bvh_bytes;                /* nodes + packed triangles + instance records */
     double   build_ms;                 /* device time of the last build (all BLAS + TLAS) */
     double   sah_cost_before, sah_cost_after; /* binary-tree SAH before/after treelet refinement, summed over meshes */
+    /* world level: instances of small meshes are stored as world-space triangles under one BVH of their own (no ray
+     * transform, no instance record on the way to them); the TLAS covers the remaining instances */
+    uint64_t baked_instances, baked_triangles, world_nodes;
 } gsb_bvh_stats;
 
 /* ---- context ------------------------------------------------------------------- */

@@ -11,7 +11,9 @@
 // What has no source in the reference is the ray/triangle intersection itself (the Vulkan
 // driver / RT hardware behind traceRayEXT): PARITY UNPINNED for that part.  The oracle
 // DEFINES it as: per instance, the world ray is taken to object space with the inverse
-// instance matrix (direction not renormalised, so t is shared with world space), every
+// instance matrix (direction not renormalised, so t is shared with world space) — or, for
+// instances of small meshes, the triangles are taken to world space once instead (the bake
+// rule next to kBakeMaxTris) and the ray is used as it is — every
 // triangle is tested with the watertight test of Woop, Benthin & Wald (JCGT 2013) in
 // float32 with individually rounded operations (no FMA contraction), candidates need
 // tmin < t < tmax (Vulkan's triangle interval), and the closest hit is the minimum of
@@ -38,6 +40,7 @@
 #include <cstdint>
 #include <cstring>
 #include <limits>
+#include <memory>
 #include <vector>
 #ifdef _OPENMP
 #include <omp.h>
@@ -167,7 +170,15 @@ struct Instance {
     float w2o[12];            // rows of the 3x4 world->object matrix
     float nrmM[9];            // upper-left 3x3 of inverse(transpose(M)), row-major (PathTracer.cpp:62)
     double wlo[3], whi[3];    // padded world bounds
+    std::shared_ptr<Mesh> world;  // baked instance: its triangles in world space (+ their BVH); null = traced in object space
 };
+
+// Bake rule (shared with the product, gpuspectral_b200/csrc/api.cu): walking the instances in gl_InstanceID order, an
+// instance whose mesh has at most kBakeMaxTris triangles is baked — its vertices are taken to world space once,
+// x' = ((m0*x + m1*y) + m2*z) + m3 per row in float32 (the operation order of gl_ObjectToWorldEXT * vec4(p, 1) in
+// rayhit.rchit:679-681), and rays meet them untransformed — as long as the baked total stays within kBakeBudget.
+constexpr uint32_t kBakeMaxTris = 16384;
+constexpr uint64_t kBakeBudget = 1ull << 22;
 
 }  // namespace
 
@@ -206,8 +217,10 @@ struct ObjRay {           // object-space ray + Woop precomputation
     float Sx, Sy, Sz;
 };
 
+// M = nullptr: the ray is used as it is (baked instances, whose triangles are stored in world space)
 inline void makeObjRay(const float* M /*3x4 rows*/, const float* o, const float* d, ObjRay& r) {
     for (int i = 0; i < 3; i++) {
+        if (!M) { r.o[i] = o[i]; r.d[i] = d[i]; continue; }
         const float* m = M + 4 * i;
         r.o[i] = ((m[0] * o[0] + m[1] * o[1]) + m[2] * o[2]) + m[3];
         r.d[i] = (m[0] * d[0] + m[1] * d[1]) + m[2] * d[2];
@@ -398,13 +411,13 @@ Hit traceF32(const or_scene& s, const float* o, const float* d, float tmin, floa
     const double od[3] = {o[0], o[1], o[2]}, dd[3] = {d[0], d[1], d[2]};
     for (uint32_t i = 0; i < (uint32_t)s.instances.size(); i++) {
         const Instance& in = s.instances[i];
-        const Mesh& m = s.meshes[in.src.mesh];
+        const Mesh& m = in.world ? *in.world : s.meshes[in.src.mesh];
         if (useBvh) {
             const double far = anyHit ? (double)tmax : (double)best.t;
             if (!slab(in.wlo, in.whi, od, dd, (double)tmin, far)) continue;
         }
         ObjRay r;
-        makeObjRay(in.w2o, o, d, r);
+        makeObjRay(in.world ? nullptr : in.w2o, o, d, r);
         if (useBvh) traceInstanceBvh(m, r, i, tmin, tmax, best, anyHit, occluded);
         else traceInstanceBrute(m, r, i, tmin, tmax, best, anyHit, occluded);
         if (occluded) { best.inst = 0; best.prim = 0; best.t = 0.0f; return best; }
@@ -1296,15 +1309,38 @@ uint32_t or_scene_add_mesh(or_scene* s, const float* positions3, const float* no
 
 int or_scene_set_instances(or_scene* s, const gsb_instance* instances, uint32_t count) {
     s->instances.clear();
+    uint64_t baked = 0;
     for (uint32_t i = 0; i < count; i++) {
         if (instances[i].mesh >= s->meshes.size()) return 1;
         Instance in;
         in.src = instances[i];
         deriveInstance(in);
         instanceBounds(*s, in);
+        const Mesh& m = s->meshes[in.src.mesh];
+        if (m.ntris > 0 && m.ntris <= kBakeMaxTris && baked + m.ntris <= kBakeBudget) {
+            baked += m.ntris;
+            in.world = std::make_shared<Mesh>();
+            in.world->ntris = m.ntris;
+            in.world->pos.resize(m.pos.size());
+            for (size_t v = 0; v < m.pos.size() / 3; v++) {
+                const float* p = &m.pos[3 * v];
+                for (int r = 0; r < 3; r++) {
+                    const float* row = in.o2w + 4 * r;
+                    in.world->pos[3 * v + r] = ((row[0] * p[0] + row[1] * p[1]) + row[2] * p[2]) + row[3];
+                }
+            }
+            buildMeshBvh(*in.world);
+            for (int a = 0; a < 3; a++) { in.wlo[a] = in.world->lo[a]; in.whi[a] = in.world->hi[a]; }
+        }
         s->instances.push_back(in);
     }
     return 0;
+}
+
+uint32_t or_scene_baked_instances(const or_scene* s) {
+    uint32_t n = 0;
+    for (const Instance& in : s->instances) n += in.world ? 1u : 0u;
+    return n;
 }
 
 int or_scene_set_bsdfs(or_scene* s, uint32_t type, const void* params, uint32_t count) {

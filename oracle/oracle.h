@@ -42,6 +42,8 @@ or_scene* or_scene_create(void);
 void or_scene_destroy(or_scene* s);
 uint32_t or_scene_add_mesh(or_scene* s, const float* positions3, const float* normals3, uint32_t nverts);
 int or_scene_set_instances(or_scene* s, const gsb_instance* instances, uint32_t count);
+/* number of instances whose triangles are stored in world space (the bake rule of oracle.cpp: kBakeMaxTris / kBakeBudget) */
+uint32_t or_scene_baked_instances(const or_scene* s);
 int or_scene_set_bsdfs(or_scene* s, uint32_t type, const void* params, uint32_t count);
 int or_scene_set_lights(or_scene* s, const gsb_triangle_light* lights, uint32_t count);
 void or_scene_set_camera(or_scene* s, const float eye[3], const float to_world[16], float fov_radians);
