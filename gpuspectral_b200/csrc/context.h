@@ -39,6 +39,7 @@ struct WavefrontState {
     float4* shadowD = nullptr;      // direction.xyz, slot id bits
     float4* shadowBase = nullptr;   // emitted without NEE .xyz, directWeight if visible
     float4* shadowNee = nullptr;    // NEE contribution .xyz
+    unsigned long long* chunkWork = nullptr;  // per slot chunk: the partly used block of work items it holds (wavefront.cu: packWork)
     uint32_t* qCount = nullptr;     // 2 x Q_COUNT queue counters
     // device statistics block: [0] live slots, [2..] totals
     unsigned long long* stats = nullptr;

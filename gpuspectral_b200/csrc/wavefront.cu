@@ -64,6 +64,18 @@ struct RenderArgs {
     float4* accum;                  // the image: rgb = sum of samples, a = samples added
 };
 
+// Which pixel-sample a slot renders next.  The work items [0, totalWork) are handed out in BLOCKS of 32 consecutive items
+// (32 neighbouring pixels of one sample: a warp's regenerated rays start out coherent) from one global block counter
+// (ST_NEXTWORK); a block belongs to the slot chunk (WorkRange::kChunk slots) whose finished slot asked for it, and the
+// chunk's other slots use up the rest of it as their paths end.  A chunk's partly used block (WavefrontState::chunkWork:
+// block index, items used, "no more work" flag) is only ever touched by the warp that holds the chunk in the current
+// launch, so only one request in ~32 costs an atomic operation — the single per-refill counter this replaces was 36 % of
+// k_extend's stall samples (r2b: about a million same-address 64-bit atomics per launch).  Nothing is stranded: a slot is
+// retired only when its chunk's block is used up and the global counter has run past the end, and whatever a chunk still
+// holds is taken by its remaining slots.
+constexpr unsigned long long kWorkExhausted = 1ull << 6;   // chunkWork: bits 0..5 items used of the block (32 = none left), bit 6, bits 7.. block
+GSB_D unsigned long long packWork(unsigned long long block, uint32_t used) { return (block << 7) | used; }
+
 // Warp-aggregated append: every lane of the warp must call this (pred false = no push).
 // key selects one of the queue counters; returns the position for lanes with pred.
 GSB_D uint32_t queueSlot(uint32_t* counters, uint32_t key, bool pred) {
@@ -114,8 +126,8 @@ __global__ void k_generate(SceneDev sc, WavefrontState wf, RenderArgs ra) {
     if (slot >= ra.slots) return;
     float4 o, d;
     uint32_t pixel;
-    if (slot < ra.totalWork) startPath(sc, wf, ra, slot, slot, o, d, pixel);
-    else { wf.sampleK[slot] = kRetired; wf.hitInst[slot] = GSB_NO_HIT; }
+    if (slot % WorkRange::kChunk == 0) wf.chunkWork[slot / WorkRange::kChunk] = packWork(0ull, 32u);   // no block yet
+    startPath(sc, wf, ra, slot, slot, o, d, pixel);   // slots <= totalWork: the first `slots` items start out in slot order
 }
 
 // ---- extend ---------------------------------------------------------------------------------------
@@ -146,8 +158,22 @@ struct ExtendSource {
     WorkRange range;
     uint32_t pix = 0;   // pixel of the lane's current path
     uint32_t traced = 0;
+    // work counters (warp-uniform): the chunk whose counter is held in registers, and the one loaded ahead
+    // work blocks (warp-uniform, kept in shared memory so that they cost no registers inside the traversal loop): the chunk
+    // whose block state is held, and the one loaded ahead
+    struct WarpWork { uint32_t wkChunk, nxChunk; unsigned long long wkV, nxV; };
+    WarpWork* ww;
 
-    GSB_D ExtendSource(const SceneDev& s, const WavefrontState& w, const RenderArgs& r, uint32_t* q) : sc(s), wf(w), ra(r), qc(q) {}
+    // writes the held block state back (chunk switch, end of the kernel)
+    GSB_D void flushWork() {
+        if (ww->wkChunk != 0xffffffffu && (threadIdx.x & 31u) == 0u) wf.chunkWork[ww->wkChunk] = ww->wkV;
+        __syncwarp();
+    }
+
+    GSB_D ExtendSource(const SceneDev& s, const WavefrontState& w, const RenderArgs& r, uint32_t* q, WarpWork* work) : sc(s), wf(w), ra(r), qc(q), ww(work) {
+        if ((threadIdx.x & 31u) == 0u) { ww->wkChunk = 0xffffffffu; ww->nxChunk = 0xffffffffu; ww->wkV = 0ull; ww->nxV = 0ull; }
+        __syncwarp();
+    }
     GSB_D bool drained() const { return range.exhausted; }
 
     GSB_D bool fetch(bool want, RayJob& job) {
@@ -178,23 +204,62 @@ struct ExtendSource {
                 atomicAdd(&ra.accum[p & ~kFinished], make_float4(res.x, res.y, res.z, 1.0f));
         }
         const uint32_t fmask = __ballot_sync(0xffffffffu, finished);
+        const uint32_t lane = threadIdx.x & 31u;
         if (fmask) {
-            // next pixel-sample for every finished slot of the warp: one atomic per warp
-            const uint32_t lane = threadIdx.x & 31u;
-            const uint32_t leader = (uint32_t)__ffs(fmask) - 1u;
-            unsigned long long base = 0;
-            if (lane == leader) base = atomicAdd(&wf.stats[ST_NEXTWORK], (unsigned long long)__popc(fmask));
-            base = __shfl_sync(0xffffffffu, base, leader);
+            // next pixel-sample for every finished slot of the warp, from the block its chunk holds (a refill spans at
+            // most two chunks: the tail of the current one and the head of the next)
+            const uint32_t chunk = slot / WorkRange::kChunk;
             bool retire = false;
-            if (finished) {
-                const unsigned long long work = base + (unsigned long long)__popc(fmask & ((1u << lane) - 1u));
-                if (work < ra.totalWork) startPath(sc, wf, ra, slot, work, o, d, p);
-                else { wf.sampleK[slot] = kRetired; wf.hitInst[slot] = GSB_NO_HIT; retire = true; live = false; }
+            uint32_t todo = fmask;
+            while (todo) {
+                const uint32_t c = __shfl_sync(0xffffffffu, chunk, (uint32_t)__ffs(todo) - 1u);
+                const uint32_t grp = __ballot_sync(0xffffffffu, finished && chunk == c);
+                todo &= ~grp;
+                if (c != ww->wkChunk) {
+                    flushWork();
+                    if (lane == 0) {
+                        ww->wkV = (c == ww->nxChunk) ? ww->nxV : wf.chunkWork[c];
+                        ww->wkChunk = c;
+                    }
+                    __syncwarp();
+                }
+                const unsigned long long wkV = ww->wkV;
+                const uint32_t n = (uint32_t)__popc(grp), used = (uint32_t)(wkV & 63ull), avail = 32u - used;
+                unsigned long long block = wkV >> 7, fresh = ~0ull;
+                bool exhausted = (wkV & kWorkExhausted) != 0ull;
+                if (n > avail && !exhausted) {
+                    // the rest of the group opens a new block: the one atomic of ~32 requests
+                    if (lane == 0) fresh = atomicAdd(&wf.stats[ST_NEXTWORK], 1ull);
+                    fresh = __shfl_sync(0xffffffffu, fresh, 0);
+                    if (fresh * 32ull >= ra.totalWork) { exhausted = true; fresh = ~0ull; }
+                }
+                if (finished && chunk == c) {
+                    const uint32_t rank = (uint32_t)__popc(grp & ((1u << lane) - 1u));
+                    unsigned long long work = ~0ull;
+                    if (rank < avail) work = block * 32ull + used + rank;
+                    else if (fresh != ~0ull) work = fresh * 32ull + (rank - avail);
+                    if (work < ra.totalWork) startPath(sc, wf, ra, slot, work, o, d, p);
+                    else { wf.sampleK[slot] = kRetired; wf.hitInst[slot] = GSB_NO_HIT; retire = true; live = false; }
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    if (n <= avail) ww->wkV = packWork(block, used + n) | (exhausted ? kWorkExhausted : 0ull);
+                    else if (fresh != ~0ull) ww->wkV = packWork(fresh, n - avail);
+                    else ww->wkV = packWork(block, 32u) | kWorkExhausted;
+                }
+                __syncwarp();
             }
             const uint32_t rmask = __ballot_sync(0xffffffffu, retire);
             if (rmask && lane == (uint32_t)__ffs(rmask) - 1u)
                 atomicAdd(&wf.stats[ST_LIVE], (unsigned long long)(-(long long)__popc(rmask)));
         }
+        // the counter of the chunk this warp moves to next: loaded one refill ahead, off the critical path
+        if (range.haveNext && lane == 0 && ww->nxChunk != range.next / WorkRange::kChunk) {
+            const uint32_t nx = range.next / WorkRange::kChunk;
+            ww->nxChunk = nx;
+            ww->nxV = nx * WorkRange::kChunk < ra.slots ? wf.chunkWork[nx] : 0ull;   // a load nobody waits for until the chunk switch
+        }
+        __syncwarp();
         // the state words of the slots this warp will take next: into L1 while the rays just fetched are traced
         const uint32_t ahead = range.peek(ra.slots);
         if (ahead != kNoTag) {
@@ -237,9 +302,11 @@ __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_extend(SceneDe
         wf.stats[ST_ITERS] += 1;
         for (int q = 0; q < Q_COUNT; q++) prev[q] = 0;
     }
-    ExtendSource src(sc, wf, ra, qc);
+    __shared__ ExtendSource::WarpWork s_work[kBlock / 32];
+    ExtendSource src(sc, wf, ra, qc, &s_work[threadIdx.x >> 5]);
     TraceStats ts = {0u, 0u, 0u};
     traceStream<false, STATS, HASINST>(sc, src, ra.refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+    src.flushWork();
     // extension rays traced by this warp -> this iteration's counter bank
     uint32_t traced = src.traced;
     for (int o = 16; o > 0; o >>= 1) traced += __shfl_xor_sync(0xffffffffu, traced, o);
@@ -566,6 +633,7 @@ void allocWavefront(gsb_context* ctx, uint32_t slots) {
     ensure(wf.sampleK, n); ensure(wf.hitTUVP, n); ensure(wf.hitInst, n);
 
     ensure(wf.shadowO, n); ensure(wf.shadowD, n); ensure(wf.shadowBase, n); ensure(wf.shadowNee, n);
+    ensure(wf.chunkWork, (n + WorkRange::kChunk - 1) / WorkRange::kChunk);
     if (!wf.qCount) ensure(wf.qCount, (size_t)2 * Q_COUNT);
     if (!wf.stats) {
         ensure(wf.stats, (size_t)ST_COUNT);
@@ -584,7 +652,7 @@ void launchShade(gsb_context* ctx, const SceneDev& sc, int grid, uint32_t parity
 void freeWavefront(gsb_context* ctx) {
     WavefrontState& wf = ctx->wf;
     void* ptrs[] = {wf.rayO, wf.rayD, wf.weightDW, wf.result, wf.sampleK, wf.hitTUVP, wf.hitInst,
-                    wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.qCount, wf.stats};
+                    wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.qCount, wf.stats, wf.chunkWork};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     wf = WavefrontState();
@@ -628,7 +696,8 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     if (count == 0) return;
     // paths in flight: enough to fill the machine several times over, small enough that the path state stays near L2
     const unsigned long long totalWork = (unsigned long long)npix * count;
-    const uint32_t slots = (uint32_t)std::min<unsigned long long>(totalWork, ctx->targetSlots);
+    uint32_t slots = (uint32_t)std::min<unsigned long long>(totalWork, ctx->targetSlots);
+    if (slots < totalWork) slots = std::max(32u, slots & ~31u);   // the work-block counter starts right behind the slots' own items
     allocWavefront(ctx, slots);
     WavefrontState& wf = ctx->wf;
     RenderArgs ra;
@@ -643,9 +712,9 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     const SceneDev sc = ctx->sceneDev();
     GSB_CUDA(cudaMemsetAsync(wf.qCount, 0, 2 * Q_COUNT * sizeof(uint32_t), s));
     const unsigned long long liveInit[2] = {(unsigned long long)slots, 0ull};
-    const unsigned long long nextInit = (unsigned long long)slots;
     GSB_CUDA(cudaMemcpyAsync(wf.stats, liveInit, sizeof(liveInit), cudaMemcpyHostToDevice, s));
-    GSB_CUDA(cudaMemcpyAsync(&wf.stats[ST_NEXTWORK], &nextInit, sizeof(nextInit), cudaMemcpyHostToDevice, s));
+    const unsigned long long nextBlock = ((unsigned long long)slots + 31ull) / 32ull;   // the first `slots` items start out in the slots
+    GSB_CUDA(cudaMemcpyAsync(&wf.stats[ST_NEXTWORK], &nextBlock, sizeof(nextBlock), cudaMemcpyHostToDevice, s));
 
     cudaEvent_t evStart = nullptr, evStop = nullptr;
     GSB_CUDA(cudaEventCreate(&evStart));
