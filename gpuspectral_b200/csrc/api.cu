@@ -88,10 +88,11 @@ struct BatchSource {
         job.ox = a.x; job.oy = a.y; job.oz = a.z; job.tmin = a.w;
         job.dx = b.x; job.dy = b.y; job.dz = b.z; job.tmax = b.w;
         job.tag = i;
+        job.aux = 0u;
         traced++;
         return true;
     }
-    GSB_D void commit(bool have, const HitRecord& h, uint32_t i) {
+    GSB_D void commit(bool have, const HitRecord& h, uint32_t i, uint32_t) {
         if (!have) return;
         gsb_hit o;
         if (ANYHIT) {
@@ -105,14 +106,14 @@ struct BatchSource {
     }
 };
 
-template <bool ANYHIT, bool STATS, bool HASINST>
+template <bool ANYHIT, bool STATS, bool HASINST, bool POOL>
 __global__ void __launch_bounds__(kTraceBlock) k_traceBatch(SceneDev sc, const gsb_ray* __restrict__ rays, uint32_t n,
                                                             gsb_hit* __restrict__ hits, unsigned long long* stats, uint32_t refillMin) {
     BatchSource<ANYHIT> src;
     src.rays = rays; src.hits = hits; src.n = n;
     src.counter = reinterpret_cast<uint32_t*>(&stats[ST_BATCHNEXT]);
     TraceStats ts = {0u, 0u, 0u};
-    traceStream<ANYHIT, STATS, HASINST>(sc, src, refillMin, &ts, (uint32_t*)&stats[ST_OVERFLOW]);
+    traceStream<ANYHIT, STATS, HASINST, POOL>(sc, src, refillMin, &ts, (uint32_t*)&stats[ST_OVERFLOW]);
     if (STATS) {
         uint32_t nn = ts.nodes, nt = ts.tris, ni = ts.insts, nr = src.traced;
         for (int o = 16; o > 0; o >>= 1) {
@@ -329,6 +330,21 @@ static void normalMatrixGlm(const float* T, float out[3][3]) {
         for (int k = 0; k < 3; k++) out[r][k] = inv4[k][r] * oneOverDet;
 }
 
+// Traversal variant per scene (traverse.cuh): rays that end after a handful of passes (a world level of a few nodes and
+// nothing else: the Cornell box) are refilled straight from the source once 24 lanes are idle; longer-lived rays go
+// through the per-warp ray pool, where a lane is refilled as soon as it is idle.  GSB_POOL = bit 0 extend, bit 1 shadow
+// overrides; GSB_POOL_REFILL = idle lanes that trigger a refill out of the pool.
+static void choosePolicy(gsb_context* ctx) {
+    const bool longRays = ctx->numTraceInstances == 0 && ctx->world.numNodes > 16;   // two-level scenes: measured better without the pool (r2g / r2h)
+    ctx->poolExtend = ctx->poolShadow = longRays;
+    if (const char* e = getenv("GSB_POOL")) { const int v = atoi(e); ctx->poolExtend = (v & 1) != 0; ctx->poolShadow = (v & 2) != 0; }
+    uint32_t poolRefill = 1u;
+    if (const char* e = getenv("GSB_POOL_REFILL")) poolRefill = (uint32_t)std::min(32, std::max(1, atoi(e)));
+    const uint32_t direct = ctx->directRefill;
+    ctx->refillMin = (ctx->refillMin & ~0xffu) | (ctx->poolExtend ? poolRefill : direct);
+    ctx->shadowControl = ctx->poolShadow ? poolRefill : direct;
+}
+
 SceneDev gsb_context::sceneDev() const {
     SceneDev sc;
     memset(&sc, 0, sizeof(sc));
@@ -381,7 +397,7 @@ gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx) {
         if (const char* e = getenv("GSB_GRAPH")) ctx->useGraphLoop = atoi(e) != 0;
         if (const char* e = getenv("GSB_REFILL")) {
             const long v = atol(e);
-            if (v >= 1 && v <= 32) ctx->refillMin = (ctx->refillMin & ~0xffu) | (uint32_t)v;
+            if (v >= 1 && v <= 32) { ctx->refillMin = (ctx->refillMin & ~0xffu) | (uint32_t)v; ctx->directRefill = (uint32_t)v; }
         }
         if (const char* e = getenv("GSB_VOTE")) {
             const long v = atol(e);
@@ -626,6 +642,7 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
         buildTlas(wlo.data(), whi.data(), trace.data(), (uint32_t)trace.size(), ctx->stream, ctx->tlas);
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
         ctx->haveInstances = true;
+        choosePolicy(ctx);
         double ms = ctx->tlas.buildMs + ctx->world.buildMs;
         std::vector<bool> seen(ctx->meshes.size(), false);
         for (uint32_t i = 0; i < count; i++)
@@ -881,23 +898,28 @@ static gsb_status traceBatch(gsb_context* ctx, const gsb_ray* rays, uint32_t cou
         int sms = 148, perSm = 4;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
         const bool hasInst = ctx->numTraceInstances > 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, hasInst ? (const void*)k_traceBatch<false, false, true> : (const void*)k_traceBatch<false, false, false>, kTraceBlock, 0);
+        using BatchKernel = void (*)(SceneDev, const gsb_ray*, uint32_t, gsb_hit*, unsigned long long*, uint32_t);
+        static const BatchKernel kernels[16] = {
+            k_traceBatch<false, false, false, false>, k_traceBatch<false, false, true, false>, k_traceBatch<false, true, false, false>, k_traceBatch<false, true, true, false>,
+            k_traceBatch<true, false, false, false>,  k_traceBatch<true, false, true, false>,  k_traceBatch<true, true, false, false>,  k_traceBatch<true, true, true, false>,
+            k_traceBatch<false, false, false, true>,  k_traceBatch<false, false, true, true>,  k_traceBatch<false, true, false, true>,  k_traceBatch<false, true, true, true>,
+            k_traceBatch<true, false, false, true>,   k_traceBatch<true, false, true, true>,   k_traceBatch<true, true, false, true>,   k_traceBatch<true, true, true, true>};
+        // the batch entry runs the same traversal variant the render kernels of this scene use (pool or direct refill)
+        const bool pool = any_hit ? ctx->poolShadow : ctx->poolExtend;
+        const BatchKernel kernel = kernels[(pool ? 8 : 0) | (any_hit ? 4 : 0) | (stats ? 2 : 0) | (hasInst ? 1 : 0)];
+        const uint32_t control = any_hit ? ctx->shadowControl : ctx->refillMin;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, (const void*)kernel, kTraceBlock, 0);
         const int grid = std::max(1, std::min((int)((count + kTraceBlock - 1) / kTraceBlock), sms * std::max(perSm, 1)));
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (out_ms) {
             GSB_CUDA(cudaEventCreate(&e0));
             GSB_CUDA(cudaEventCreate(&e1));
         }
-        using BatchKernel = void (*)(SceneDev, const gsb_ray*, uint32_t, gsb_hit*, unsigned long long*, uint32_t);
-        static const BatchKernel kernels[8] = {
-            k_traceBatch<false, false, false>, k_traceBatch<false, false, true>, k_traceBatch<false, true, false>, k_traceBatch<false, true, true>,
-            k_traceBatch<true, false, false>,  k_traceBatch<true, false, true>,  k_traceBatch<true, true, false>,  k_traceBatch<true, true, true>};
-        const BatchKernel kernel = kernels[(any_hit ? 4 : 0) | (stats ? 2 : 0) | (hasInst ? 1 : 0)];
         for (int r = 0; r < repeats + (out_ms ? 1 : 0); r++) {
             if (out_ms && r == 1) GSB_CUDA(cudaEventRecord(e0, ctx->stream));  // launch 0 is a warm-up
             if (count == 0) break;
             GSB_CUDA(cudaMemsetAsync(&ctx->wf.stats[ST_BATCHNEXT], 0, sizeof(unsigned long long), ctx->stream));  // the stream's work counter
-            kernel<<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, ctx->refillMin);
+            kernel<<<grid, kTraceBlock, 0, ctx->stream>>>(sc, dRays, count, dHits, ctx->wf.stats, control);
         }
         GSB_CUDA(cudaGetLastError());
         if (out_ms) {

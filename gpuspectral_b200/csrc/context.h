@@ -91,6 +91,9 @@ struct gsb_context {
     // (bits 0..7, GSB_REFILL), lanes that make a quorum for a traversal phase (8..15, GSB_VOTE; closest-hit kernel only,
     // the any-hit kernel measured best without a quorum), lanes that keep the triangle loop spinning (16..23, GSB_TRIMIN)
     uint32_t refillMin = 24u | (4u << 8) | (2u << 16);
+    uint32_t directRefill = 24u;   // idle lanes that trigger a refill straight from the source (GSB_REFILL)
+    uint32_t shadowControl = 24u;  // the any-hit kernel's control word (no phase quorum measured best)
+    bool poolExtend = false, poolShadow = false;   // traverse.cuh: ray pool (true) or direct refill; chosen per scene in gsb_scene_set_instances, GSB_POOL overrides
     uint32_t shadeDirectMin = 32;  // k_shade: matching lanes from which a tile is shaded in place (GSB_SHADE_DIRECT; measured flat from 12 to 32)
     bool useGraphLoop = true;    // device-side render loop (conditional CUDA graph); GSB_GRAPH=0 or a failed build disables it
     int instrumented = 0;        // bit 0: count fetches of extension rays, bit 1: of shadow rays

@@ -178,6 +178,7 @@ GSB_D void intersectNode(const uint4* __restrict__ nodes, uint32_t nodeIndex, fl
 struct RayJob {
     float ox, oy, oz, dx, dy, dz, tmin, tmax;
     uint32_t tag;
+    uint32_t aux;   // a word of the source's own that travels with the ray and comes back in commit (extend: pixel, shadow: slot word)
 };
 constexpr uint32_t kNoTag = 0xffffffffu;
 
@@ -237,14 +238,20 @@ GSB_D void prefetchL1(const void* p) { asm volatile("prefetch.global.L1 [%0];" :
 GSB_D void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 // Traces a stream of rays with one persistent warp: the traversal loop never waits for the slowest ray of a
-// batch — a lane whose ray is finished hands its result to `src.commit` and gets the next ray from `src.fetch`
-// at the top of the next pass (dynamic ray fetch, Aila & Laine 2009), so all 32 lanes stay in flight until the
-// stream runs dry.
+// batch — a lane whose ray is finished hands its result to `src.commit` and takes the next ray at the top of the next
+// pass (dynamic ray fetch, Aila & Laine 2009), so all 32 lanes stay in flight until the stream runs dry.
 //
 // Source concept (all members are called by all 32 lanes together, warp-synchronously):
-//   void commit(bool have, const HitRecord& hit, uint32_t tag)   result of a finished ray (have = lane has one)
-//   bool fetch(bool want, RayJob& job)                           next ray for idle lanes; false = lane got none
+//   void commit(bool have, const HitRecord& hit, uint32_t tag, uint32_t aux)   result of a finished ray (have = lane has one)
+//   bool fetch(bool want, RayJob& job)                           next ray for the lanes that want one; false = lane got none
 //   bool drained()                                               warp-uniform: no more rays will ever come
+//
+// Ray pool.  Taking rays from the source is expensive (state loads from HBM, for k_extend also the end of the previous
+// path and the start of the next one), so it is never done for a few idle lanes: the warp fetches 32 rays at a time with
+// all lanes (coalesced loads, full lanes for the per-ray set-up: reciprocal direction, octant, the triangle test's shear
+// constants) into a ring of kPoolSize prepared rays in shared memory, and a lane whose ray has ended picks its next one
+// out of that ring at the top of the very next pass — four 128-bit shared-memory loads.  Round 1 refilled straight from
+// the source once 24 lanes were idle, which left 20 of 32 lanes active on the Cornell box (r1k / r2b ncu tables).
 //
 // Levels.  Every ray first walks the WORLD level: one BVH over the triangles of all baked instances, stored in world
 // space (api.cu: the bake rule; v0.w = gl_PrimitiveID, v1.w = gl_InstanceID per triangle), which the ray meets as it
@@ -262,25 +269,53 @@ GSB_D void prefetchL2(const void* p) { asm volatile("prefetch.global.L2 [%0];" :
 // pass makes progress); a lane whose phase sits the pass out simply keeps its state.  Lanes that arrive at a phase
 // while it runs (phase 1 hands triangles to 2b, 2a hands direct triangles to 2b) ride along.  Per-lane operation
 // order is unchanged, so results and fetch counts do not depend on the vote threshold.
-// `control` packs refillMin (bits 0..7), vote (8..15) and triMin (16..23: lanes needed to keep the triangle loop of
+// `control` packs vote (bits 8..15) and triMin (16..23: lanes needed to keep the triangle loop of
 // phase 2b spinning after its first round).  ANYHIT: a ray ends at the first triangle with tmin < t < tmax
 // (hit.inst = 0).  The first kSmemStack stack entries live in shared memory ([entry][thread]: conflict-free 64-bit
 // accesses); deeper entries spill to local memory.  Closest hit: u and v are kept as numerators (hit.u = V,
 // hit.v = W, with `hitDet`) while the ray is in flight and divided once when it is handed in.
-template <bool ANYHIT, bool STATS, bool HASINST, class Source>
+#ifndef GSB_POOL_SIZE
+#define GSB_POOL_SIZE 48
+#endif
+#ifndef GSB_POOL_SIZE_INST
+#define GSB_POOL_SIZE_INST 48   // two-level scenes carry one more row per entry: 48 entries keep 8 blocks per SM inside 227 KB
+#endif
+
+// POOL = false is round 1's scheme without the ring: rays go from the source straight into the lanes once `refillMin`
+// (control bits 0..7) of them are idle.  It wins on scenes whose rays end after a handful of passes (the Cornell box:
+// 1.6 nodes and 4.5 triangles per ray), where the pool's extra copy through shared memory costs more than the idle
+// lanes; the pool wins as soon as rays live longer (gallery: -18 % k_extend time; numbers in profiles/README.md, r2f).
+template <bool ANYHIT, bool STATS, bool HASINST, bool POOL, class Source>
 GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceStats* stats, uint32_t* overflowFlag) {
     const uint32_t refillMin = control & 0xffu;
     const int vote = (int)((control >> 8) & 0xffu);
     const int triMin = (int)((control >> 16) & 0xffu);
     constexpr int kLocalStack = HASINST ? kStackSize - kSmemStack : kWorldStackSize - kSmemStack;
+    constexpr int kPoolWords = HASINST ? 5 : 4;
+    constexpr uint32_t kPoolSize = HASINST ? GSB_POOL_SIZE_INST : GSB_POOL_SIZE;   // prepared rays per warp; 32 more are fetched when at most kPoolSize - 32 are left
+    auto wrap = [](uint32_t e) { return e >= kPoolSize ? e - kPoolSize : e; };
     __shared__ uint2 s_stack[kSmemStack][kTraceBlock];
+    // pool entry, one float4 per row: A = origin.xyz, tmax | B = 1/d .xyz (slab tests), octant + 8 * dominant axis |
+    // C = shear constants Sx, Sy, Sz, tag | D = tmin, aux, -, - | E (two-level scenes) = direction.xyz, -
+    __shared__ float4 s_pool[POOL ? kTraceBlock / 32 : 1][POOL ? kPoolWords : 1][POOL ? kPoolSize : 1];
+    // Cold per-lane state lives in shared memory ([word][thread]: conflict-free), not in registers: it is written when a
+    // ray starts or a closer hit is accepted and read when the ray is handed in (or, the world ray, when an instance is
+    // entered / left), never inside the node and triangle tests.  Rows: tag, aux, hit u, v, det, inst, prim, and for
+    // two-level scenes the world ray's origin and direction.
+    constexpr int kColdWords = HASINST ? 13 : 7;
+    __shared__ uint32_t s_cold[kColdWords][kTraceBlock];
+    enum { C_TAG = 0, C_AUX, C_U, C_V, C_DET, C_INST, C_PRIM, C_OX, C_OY, C_OZ, C_DX, C_DY, C_DZ };
+#define GSB_COLD(w) s_cold[w][tid]
+#define GSB_COLDF(w) __uint_as_float(s_cold[w][tid])
     uint2 lstack[kLocalStack];
-    const uint32_t tid = threadIdx.x;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    float4 (*pool)[POOL ? kPoolSize : 1] = s_pool[POOL ? tid >> 5 : 0];
+    uint32_t poolHead = 0, poolCount = 0;   // warp-uniform ring state
 
-    RayJob job;
-    job.tag = kNoTag;
-    HitRecord hit;
-    float hitDet = 1.0f;
+    // the lane's ray
+    bool hasRay = false;       // the lane holds a ray (in flight, or ended and not yet handed in)
+    float tmin = 0.0f, tmax = 0.0f;
+    float hitT = 0.0f;         // closest accepted t so far (tmax while there is none); the rest of the hit record is cold
     bool active = false;
     int sp = 0;
     // current level: origin, reciprocal direction and octant used by the node tests; shear constants used by the triangle tests
@@ -303,36 +338,127 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
     } while (0)
 
     for (;;) {
-        // ---- refill: hand in finished rays, take new ones (warp-uniform branch).  While the stream still has rays
-        // a refill waits until refillMin lanes are idle, so that its fixed cost (and the latency of the state
-        // loads) is shared by several rays.
+        if (POOL) {
+        // ---- hand in the rays that ended in the last pass
         const uint32_t idle = __ballot_sync(0xffffffffu, !active);
-        const uint32_t pending = __ballot_sync(0xffffffffu, !active && job.tag != kNoTag);
-        if (idle == 0xffffffffu || (src.drained() ? pending != 0u : (uint32_t)__popc(idle) >= refillMin)) {
-            if (!ANYHIT && !active && job.tag != kNoTag && hit.inst != GSB_NO_HIT) {
-                hit.u = __fdiv_rn(hit.u, hitDet);
-                hit.v = __fdiv_rn(hit.v, hitDet);
+        if (idle) {
+            const bool done = !active && hasRay;
+            if (__any_sync(0xffffffffu, done)) {
+                HitRecord hit;
+                hit.t = hitT; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT;
+                uint32_t tag = kNoTag, aux = 0u;
+                if (done) {
+                    tag = GSB_COLD(C_TAG); aux = GSB_COLD(C_AUX);
+                    hit.inst = GSB_COLD(C_INST); hit.prim = GSB_COLD(C_PRIM);
+                    if (!ANYHIT && hit.inst != GSB_NO_HIT) {
+                        const float det = GSB_COLDF(C_DET);
+                        hit.u = __fdiv_rn(GSB_COLDF(C_U), det);
+                        hit.v = __fdiv_rn(GSB_COLDF(C_V), det);
+                    }
+                }
+                src.commit(done, hit, tag, aux);
+                if (done) hasRay = false;
             }
-            src.commit(!active && job.tag != kNoTag, hit, job.tag);
-            if (!active) job.tag = kNoTag;
+        }
+        // ---- keep the pool stocked: 32 rays from the source with all lanes, prepared, appended to the ring
+        if (poolCount <= kPoolSize - 32u && !src.drained()) {
+            RayJob job;
+            const bool got = src.fetch(true, job);
+            const uint32_t m = __ballot_sync(0xffffffffu, got);
+            if (got) {
+                const uint32_t e = wrap(wrap(poolHead + poolCount) + (uint32_t)__popc(m & ((1u << lane) - 1u)));
+                ObjRay r;
+                makeObjRay(job.ox, job.oy, job.oz, job.dx, job.dy, job.dz, r);
+                const uint32_t oct = (job.dx < 0.0f ? 0u : 4u) | (job.dy < 0.0f ? 0u : 2u) | (job.dz < 0.0f ? 0u : 1u);
+                pool[0][e] = make_float4(job.ox, job.oy, job.oz, job.tmax);
+                pool[1][e] = make_float4(slabInv(job.dx), slabInv(job.dy), slabInv(job.dz), __uint_as_float(oct | (r.perm << 3)));
+                pool[2][e] = make_float4(r.Sx, r.Sy, r.Sz, __uint_as_float(job.tag));
+                pool[3][e] = make_float4(job.tmin, __uint_as_float(job.aux), 0.0f, 0.0f);
+                if (HASINST) pool[4][e] = make_float4(job.dx, job.dy, job.dz, 0.0f);
+            }
+            poolCount += (uint32_t)__popc(m);
+            __syncwarp();
+        }
+        // ---- idle lanes take their next ray out of the pool
+        if (idle && poolCount && ((uint32_t)__popc(idle) >= refillMin || idle == 0xffffffffu || src.drained())) {
+            const uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
+            const uint32_t n = min((uint32_t)__popc(idle), poolCount);
+            if (!active && rank < n) {
+                const uint32_t e = wrap(poolHead + rank);
+                const float4 a = pool[0][e], b = pool[1][e], c = pool[2][e], d = pool[3][e];
+                active = true;
+                cox = a.x; coy = a.y; coz = a.z; tmax = a.w;
+                cidx = b.x; cidy = b.y; cidz = b.z;
+                const uint32_t bits = __float_as_uint(b.w);
+                oct7 = bits & 7u;
+                oray.perm = bits >> 3;
+                permute(oray.perm, a.x, a.y, a.z, oray.ox, oray.oy, oray.oz);
+                oray.Sx = c.x; oray.Sy = c.y; oray.Sz = c.z;
+                hasRay = true;
+                GSB_COLD(C_TAG) = __float_as_uint(c.w);
+                tmin = d.x; GSB_COLD(C_AUX) = __float_as_uint(d.y);
+                if (HASINST) {
+                    const float4 dd = pool[4][e];
+                    GSB_COLD(C_OX) = __float_as_uint(a.x); GSB_COLD(C_OY) = __float_as_uint(a.y); GSB_COLD(C_OZ) = __float_as_uint(a.z);
+                    GSB_COLD(C_DX) = __float_as_uint(dd.x); GSB_COLD(C_DY) = __float_as_uint(dd.y); GSB_COLD(C_DZ) = __float_as_uint(dd.z);
+                    spMark = 0; inWorld = true; nodes = sc.worldNodes; tris = sc.worldTris;
+                }
+                hitT = tmax; GSB_COLD(C_INST) = GSB_NO_HIT; GSB_COLD(C_PRIM) = GSB_NO_HIT;
+                sp = 0;
+                G = make_uint2(0u, 0x80000000u);  // root group: bit 31, imask 0 -> node childBase + 0
+                T = make_uint2(0u, 0u);
+            }
+            poolHead = wrap(poolHead + n);
+            poolCount -= n;
+            __syncwarp();   // the entries just read may be overwritten by the next fetch
+        }
+        } else {
+        // ---- refill straight from the source: hand in finished rays, take new ones (warp-uniform branch).  While the
+        // stream still has rays a refill waits until refillMin lanes are idle, so that its fixed cost (and the latency
+        // of the state loads) is shared by several rays.
+        const uint32_t idle = __ballot_sync(0xffffffffu, !active);
+        const uint32_t pending = __ballot_sync(0xffffffffu, !active && hasRay);
+        if (idle == 0xffffffffu || (src.drained() ? pending != 0u : (uint32_t)__popc(idle) >= refillMin)) {
+            const bool done = !active && hasRay;
+            HitRecord hit;
+            hit.t = hitT; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT;
+            uint32_t tag = kNoTag, aux = 0u;
+            if (done) {
+                tag = GSB_COLD(C_TAG); aux = GSB_COLD(C_AUX);
+                hit.inst = GSB_COLD(C_INST); hit.prim = GSB_COLD(C_PRIM);
+                if (!ANYHIT && hit.inst != GSB_NO_HIT) {
+                    const float det = GSB_COLDF(C_DET);
+                    hit.u = __fdiv_rn(GSB_COLDF(C_U), det);
+                    hit.v = __fdiv_rn(GSB_COLDF(C_V), det);
+                }
+            }
+            src.commit(done, hit, tag, aux);
+            if (!active) hasRay = false;
+            RayJob job;
             const bool got = src.fetch(!active, job);
             if (got) {
                 active = true;
-                hit.t = job.tmax; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT;
-                // the world level: the ray as it is
+                hasRay = true;
+                GSB_COLD(C_TAG) = job.tag; GSB_COLD(C_AUX) = job.aux; tmin = job.tmin; tmax = job.tmax;
+                hitT = tmax; GSB_COLD(C_INST) = GSB_NO_HIT; GSB_COLD(C_PRIM) = GSB_NO_HIT;
                 cox = job.ox; coy = job.oy; coz = job.oz;
                 cidx = slabInv(job.dx); cidy = slabInv(job.dy); cidz = slabInv(job.dz);
                 oct7 = (job.dx < 0.0f ? 0u : 4u) | (job.dy < 0.0f ? 0u : 2u) | (job.dz < 0.0f ? 0u : 1u);
                 makeObjRay(job.ox, job.oy, job.oz, job.dx, job.dy, job.dz, oray);
+                if (HASINST) {
+                    GSB_COLD(C_OX) = __float_as_uint(job.ox); GSB_COLD(C_OY) = __float_as_uint(job.oy); GSB_COLD(C_OZ) = __float_as_uint(job.oz);
+                    GSB_COLD(C_DX) = __float_as_uint(job.dx); GSB_COLD(C_DY) = __float_as_uint(job.dy); GSB_COLD(C_DZ) = __float_as_uint(job.dz);
+                    spMark = 0; inWorld = true; nodes = sc.worldNodes; tris = sc.worldTris;
+                }
                 sp = 0;
-                if (HASINST) { spMark = 0; inWorld = true; nodes = sc.worldNodes; tris = sc.worldTris; }
                 G = make_uint2(0u, 0x80000000u);  // root group: bit 31, imask 0 -> node childBase + 0
                 T = make_uint2(0u, 0u);
             }
-            if (!__any_sync(0xffffffffu, active)) {
-                if (src.drained()) break;
-                continue;
-            }
+        }
+        }
+        if (!__any_sync(0xffffffffu, active)) {
+            if (poolCount == 0u && src.drained()) break;
+            continue;
         }
         // ---- vote: which phases run in this pass
         bool run1, run2a = false, run2b;
@@ -357,7 +483,7 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
             const uint32_t nodeIndex = G.x + __popc(G.y & ((1u << slot) - 1u) & 0xffu);
             if (G.y & 0xff000000u) GSB_PUSH(G);
             if (STATS) stats->nodes++;
-            intersectNode(HASINST ? nodes : sc.worldNodes, nodeIndex, cox, coy, coz, cidx, cidy, cidz, job.tmin, hit.t, oct7, G, T);
+            intersectNode(HASINST ? nodes : sc.worldNodes, nodeIndex, cox, coy, coz, cidx, cidy, cidz, tmin, hitT, oct7, G, T);
         }
         // ---- phase 2a (top level): enter one instance, park the rest of this node
         if (HASINST && run2a && active && spMark < 0 && T.y) {
@@ -371,7 +497,7 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
             const uint4 tail = __ldg(reinterpret_cast<const uint4*>(ti) + 3);
             if (STATS) stats->insts++;
             // o' = M^-1 (o,1), d' = M^-1 (d,0); rounded op by op, same order as the checker
-            const float ox = job.ox, oy = job.oy, oz = job.oz, dx = job.dx, dy = job.dy, dz = job.dz;
+            const float ox = GSB_COLDF(C_OX), oy = GSB_COLDF(C_OY), oz = GSB_COLDF(C_OZ), dx = GSB_COLDF(C_DX), dy = GSB_COLDF(C_DY), dz = GSB_COLDF(C_DZ);
             const float tox = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r0.x, ox), __fmul_rn(r0.y, oy)), __fmul_rn(r0.z, oz)), r0.w);
             const float toy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r1.x, ox), __fmul_rn(r1.y, oy)), __fmul_rn(r1.z, oz)), r1.w);
             const float toz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r2.x, ox), __fmul_rn(r2.y, oy)), __fmul_rn(r2.z, oz)), r2.w);
@@ -412,17 +538,24 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
                     float Tn, V, W, det;
                     if (woopEdges(oray, v0, v1, v2, Tn, V, W, det)) {
                         const float t = __fdiv_rn(Tn, det);
-                        if (t > job.tmin && t < job.tmax) {
+                        if (t > tmin && t < tmax) {
                             if (ANYHIT) {
                                 // occluded: drop everything still pending, phase 3 ends the ray
-                                hit.inst = 0u; hit.prim = 0u; hit.t = 0.0f;
+                                GSB_COLD(C_INST) = 0u; GSB_COLD(C_PRIM) = 0u; hitT = 0.0f;
                                 T.y = 0u; G.y = 0u; sp = 0;
                                 if (HASINST) spMark = -1;
                             } else {
                                 const uint32_t prim = __float_as_uint(v0.w);
                                 const uint32_t inst = (!HASINST || inWorld) ? __float_as_uint(v1.w) : curInst;
-                                if (t < hit.t || (t == hit.t && (inst < hit.inst || (inst == hit.inst && prim < hit.prim)))) {
-                                    hit.t = t; hit.u = V; hit.v = W; hitDet = det; hit.inst = inst; hit.prim = prim;
+                                bool closer = t < hitT;
+                                if (t == hitT) {   // a tie: the smaller (instance, primitive) wins
+                                    const uint32_t hi = GSB_COLD(C_INST), hp = GSB_COLD(C_PRIM);
+                                    closer = inst < hi || (inst == hi && prim < hp);
+                                }
+                                if (closer) {
+                                    hitT = t;
+                                    GSB_COLD(C_U) = __float_as_uint(V); GSB_COLD(C_V) = __float_as_uint(W); GSB_COLD(C_DET) = __float_as_uint(det);
+                                    GSB_COLD(C_INST) = inst; GSB_COLD(C_PRIM) = prim;
                                 }
                             }
                         }
@@ -437,9 +570,10 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
                 // back to the top level: the world ray again
                 spMark = -1;
                 nodes = sc.tlasNodes;
-                cox = job.ox; coy = job.oy; coz = job.oz;
-                cidx = slabInv(job.dx); cidy = slabInv(job.dy); cidz = slabInv(job.dz);
-                oct7 = (job.dx < 0.0f ? 0u : 4u) | (job.dy < 0.0f ? 0u : 2u) | (job.dz < 0.0f ? 0u : 1u);
+                cox = GSB_COLDF(C_OX); coy = GSB_COLDF(C_OY); coz = GSB_COLDF(C_OZ);
+                const float wdx = GSB_COLDF(C_DX), wdy = GSB_COLDF(C_DY), wdz = GSB_COLDF(C_DZ);
+                cidx = slabInv(wdx); cidy = slabInv(wdy); cidz = slabInv(wdz);
+                oct7 = (wdx < 0.0f ? 0u : 4u) | (wdy < 0.0f ? 0u : 2u) | (wdz < 0.0f ? 0u : 1u);
                 if (inWorld) {
                     // the world level is done: start the top level at its root
                     inWorld = false;
@@ -449,7 +583,7 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
             }
             if (pop) {
                 if (sp == 0) {
-                    active = false;  // this ray is done; its result is handed in at the next refill
+                    active = false;  // this ray is done; its result is handed in at the top of the next pass
                 } else {
                     --sp;
                     const uint2 e = sp < kSmemStack ? s_stack[sp][tid] : lstack[sp - kSmemStack];
@@ -460,6 +594,8 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
         }
     }
 #undef GSB_PUSH
+#undef GSB_COLD
+#undef GSB_COLDF
 }
 
 }  // namespace gsb

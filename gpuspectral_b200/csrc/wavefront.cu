@@ -156,7 +156,6 @@ struct ExtendSource {
     const RenderArgs& ra;
     uint32_t* qc;       // this iteration's counter bank
     WorkRange range;
-    uint32_t pix = 0;   // pixel of the lane's current path
     uint32_t traced = 0;
     // work counters (warp-uniform): the chunk whose counter is held in registers, and the one loaded ahead
     // work blocks (warp-uniform, kept in shared memory so that they cost no registers inside the traversal loop): the chunk
@@ -275,13 +274,13 @@ struct ExtendSource {
         job.dx = d.x; job.dy = d.y; job.dz = d.z;
         job.tmin = 0.0f; job.tmax = 1e10f;                              // raygen.rgen:54-58
         job.tag = slot;
-        pix = p;
+        job.aux = p;        // the path's pixel travels with the ray
         traced++;
         return true;
     }
 
     // stores only: k_shade finds its work by scanning hitInst in slot order
-    GSB_D void commit(bool have, const HitRecord& hit, uint32_t slot) {
+    GSB_D void commit(bool have, const HitRecord& hit, uint32_t slot, uint32_t pix) {
         if (!have) return;
         wf.hitInst[slot] = hit.inst;
         if (hit.inst == GSB_NO_HIT) wf.sampleK[slot] = pix | kFinished;   // miss.rmiss: done = 1, nothing is added
@@ -289,7 +288,7 @@ struct ExtendSource {
     }
 };
 
-template <bool STATS, bool HASINST>
+template <bool STATS, bool HASINST, bool POOL>
 __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_extend(SceneDev sc, WavefrontState wf, RenderArgs ra, uint32_t parity) {
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -305,7 +304,7 @@ __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_extend(SceneDe
     __shared__ ExtendSource::WarpWork s_work[kBlock / 32];
     ExtendSource src(sc, wf, ra, qc, &s_work[threadIdx.x >> 5]);
     TraceStats ts = {0u, 0u, 0u};
-    traceStream<false, STATS, HASINST>(sc, src, ra.refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+    traceStream<false, STATS, HASINST, POOL>(sc, src, ra.refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
     src.flushWork();
     // extension rays traced by this warp -> this iteration's counter bank
     uint32_t traced = src.traced;
@@ -543,7 +542,6 @@ struct ShadowSource {
     uint32_t* qc;
     uint32_t count;
     WorkRange range;
-    uint32_t slot = 0;
     uint32_t traced = 0;
 
     GSB_D ShadowSource(const SceneDev& s, const WavefrontState& w, uint32_t* q) : sc(s), wf(w), qc(q), count(q[Q_SHADOW]) {}
@@ -562,12 +560,12 @@ struct ShadowSource {
         job.dx = d.x; job.dy = d.y; job.dz = d.z;
         job.tmin = 0.01f; job.tmax = o.w;                                            // rayhit.rchit:737-748
         job.tag = i;
-        slot = __float_as_uint(d.w);      // bit 31 (kShadowHasBase) stays in until commit
+        job.aux = __float_as_uint(d.w);   // the path slot; bit 31 (kShadowHasBase) stays in until commit
         traced++;
         return true;
     }
 
-    GSB_D void commit(bool have, const HitRecord& hit, uint32_t i) {
+    GSB_D void commit(bool have, const HitRecord& hit, uint32_t i, uint32_t slot) {
         if (!have) return;
         const bool visible = hit.inst == GSB_NO_HIT;
         const bool hasBase = (slot & kShadowHasBase) != 0u;
@@ -589,11 +587,11 @@ struct ShadowSource {
     }
 };
 
-template <bool STATS, bool HASINST>
+template <bool STATS, bool HASINST, bool POOL>
 __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_shadow(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t refillMin) {
     ShadowSource src(sc, wf, wf.qCount + parity * Q_COUNT);
     TraceStats ts = {0u, 0u, 0u};
-    traceStream<true, STATS, HASINST>(sc, src, refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
+    traceStream<true, STATS, HASINST, POOL>(sc, src, refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
     if (STATS) flushTraceStats(wf.stats, ts, src.traced);
 }
 
@@ -734,11 +732,13 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     // the traversal kernels exist per (instrumented, scene has instances that are not baked)
     using ExtendKernel = void (*)(SceneDev, WavefrontState, RenderArgs, uint32_t);
     using ShadowKernel = void (*)(SceneDev, WavefrontState, uint32_t, uint32_t);
-    static const ExtendKernel extendKernels[4] = {k_extend<false, false>, k_extend<false, true>, k_extend<true, false>, k_extend<true, true>};
-    static const ShadowKernel shadowKernels[4] = {k_shadow<false, false>, k_shadow<false, true>, k_shadow<true, false>, k_shadow<true, true>};
+    static const ExtendKernel extendKernels[8] = {k_extend<false, false, false>, k_extend<false, true, false>, k_extend<true, false, false>, k_extend<true, true, false>,
+                                                  k_extend<false, false, true>,  k_extend<false, true, true>,  k_extend<true, false, true>,  k_extend<true, true, true>};
+    static const ShadowKernel shadowKernels[8] = {k_shadow<false, false, false>, k_shadow<false, true, false>, k_shadow<true, false, false>, k_shadow<true, true, false>,
+                                                  k_shadow<false, false, true>,  k_shadow<false, true, true>,  k_shadow<true, false, true>,  k_shadow<true, true, true>};
     const int hasInst = ctx->numTraceInstances > 0 ? 1 : 0;
-    const ExtendKernel extendKernel = extendKernels[((ctx->instrumented & 1) ? 2 : 0) | hasInst];
-    const ShadowKernel shadowKernel = shadowKernels[((ctx->instrumented & 2) ? 2 : 0) | hasInst];
+    const ExtendKernel extendKernel = extendKernels[(ctx->poolExtend ? 4 : 0) | ((ctx->instrumented & 1) ? 2 : 0) | hasInst];
+    const ShadowKernel shadowKernel = shadowKernels[(ctx->poolShadow ? 4 : 0) | ((ctx->instrumented & 2) ? 2 : 0) | hasInst];
     const int extendGrid = residentGrid((const void*)extendKernel);
     const int shadowGrid = residentGrid((const void*)shadowKernel);
     k_generate<<<fullGrid, kBlock, 0, s>>>(sc, wf, ra);
@@ -773,7 +773,7 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         if (ctx->typeUsed[7]) launchShade<7>(ctx, sc, queueGrid, parity, slots);
         if (ctx->typeUsed[8]) launchShade<8>(ctx, sc, queueGrid, parity, slots);
         mark();
-        shadowKernel<<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ra.refillMin & 0xffu);
+        shadowKernel<<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ctx->shadowControl);
         mark();
         mark();
         parity ^= 1u;
