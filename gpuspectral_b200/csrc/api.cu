@@ -100,7 +100,8 @@ struct BatchSource {
             o.inst = h.inst == GSB_NO_HIT ? GSB_NO_HIT : 0u;
             o.prim = o.inst;
         } else {
-            o.t = h.t; o.u = h.u; o.v = h.v; o.inst = h.inst; o.prim = h.prim;
+            o.t = h.t; o.u = h.u; o.v = h.v; o.prim = h.prim;
+            o.inst = h.inst == GSB_NO_HIT ? GSB_NO_HIT : (h.inst & kInstMask);   // gl_InstanceID out of the instance word
         }
         hits[i] = o;
     }
@@ -131,11 +132,13 @@ __global__ void __launch_bounds__(kTraceBlock) k_traceBatch(SceneDev sc, const g
     }
 }
 
-// Bake rule, device side: vertex k of triangle t of instance `inst` in world space, x' = ((m0*x + m1*y) + m2*z) + m3 per
+// Bake rule, device side: vertex k of triangle t of an instance in world space, x' = ((m0*x + m1*y) + m2*z) + m3 per
 // row, every operation rounded on its own (no FMA) — the order of gl_ObjectToWorldEXT * vec4(p, 1) (rayhit.rchit:679-681)
-// and of the checker.  .w carries the ids the world level reports: v0.w = gl_PrimitiveID, v1.w = gl_InstanceID.
-__global__ void k_bakeInstance(const float4* __restrict__ vpos, uint32_t ntris, float4 m0, float4 m1, float4 m2, uint32_t inst,
-                               float4* __restrict__ out) {
+// and of the checker — and its normal through transformInvT, (n0*x + n1*y) + n2*z per row (rayhit.rchit:686-688).
+// .w of the positions carries what the world level reports: v0.w = gl_PrimitiveID, v1.w = the instance word.
+__global__ void k_bakeInstance(const float4* __restrict__ vpos, const float4* __restrict__ vnrm, uint32_t ntris, float4 m0, float4 m1,
+                               float4 m2, float4 n0, float4 n1, float4 n2, uint32_t instWord, float4* __restrict__ outPos,
+                               float4* __restrict__ outNrm) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= ntris) return;
 #pragma unroll
@@ -144,8 +147,22 @@ __global__ void k_bakeInstance(const float4* __restrict__ vpos, uint32_t ntris, 
         const float x = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m0.x, p.x), __fmul_rn(m0.y, p.y)), __fmul_rn(m0.z, p.z)), m0.w);
         const float y = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m1.x, p.x), __fmul_rn(m1.y, p.y)), __fmul_rn(m1.z, p.z)), m1.w);
         const float z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m2.x, p.x), __fmul_rn(m2.y, p.y)), __fmul_rn(m2.z, p.z)), m2.w);
-        out[3 * (size_t)t + k] = make_float4(x, y, z, __uint_as_float(k == 0 ? t : (k == 1 ? inst : 0u)));
+        outPos[3 * (size_t)t + k] = make_float4(x, y, z, __uint_as_float(k == 0 ? t : (k == 1 ? instWord : 0u)));
+        const float4 n = __ldg(vnrm + 3 * (size_t)t + k);
+        const float nx = __fadd_rn(__fadd_rn(__fmul_rn(n0.x, n.x), __fmul_rn(n0.y, n.y)), __fmul_rn(n0.z, n.z));
+        const float ny = __fadd_rn(__fadd_rn(__fmul_rn(n1.x, n.x), __fmul_rn(n1.y, n.y)), __fmul_rn(n1.z, n.z));
+        const float nz = __fadd_rn(__fadd_rn(__fmul_rn(n2.x, n.x), __fmul_rn(n2.y, n.y)), __fmul_rn(n2.z, n.z));
+        outNrm[3 * (size_t)t + k] = make_float4(nx, ny, nz, 0.0f);
     }
+}
+
+// world-level normals from bake order into leaf order (position k of the world level holds baked triangle leafPrim[k])
+__global__ void k_gatherNormals(const uint32_t* __restrict__ leafPrim, uint32_t n, const float4* __restrict__ in, float4* __restrict__ out) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const uint32_t p = leafPrim[k];
+#pragma unroll
+    for (int j = 0; j < 3; j++) out[3 * (size_t)k + j] = __ldg(in + 3 * (size_t)p + j);
 }
 
 __global__ void k_resolve(const float4* __restrict__ accum, uint32_t npix, float4* __restrict__ hdr, uchar4* __restrict__ ldr) {
@@ -350,6 +367,8 @@ SceneDev gsb_context::sceneDev() const {
     memset(&sc, 0, sizeof(sc));
     sc.worldNodes = world.buffer;
     sc.worldTris = reinterpret_cast<const float4*>(world.buffer + world.leafOffset16);
+    sc.worldNrm = dWorldNrm;
+    sc.instSmall = dInstSmall;
     sc.tlasNodes = tlas.buffer;
     sc.tlasInst = reinterpret_cast<const TraceInstance*>(tlas.buffer + tlas.leafOffset16);
     sc.shadeInst = dShade;
@@ -435,6 +454,8 @@ gsb_status gsb_destroy(gsb_context* ctx) {
         freeBvh(ctx->tlas);
         freeBvh(ctx->world);
         cudaFree(ctx->dWorldVerts);
+        cudaFree(ctx->dWorldNrm);
+        cudaFree(ctx->dInstSmall);
         cudaFree(ctx->dShade);
         cudaFree(ctx->dInstBsdf);
         for (void* p : ctx->dBsdf) cudaFree(p);
@@ -527,6 +548,7 @@ gsb_status gsb_scene_set_lights(gsb_context* ctx, const gsb_triangle_light* ligh
 
 gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instances, uint32_t count) {
     if (!ctx || (count && !instances)) return fail(GSB_ERR_INVALID, "gsb_scene_set_instances: null argument");
+    if (count > kMaxInstances) return fail(GSB_ERR_INVALID, "gsb_scene_set_instances: more than 2^27 - 1 instances");
     for (uint32_t i = 0; i < count; i++) {
         if (instances[i].mesh >= ctx->meshes.size() || !ctx->meshes[instances[i].mesh].alive)
             return fail(GSB_ERR_INVALID, "gsb_scene_set_instances: instance " + std::to_string(i) + " references an unknown mesh");
@@ -542,7 +564,7 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
         std::vector<TraceInstance> trace;
         std::vector<uint32_t> handles(count);
         std::vector<float> wlo, whi;
-        // Bake rule (shared with the checker, oracle.cpp: kBakeMaxTris / kBakeBudget): in gl_InstanceID order, an instance
+        // Bake rule (shared with the checker: kBakeMaxTris / kBakeBudget): in gl_InstanceID order, an instance
         // whose mesh has at most kBakeMaxTris triangles goes to the world level while the baked total fits the budget.
         std::vector<uint64_t> bakeOffset(count, ~0ull);   // first world-level triangle of a baked instance
         uint64_t baked = 0;
@@ -551,12 +573,20 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
             if (nt > 0 && nt <= kBakeMaxTris && baked + nt <= kBakeBudget) { bakeOffset[i] = baked; baked += nt; }
         }
         cudaFree(ctx->dWorldVerts);
+        cudaFree(ctx->dWorldNrm);
         ctx->dWorldVerts = nullptr;
+        ctx->dWorldNrm = nullptr;
+        float4* nrmSoup = nullptr;   // world normals in bake order, gathered into leaf order after the build
         if (baked) {
             void* q = nullptr;
             GSB_CUDA(cudaMalloc(&q, (size_t)baked * 3 * sizeof(float4)));
             ctx->dWorldVerts = (float4*)q;
+            GSB_CUDA(cudaMalloc(&q, (size_t)baked * 3 * sizeof(float4)));
+            ctx->dWorldNrm = (float4*)q;
+            GSB_CUDA(cudaMalloc(&q, (size_t)baked * 3 * sizeof(float4)));
+            nrmSoup = (float4*)q;
         }
+        std::vector<float4> small(count);
         for (bool& u : ctx->typeUsed) u = false;
         for (uint32_t i = 0; i < count; i++) {
             const gsb_instance& in = instances[i];
@@ -595,9 +625,14 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
             sh.pad[0] = sh.pad[1] = 0;
             handles[i] = in.bsdf;
             ctx->typeUsed[in.bsdf >> 16] = true;
+            const uint32_t smallBits = (in.bsdf & 0xffffu) | (std::min(in.twofaced, 0xffffu) << 16);
+            small[i] = make_float4(in.emission[0], in.emission[1], in.emission[2], 0.0f);
+            memcpy(&small[i].w, &smallBits, sizeof(float));
+            const uint32_t instWord = i | ((in.bsdf >> 16) << kInstTypeShift) | (bakeOffset[i] != ~0ull ? kInstBaked : 0u);
             if (bakeOffset[i] != ~0ull) {
-                k_bakeInstance<<<(mesh.ntris + 127) / 128, 128, 0, ctx->stream>>>(mesh.vpos, mesh.ntris, sh.o2w[0], sh.o2w[1], sh.o2w[2], i,
-                                                                                  ctx->dWorldVerts + 3 * bakeOffset[i]);
+                k_bakeInstance<<<(mesh.ntris + 127) / 128, 128, 0, ctx->stream>>>(mesh.vpos, mesh.vnrm, mesh.ntris, sh.o2w[0], sh.o2w[1], sh.o2w[2],
+                                                                                  sh.nrm[0], sh.nrm[1], sh.nrm[2], instWord,
+                                                                                  ctx->dWorldVerts + 3 * bakeOffset[i], nrmSoup + 3 * bakeOffset[i]);
                 continue;
             }
             TraceInstance tr;
@@ -608,7 +643,7 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
             tr.blas = mesh.blas.buffer;
             // meshes of <= 4 triangles are traced without their (single) node: the TLAS box test already covered them
             tr.triOffset16 = mesh.blas.leafOffset16 | ((mesh.ntris >= 1 && mesh.ntris <= 4) ? (mesh.ntris << kDirectShift) : 0u);
-            tr.instId = i;
+            tr.instId = instWord;
             trace.push_back(tr);
             // padded world bounds of the padded object box
             double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -634,8 +669,15 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
         cudaFree(ctx->dInstBsdf);
         ctx->dShade = uploadArray(shade.data(), count, ctx->stream);
         ctx->dInstBsdf = uploadArray(handles.data(), count, ctx->stream);
+        cudaFree(ctx->dInstSmall);
+        ctx->dInstSmall = uploadArray(small.data(), count, ctx->stream);
         freeBvh(ctx->world);
-        buildBlas(ctx->dWorldVerts, (uint32_t)baked, ctx->stream, ctx->world, true);
+        uint32_t* leafPrim = nullptr;
+        buildBlas(ctx->dWorldVerts, (uint32_t)baked, ctx->stream, ctx->world, true, &leafPrim);
+        if (baked) k_gatherNormals<<<((uint32_t)baked + 127) / 128, 128, 0, ctx->stream>>>(leafPrim, (uint32_t)baked, nrmSoup, ctx->dWorldNrm);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        cudaFree(leafPrim);
+        cudaFree(nrmSoup);
         freeBvh(ctx->tlas);
         ctx->numTraceInstances = (uint32_t)trace.size();
         ctx->numBakedTriangles = (uint32_t)baked;

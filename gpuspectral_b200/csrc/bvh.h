@@ -33,9 +33,11 @@ constexpr float kBoxPadRel = 1.0f / 32768.0f;
 // 3 copies (one per dominant ray axis, pre-rotated) of 3 x float4 (v0.xyz | primId bits, v1.xyz, v2.xyz) = 144 B.
 // idsInVertices: the leaf records take v0.w / v1.w from the input vertices (world level: primitive and instance id of
 // every baked triangle) instead of the position of the triangle in the soup.
-void buildBlas(const float4* dVertices, uint32_t numTriangles, cudaStream_t stream, DeviceBvh& out, bool idsInVertices = false);
+// outLeafPrim (optional): receives a cudaMalloc'ed array with the input triangle index of every leaf position (the caller frees it).
+void buildBlas(const float4* dVertices, uint32_t numTriangles, cudaStream_t stream, DeviceBvh& out, bool idsInVertices = false,
+               uint32_t** outLeafPrim = nullptr);
 
-// Bake rule (shared with the checker, oracle/oracle.cpp): in gl_InstanceID order an instance whose mesh has at most
+// Bake rule (shared with the checker): in gl_InstanceID order an instance whose mesh has at most
 // kBakeMaxTris triangles is stored in world space at the world level, while the baked total stays within kBakeBudget.
 constexpr uint32_t kBakeMaxTris = 16384;
 constexpr uint64_t kBakeBudget = 1ull << 22;

@@ -553,7 +553,7 @@ void freeBvh(DeviceBvh& bvh) {
     bvh = DeviceBvh();
 }
 
-void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out, bool idsInVertices) {
+void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out, bool idsInVertices, uint32_t** outLeafPrim) {
     cudaEvent_t e0, e1;
     GSB_CUDA(cudaEventCreate(&e0));
     GSB_CUDA(cudaEventCreate(&e1));
@@ -587,6 +587,15 @@ void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBv
         if (ntris > 0)
             k_packTriangles<<<(ntris + B - 1) / B, B, 0, s>>>(r.leafPrim, ntris, dVertices,
                                                               reinterpret_cast<float4*>(out.buffer + out.leafOffset16), idsInVertices);
+        if (outLeafPrim) {
+            *outLeafPrim = nullptr;
+            if (ntris > 0) {
+                void* q = nullptr;
+                GSB_CUDA(cudaMalloc(&q, (size_t)ntris * sizeof(uint32_t)));
+                GSB_CUDA(cudaMemcpyAsync(q, r.leafPrim, (size_t)ntris * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+                *outLeafPrim = (uint32_t*)q;
+            }
+        }
         GSB_CUDA(cudaGetLastError());
         for (int a = 0; a < 3; a++) { out.lo[a] = lo[a] - pad; out.hi[a] = hi[a] + pad; }
     }

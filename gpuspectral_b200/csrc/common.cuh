@@ -102,10 +102,21 @@ struct TraceInstance {
 };
 static_assert(sizeof(TraceInstance) == 64, "TraceInstance must stay 64 bytes");
 
+// The instance word a hit carries (WavefrontState::hitInst, world-level triangle records, TraceInstance::instId):
+// bits 0..26 gl_InstanceID, bit 27 the instance is baked (its triangles sit at the world level), bits 28..31 the BSDF type
+// of the instance — k_shade<TYPE> finds its work from this word alone.  GSB_NO_HIT (all ones) decodes to no valid type.
+constexpr uint32_t kInstMask = 0x07ffffffu;
+constexpr uint32_t kInstBaked = 1u << 27;
+constexpr uint32_t kInstTypeShift = 28;
+constexpr uint32_t kMaxInstances = kInstMask;   // gsb_scene_set_instances rejects more
+constexpr uint32_t kNoLeaf = 0xffffffffu;
+
 // Everything the kernels need to know about the scene; passed by value as a kernel parameter.
 struct SceneDev {
     const uint4* worldNodes;         // world level: 8-wide nodes over the triangles of all baked instances (world space)
-    const float4* worldTris;         //   their leaf records (3 rotated copies of 3 float4; v0.w = primitive, v1.w = instance)
+    const float4* worldTris;         //   their leaf records (3 rotated copies of 3 float4; v0.w = primitive, v1.w = instance word)
+    const float4* worldNrm;          //   their vertex normals in world space (transformInvT * n), 3 float4 per triangle, leaf order
+    const float4* instSmall;         // per instance: emission.xyz, bits(bsdf index | twofaced << 16) — all a baked hit needs of its instance
     const uint4* tlasNodes;          // 8-wide nodes of the top level over the instances that are not baked
     const TraceInstance* tlasInst;   // instance records in TLAS leaf order
     const ShadeInstance* shadeInst;  // instance records in gl_InstanceID order

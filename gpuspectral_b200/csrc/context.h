@@ -64,6 +64,8 @@ struct gsb_context {
     std::vector<gsb_instance> instances;
     gsb::DeviceBvh world;              // world level: BVH over the triangles of all baked instances, in world space
     float4* dWorldVerts = nullptr;     //   their vertices (3 float4 per triangle; v0.w = primitive id, v1.w = instance id)
+    float4* dWorldNrm = nullptr;       //   their vertex normals in world space, leaf order (shading reads them straight from here)
+    float4* dInstSmall = nullptr;      // per instance: emission, bsdf index, twofaced (what a baked hit needs of its instance)
     uint32_t numBakedTriangles = 0;
     gsb::DeviceBvh tlas;               // top level over the instances that are not baked
     uint32_t numTraceInstances = 0;

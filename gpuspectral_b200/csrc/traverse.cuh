@@ -40,7 +40,8 @@ struct TraceStats { uint32_t nodes, tris, insts; };
 
 struct HitRecord {
     float t, u, v;
-    uint32_t inst, prim;
+    uint32_t inst, prim;   // inst: the instance word (common.cuh: kInstMask / kInstBaked / type), GSB_NO_HIT on a miss
+    uint32_t leaf;         // world-level hits: position of the triangle in the world level's leaf order; kNoLeaf otherwise
 };
 
 // object-space ray with the Woop shear constants
@@ -300,11 +301,11 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
     __shared__ float4 s_pool[POOL ? kTraceBlock / 32 : 1][POOL ? kPoolWords : 1][POOL ? kPoolSize : 1];
     // Cold per-lane state lives in shared memory ([word][thread]: conflict-free), not in registers: it is written when a
     // ray starts or a closer hit is accepted and read when the ray is handed in (or, the world ray, when an instance is
-    // entered / left), never inside the node and triangle tests.  Rows: tag, aux, hit u, v, det, inst, prim, and for
+    // entered / left), never inside the node and triangle tests.  Rows: tag, aux, hit u, v, det, inst, prim, leaf, and for
     // two-level scenes the world ray's origin and direction.
-    constexpr int kColdWords = HASINST ? 13 : 7;
+    constexpr int kColdWords = HASINST ? 14 : 8;
     __shared__ uint32_t s_cold[kColdWords][kTraceBlock];
-    enum { C_TAG = 0, C_AUX, C_U, C_V, C_DET, C_INST, C_PRIM, C_OX, C_OY, C_OZ, C_DX, C_DY, C_DZ };
+    enum { C_TAG = 0, C_AUX, C_U, C_V, C_DET, C_INST, C_PRIM, C_LEAF, C_OX, C_OY, C_OZ, C_DX, C_DY, C_DZ };
 #define GSB_COLD(w) s_cold[w][tid]
 #define GSB_COLDF(w) __uint_as_float(s_cold[w][tid])
     uint2 lstack[kLocalStack];
@@ -345,11 +346,11 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
             const bool done = !active && hasRay;
             if (__any_sync(0xffffffffu, done)) {
                 HitRecord hit;
-                hit.t = hitT; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT;
+                hit.t = hitT; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT; hit.leaf = kNoLeaf;
                 uint32_t tag = kNoTag, aux = 0u;
                 if (done) {
                     tag = GSB_COLD(C_TAG); aux = GSB_COLD(C_AUX);
-                    hit.inst = GSB_COLD(C_INST); hit.prim = GSB_COLD(C_PRIM);
+                    hit.inst = GSB_COLD(C_INST); hit.prim = GSB_COLD(C_PRIM); hit.leaf = GSB_COLD(C_LEAF);
                     if (!ANYHIT && hit.inst != GSB_NO_HIT) {
                         const float det = GSB_COLDF(C_DET);
                         hit.u = __fdiv_rn(GSB_COLDF(C_U), det);
@@ -421,11 +422,11 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
         if (idle == 0xffffffffu || (src.drained() ? pending != 0u : (uint32_t)__popc(idle) >= refillMin)) {
             const bool done = !active && hasRay;
             HitRecord hit;
-            hit.t = hitT; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT;
+            hit.t = hitT; hit.u = 0.0f; hit.v = 0.0f; hit.inst = GSB_NO_HIT; hit.prim = GSB_NO_HIT; hit.leaf = kNoLeaf;
             uint32_t tag = kNoTag, aux = 0u;
             if (done) {
                 tag = GSB_COLD(C_TAG); aux = GSB_COLD(C_AUX);
-                hit.inst = GSB_COLD(C_INST); hit.prim = GSB_COLD(C_PRIM);
+                hit.inst = GSB_COLD(C_INST); hit.prim = GSB_COLD(C_PRIM); hit.leaf = GSB_COLD(C_LEAF);
                 if (!ANYHIT && hit.inst != GSB_NO_HIT) {
                     const float det = GSB_COLDF(C_DET);
                     hit.u = __fdiv_rn(GSB_COLDF(C_U), det);
@@ -548,14 +549,16 @@ GSB_D void traceStream(const SceneDev& sc, Source& src, uint32_t control, TraceS
                                 const uint32_t prim = __float_as_uint(v0.w);
                                 const uint32_t inst = (!HASINST || inWorld) ? __float_as_uint(v1.w) : curInst;
                                 bool closer = t < hitT;
-                                if (t == hitT) {   // a tie: the smaller (instance, primitive) wins
-                                    const uint32_t hi = GSB_COLD(C_INST), hp = GSB_COLD(C_PRIM);
-                                    closer = inst < hi || (inst == hi && prim < hp);
+                                if (t == hitT) {   // a tie: the smaller (gl_InstanceID, gl_PrimitiveID) wins
+                                    const uint32_t hw = GSB_COLD(C_INST), hp = GSB_COLD(C_PRIM);
+                                    const uint32_t hi = hw == GSB_NO_HIT ? GSB_NO_HIT : (hw & kInstMask), ci = inst & kInstMask;
+                                    closer = ci < hi || (ci == hi && prim < hp);
                                 }
                                 if (closer) {
                                     hitT = t;
                                     GSB_COLD(C_U) = __float_as_uint(V); GSB_COLD(C_V) = __float_as_uint(W); GSB_COLD(C_DET) = __float_as_uint(det);
                                     GSB_COLD(C_INST) = inst; GSB_COLD(C_PRIM) = prim;
+                                    GSB_COLD(C_LEAF) = (!HASINST || inWorld) ? T.x + bit : kNoLeaf;
                                 }
                             }
                         }

@@ -284,7 +284,8 @@ struct ExtendSource {
         if (!have) return;
         wf.hitInst[slot] = hit.inst;
         if (hit.inst == GSB_NO_HIT) wf.sampleK[slot] = pix | kFinished;   // miss.rmiss: done = 1, nothing is added
-        else wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.prim));
+        // a baked hit is shaded from the world level's own records: it carries its leaf position instead of gl_PrimitiveID
+        else wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float((hit.inst & kInstBaked) ? hit.leaf : hit.prim));
     }
 };
 
@@ -318,7 +319,7 @@ __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_extend(SceneDe
 // hit carries a BSDF of this kernel's TYPE.  A tile with at least directMin matching lanes is shaded as it is — the
 // path-state streams are then read and written coalesced; sparser tiles are compacted through a 64-entry per-warp
 // buffer in shared memory and shaded 32 at a time (entries wait there across in-place tiles).
-template <int TYPE>
+template <int TYPE, bool HASINST>
 __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t slots, uint32_t directMin) {
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
     __shared__ uint32_t s_buf[kBlock / 32][64];
@@ -332,8 +333,7 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
         const uint32_t cand = tile * 32u + lane;
         bool match = false;
         if (scanning && cand < slots) {
-            const uint32_t hi = wf.hitInst[cand];
-            match = hi != GSB_NO_HIT && (__ldg(sc.instBsdf + hi) >> 16) == (uint32_t)TYPE;
+            match = (wf.hitInst[cand] >> kInstTypeShift) == (uint32_t)TYPE;   // the instance word carries the BSDF type; GSB_NO_HIT decodes to none
         }
         const uint32_t mm = __ballot_sync(0xffffffffu, match);
 #if GSB_SHADE_PREFETCH
@@ -390,7 +390,7 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
             const float4 ro = wf.rayO[slot], rd = wf.rayD[slot];
             const float4 hit = wf.hitTUVP[slot];
 #endif
-            const uint32_t inst = wf.hitInst[slot];
+            const uint32_t instWord = wf.hitInst[slot];
             uint32_t rng = __float_as_uint(ro.w);                                 // rayhit.rchit:668
 #if GSB_SHADE_STREAM
             float4 wdw = __ldcs(wf.weightDW + slot);
@@ -401,26 +401,41 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
             float3 weight = xyz(wdw);
             const float directWeight = wdw.w;
             const uint32_t prim = __float_as_uint(hit.w);
+            const uint32_t inst = instWord & kInstMask;
 
             // :671-688 instance record, positions through object->world, normals through transformInvT
-            const float4* si = reinterpret_cast<const float4*>(sc.shadeInst + inst);
-            const float4 m0 = __ldg(si), m1 = __ldg(si + 1), m2 = __ldg(si + 2);
-            const float4 n0 = __ldg(si + 3), n1 = __ldg(si + 4), n2 = __ldg(si + 5);
-            const uint4 p0 = __ldg(reinterpret_cast<const uint4*>(si) + 6);
-            const uint4 p1 = __ldg(reinterpret_cast<const uint4*>(si) + 7);
-            const float4* vpos = reinterpret_cast<const float4*>(((uint64_t)p0.y << 32) | p0.x);
-            const float4* vnrm = reinterpret_cast<const float4*>(((uint64_t)p0.w << 32) | p0.z);
-            const uint32_t handle = p1.x, twofaced = p1.y;
-            const float3 emission = f3(n0.w, n1.w, n2.w);
-            float3 pos[3], nrm[3];
+            float3 pos[3], nrm[3], emission;
+            uint32_t handle, twofaced;
+            if (!HASINST || (instWord & kInstBaked)) {
+                // baked instance: both products were formed once when the scene was set (api.cu: k_bakeInstance, same
+                // operation order), hit.w is the triangle's position in the world level: two independent fetches
+                const float4 small = __ldg(sc.instSmall + inst);
+                const float4* wp = sc.worldTris + 9 * (size_t)prim + 6;   // the copy in x, y, z order
+                const float4* wn = sc.worldNrm + 3 * (size_t)prim;
 #pragma unroll
-            for (int k = 0; k < 3; k++) {
-                const float4 p = __ldg(vpos + 3 * (size_t)prim + k);
-                const float4 n = __ldg(vnrm + 3 * (size_t)prim + k);
-                pos[k] = f3(m0.x * p.x + m0.y * p.y + m0.z * p.z + m0.w, m1.x * p.x + m1.y * p.y + m1.z * p.z + m1.w,
-                            m2.x * p.x + m2.y * p.y + m2.z * p.z + m2.w);
-                nrm[k] = f3(n0.x * n.x + n0.y * n.y + n0.z * n.z, n1.x * n.x + n1.y * n.y + n1.z * n.z,
-                            n2.x * n.x + n2.y * n.y + n2.z * n.z);
+                for (int k = 0; k < 3; k++) { pos[k] = xyz(__ldg(wp + k)); nrm[k] = xyz(__ldg(wn + k)); }
+                emission = xyz(small);
+                handle = __float_as_uint(small.w) & 0xffffu;
+                twofaced = __float_as_uint(small.w) >> 16;
+            } else {
+                const float4* si = reinterpret_cast<const float4*>(sc.shadeInst + inst);
+                const float4 m0 = __ldg(si), m1 = __ldg(si + 1), m2 = __ldg(si + 2);
+                const float4 n0 = __ldg(si + 3), n1 = __ldg(si + 4), n2 = __ldg(si + 5);
+                const uint4 p0 = __ldg(reinterpret_cast<const uint4*>(si) + 6);
+                const uint4 p1 = __ldg(reinterpret_cast<const uint4*>(si) + 7);
+                const float4* vpos = reinterpret_cast<const float4*>(((uint64_t)p0.y << 32) | p0.x);
+                const float4* vnrm = reinterpret_cast<const float4*>(((uint64_t)p0.w << 32) | p0.z);
+                handle = p1.x; twofaced = p1.y;
+                emission = f3(n0.w, n1.w, n2.w);
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                    const float4 p = __ldg(vpos + 3 * (size_t)prim + k);
+                    const float4 n = __ldg(vnrm + 3 * (size_t)prim + k);
+                    pos[k] = f3(m0.x * p.x + m0.y * p.y + m0.z * p.z + m0.w, m1.x * p.x + m1.y * p.y + m1.z * p.z + m1.w,
+                                m2.x * p.x + m2.y * p.y + m2.z * p.z + m2.w);
+                    nrm[k] = f3(n0.x * n.x + n0.y * n.y + n0.z * n.z, n1.x * n.x + n1.y * n.y + n1.z * n.z,
+                                n2.x * n.x + n2.y * n.y + n2.z * n.z);
+                }
             }
             const float3 bary = f3(1.0f - hit.y - hit.z, hit.y, hit.z);               // :690
             const float3 rayDir = xyz(rd);                                          // :696
@@ -642,7 +657,8 @@ void allocWavefront(gsb_context* ctx, uint32_t slots) {
 
 template <int TYPE>
 void launchShade(gsb_context* ctx, const SceneDev& sc, int grid, uint32_t parity, uint32_t slots) {
-    k_shade<TYPE><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots, ctx->shadeDirectMin);
+    if (ctx->numTraceInstances > 0) k_shade<TYPE, true><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots, ctx->shadeDirectMin);
+    else k_shade<TYPE, false><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots, ctx->shadeDirectMin);
 }
 
 }  // namespace
