@@ -48,12 +48,13 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-instrumented", action="store_true", help="skip the untimed fetch-count pass (profiler runs)")
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-extra", action="store_true", help="skip the short runs of configs[2], [3] and the 4096x2160 frame (N = 1 only)")
     return ap.parse_args()
 
 
-def workload_name(a, n):
-    return (f"{a.scene}{' box' if a.scene == 'cornell' else ' scene'} {a.width}x{a.height}, NEE+MIS, max_depth {a.max_depth}, {a.spp_per_step} spp per step per GPU"
-            f" (sample-index sharding over {n} GPU{'s' if n > 1 else ''})")
+def workload_name(a):
+    """The workload both arms run (BASELINE.json configs[1] by default); how much of it one step covers is in config.spp_per_step."""
+    return f"{a.scene}{' box' if a.scene == 'cornell' else ' scene'} {a.width}x{a.height}, NEE+MIS, max_depth {a.max_depth}"
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -113,36 +114,72 @@ def host_threads():
 
 
 def run_reference(a, rank, world):
-    """The reference has no CPU implementation of this path and its Vulkan path is unavailable on this box, so the
-    reference arm is the CPU oracle (oracle/, a restatement of the shaders: kind "port") on all host cores.
-    Each step is a bounded sample of the workload: the full frame at 1 spp."""
+    """The reference has no CPU implementation of this path and its Vulkan path is unavailable on this box.  What of it
+    does compile for the host is its own shader text (oracle/_ref/libgsref.so: pt_common.glsl, raygen.rgen, rayhit.rchit,
+    miss / shadowmiss compiled as C++ against the reference's glm, OpenMP over pixels; the ray/triangle search, which has
+    no source in the reference, is the oracle's intersector): that is the reference arm (kind "reference") when the
+    library is there; otherwise the oracle port of the shaders (kind "port").  Each step is a bounded sample of the
+    workload: the full frame at 1 spp."""
     if rank != 0:
         return
-    import gpuspectral_b200 as g          # host layer only (scene arrays); no product compute on this arm
     from oracle import oracle as orc
+    from oracle import ref as oref
     orc.build()
-    scene = g.Scene.builtin(a.scene, *scene_params(a))
-    o = orc.OracleScene.from_host_scene(scene)
+    archive = os.path.join(ROOT, "tests", "golden", f"scene_{a.scene}.npz")
+    use_ref = oref.available() and a.scene != "gallery"      # the gallery holds a rough dielectric: no reference source
+    if os.path.exists(archive) and not a.scene_params:
+        # the scene's flat records from a committed archive (tests/golden/make_scene_npz.py): nothing of the product is
+        # imported or loaded on this arm
+        o = orc.OracleScene.from_npz(archive)
+        r = oref.RefScene.from_npz(archive) if use_ref else None
+        scene_source = os.path.relpath(archive, ROOT)
+    else:
+        import gpuspectral_b200 as g      # no archive for this scene: the host layer builds the arrays (no product compute)
+        hs = g.Scene.builtin(a.scene, *scene_params(a))
+        o = orc.OracleScene.from_host_scene(hs)
+        r = oref.RefScene.from_host_scene(hs) if use_ref else None
+        scene_source = "host layer (gpuspectral_b200.Scene.builtin)"
     o.set_params(max_depth=a.max_depth)
+    if use_ref:
+        oref.set_max_depth(a.max_depth)
     spp = 1
-    img = np.zeros((a.height, a.width, 4), np.float32)
-    paths = ext = sh = 0
     ncpu = host_threads()
-    threads = 0
+    img = np.zeros((a.height, a.width, 4), np.float32)
+
+    def one(k):
+        """One step: timestamp k for every pixel -> (paths, extension rays, shadow rays, threads used)."""
+        if use_ref:
+            _, e, s_ = r.render(o, a.width, a.height, k, spp, image=img, threads=ncpu)     # the reference's running mean
+            return a.width * a.height * spp, e, s_, ncpu
+        _, c, th = o.render(a.width, a.height, k, spp, 1, image=img, sum_mode=True, threads=ncpu)
+        return c["paths"], c["extension_rays"], c["shadow_rays"], th
+
+    paths = ext = sh = threads = 0
     for k in range(a.warmup):
-        o.render(a.width, a.height, k, spp, 1, image=img, sum_mode=True, threads=ncpu)
+        one(k)
     t0 = time.perf_counter()
     for k in range(a.steps):
-        _, c, threads = o.render(a.width, a.height, a.warmup + k, spp, 1, image=img, sum_mode=True, threads=ncpu)
-        paths += c["paths"]; ext += c["extension_rays"]; sh += c["shadow_rays"]
+        p_, e_, s_, threads = one(a.warmup + k)
+        paths += p_; ext += e_; sh += s_
     dt = time.perf_counter() - t0
     val = paths / dt / 1e6
+    # the oracle port on the same sample, for the record (it is the faster of the two CPU codes)
+    port = None
+    if use_ref:
+        t1 = time.perf_counter()
+        _, c, _ = o.render(a.width, a.height, a.warmup + a.steps, spp, 1, sum_mode=True, threads=ncpu)
+        port = c["paths"] / (time.perf_counter() - t1) / 1e6
+    kind = "reference" if use_ref else "port"
+    what = ("the reference's shader text compiled as C++ (oracle/_ref), ray/triangle search by the oracle's intersector" if use_ref
+            else "CPU oracle (port of the shaders, pinned bit for bit to the reference's shader text compiled as C++)")
     sample = f"{a.width}x{a.height} x {spp} spp per step ({a.steps} steps), same scene/params"
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": dt / max(a.steps, 1) * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "mrays_per_s": (ext + sh) / dt / 1e6,
-            "config": {"workload": workload_name(a, a.gpus), "note": "CPU oracle (port of the shaders); reference's Vulkan path unavailable on this box"},
-            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "config": {"workload": workload_name(a), "width": a.width, "height": a.height, "spp_per_step": spp, "max_depth": a.max_depth,
+                       "scene": a.scene, "scene_source": scene_source, "parallelism": f"{threads} host threads (OpenMP over pixels)",
+                       "note": what + "; the reference's Vulkan path is unavailable on this box; one step = the full frame at 1 spp (bounded sample)"},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample, "oracle_port_value": port},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
@@ -182,6 +219,133 @@ def per_frame_upload(ctx, scene, mesh_map):
         inst[i].mesh = mesh_map[inst[i].mesh]
     ctx.set_instances(inst, ni)
     ctx.set_camera(*scene.camera)
+
+
+def load_peaks():
+    """Roofline denominators: HBM copy bandwidth from MEASURED_PEAKS.json (driver-written), L2 read bandwidth and FP32 FMA
+    rate from profiles/peaks_b200.json (lib/gsb_peaks run on a B200 of this pool; SURVEY 8d: not in MEASURED_PEAKS.json)."""
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        hbm, hbm_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy)"
+    else:
+        hbm, hbm_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+    l2 = fp32 = None
+    ppath = os.path.join(ROOT, "profiles", "peaks_b200.json")
+    if os.path.exists(ppath):
+        pk = json.load(open(ppath))
+        l2, fp32 = pk.get("l2_read_gbs"), pk.get("fp32_fma_tflops")
+    return {"hbm": hbm, "hbm_src": hbm_src, "l2": l2, "fp32": fp32}
+
+
+def fetch_counts(ctx, W, H):
+    """Untimed instrumented passes: nodes / triangles / instance records fetched per extension ray and per shadow ray,
+    on the rays this workload really traces (the instrumented variant of the same kernels)."""
+    out = []
+    for mode in (1, 2):
+        ctx.set_instrumented(mode)
+        ctx.reset_counters()
+        ctx.render(W, H, 1 << 20, 2, 1)
+        c = ctx.counters()
+        out.append({k: c[k] / max(c["rays_counted"], 1) for k in ("nodes_visited", "tris_tested", "inst_entered")})
+    ctx.set_instrumented(0)
+    ctx.clear()
+    return out
+
+
+def ray_bytes(fetch, stream_bytes):
+    """80 B per 8-wide node, 48 B per triangle, 64 B per instance record + the wavefront streams of the ray."""
+    return 80 * fetch["nodes_visited"] + 48 * fetch["tris_tested"] + 64 * fetch["inst_entered"] + stream_bytes
+
+
+# bytes a shaded vertex moves through k_shade (DESIGN.md section 3): 72 in (ray origin / direction, hit record, weight,
+# instance word), 48 out (next ray, weight), 48 for its shadow-queue entry
+SHADE_BYTES_PER_VERTEX = 168
+
+
+def traversal_roofline(bvh, peaks, ext_fetch, sh_fetch, stage, iters, ext_rays, sh_rays, vertices):
+    """`roofline` of the dominant kernel (k_extend) + the side figures of k_shadow and k_shade, from per-stage CUDA-event
+    times on the render stream.  Bound: L2 when the BVH fits the 126 MB L2 with room to spare (configs[1], [2]), HBM
+    otherwise (configs[3]) — SURVEY 8(d)."""
+    ext_b, sh_b = ray_bytes(ext_fetch, 32 + 24), ray_bytes(sh_fetch, 32 + 4)
+    ext_ms, sh_ms, shade_ms = stage["extend"] / max(iters, 1), stage["shadow"] / max(iters, 1), stage["shade"] / max(iters, 1)
+    achieved = ext_b * (ext_rays / max(iters, 1)) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
+    sh_achieved = sh_b * (sh_rays / max(iters, 1)) / (sh_ms * 1e-3) / 1e9 if sh_ms > 0 else 0.0
+    in_l2 = bvh.get("bvh_bytes", 0) < 64 * 1024 * 1024 and peaks["l2"]
+    peak = peaks["l2"] if in_l2 else peaks["hbm"]
+    total = sum(stage.values())
+    shade_gbs = SHADE_BYTES_PER_VERTEX * vertices / (stage["shade"] * 1e-3) / 1e9 if stage["shade"] > 0 else 0.0
+    ops = None
+    opath = os.path.join(ROOT, "profiles", "shade_ops.json")
+    if os.path.exists(opath):
+        ops = json.load(open(opath))
+    flops_v = ops.get("flops_per_vertex") if ops else None
+    roof = {"kernel": "k_extend (closest-hit traversal)", "bound": "l2" if in_l2 else "hbm", "achieved": achieved, "peak": peak,
+            "unit": "GB/s", "frac": achieved / peak if peak else None,
+            "peak_source": "profiles/peaks_b200.json l2_read_gbs (lib/gsb_peaks on a B200 of this pool)" if in_l2 else peaks["hbm_src"],
+            "frac_of_hbm_peak": achieved / peaks["hbm"], "hbm_peak": peaks["hbm"], "l2_peak": peaks["l2"],
+            "frac_of_l2_peak": (achieved / peaks["l2"]) if peaks["l2"] else None,
+            "bytes_per_ray": ext_b, "rays_per_launch": ext_rays / max(iters, 1), "ms_per_launch": ext_ms,
+            "fetch_per_ray": ext_fetch, "launches": iters,
+            "share_of_step": {k: v / total for k, v in stage.items()} if total > 0 else None,
+            "shadow": {"bytes_per_ray": sh_b, "fetch_per_ray": sh_fetch, "achieved": sh_achieved, "ms_per_launch": sh_ms,
+                       "frac": sh_achieved / peak if peak else None},
+            "note": "achieved = algorithmic bytes (instrumented fetch counts x record sizes + the ray's wavefront streams) per second "
+                    "of k_extend; the kernel is issue-bound, its DRAM traffic is `traffic`"}
+    shade = {"kernel": "k_shade<TYPE> (all BSDF types of the scene)", "bytes_per_vertex": SHADE_BYTES_PER_VERTEX,
+             "vertices_per_launch": vertices / max(iters, 1), "ms_per_launch": shade_ms, "achieved_gbs": shade_gbs,
+             "frac_hbm": shade_gbs / peaks["hbm"], "flops_per_vertex": flops_v,
+             "achieved_tflops": (flops_v * vertices / (stage["shade"] * 1e-3) / 1e12) if flops_v and stage["shade"] > 0 else None,
+             "fp32_peak_tflops": peaks["fp32"],
+             "frac_fp32": (flops_v * vertices / (stage["shade"] * 1e-3) / 1e12 / peaks["fp32"]) if flops_v and peaks["fp32"] and stage["shade"] > 0 else None,
+             "flops_source": ops.get("source") if ops else None}
+    return roof, shade
+
+
+def short_run(g, torch, dev, stream, name, scene, W, H, S, max_depth, peaks, steps=2, warmup=2):
+    """A short driver-run measurement of another BASELINE.json configuration on this GPU: value, stage times, fetch counts,
+    roofline fractions (same method as the main line, fewer steps; no e2e / CPU legs)."""
+    t_build = time.perf_counter()
+    ctx = g.Context(dev.index)
+    ctx.set_stream(stream.cuda_stream)
+    ctx.upload(scene)
+    ctx.set_params(max_depth=max_depth)
+    bvh = ctx.bvh_stats()
+    ctx.render(W, H, 0, 0)
+    ctx.clear()
+    torch.cuda.synchronize()
+    t_build = time.perf_counter() - t_build
+    ext_fetch, sh_fetch = fetch_counts(ctx, W, H)
+    for k in range(warmup):
+        ctx.render(W, H, k * S, S, 1)
+    ctx.clear()
+    ctx.reset_counters()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for k in range(steps):
+        ctx.render(W, H, (warmup + k) * S, S, 1)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    c = ctx.counters()
+    ctx.set_profiling(True)
+    c0 = ctx.counters()
+    ctx.render(W, H, (warmup + steps) * S, S, 1)
+    stage = {k: v for k, v in ctx.last_render_ms().items() if k != "total"}
+    iters = ctx.launch_info()[1]
+    c1 = ctx.counters()
+    ctx.set_profiling(False)
+    img = ctx.read_hdr()
+    ok = bool(np.isfinite(img).all() and img[..., :3].mean() > 1e-3)
+    ctx.close()
+    d_ext, d_sh = c1["extension_rays"] - c0["extension_rays"], c1["shadow_rays"] - c0["shadow_rays"]
+    roof, shade = traversal_roofline(bvh, peaks, ext_fetch, sh_fetch, stage, iters, d_ext, d_sh, c1["shaded_vertices"] - c0["shaded_vertices"])
+    return {"workload": f"{name} {W}x{H}, NEE+MIS, max_depth {max_depth}, {S} spp per step", "value": c["paths"] / (ms * 1e-3) / 1e6,
+            "unit": UNIT, "mrays_per_s": (c["extension_rays"] + c["shadow_rays"]) / (ms * 1e-3) / 1e6, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms / steps, "stage_ms_per_step": stage, "image_ok": ok, "setup_s": t_build,
+            "rays_per_path": {"extension": c["extension_rays"] / c["paths"], "shadow": c["shadow_rays"] / c["paths"]},
+            "roofline": {k: roof[k] for k in ("bound", "achieved", "peak", "frac", "frac_of_hbm_peak", "frac_of_l2_peak", "bytes_per_ray", "fetch_per_ray", "ms_per_launch")},
+            "shade_gbs": shade["achieved_gbs"], "bvh": bvh}
 
 
 def run_ours(a, rank, world, local_rank):
@@ -225,23 +389,9 @@ def run_ours(a, rank, world, local_rank):
                 accum.zero_()       # rank 0 keeps the running global sum; the others restart their partial sums
 
     # ---- instrumented pass (untimed): fetch counts of the rays this workload really traces ------------------
-    ci = cs = {"nodes_visited": 0, "tris_tested": 0, "inst_entered": 0, "rays_counted": 0}
-    if not a.no_instrumented:
-        ctx.set_instrumented(1)
-        ctx.reset_counters()
-        ctx.render(W, H, 1 << 20, 2, 1)
-        ci = ctx.counters()
-        ctx.set_instrumented(2)
-        ctx.reset_counters()
-        ctx.render(W, H, 1 << 20, 2, 1)
-        cs = ctx.counters()
-        ctx.set_instrumented(0)
-    ext_fetch = {k: ci[k] / max(ci["rays_counted"], 1) for k in ("nodes_visited", "tris_tested", "inst_entered")}
-    sh_fetch = {k: cs[k] / max(cs["rays_counted"], 1) for k in ("nodes_visited", "tris_tested", "inst_entered")}
-    # 80 B per 8-wide node, 48 B per triangle, 64 B per instance record, + the wavefront streams of the
-    # ray (ray in 32 B; hit record out 20 B + 4 B queue entry)
-    ext_bytes_per_ray = 80 * ext_fetch["nodes_visited"] + 48 * ext_fetch["tris_tested"] + 64 * ext_fetch["inst_entered"] + 32 + 24
-    sh_bytes_per_ray = 80 * sh_fetch["nodes_visited"] + 48 * sh_fetch["tris_tested"] + 64 * sh_fetch["inst_entered"] + 32 + 4
+    peaks = load_peaks()
+    zero = {"nodes_visited": 0.0, "tris_tested": 0.0, "inst_entered": 0.0}
+    ext_fetch, sh_fetch = (zero, zero) if a.no_instrumented else fetch_counts(ctx, W, H)
     ctx.clear()
     accum.zero_()
 
@@ -269,7 +419,7 @@ def run_ours(a, rank, world, local_rank):
     stage = {"extend": 0.0, "shade": 0.0, "shadow": 0.0, "finish": 0.0}
     iters = 0
     prof_steps = max(1, min(a.steps, 2))
-    prof_ext = 0
+    prof_ext = prof_sh = prof_vert = 0
     for k in range(prof_steps):
         c0 = ctx.counters()
         ctx.render(W, H, (a.warmup + a.steps + k) * S * world + rank, S, world)
@@ -277,7 +427,10 @@ def run_ours(a, rank, world, local_rank):
         for name in stage:
             stage[name] += ms[name]
         iters += ctx.launch_info()[1]
-        prof_ext += ctx.counters()["extension_rays"] - c0["extension_rays"]
+        c1 = ctx.counters()
+        prof_ext += c1["extension_rays"] - c0["extension_rays"]
+        prof_sh += c1["shadow_rays"] - c0["shadow_rays"]
+        prof_vert += c1["shaded_vertices"] - c0["shaded_vertices"]
     ctx.set_profiling(False)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
@@ -299,35 +452,13 @@ def run_ours(a, rank, world, local_rank):
         samples = float(accum.view(-1, 4)[:, 3].mean().item())
         assert abs(samples - (a.steps * world + prof_steps) * S) < 0.5, f"sum buffer holds {samples} samples per pixel"
 
-    # ---- roofline of the dominant kernel (k_extend: closest-hit traversal), from this rank's timed region -----------
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy)"
-    else:
-        peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
-    ext_per_launch = prof_ext / max(iters, 1)
-    ext_ms_per_launch = stage["extend"] / max(iters, 1)
-    achieved = ext_bytes_per_ray * ext_per_launch / (ext_ms_per_launch * 1e-3) / 1e9 if ext_ms_per_launch > 0 else 0.0
+    # ---- roofline of the dominant kernel (k_extend: closest-hit traversal), from this rank's profiled steps ----------
+    roofline, roofline_shade = traversal_roofline(bvh, peaks, ext_fetch, sh_fetch, stage, iters, prof_ext, prof_sh, prof_vert)
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "extend_traffic.json")
-    if os.path.exists(tpath):
+    if os.path.exists(tpath) and a.scene == "cornell":
         traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
-    # L2 / FP32 denominators measured on a B200 of this pool by lib/gsb_peaks (not in MEASURED_PEAKS.json)
-    l2_peak = fp32_peak = None
-    ppath = os.path.join(ROOT, "profiles", "peaks_b200.json")
-    if os.path.exists(ppath):
-        pk = json.load(open(ppath))
-        l2_peak, fp32_peak = pk.get("l2_read_gbs"), pk.get("fp32_fma_tflops")
-    stage_total = sum(stage.values())
-    roofline = {"kernel": "k_extend (closest-hit traversal)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                "l2_peak": l2_peak, "frac_of_l2_peak": (achieved / l2_peak) if l2_peak else None, "fp32_peak_tflops": fp32_peak,
-                "bytes_per_ray": ext_bytes_per_ray, "rays_per_launch": ext_per_launch, "ms_per_launch": ext_ms_per_launch,
-                "fetch_per_ray": ext_fetch, "launches": iters,
-                "share_of_step": {k: v / stage_total for k, v in stage.items()} if stage_total > 0 else None,
-                "shadow": {"bytes_per_ray": sh_bytes_per_ray, "fetch_per_ray": sh_fetch,
-                           "achieved": (sh_bytes_per_ray * c["shadow_rays"] * prof_steps / a.steps / (stage["shadow"] * 1e-3) / 1e9) if stage["shadow"] > 0 else 0.0},
-                "note": "scene BVH is a few KB (L1/L2 resident): the HBM figure is the algorithmic-byte rate, not DRAM traffic"}
+    roofline["traffic"] = traffic
 
     # ---- e2e: the per-frame API with host buffers ----------------------------------------------------------------------
     e2e = None
@@ -386,17 +517,28 @@ def run_ours(a, rank, world, local_rank):
                "mrays_per_s": (oc["extension_rays"] + oc["shadow_rays"]) / dt / 1e6,
                "sample": f"{W}x{H} x {spp} spp of the same scene/params ({oc['paths']} paths, {dt:.1f} s)"}
 
+    # ---- the other BASELINE.json configurations, short runs on this GPU (N = 1 only) ------------------------------------
+    extra = None
+    if rank == 0 and world == 1 and not a.no_extra and a.scene == "cornell" and not a.scene_params:
+        extra = {}
+        for name, scn, (ew, eh, es) in (("gallery", "gallery", (1920, 1080, 64)), ("field", "field", (1920, 1080, 16)),
+                                        ("cornell_4k", "cornell", (4096, 2160, 32))):
+            try:
+                extra[name] = short_run(g, torch, dev, stream, scn, g.Scene.builtin(scn), ew, eh, es, a.max_depth, peaks)
+            except Exception as e:      # a failed side run must not take the headline line with it
+                extra[name] = {"error": repr(e)}
+
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": elapsed_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "mrays_per_s": mrays,
                 "rays_per_path": {"extension": ext / paths, "shadow": sh / paths},
-                "config": {"workload": workload_name(a, world), "width": W, "height": H, "spp_per_step": S, "max_depth": a.max_depth,
+                "config": {"workload": workload_name(a), "width": W, "height": H, "spp_per_step": S, "max_depth": a.max_depth,
                            "scene": a.scene, "parallelism": f"sample-index sharding x{world}" + (", 1 NCCL reduce per step" if world > 1 else ""),
                            "l2": "path state streams of a step (up to 4.2 M slots x ~230 B) exceed the 126 MB L2; scene data is meant to be cache resident"},
-                "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(launches),
+                "e2e": e2e, "roofline": roofline, "roofline_shade": roofline_shade, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(launches),
                 "stage_ms_per_step": {k: v / prof_steps for k, v in stage.items()},
-                "device_ms_per_step": device_ms / a.steps, "bvh": bvh}
+                "device_ms_per_step": device_ms / a.steps, "bvh": bvh, "extra_workloads": extra}
         print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:

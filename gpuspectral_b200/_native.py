@@ -45,7 +45,7 @@ class Params(C.Structure):
 
 class Counters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("paths", "extension_rays", "shadow_rays", "iterations",
-                                          "nodes_visited", "tris_tested", "inst_entered", "rays_counted")]
+                                          "nodes_visited", "tris_tested", "inst_entered", "rays_counted", "shaded_vertices")]
 
 
 class BvhStats(C.Structure):

@@ -863,6 +863,7 @@ gsb_status gsb_get_counters(gsb_context* ctx, gsb_counters* out) {
         out->tris_tested = h[ST_TRIS];
         out->inst_entered = h[ST_INSTS];
         out->rays_counted = h[ST_RAYS];
+        out->shaded_vertices = h[ST_VERTICES];
         return GSB_OK;
     });
 }

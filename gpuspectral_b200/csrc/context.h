@@ -45,7 +45,7 @@ struct WavefrontState {
     unsigned long long* stats = nullptr;
 };
 
-enum { ST_LIVE = 0, ST_RETIRED = 1, ST_PATHS = 2, ST_EXT = 3, ST_SHADOW = 4, ST_ITERS = 5, ST_NODES = 6, ST_TRIS = 7, ST_INSTS = 8, ST_RAYS = 9, ST_OVERFLOW = 10, ST_NEXTWORK = 11, ST_BATCHNEXT = 12, ST_LOOPITERS = 13, ST_COUNT = 16 };
+enum { ST_LIVE = 0, ST_RETIRED = 1, ST_PATHS = 2, ST_EXT = 3, ST_SHADOW = 4, ST_ITERS = 5, ST_NODES = 6, ST_TRIS = 7, ST_INSTS = 8, ST_RAYS = 9, ST_OVERFLOW = 10, ST_NEXTWORK = 11, ST_BATCHNEXT = 12, ST_LOOPITERS = 13, ST_VERTICES = 14, ST_COUNT = 16 };
 
 // A render call that was launched as a device-side loop and has not been waited for yet.
 struct PendingRender {

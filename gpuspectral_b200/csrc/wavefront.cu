@@ -328,6 +328,7 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
     const uint32_t warpsTotal = gridDim.x * (kBlock / 32), warpId = blockIdx.x * (kBlock / 32) + (threadIdx.x >> 5);
     const uint32_t tiles = (slots + 31u) / 32u;
     uint32_t pendingCount = 0;
+    uint32_t shaded = 0;   // warp-uniform: vertices this warp shaded (gsb_counters::shaded_vertices)
     for (uint32_t tile = warpId;; tile += warpsTotal) {
         const bool scanning = tile < tiles;
         const uint32_t cand = tile * 32u + lane;
@@ -381,6 +382,7 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
         }
         bool terminate = false, needShadow = false, hasBase = false;
         float4 shO, shD, shBase, shNee;
+        shaded += (uint32_t)__popc(__ballot_sync(0xffffffffu, active));
         if (active) {
 #if GSB_SHADE_STREAM
             // read-once state streams go past L1 (evict-first), which then keeps the scene records the hit points to
@@ -547,6 +549,7 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
         }
         if (!scanning && pendingCount == 0u) break;
     }
+    if (lane == 0u && shaded) atomicAdd(&wf.stats[ST_VERTICES], (unsigned long long)shaded);
 }
 
 // ---- shadow ---------------------------------------------------------------------------------------

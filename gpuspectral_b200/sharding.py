@@ -54,7 +54,11 @@ class ShardedRenderer:
         self.width, self.height = width, height
         self.device = torch.device("cuda", device_index)
         self.ctx = Context(device_index)
-        self.stream = torch.cuda.current_stream(self.device)
+        # An explicit stream shared by the render, the NCCL reduce and the buffer resets.  torch's default stream has the
+        # handle 0, which gsb_set_stream reads as "create a private stream": the reduce would then not be ordered after
+        # the (asynchronous) render.  Every torch call below therefore runs under `with torch.cuda.stream(self.stream)`.
+        self.stream = torch.cuda.Stream(device=self.device)
+        assert self.stream.cuda_stream != 0
         self.ctx.set_stream(self.stream.cuda_stream)
         self.ctx.upload(scene)
         if params:
@@ -68,11 +72,16 @@ class ShardedRenderer:
     def render(self, spp_total):
         """Adds `spp_total` samples per pixel to the frame, split over the ranks; rank 0 ends up holding the global sum."""
         first, n, stride = shard_samples(self.next_sample, spp_total, self.rank, self.world)
-        self.ctx.render(self.width, self.height, first, n, stride)
-        reduce_frame(self.accum, 0)
-        if self.rank != 0:
-            self.accum.zero_()
+        import torch
+        self.ctx.render(self.width, self.height, first, n, stride)    # asynchronous, on self.stream
+        with torch.cuda.stream(self.stream):
+            reduce_frame(self.accum, 0)
+            if self.rank != 0:
+                self.accum.zero_()
         self.next_sample += spp_total
+
+    def synchronize(self):
+        self.stream.synchronize()
 
     def read_hdr(self, out=None):
         return self.ctx.read_hdr(out)

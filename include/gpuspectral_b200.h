@@ -127,6 +127,7 @@ typedef struct gsb_counters {
     uint64_t tris_tested;     /* triangles fetched (48 B each) */
     uint64_t inst_entered;    /* instance records fetched (64 B each) */
     uint64_t rays_counted;
+    uint64_t shaded_vertices; /* path vertices shaded by k_shade (extension rays that hit a surface) */
 } gsb_counters;
 
 /* Acceleration-structure statistics of the current scene. */

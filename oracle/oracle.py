@@ -113,6 +113,44 @@ class OracleScene:
         o.set_camera(*scene.camera)
         return o
 
+    # ---- scene archives: the flat records of a host scene as one .npz, so that the CPU arm of bench.py can run without the
+    # product package (tests/golden/make_scene_npz.py writes them; tests/test_oracle_cpu.py checks archive == host scene)
+    @staticmethod
+    def dump_host_scene(scene, path):
+        import ctypes
+        arrays = {"mesh_count": np.array([scene.mesh_count], np.uint32)}
+        for i in range(scene.mesh_count):
+            p, q = scene.mesh(i)
+            arrays[f"mesh{i}_p"], arrays[f"mesh{i}_n"] = p, q
+        for t in range(9):
+            raw, n = scene.bsdfs(t)
+            arrays[f"bsdf{t}"] = np.frombuffer(raw, np.uint8)
+            arrays[f"bsdf{t}_count"] = np.array([n], np.uint32)
+        lights, nl = scene.lights
+        arrays["lights"] = np.frombuffer(ctypes.string_at(lights, ctypes.sizeof(lights)), np.uint8)
+        arrays["lights_count"] = np.array([nl], np.uint32)
+        inst, ni = scene.instances
+        arrays["instances"] = np.frombuffer(ctypes.string_at(inst, ctypes.sizeof(inst)), np.uint8)
+        arrays["instances_count"] = np.array([ni], np.uint32)
+        eye, tw, fov = scene.camera
+        arrays["eye"], arrays["to_world"], arrays["fov"] = eye, tw, np.array([fov], np.float32)
+        np.savez_compressed(path, **arrays)
+
+    @staticmethod
+    def from_npz(path):
+        z = np.load(path)
+        o = OracleScene()
+        for i in range(int(z["mesh_count"][0])):
+            o.add_mesh(z[f"mesh{i}_p"], z[f"mesh{i}_n"])
+        for t in range(9):
+            o.set_bsdfs(t, z[f"bsdf{t}"].tobytes(), int(z[f"bsdf{t}_count"][0]))
+        lights = C.create_string_buffer(z["lights"].tobytes(), max(1, z["lights"].size))
+        o.set_lights(lights, int(z["lights_count"][0]))
+        inst = C.create_string_buffer(z["instances"].tobytes(), max(1, z["instances"].size))
+        o.set_instances(inst, int(z["instances_count"][0]))
+        o.set_camera(z["eye"], z["to_world"], float(z["fov"][0]))
+        return o
+
     def add_mesh(self, positions, normals):
         p = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
         q = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)

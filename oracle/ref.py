@@ -65,6 +65,7 @@ def lib():
             "ref_render": (C.c_int, [P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, f32p, P, P, C.c_int, u64p, u64p]),
             "ref_path_probe": (C.c_int, [P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, f32p, P, C.c_uint32, P, P]),
             "ref_closest_hit": (C.c_int, [P, f32p, P, f32p, P, P]),
+            "ref_set_max_depth": (C.c_int, [C.c_int]),
         }
         for name, (res, args) in sig.items():
             f = getattr(L, name)
@@ -74,6 +75,11 @@ def lib():
 
 
 _fp, _up = orc._fp, orc._up
+
+
+def set_max_depth(depth=0):
+    """raygen.rgen's MAX_DEPTH for the following renders (process-wide); 0 restores the shader's literal (50)."""
+    return lib().ref_set_max_depth(int(depth))
 
 
 def _oracle_intersector():
@@ -91,6 +97,20 @@ class RefScene:
         s, self._s = getattr(self, "_s", None), None
         if s and _lib is not None:
             _lib.ref_scene_destroy(s)
+
+    @staticmethod
+    def from_npz(path):
+        """The flat records of a scene archive (oracle.OracleScene.dump_host_scene)."""
+        z = np.load(path)
+        r = RefScene()
+        for i in range(int(z["mesh_count"][0])):
+            r.add_mesh(z[f"mesh{i}_p"], z[f"mesh{i}_n"])
+        for t in range(8):
+            r.set_bsdfs(t, z[f"bsdf{t}"].tobytes(), int(z[f"bsdf{t}_count"][0]))
+        r.set_lights(C.create_string_buffer(z["lights"].tobytes(), max(1, z["lights"].size)), int(z["lights_count"][0]))
+        r.set_instances(C.create_string_buffer(z["instances"].tobytes(), max(1, z["instances"].size)), int(z["instances_count"][0]))
+        r.set_camera(z["eye"], z["to_world"], float(z["fov"][0]))
+        return r
 
     @staticmethod
     def from_host_scene(scene):

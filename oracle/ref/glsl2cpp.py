@@ -27,6 +27,10 @@ as written.  Each rule and why it does not change the meaning:
 10. `vec2(randUniform(), randUniform())` -> `vec2{randUniform(), randUniform()}`: GLSL evaluates constructor arguments
     left to right (GLSL 4.60 spec, section 6.1.1 / 5.9 "order of evaluation"), C++ only guarantees that order for
     braced initialisers.  The script refuses to run if any OTHER expression holds two RNG calls.
+11. raygen.rgen's `#define MAX_DEPTH 50` -> `#define REF_MAX_DEPTH_LITERAL 50` + `#define MAX_DEPTH (gsref::g_maxDepth)`: the
+    bound becomes a run-time integer that STARTS OUT as the shader's literal (ref_glue.cpp: g_maxDepth), so that
+    BASELINE.json's "max depth 8" configurations can be run through the shader text (ref_set_max_depth); every pinning
+    test runs with the literal.
 """
 import os
 import re
@@ -61,6 +65,9 @@ def convert(name, text):
     for stmt in strip_comments_for_check(text).split(";"):
         if len(re.findall(r"(?<!float )(?<!uint )\brand(?:Uniform|Pcg)\s*\(\s*\)", stmt)) > 1 and "vec2{randUniform(), randUniform()}" not in stmt:
             raise SystemExit(f"{name}: an expression with two RNG calls needs an evaluation-order rule: {stmt.strip()[:120]}")
+    text, n_depth = re.subn(r"^#define\s+MAX_DEPTH\s+(\d+)\s*$", r"#define REF_MAX_DEPTH_LITERAL \1\n#define MAX_DEPTH (gsref::g_maxDepth)", text, flags=re.M)
+    if name == "raygen.rgen" and n_depth != 1:
+        raise SystemExit("raygen.rgen: expected exactly one '#define MAX_DEPTH <int>'")
     text = BUFFER_REF.sub(lambda m: f"REF_BUFFER({m.group(1)}, {m.group(2)}, {m.group(3)})", text)
     text = UNIFORM_BLOCK.sub("", text)
     text = INTERFACE_VAR.sub("", text)

@@ -102,6 +102,7 @@ struct Pipeline {
     uint64_t extRays = 0, shadowRays = 0;
 };
 thread_local Pipeline P;
+extern int g_maxDepth;   // raygen.rgen's MAX_DEPTH (glsl2cpp.py rule 11): the shader's literal unless ref_set_max_depth changed it
 
 void traceRayEXT(accelerationStructureEXT tlas, uint rayFlags, uint cullMask, int sbtOffset, int sbtStride, int missIndex,
                  vec3 origin, float tmin, vec3 direction, float tmax, int payload);
@@ -135,6 +136,8 @@ namespace rmiss {
 namespace shadowmiss {
 #include "shadowmiss.rmiss.cpp"
 }
+
+int g_maxDepth = REF_MAX_DEPTH_LITERAL;
 
 #undef prd
 #undef shadowed
@@ -443,6 +446,12 @@ REF_API int ref_render(ref_scene* s, uint32_t width, uint32_t height, uint32_t f
     if (ext_rays) *ext_rays = ext;
     if (shadow_rays) *shadow_rays = sh;
     return 0;
+}
+
+// raygen.rgen's MAX_DEPTH for the following renders; <= 0 restores the shader's literal.  Returns the value in force.
+REF_API int ref_set_max_depth(int depth) {
+    gsref::g_maxDepth = depth > 0 ? depth : REF_MAX_DEPTH_LITERAL;
+    return gsref::g_maxDepth;
 }
 
 // one pixel-sample with per-bounce records; the pixel's value goes to out_rgb (timestamp 0 semantics: the sample itself)

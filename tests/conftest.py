@@ -91,3 +91,49 @@ def random_rays(scene, n, seed, spread=1.5):
     d /= np.linalg.norm(d, axis=1, keepdims=True)
     import gpuspectral_b200 as g
     return g.make_rays(o.astype(np.float32), d.astype(np.float32), 0.0, 1e10)
+
+
+class ArchiveScene:
+    """A scene archive (oracle.OracleScene.dump_host_scene -> tests/golden/scene_*.npz) with the host Scene's read interface
+    (mesh_count, mesh, bsdfs, lights, instances, camera), so that Context.upload / OracleScene.from_host_scene /
+    random_rays take it like a Scene.  Lets scenes of the reference checkout travel to the GPU box as flat records."""
+
+    def __init__(self, path):
+        import ctypes as C
+
+        import gpuspectral_b200._native as N
+        z = np.load(path)
+        self._z = z
+        self.mesh_count = int(z["mesh_count"][0])
+        ni, nl = int(z["instances_count"][0]), int(z["lights_count"][0])
+        self._inst = (N.Instance * max(1, ni))()
+        C.memmove(self._inst, z["instances"].tobytes(), ni * C.sizeof(N.Instance))
+        self._ni = ni
+        self._lights = (N.TriangleLight * max(1, nl))()
+        C.memmove(self._lights, z["lights"].tobytes(), nl * C.sizeof(N.TriangleLight))
+        self._nl = nl
+
+    def mesh(self, i):
+        return self._z[f"mesh{i}_p"], self._z[f"mesh{i}_n"]
+
+    def bsdfs(self, t):
+        return self._z[f"bsdf{t}"].tobytes(), int(self._z[f"bsdf{t}_count"][0])
+
+    @property
+    def lights(self):
+        return self._lights, self._nl
+
+    @property
+    def instances(self):
+        import ctypes as C
+        copy = type(self._inst)()
+        C.memmove(copy, self._inst, C.sizeof(copy))
+        return copy, self._ni
+
+    @property
+    def camera(self):
+        return self._z["eye"], self._z["to_world"], float(self._z["fov"][0])
+
+    @property
+    def instanced_triangles(self):
+        return sum(len(self._z[f"mesh{self._inst[i].mesh}_p"]) // 3 for i in range(self._ni))

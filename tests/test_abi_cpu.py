@@ -40,7 +40,7 @@ def test_record_layouts_match_reference(gsb):
     assert gsb.BSDF_STRIDES[8] == 16 and gsb.BSDF_TYPE_COUNT == 9      # the rough dielectric extension
     from gpuspectral_b200 import _native as N
     assert C.sizeof(N.TriangleLight) == 64 and C.sizeof(N.Ray) == 32 and C.sizeof(N.Instance) == 88
-    assert C.sizeof(N.Params) == 16 and C.sizeof(N.Counters) == 64
+    assert C.sizeof(N.Params) == 16 and C.sizeof(N.Counters) == 72
     p = gsb.Context.default_params()
     assert (p.max_depth, p.rr_start, p.cutoff, p.nee) == (50, 10, 20.0, 1)   # raygen.rgen:27,60,66; rayhit.rchit:656
 
@@ -105,3 +105,25 @@ def test_xml_scene_equals_builtin(gsb):
     for m in range(a.mesh_count):
         assert np.array_equal(a.mesh(m)[0], b.mesh(m)[0]) and np.array_equal(a.mesh(m)[1], b.mesh(m)[1])
     assert bytes(a.lights[0]) == bytes(b.lights[0])
+
+
+ASSETS = "/root/reference/src/GPUSpectral/assets"
+_XML = """<scene version="0.6.0"><sensor type="perspective"><float name="fov" value="40"/>
+<transform name="to_world"><lookat origin="0,0,5" target="0,0,0" up="0,1,0"/></transform></sensor>
+<bsdf type="diffuse" id="m"><rgb name="reflectance" value="0.5,0.5,0.5"/></bsdf>
+%s</scene>"""
+
+
+@pytest.mark.skipif(not os.path.exists(ASSETS + "/rect.obj"), reason="reference checkout not present")
+@pytest.mark.parametrize("shape,obj", [("rectangle", "rect.obj"), ("cube", "box.obj")])
+def test_builtin_shapes_equal_the_reference_obj_files(gsb, shape, obj):
+    """engine/Loader.cpp:269-277 loads assets/rect.obj / assets/box.obj for <shape type="rectangle|cube">; the host layer
+    builds those two meshes procedurally (no asset directory needed at run time).  Same triangles in the same order with
+    the same vertex order and normals as the reference's files read through the OBJ loader."""
+    a = gsb.Scene.from_xml_string(_XML % f'<shape type="{shape}"><ref id="m"/></shape>', ".")
+    b = gsb.Scene.from_xml_string(_XML % f'<shape type="obj"><string name="filename" value="{obj}"/><ref id="m"/></shape>', ASSETS)
+    assert a.warnings == [] and b.warnings == []
+    (pa, na), (pb, nb) = a.mesh(0), b.mesh(0)
+    assert pa.shape == pb.shape and len(pa) in (6, 36)
+    assert np.array_equal(pa, pb)
+    assert np.array_equal(na, nb)
