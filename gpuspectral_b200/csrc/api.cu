@@ -357,9 +357,18 @@ static void choosePolicy(gsb_context* ctx) {
     if (const char* e = getenv("GSB_POOL")) { const int v = atoi(e); ctx->poolExtend = (v & 1) != 0; ctx->poolShadow = (v & 2) != 0; }
     uint32_t poolRefill = 1u;
     if (const char* e = getenv("GSB_POOL_REFILL")) poolRefill = (uint32_t)std::min(32, std::max(1, atoi(e)));
-    const uint32_t direct = ctx->directRefill;
+    // idle lanes that trigger a refill straight from the source (measured, r2e: taking a ray is two loads since k_regen
+    // starts the paths, so refilling early pays: Cornell 24 -> 12 lanes = -10 % k_extend; two-level scenes 8 for both kernels;
+    // the any-hit kernel of world-only scenes stays at 24).  GSB_REFILL / GSB_SHADOW_REFILL override.
+    const bool twoLevel = ctx->numTraceInstances > 0;
+    const uint32_t direct = ctx->directRefill ? ctx->directRefill : (twoLevel ? 8u : 12u);
+    const uint32_t directShadow = ctx->shadowRefill ? ctx->shadowRefill : (twoLevel ? 8u : 24u);
     ctx->refillMin = (ctx->refillMin & ~0xffu) | (ctx->poolExtend ? poolRefill : direct);
-    ctx->shadowControl = ctx->poolShadow ? poolRefill : direct;
+    ctx->shadowControl = ctx->poolShadow ? poolRefill : directShadow;
+    // Ray sorting between bounces (wavefront.cu: sortKey): pays when the BVH is much larger than the caches, i.e. when
+    // incoherent rays cost memory latency and lane divergence; GSB_SORT = grid bits per axis (0 = off) overrides.
+    ctx->sortBits = ctx->numTraceInstances > 0 ? 6u : 0u;
+    if (const char* e = getenv("GSB_SORT")) ctx->sortBits = (uint32_t)std::min(9, std::max(0, atoi(e)));
 }
 
 SceneDev gsb_context::sceneDev() const {
@@ -381,6 +390,16 @@ SceneDev gsb_context::sceneDev() const {
     memcpy(sc.view, view, sizeof(view));
     sc.fov = fov;
     sc.params = params;
+    sc.sortBits = sortBits;
+    for (int a = 0; a < 3; a++) {
+        // bounds of everything a ray can hit: the world level and the top level
+        float lo = 1e30f, hi = -1e30f;
+        if (world.numPrims) { lo = std::min(lo, world.lo[a]); hi = std::max(hi, world.hi[a]); }
+        if (numTraceInstances) { lo = std::min(lo, tlas.lo[a]); hi = std::max(hi, tlas.hi[a]); }
+        if (!(hi > lo)) { lo = 0.0f; hi = 1.0f; }
+        sc.sortLo[a] = lo;
+        sc.sortScale[a] = (float)(1u << sortBits) / (hi - lo);
+    }
     return sc;
 }
 
@@ -417,6 +436,10 @@ gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx) {
         if (const char* e = getenv("GSB_REFILL")) {
             const long v = atol(e);
             if (v >= 1 && v <= 32) { ctx->refillMin = (ctx->refillMin & ~0xffu) | (uint32_t)v; ctx->directRefill = (uint32_t)v; }
+        }
+        if (const char* e = getenv("GSB_SHADOW_REFILL")) {
+            const long v = atol(e);
+            if (v >= 1 && v <= 32) ctx->shadowRefill = (uint32_t)v;
         }
         if (const char* e = getenv("GSB_VOTE")) {
             const long v = atol(e);

@@ -130,6 +130,9 @@ struct SceneDev {
     float view[16];  // column-major toWorld
     float fov;
     gsb_params params;
+    // ray sorting: origin cell = (o - sortLo) * sortScale per axis, clamped to [0, 2^sortBits); sortBits = 0: no sorting
+    float sortLo[3], sortScale[3];
+    uint32_t sortBits;
 };
 
 }  // namespace gsb

@@ -27,8 +27,11 @@ enum { Q_MATERIAL0 = 0, Q_TRACED = GSB_BSDF_TYPE_COUNT, Q_SHADOW = GSB_BSDF_TYPE
 // (+ pixel sample index and the hit record) spread over 16-byte and 4-byte streams.
 struct WavefrontState {
     uint32_t capacity = 0;      // slots allocated
-    float4* rayO = nullptr;     // origin.xyz, RNG state of the path (payload `seed`) in .w
-    float4* rayD = nullptr;     // direction.xyz, path flags in .w: depth (bits 0-15), wasDelta, countEmitted
+    // the path's ray, 2 float4 per slot: origin.xyz + RNG state of the path (payload `seed`) in .w, direction.xyz + path flags
+    // in .w (depth bits 0-15, wasDelta, countEmitted, dead).  One 32-byte record per slot (wavefront.cu: rayOrigin /
+    // rayDirection), so that the scattered accesses — paths started by k_regen, rays gathered in sorted order — cost one
+    // sector instead of two; GSB_RAY_AOS=0 builds the two-stream layout for comparison
+    float4* ray = nullptr;
     float4* weightDW = nullptr; // weight.xyz, directWeight
     float4* result = nullptr;   // radiance of the current sample .xyz; only touched by vertices that add light
     uint32_t* sampleK = nullptr;  // pixel the slot's current path belongs to; bit 31: path finished, add it to the image;
@@ -39,7 +42,14 @@ struct WavefrontState {
     float4* shadowD = nullptr;      // direction.xyz, slot id bits
     float4* shadowBase = nullptr;   // emitted without NEE .xyz, directWeight if visible
     float4* shadowNee = nullptr;    // NEE contribution .xyz
-    unsigned long long* chunkWork = nullptr;  // per slot chunk: the partly used block of work items it holds (wavefront.cu: packWork)
+    // ray sorting (optional): key per slot (written with the ray by k_regen / k_shade), the sorted keys, the slot order
+    // k_extend follows, the identity permutation that is the sort's value input, cub's scratch space
+    uint32_t* sortKey = nullptr;
+    uint32_t* sortKeyOut = nullptr;
+    uint32_t* order = nullptr;
+    uint32_t* iota = nullptr;
+    void* sortTemp = nullptr;
+    size_t sortTempBytes = 0;
     uint32_t* qCount = nullptr;     // 2 x Q_COUNT queue counters
     // device statistics block: [0] live slots, [2..] totals
     unsigned long long* stats = nullptr;
@@ -93,8 +103,10 @@ struct gsb_context {
     // (bits 0..7, GSB_REFILL), lanes that make a quorum for a traversal phase (8..15, GSB_VOTE; closest-hit kernel only,
     // the any-hit kernel measured best without a quorum), lanes that keep the triangle loop spinning (16..23, GSB_TRIMIN)
     uint32_t refillMin = 24u | (4u << 8) | (2u << 16);
-    uint32_t directRefill = 24u;   // idle lanes that trigger a refill straight from the source (GSB_REFILL)
+    uint32_t directRefill = 0u;    // idle lanes that trigger a refill straight from the source (GSB_REFILL); 0 = per-scene default (api.cu: choosePolicy)
+    uint32_t shadowRefill = 0u;    // the same for the any-hit kernel (GSB_SHADOW_REFILL)
     uint32_t shadowControl = 24u;  // the any-hit kernel's control word (no phase quorum measured best)
+    uint32_t sortBits = 0;         // ray sorting: grid bits per axis of the origin cell in the sort key; 0 = rays are traced in slot order
     bool poolExtend = false, poolShadow = false;   // traverse.cuh: ray pool (true) or direct refill; chosen per scene in gsb_scene_set_instances, GSB_POOL overrides
     uint32_t shadeDirectMin = 32;  // k_shade: matching lanes from which a tile is shaded in place (GSB_SHADE_DIRECT; measured flat from 12 to 32)
     bool useGraphLoop = true;    // device-side render loop (conditional CUDA graph); GSB_GRAPH=0 or a failed build disables it

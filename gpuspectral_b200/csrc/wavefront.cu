@@ -4,14 +4,15 @@
 // rayhit.rchit:666-797 through traceRayEXT).  Here the same per-path state machine is cut
 // into stages that each run as one wide kernel over many paths:
 //
-//   k_extend   first, for slots whose path has ended: adds the sample to the image (raygen.rgen:84-108) and
-//              starts the slot's next pixel-sample (raygen.rgen:31-48); then closest-hit traversal of every
-//              live path's ray (raygen.rgen:54-58), bins the hits into one queue per BSDF type; a miss
-//              (miss.rmiss) ends the path
+//   k_regen    for slots whose path has ended: adds the sample to the image (raygen.rgen:84-108) and starts the slot's
+//              next pixel-sample (raygen.rgen:31-48), all lanes busy (ended slots are compacted per block)
+//   [sort]     optional: slot indices ordered by (origin cell, direction octant) so that a warp's rays walk the same
+//              part of the BVH (cub radix sort over keys written by k_regen / k_shade)
+//   k_extend   closest-hit traversal of every live path's ray (raygen.rgen:54-58); a miss (miss.rmiss) ends the path
 //   k_shade<T> material-sorted closest-hit shading             (rayhit.rchit:666-797) + the
 //              per-bounce bookkeeping of the raygen loop       (raygen.rgen:59-80)
 //   k_shadow   any-hit traversal of the NEE segments           (rayhit.rchit:737-757)
-// Three launches per wavefront iteration (for one BSDF type in use); queue counters are double-banked by
+// Four launches per wavefront iteration (for one BSDF type in use); queue counters are double-banked by
 // iteration parity so that no separate reset kernel is needed.
 //
 // Slots are not tied to pixels: a slot whose path ends takes the next pixel-sample from a global work counter
@@ -19,6 +20,8 @@
 // only the last few iterations of a call run with a thinning wavefront.  Finished samples are added to the image with
 // one 128-bit atomic add (rgb, count).  Every path carries its own RNG word; each stage consumes draws in the order
 // the shader does, which makes per-path results match the checker's.
+#include <cub/device/device_radix_sort.cuh>
+
 #include <algorithm>
 #include <cstdio>
 #include <vector>
@@ -38,8 +41,10 @@ constexpr int kBlock = kTraceBlock;
 #ifndef GSB_SHADE_MIN_BLOCKS
 #define GSB_SHADE_MIN_BLOCKS 8   // resident blocks per SM the shading kernels are compiled for (register cap 80)
 #endif
-constexpr uint32_t kRetired = 0xffffffffu;
-constexpr uint32_t kFinished = 0x80000000u;  // sampleK bit: the path has ended, its sample waits to be added to the image
+constexpr uint32_t kRetired = 0xffffffffu;   // sampleK: the slot has no path and will get none (the call's work is used up)
+// hitInst of a slot whose path has not been traced yet (k_generate): any word that is neither GSB_NO_HIT (= path ended)
+// nor carries a valid BSDF type in bits 28..31
+constexpr uint32_t kInstFresh = 0xfffffffeu;
 #ifndef GSB_SHADE_PREFETCH
 #define GSB_SHADE_PREFETCH 0  // k_shade prefetches its next tile's state: 1 into L1, 2 into L2
 #endif
@@ -51,6 +56,12 @@ constexpr uint32_t kFinished = 0x80000000u;  // sampleK bit: the path has ended,
 #endif
 constexpr uint32_t kFlagWasDelta = 1u << 16;
 constexpr uint32_t kFlagCountEmitted = 1u << 17;
+constexpr uint32_t kFlagDead = 1u << 18;        // direction.w of a retired slot: k_extend skips it
+#ifndef GSB_RAY_AOS
+#define GSB_RAY_AOS 1
+#endif
+GSB_D float4* rayOrigin(const WavefrontState& wf, uint32_t slot) { return GSB_RAY_AOS ? wf.ray + 2 * (size_t)slot : wf.ray + slot; }
+GSB_D float4* rayDirection(const WavefrontState& wf, uint32_t slot) { return GSB_RAY_AOS ? wf.ray + 2 * (size_t)slot + 1 : wf.ray + (size_t)wf.capacity + slot; }
 constexpr uint32_t kShadowHasBase = 1u << 31;   // shadowD.w = path slot | this bit when shadowBase holds surface emission
 
 struct RenderArgs {
@@ -62,19 +73,8 @@ struct RenderArgs {
     float camZ;                     // (max(W,H)/2) / tan(fov/2) of rayDir(), raygen.rgen:20-25 (evaluated once on the host)
     unsigned long long totalWork;   // npix * count pixel-samples
     float4* accum;                  // the image: rgb = sum of samples, a = samples added
+    const uint32_t* order;          // ray sorting: slot of the i-th ray k_extend takes (nullptr: slot order)
 };
-
-// Which pixel-sample a slot renders next.  The work items [0, totalWork) are handed out in BLOCKS of 32 consecutive items
-// (32 neighbouring pixels of one sample: a warp's regenerated rays start out coherent) from one global block counter
-// (ST_NEXTWORK); a block belongs to the slot chunk (WorkRange::kChunk slots) whose finished slot asked for it, and the
-// chunk's other slots use up the rest of it as their paths end.  A chunk's partly used block (WavefrontState::chunkWork:
-// block index, items used, "no more work" flag) is only ever touched by the warp that holds the chunk in the current
-// launch, so only one request in ~32 costs an atomic operation — the single per-refill counter this replaces was 36 % of
-// k_extend's stall samples (r2b: about a million same-address 64-bit atomics per launch).  Nothing is stranded: a slot is
-// retired only when its chunk's block is used up and the global counter has run past the end, and whatever a chunk still
-// holds is taken by its remaining slots.
-constexpr unsigned long long kWorkExhausted = 1ull << 6;   // chunkWork: bits 0..5 items used of the block (32 = none left), bit 6, bits 7.. block
-GSB_D unsigned long long packWork(unsigned long long block, uint32_t used) { return (block << 7) | used; }
 
 // Warp-aggregated append: every lane of the warp must call this (pred false = no push).
 // key selects one of the queue counters; returns the position for lanes with pred.
@@ -87,6 +87,25 @@ GSB_D uint32_t queueSlot(uint32_t* counters, uint32_t key, bool pred) {
     if (pred && lane == leader) base = atomicAdd(&counters[key], (uint32_t)__popc(peers));
     base = __shfl_sync(0xffffffffu, base, leader);
     return base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+}
+
+// Sort key of a ray: Morton code of the origin's cell in a (2^sortBits)^3 grid over the scene bounds, then the direction
+// octant — rays that start in the same region and head the same way are neighbours in the sorted order, so the lanes of a
+// traversal warp fetch the same nodes and stay in the same phase for longer.
+GSB_D uint32_t spreadBits3(uint32_t v) {   // 10 bits -> every third bit
+    v = (v | (v << 16)) & 0x030000ffu;
+    v = (v | (v << 8)) & 0x0300f00fu;
+    v = (v | (v << 4)) & 0x030c30c3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+GSB_D uint32_t sortKey(const SceneDev& sc, float3 o, float3 d) {
+    const float top = (float)((1u << sc.sortBits) - 1u);
+    const uint32_t cx = (uint32_t)fminf(fmaxf((o.x - sc.sortLo[0]) * sc.sortScale[0], 0.0f), top);
+    const uint32_t cy = (uint32_t)fminf(fmaxf((o.y - sc.sortLo[1]) * sc.sortScale[1], 0.0f), top);
+    const uint32_t cz = (uint32_t)fminf(fmaxf((o.z - sc.sortLo[2]) * sc.sortScale[2], 0.0f), top);
+    const uint32_t oct = (d.x < 0.0f ? 0u : 4u) | (d.y < 0.0f ? 0u : 2u) | (d.z < 0.0f ? 0u : 1u);
+    return ((spreadBits3(cx) | (spreadBits3(cy) << 1) | (spreadBits3(cz) << 2)) << 3) | oct;
 }
 
 // raygen.rgen:20-48: seed + primary ray + payload initialisation for work item `work` (sample work / npix of
@@ -113,11 +132,12 @@ GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderA
     // .w: the path's RNG state (raygen.rgen:37)
     o = make_float4(sc.eye[0], sc.eye[1], sc.eye[2], __uint_as_float(pcgHash(tea(ra.width * y + x, timestamp))));
     dOut = make_float4(d.x, d.y, d.z, __uint_as_float(kFlagCountEmitted));   // .w: depth 0, wasDelta 0, countEmitted 1
-    wf.rayO[slot] = o;
-    wf.rayD[slot] = dOut;
-    wf.weightDW[slot] = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+    *rayOrigin(wf, slot) = o;
+    *rayDirection(wf, slot) = dOut;
+    // weight and directWeight start out as 1: k_shade knows that from depth 0 and does not read them (nothing is written here)
     wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     wf.sampleK[slot] = pixel;
+    if (wf.sortKey) wf.sortKey[slot] = sortKey(sc, xyz(o), d);
     pixelOut = pixel;
 }
 
@@ -126,8 +146,72 @@ __global__ void k_generate(SceneDev sc, WavefrontState wf, RenderArgs ra) {
     if (slot >= ra.slots) return;
     float4 o, d;
     uint32_t pixel;
-    if (slot % WorkRange::kChunk == 0) wf.chunkWork[slot / WorkRange::kChunk] = packWork(0ull, 32u);   // no block yet
     startPath(sc, wf, ra, slot, slot, o, d, pixel);   // slots <= totalWork: the first `slots` items start out in slot order
+    wf.hitInst[slot] = kInstFresh;   // not traced yet: k_regen of the first iteration must not take it for an ended path
+}
+
+// ---- regenerate ------------------------------------------------------------------------------------
+// raygen.rgen:84-108 + :31-48 for every slot whose path ended in the last iteration (hitInst == GSB_NO_HIT: a miss,
+// or k_shade ended it).  One block owns kRegenSpan consecutive slots: it counts its ended slots, reserves that many
+// consecutive work items with ONE atomic (work item w = sample w / npix of pixel w % npix, so a block's new paths are
+// neighbouring pixels of one sample), and starts them.  A slot that finds no work left is retired.
+constexpr int kRegenBlock = 256, kRegenPer = 8, kRegenSpan = kRegenBlock * kRegenPer;
+__global__ void __launch_bounds__(kRegenBlock) k_regen(SceneDev sc, WavefrontState wf, RenderArgs ra) {
+    __shared__ uint32_t s_warp[kRegenBlock / 32];
+    __shared__ unsigned long long s_base;
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t base = blockIdx.x * (uint32_t)kRegenSpan;
+    uint32_t ended = 0;   // bit k: slot base + k * kRegenBlock + tid holds an ended path
+#pragma unroll
+    for (int k = 0; k < kRegenPer; k++) {
+        const uint32_t slot = base + (uint32_t)k * kRegenBlock + tid;
+        if (slot < ra.slots && wf.hitInst[slot] == GSB_NO_HIT && wf.sampleK[slot] != kRetired) ended |= 1u << k;
+    }
+    // exclusive prefix of the ended counts over the block
+    const uint32_t n = (uint32_t)__popc(ended);
+    uint32_t incl = n;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= (uint32_t)o) incl += v;
+    }
+    if (lane == 31u) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kRegenBlock / 32; w++) {
+        const uint32_t c = s_warp[w];
+        if ((uint32_t)w < warp) before += c;
+        total += c;
+    }
+    if (total == 0u) return;
+    if (tid == 0u) s_base = atomicAdd(&wf.stats[ST_NEXTWORK], (unsigned long long)total);
+    __syncthreads();
+    unsigned long long work = s_base + before + (incl - n);
+    uint32_t retired = 0;
+#pragma unroll
+    for (int k = 0; k < kRegenPer; k++) {
+        if (!(ended & (1u << k))) continue;
+        const uint32_t slot = base + (uint32_t)k * kRegenBlock + tid;
+        const uint32_t pixel = wf.sampleK[slot];
+        const float4 res = wf.result[slot];
+        // raygen.rgen:106-108: a NaN sample leaves the image untouched
+        if (!(isnan(res.x) || isnan(res.y) || isnan(res.z))) atomicAdd(&ra.accum[pixel], make_float4(res.x, res.y, res.z, 1.0f));
+        if (work < ra.totalWork) {
+            float4 o, d;
+            uint32_t p;
+            startPath(sc, wf, ra, slot, work, o, d, p);
+        } else {
+            wf.sampleK[slot] = kRetired;
+            *rayDirection(wf, slot) = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kFlagDead));
+            if (wf.sortKey) wf.sortKey[slot] = 0xffffffffu;   // sorts behind every live ray
+            retired++;
+        }
+        work++;
+    }
+    // live-slot count: one atomic per warp that retired something
+    for (int o = 16; o > 0; o >>= 1) retired += __shfl_xor_sync(0xffffffffu, retired, o);
+    if (lane == 0u && retired) atomicAdd(&wf.stats[ST_LIVE], (unsigned long long)(-(long long)retired));
 }
 
 // ---- extend ---------------------------------------------------------------------------------------
@@ -148,8 +232,8 @@ GSB_D void flushTraceStats(unsigned long long* stats, TraceStats ts, uint32_t tr
     }
 }
 
-// The ray stream of k_extend: work index = path slot.  A slot whose path ended last iteration is first given its
-// raygen epilogue (sample added to the image, raygen.rgen:84-108) and prologue (next pixel-sample, raygen.rgen:31-48).
+// The ray stream of k_extend: the i-th ray is the one of slot order[i] (ray sorting) or of slot i.  Two 128-bit loads per
+// ray in, the instance word (and the hit record on a hit) out; a retired slot carries kFlagDead and is skipped.
 struct ExtendSource {
     const SceneDev& sc;
     const WavefrontState& wf;
@@ -157,135 +241,41 @@ struct ExtendSource {
     uint32_t* qc;       // this iteration's counter bank
     WorkRange range;
     uint32_t traced = 0;
-    // work counters (warp-uniform): the chunk whose counter is held in registers, and the one loaded ahead
-    // work blocks (warp-uniform, kept in shared memory so that they cost no registers inside the traversal loop): the chunk
-    // whose block state is held, and the one loaded ahead
-    struct WarpWork { uint32_t wkChunk, nxChunk; unsigned long long wkV, nxV; };
-    WarpWork* ww;
 
-    // writes the held block state back (chunk switch, end of the kernel)
-    GSB_D void flushWork() {
-        if (ww->wkChunk != 0xffffffffu && (threadIdx.x & 31u) == 0u) wf.chunkWork[ww->wkChunk] = ww->wkV;
-        __syncwarp();
-    }
-
-    GSB_D ExtendSource(const SceneDev& s, const WavefrontState& w, const RenderArgs& r, uint32_t* q, WarpWork* work) : sc(s), wf(w), ra(r), qc(q), ww(work) {
-        if ((threadIdx.x & 31u) == 0u) { ww->wkChunk = 0xffffffffu; ww->nxChunk = 0xffffffffu; ww->wkV = 0ull; ww->nxV = 0ull; }
-        __syncwarp();
-    }
+    GSB_D ExtendSource(const SceneDev& s, const WavefrontState& w, const RenderArgs& r, uint32_t* q) : sc(s), wf(w), ra(r), qc(q) {}
     GSB_D bool drained() const { return range.exhausted; }
 
     GSB_D bool fetch(bool want, RayJob& job) {
-        const uint32_t slot = range.take(&qc[Q_NEXT_EXTEND], ra.slots, want);
-        // the slot's state words are loaded together (one memory latency, not a dependent chain); `result` is only
-        // needed when the path has ended
-        uint32_t p = kRetired;
-        float4 o = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d = o;
-#if !GSB_LAZY_RESULT
-        float4 res = o;
-#endif
-        if (slot != kNoTag) {
-            p = wf.sampleK[slot];
-            o = wf.rayO[slot];
-            d = wf.rayD[slot];
-#if !GSB_LAZY_RESULT
-            res = wf.result[slot];
-#endif
-        }
-        bool live = p != kRetired;
-        const bool finished = live && (p & kFinished);
-        if (finished) {
-#if GSB_LAZY_RESULT
-            const float4 res = wf.result[slot];
-#endif
-            // raygen.rgen:106-108: a NaN sample leaves the image untouched
-            if (!(isnan(res.x) || isnan(res.y) || isnan(res.z)))
-                atomicAdd(&ra.accum[p & ~kFinished], make_float4(res.x, res.y, res.z, 1.0f));
-        }
-        const uint32_t fmask = __ballot_sync(0xffffffffu, finished);
-        const uint32_t lane = threadIdx.x & 31u;
-        if (fmask) {
-            // next pixel-sample for every finished slot of the warp, from the block its chunk holds (a refill spans at
-            // most two chunks: the tail of the current one and the head of the next)
-            const uint32_t chunk = slot / WorkRange::kChunk;
-            bool retire = false;
-            uint32_t todo = fmask;
-            while (todo) {
-                const uint32_t c = __shfl_sync(0xffffffffu, chunk, (uint32_t)__ffs(todo) - 1u);
-                const uint32_t grp = __ballot_sync(0xffffffffu, finished && chunk == c);
-                todo &= ~grp;
-                if (c != ww->wkChunk) {
-                    flushWork();
-                    if (lane == 0) {
-                        ww->wkV = (c == ww->nxChunk) ? ww->nxV : wf.chunkWork[c];
-                        ww->wkChunk = c;
-                    }
-                    __syncwarp();
-                }
-                const unsigned long long wkV = ww->wkV;
-                const uint32_t n = (uint32_t)__popc(grp), used = (uint32_t)(wkV & 63ull), avail = 32u - used;
-                unsigned long long block = wkV >> 7, fresh = ~0ull;
-                bool exhausted = (wkV & kWorkExhausted) != 0ull;
-                if (n > avail && !exhausted) {
-                    // the rest of the group opens a new block: the one atomic of ~32 requests
-                    if (lane == 0) fresh = atomicAdd(&wf.stats[ST_NEXTWORK], 1ull);
-                    fresh = __shfl_sync(0xffffffffu, fresh, 0);
-                    if (fresh * 32ull >= ra.totalWork) { exhausted = true; fresh = ~0ull; }
-                }
-                if (finished && chunk == c) {
-                    const uint32_t rank = (uint32_t)__popc(grp & ((1u << lane) - 1u));
-                    unsigned long long work = ~0ull;
-                    if (rank < avail) work = block * 32ull + used + rank;
-                    else if (fresh != ~0ull) work = fresh * 32ull + (rank - avail);
-                    if (work < ra.totalWork) startPath(sc, wf, ra, slot, work, o, d, p);
-                    else { wf.sampleK[slot] = kRetired; wf.hitInst[slot] = GSB_NO_HIT; retire = true; live = false; }
-                }
-                __syncwarp();
-                if (lane == 0) {
-                    if (n <= avail) ww->wkV = packWork(block, used + n) | (exhausted ? kWorkExhausted : 0ull);
-                    else if (fresh != ~0ull) ww->wkV = packWork(fresh, n - avail);
-                    else ww->wkV = packWork(block, 32u) | kWorkExhausted;
-                }
-                __syncwarp();
-            }
-            const uint32_t rmask = __ballot_sync(0xffffffffu, retire);
-            if (rmask && lane == (uint32_t)__ffs(rmask) - 1u)
-                atomicAdd(&wf.stats[ST_LIVE], (unsigned long long)(-(long long)__popc(rmask)));
-        }
-        // the counter of the chunk this warp moves to next: loaded one refill ahead, off the critical path
-        if (range.haveNext && lane == 0 && ww->nxChunk != range.next / WorkRange::kChunk) {
-            const uint32_t nx = range.next / WorkRange::kChunk;
-            ww->nxChunk = nx;
-            ww->nxV = nx * WorkRange::kChunk < ra.slots ? wf.chunkWork[nx] : 0ull;   // a load nobody waits for until the chunk switch
-        }
-        __syncwarp();
-        // the state words of the slots this warp will take next: into L1 while the rays just fetched are traced
+        const uint32_t idx = range.take(&qc[Q_NEXT_EXTEND], ra.slots, want);
         const uint32_t ahead = range.peek(ra.slots);
-        if (ahead != kNoTag) {
-            prefetchL1(wf.sampleK + ahead);
-            prefetchL1(wf.rayO + ahead);
-            prefetchL1(wf.rayD + ahead);
-#if !GSB_LAZY_RESULT
-            prefetchL1(wf.result + ahead);
-#endif
+        uint32_t slot = idx;
+        if (ra.order) {
+            if (idx != kNoTag) slot = ra.order[idx];
+            if (ahead != kNoTag) prefetchL1(ra.order + ahead);
+        } else if (ahead != kNoTag) {
+            // the state words of the slots this warp will take next: into L1 while the rays just fetched are traced
+            prefetchL1(rayOrigin(wf, ahead));
+            if (!GSB_RAY_AOS) prefetchL1(rayDirection(wf, ahead));
         }
-        if (!live) return false;
+        if (idx == kNoTag) return false;
+        const float4 o = *rayOrigin(wf, slot), d = *rayDirection(wf, slot);
+        if (__float_as_uint(d.w) & kFlagDead) return false;
         job.ox = o.x; job.oy = o.y; job.oz = o.z;
         job.dx = d.x; job.dy = d.y; job.dz = d.z;
         job.tmin = 0.0f; job.tmax = 1e10f;                              // raygen.rgen:54-58
         job.tag = slot;
-        job.aux = p;        // the path's pixel travels with the ray
+        job.aux = 0u;
         traced++;
         return true;
     }
 
-    // stores only: k_shade finds its work by scanning hitInst in slot order
-    GSB_D void commit(bool have, const HitRecord& hit, uint32_t slot, uint32_t pix) {
+    // stores only: k_shade finds its work by scanning hitInst in slot order; GSB_NO_HIT (miss.rmiss: done = 1, nothing is
+    // added) is also what k_regen reads as "this path has ended"
+    GSB_D void commit(bool have, const HitRecord& hit, uint32_t slot, uint32_t) {
         if (!have) return;
         wf.hitInst[slot] = hit.inst;
-        if (hit.inst == GSB_NO_HIT) wf.sampleK[slot] = pix | kFinished;   // miss.rmiss: done = 1, nothing is added
         // a baked hit is shaded from the world level's own records: it carries its leaf position instead of gl_PrimitiveID
-        else wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float((hit.inst & kInstBaked) ? hit.leaf : hit.prim));
+        if (hit.inst != GSB_NO_HIT) wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float((hit.inst & kInstBaked) ? hit.leaf : hit.prim));
     }
 };
 
@@ -302,11 +292,9 @@ __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_extend(SceneDe
         wf.stats[ST_ITERS] += 1;
         for (int q = 0; q < Q_COUNT; q++) prev[q] = 0;
     }
-    __shared__ ExtendSource::WarpWork s_work[kBlock / 32];
-    ExtendSource src(sc, wf, ra, qc, &s_work[threadIdx.x >> 5]);
+    ExtendSource src(sc, wf, ra, qc);
     TraceStats ts = {0u, 0u, 0u};
     traceStream<false, STATS, HASINST, POOL>(sc, src, ra.refillMin, &ts, (uint32_t*)&wf.stats[ST_OVERFLOW]);
-    src.flushWork();
     // extension rays traced by this warp -> this iteration's counter bank
     uint32_t traced = src.traced;
     for (int o = 16; o > 0; o >>= 1) traced += __shfl_xor_sync(0xffffffffu, traced, o);
@@ -349,8 +337,8 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
 #define GSB_PF prefetchL2
 #endif
                 GSB_PF(wf.hitInst + nxt);
-                GSB_PF(wf.rayO + nxt);
-                GSB_PF(wf.rayD + nxt);
+                GSB_PF(rayOrigin(wf, nxt));
+                GSB_PF(rayDirection(wf, nxt));
                 GSB_PF(wf.hitTUVP + nxt);
                 GSB_PF(wf.weightDW + nxt);
 #undef GSB_PF
@@ -386,20 +374,24 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
         if (active) {
 #if GSB_SHADE_STREAM
             // read-once state streams go past L1 (evict-first), which then keeps the scene records the hit points to
-            const float4 ro = __ldcs(wf.rayO + slot), rd = __ldcs(wf.rayD + slot);
+            const float4 ro = __ldcs(rayOrigin(wf, slot)), rd = __ldcs(rayDirection(wf, slot));
             const float4 hit = __ldcs(wf.hitTUVP + slot);
 #else
-            const float4 ro = wf.rayO[slot], rd = wf.rayD[slot];
+            const float4 ro = *rayOrigin(wf, slot), rd = *rayDirection(wf, slot);
             const float4 hit = wf.hitTUVP[slot];
 #endif
             const uint32_t instWord = wf.hitInst[slot];
             uint32_t rng = __float_as_uint(ro.w);                                 // rayhit.rchit:668
-#if GSB_SHADE_STREAM
-            float4 wdw = __ldcs(wf.weightDW + slot);
-#else
-            float4 wdw = wf.weightDW[slot];
-#endif
             uint32_t flags = __float_as_uint(rd.w);
+            // weight and directWeight of a path's first vertex are 1 (raygen.rgen:42-47): nothing was stored for them
+            float4 wdw = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+            if ((flags & 0xffffu) != 0u) {
+#if GSB_SHADE_STREAM
+                wdw = __ldcs(wf.weightDW + slot);
+#else
+                wdw = wf.weightDW[slot];
+#endif
+            }
             float3 weight = xyz(wdw);
             const float directWeight = wdw.w;
             const uint32_t prim = __float_as_uint(hit.w);
@@ -534,12 +526,13 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
                 }
             }
             if (!terminate) {
-                wf.rayO[slot] = make_float4(newO.x, newO.y, newO.z, __uint_as_float(rng));   // rayhit.rchit:759
-                wf.rayD[slot] = make_float4(newD.x, newD.y, newD.z, __uint_as_float(flags));
+                *rayOrigin(wf, slot) = make_float4(newO.x, newO.y, newO.z, __uint_as_float(rng));   // rayhit.rchit:759
+                *rayDirection(wf, slot) = make_float4(newD.x, newD.y, newD.z, __uint_as_float(flags));
                 wf.weightDW[slot] = make_float4(weight.x, weight.y, weight.z, 1.0f);  // directWeight 1 unless the shadow stage finds the light
+                if (wf.sortKey) wf.sortKey[slot] = sortKey(sc, newO, newD);
             }
         }
-        if (terminate) wf.sampleK[slot] |= kFinished;   // k_extend adds the sample to the image next iteration
+        if (terminate) wf.hitInst[slot] = GSB_NO_HIT;   // the path has ended: k_regen adds the sample to the image next iteration
         const uint32_t sp = queueSlot(qc, Q_SHADOW, needShadow);
         if (needShadow) {
             wf.shadowO[sp] = shO;
@@ -641,15 +634,39 @@ void ensure(T*& p, size_t count) {
     p = (T*)q;
 }
 
-void allocWavefront(gsb_context* ctx, uint32_t slots) {
+__global__ void k_iota(uint32_t* out, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = i;
+}
+
+void freeSort(WavefrontState& wf) {
+    void* ptrs[] = {wf.sortKey, wf.sortKeyOut, wf.order, wf.iota, wf.sortTemp};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    wf.sortKey = wf.sortKeyOut = wf.order = wf.iota = nullptr;
+    wf.sortTemp = nullptr;
+    wf.sortTempBytes = 0;
+}
+
+void allocWavefront(gsb_context* ctx, uint32_t slots, bool sorting) {
     WavefrontState& wf = ctx->wf;
+    if (!sorting && wf.sortKey) freeSort(wf);
+    if (sorting && (!wf.sortKey || wf.capacity < slots)) {
+        freeSort(wf);
+        const size_t m = std::max(slots, wf.capacity);
+        ensure(wf.sortKey, m); ensure(wf.sortKeyOut, m); ensure(wf.order, m); ensure(wf.iota, m);
+        k_iota<<<(unsigned)((m + 255) / 256), 256, 0, ctx->stream>>>(wf.iota, (uint32_t)m);
+        size_t bytes = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, bytes, wf.sortKey, wf.sortKeyOut, wf.iota, wf.order, (int)m, 0, 32, ctx->stream);
+        GSB_CUDA(cudaMalloc(&wf.sortTemp, std::max<size_t>(bytes, 16)));
+        wf.sortTempBytes = bytes;
+    }
     if (wf.capacity >= slots && wf.qCount) return;
     const size_t n = slots;
-    ensure(wf.rayO, n); ensure(wf.rayD, n); ensure(wf.weightDW, n); ensure(wf.result, n);
+    ensure(wf.ray, 2 * n); ensure(wf.weightDW, n); ensure(wf.result, n);
     ensure(wf.sampleK, n); ensure(wf.hitTUVP, n); ensure(wf.hitInst, n);
 
     ensure(wf.shadowO, n); ensure(wf.shadowD, n); ensure(wf.shadowBase, n); ensure(wf.shadowNee, n);
-    ensure(wf.chunkWork, (n + WorkRange::kChunk - 1) / WorkRange::kChunk);
     if (!wf.qCount) ensure(wf.qCount, (size_t)2 * Q_COUNT);
     if (!wf.stats) {
         ensure(wf.stats, (size_t)ST_COUNT);
@@ -668,8 +685,9 @@ void launchShade(gsb_context* ctx, const SceneDev& sc, int grid, uint32_t parity
 
 void freeWavefront(gsb_context* ctx) {
     WavefrontState& wf = ctx->wf;
-    void* ptrs[] = {wf.rayO, wf.rayD, wf.weightDW, wf.result, wf.sampleK, wf.hitTUVP, wf.hitInst,
-                    wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.qCount, wf.stats, wf.chunkWork};
+    void* ptrs[] = {wf.ray, wf.weightDW, wf.result, wf.sampleK, wf.hitTUVP, wf.hitInst,
+                    wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.qCount, wf.stats,
+                    wf.sortKey, wf.sortKeyOut, wf.order, wf.iota, wf.sortTemp};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     wf = WavefrontState();
@@ -714,8 +732,10 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     // paths in flight: enough to fill the machine several times over, small enough that the path state stays near L2
     const unsigned long long totalWork = (unsigned long long)npix * count;
     uint32_t slots = (uint32_t)std::min<unsigned long long>(totalWork, ctx->targetSlots);
-    if (slots < totalWork) slots = std::max(32u, slots & ~31u);   // the work-block counter starts right behind the slots' own items
-    allocWavefront(ctx, slots);
+    if (slots < totalWork) slots = std::max(32u, slots & ~31u);
+    const SceneDev sc = ctx->sceneDev();
+    const bool sorting = sc.sortBits > 0u;
+    allocWavefront(ctx, slots, sorting);
     WavefrontState& wf = ctx->wf;
     RenderArgs ra;
     ra.width = width; ra.height = height; ra.npix = npix;
@@ -726,12 +746,12 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     ra.invNpix = 1.0 / (double)npix;
     ra.refillMin = ctx->refillMin;
     ra.camZ = (std::fmax((float)width, (float)height) / 2.0f) / std::tan(ctx->fov / 2.0f);
-    const SceneDev sc = ctx->sceneDev();
+    ra.order = sorting ? wf.order : nullptr;
     GSB_CUDA(cudaMemsetAsync(wf.qCount, 0, 2 * Q_COUNT * sizeof(uint32_t), s));
     const unsigned long long liveInit[2] = {(unsigned long long)slots, 0ull};
     GSB_CUDA(cudaMemcpyAsync(wf.stats, liveInit, sizeof(liveInit), cudaMemcpyHostToDevice, s));
-    const unsigned long long nextBlock = ((unsigned long long)slots + 31ull) / 32ull;   // the first `slots` items start out in the slots
-    GSB_CUDA(cudaMemcpyAsync(&wf.stats[ST_NEXTWORK], &nextBlock, sizeof(nextBlock), cudaMemcpyHostToDevice, s));
+    const unsigned long long nextWork = slots;   // the first `slots` work items start out in the slots (k_generate)
+    GSB_CUDA(cudaMemcpyAsync(&wf.stats[ST_NEXTWORK], &nextWork, sizeof(nextWork), cudaMemcpyHostToDevice, s));
 
     cudaEvent_t evStart = nullptr, evStop = nullptr;
     GSB_CUDA(cudaEventCreate(&evStart));
@@ -778,7 +798,16 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     };
 
     uint32_t parity = 0;
+    const int regenGrid = (int)((slots + kRegenSpan - 1) / kRegenSpan);
+    // key bits that matter: 3 per grid level + the octant
+    const int sortEndBit = (int)std::min(32u, 3u * sc.sortBits + 3u);
     auto iteration = [&]() {
+        mark();
+        k_regen<<<regenGrid, kRegenBlock, 0, s>>>(sc, wf, ra);
+        if (sorting) {
+            size_t bytes = wf.sortTempBytes;
+            cub::DeviceRadixSort::SortPairs(wf.sortTemp, bytes, wf.sortKey, wf.sortKeyOut, wf.iota, wf.order, (int)slots, 0, sortEndBit, s);
+        }
         mark();
         extendKernel<<<extendGrid, kBlock, 0, s>>>(sc, wf, ra, parity);
         mark();
@@ -794,9 +823,8 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
         mark();
         shadowKernel<<<shadowGrid, kBlock, 0, s>>>(sc, wf, parity, ctx->shadowControl);
         mark();
-        mark();
         parity ^= 1u;
-        ctx->launches += 2 + (uint64_t)typesUsed;
+        ctx->launches += 3 + (uint64_t)typesUsed;
         ctx->lastRenderIters++;
     };
 
@@ -846,9 +874,9 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
             GSB_CUDA(cudaEventRecord(evStop, s));
             PendingRender pr;
             pr.exec = exec; pr.graph = graph; pr.start = evStart; pr.stop = evStop;
-            pr.launchesPerIter = 2u + (uint32_t)typesUsed;
+            pr.launchesPerIter = 3u + (uint32_t)typesUsed;
             ctx->pending.push_back(pr);
-            ctx->launches -= 2ull * (2 + (uint64_t)typesUsed);   // iteration() ran twice on the host during capture
+            ctx->launches -= 2ull * (3 + (uint64_t)typesUsed);   // iteration() ran twice on the host during capture
             ctx->launches += 1;
             return;
         }
@@ -889,10 +917,12 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     for (int k = 1; k < 5; k++) ctx->lastRenderMs[k] = 0.0;
     if (prof) {
         for (size_t i = 0; i + 4 < pev.size(); i += 5) {
+            // marks of one iteration: regenerate (+ sort) | extend | shade | shadow  ->  finish, extend, shade, shadow
+            static const int where[4] = {4, 1, 2, 3};
             for (int k = 0; k < 4; k++) {
                 float t = 0.0f;
                 cudaEventElapsedTime(&t, pev[i + k], pev[i + k + 1]);
-                ctx->lastRenderMs[1 + k] += t;
+                ctx->lastRenderMs[where[k]] += t;
             }
         }
         for (cudaEvent_t e : pev) cudaEventDestroy(e);
