@@ -52,7 +52,7 @@ class BvhStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("num_meshes", "num_instances", "unique_triangles", "instanced_triangles",
                                           "blas_nodes", "tlas_nodes", "bvh_bytes")] + \
                [("build_ms", C.c_double), ("sah_cost_before", C.c_double), ("sah_cost_after", C.c_double)] + \
-               [(n, C.c_uint64) for n in ("baked_instances", "baked_triangles", "world_nodes")]
+               [(n, C.c_uint64) for n in ("baked_instances", "baked_triangles", "world_nodes", "refits")] + [("refit_ms", C.c_double)]
 
 
 assert C.sizeof(Instance) == 88 and C.sizeof(TriangleLight) == 64 and C.sizeof(Ray) == 32 and C.sizeof(Hit) == 20
@@ -69,6 +69,7 @@ CORE_API = {
     "gsb_mesh_create": (C.c_int, [_P, _f32p, _f32p, C.c_uint32, _u32p]),
     "gsb_mesh_destroy": (C.c_int, [_P, C.c_uint32]),
     "gsb_scene_set_instances": (C.c_int, [_P, C.POINTER(Instance), C.c_uint32]),
+    "gsb_scene_update_transforms": (C.c_int, [_P, C.c_uint32, C.c_uint32, C.POINTER(C.c_float)]),
     "gsb_scene_set_bsdfs": (C.c_int, [_P, C.c_uint32, _P, C.c_uint32]),
     "gsb_scene_set_lights": (C.c_int, [_P, C.POINTER(TriangleLight), C.c_uint32]),
     "gsb_set_camera": (C.c_int, [_P, _f32p, _f32p, C.c_float]),

@@ -186,6 +186,11 @@ class Context:
     def set_instances(self, instances, count):
         _check(N.core.gsb_scene_set_instances(self._c, instances, count), "gsb_scene_set_instances")
 
+    def update_transforms(self, first, transforms):
+        """transforms: (n, 16) column-major 4x4 matrices for instances first .. first+n-1 (moved instances: refit, no re-upload)."""
+        t = np.ascontiguousarray(transforms, np.float32).reshape(-1, 16)
+        _check(N.core.gsb_scene_update_transforms(self._c, first, len(t), _fp(t)), "gsb_scene_update_transforms")
+
     def set_bsdfs(self, btype, raw, count):
         buf = C.create_string_buffer(raw, max(1, len(raw)))
         _check(N.core.gsb_scene_set_bsdfs(self._c, btype, C.cast(buf, C.c_void_p), count), "gsb_scene_set_bsdfs")

@@ -478,6 +478,7 @@ gsb_status gsb_destroy(gsb_context* ctx) {
         freeBvh(ctx->world);
         cudaFree(ctx->dWorldVerts);
         cudaFree(ctx->dWorldNrm);
+        cudaFree(ctx->dNrmSoup);
         cudaFree(ctx->dInstSmall);
         cudaFree(ctx->dShade);
         cudaFree(ctx->dInstBsdf);
@@ -569,6 +570,167 @@ gsb_status gsb_scene_set_lights(gsb_context* ctx, const gsb_triangle_light* ligh
     });
 }
 
+// Everything the kernels keep per instance, derived from its gsb_instance (PathTracer.cpp:58-75): shading record,
+// the 16-byte record of a baked hit, and for a TLAS instance its trace record and padded world bounds.
+struct InstanceRecords {
+    ShadeInstance sh;
+    float4 small;
+    TraceInstance tr;
+    float wlo[3], whi[3];
+    uint32_t instWord;
+};
+
+static void instanceRecords(const gsb_context* ctx, uint32_t i, bool baked, InstanceRecords& out) {
+    const gsb_instance& in = ctx->instances[i];
+    const MeshRec& mesh = ctx->meshes[in.mesh];
+    const float* T = in.transform;  // column-major: T[c*4 + r]
+    double M[3][4];
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 4; c++) M[r][c] = T[c * 4 + r];
+    // inverse of the linear part by cofactors, float64, rounded once to float32
+    const double c00 = M[1][1] * M[2][2] - M[1][2] * M[2][1], c01 = M[1][2] * M[2][0] - M[1][0] * M[2][2],
+                 c02 = M[1][0] * M[2][1] - M[1][1] * M[2][0];
+    const double det = M[0][0] * c00 + M[0][1] * c01 + M[0][2] * c02;
+    const double id = 1.0 / det;
+    double inv[3][3];
+    inv[0][0] = c00 * id;
+    inv[1][0] = c01 * id;
+    inv[2][0] = c02 * id;
+    inv[0][1] = (M[0][2] * M[2][1] - M[0][1] * M[2][2]) * id;
+    inv[1][1] = (M[0][0] * M[2][2] - M[0][2] * M[2][0]) * id;
+    inv[2][1] = (M[0][1] * M[2][0] - M[0][0] * M[2][1]) * id;
+    inv[0][2] = (M[0][1] * M[1][2] - M[0][2] * M[1][1]) * id;
+    inv[1][2] = (M[0][2] * M[1][0] - M[0][0] * M[1][2]) * id;
+    inv[2][2] = (M[0][0] * M[1][1] - M[0][1] * M[1][0]) * id;
+    // transformInvT = glm::inverse(glm::transpose(M)) in float32 as the reference's host computes it (PathTracer.cpp:62)
+    float nrm[3][3];
+    normalMatrixGlm(T, nrm);
+    ShadeInstance& sh = out.sh;
+    for (int r = 0; r < 3; r++) {
+        sh.o2w[r] = make_float4((float)M[r][0], (float)M[r][1], (float)M[r][2], (float)M[r][3]);
+        sh.nrm[r] = make_float4(nrm[r][0], nrm[r][1], nrm[r][2], in.emission[r]);
+    }
+    sh.vpos = mesh.vpos;
+    sh.vnrm = mesh.vnrm;
+    sh.bsdf = in.bsdf;
+    sh.twofaced = in.twofaced;
+    sh.pad[0] = sh.pad[1] = 0;
+    const uint32_t smallBits = (in.bsdf & 0xffffu) | (std::min(in.twofaced, 0xffffu) << 16);
+    out.small = make_float4(in.emission[0], in.emission[1], in.emission[2], 0.0f);
+    memcpy(&out.small.w, &smallBits, sizeof(float));
+    out.instWord = i | ((in.bsdf >> 16) << kInstTypeShift) | (baked ? kInstBaked : 0u);
+    if (baked) return;
+    TraceInstance& tr = out.tr;
+    for (int r = 0; r < 3; r++) {
+        const double tw = -(inv[r][0] * M[0][3] + inv[r][1] * M[1][3] + inv[r][2] * M[2][3]);
+        tr.w2o[r] = make_float4((float)inv[r][0], (float)inv[r][1], (float)inv[r][2], (float)tw);
+    }
+    tr.blas = mesh.blas.buffer;
+    // meshes of <= 4 triangles are traced without their (single) node: the TLAS box test already covered them
+    tr.triOffset16 = mesh.blas.leafOffset16 | ((mesh.ntris >= 1 && mesh.ntris <= 4) ? (mesh.ntris << kDirectShift) : 0u);
+    tr.instId = out.instWord;
+    // padded world bounds of the padded object box
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int corner = 0; corner < 8; corner++) {
+        const double p[3] = {(corner & 1) ? mesh.blas.hi[0] : mesh.blas.lo[0], (corner & 2) ? mesh.blas.hi[1] : mesh.blas.lo[1],
+                             (corner & 4) ? mesh.blas.hi[2] : mesh.blas.lo[2]};
+        for (int r = 0; r < 3; r++) {
+            const double w = M[r][0] * p[0] + M[r][1] * p[1] + M[r][2] * p[2] + M[r][3];
+            lo[r] = std::fmin(lo[r], w);
+            hi[r] = std::fmax(hi[r], w);
+        }
+    }
+    double scale = 0.0;
+    for (int a = 0; a < 3; a++) scale = std::fmax(scale, std::fmax(std::fabs(lo[a]), std::fabs(hi[a])));
+    const double pad = scale * (double)kBoxPadRel;
+    for (int a = 0; a < 3; a++) {
+        out.wlo[a] = std::nextafter((float)(lo[a] - pad), -INFINITY);
+        out.whi[a] = std::nextafter((float)(hi[a] + pad), INFINITY);
+    }
+}
+
+static void bakeInstance(gsb_context* ctx, uint32_t i, const InstanceRecords& r) {
+    const MeshRec& mesh = ctx->meshes[ctx->instances[i].mesh];
+    k_bakeInstance<<<(mesh.ntris + 127) / 128, 128, 0, ctx->stream>>>(mesh.vpos, mesh.vnrm, mesh.ntris, r.sh.o2w[0], r.sh.o2w[1], r.sh.o2w[2],
+                                                                      r.sh.nrm[0], r.sh.nrm[1], r.sh.nrm[2], r.instWord,
+                                                                      ctx->dWorldVerts + 3 * ctx->bakeOffset[i], ctx->dNrmSoup + 3 * ctx->bakeOffset[i]);
+}
+
+// Builds everything that depends on the instance list (ctx->instances): per-instance records, the world level over the
+// baked instances, the top level over the others.  What VulkanRays::buildTLAS + PathTracer::prepareScene do per frame.
+static void rebuildScene(gsb_context* ctx) {
+    const uint32_t count = (uint32_t)ctx->instances.size();
+    std::vector<ShadeInstance> shade(count);
+    std::vector<uint32_t> handles(count);
+    std::vector<float4> small(count);
+    // Bake rule (shared with the checker: kBakeMaxTris / kBakeBudget): in gl_InstanceID order, an instance
+    // whose mesh has at most kBakeMaxTris triangles goes to the world level while the baked total fits the budget.
+    ctx->bakeOffset.assign(count, ~0ull);   // first world-level triangle of a baked instance
+    ctx->traceIndex.assign(count, -1);
+    ctx->hostTrace.clear();
+    ctx->hostWlo.clear();
+    ctx->hostWhi.clear();
+    uint64_t baked = 0;
+    for (uint32_t i = 0; i < count; i++) {
+        const uint32_t nt = ctx->meshes[ctx->instances[i].mesh].ntris;
+        if (nt > 0 && nt <= kBakeMaxTris && baked + nt <= kBakeBudget) { ctx->bakeOffset[i] = baked; baked += nt; }
+    }
+    cudaFree(ctx->dWorldVerts);
+    cudaFree(ctx->dWorldNrm);
+    cudaFree(ctx->dNrmSoup);
+    ctx->dWorldVerts = ctx->dWorldNrm = ctx->dNrmSoup = nullptr;
+    if (baked) {
+        void* q = nullptr;
+        GSB_CUDA(cudaMalloc(&q, (size_t)baked * 3 * sizeof(float4)));
+        ctx->dWorldVerts = (float4*)q;
+        GSB_CUDA(cudaMalloc(&q, (size_t)baked * 3 * sizeof(float4)));
+        ctx->dWorldNrm = (float4*)q;
+        GSB_CUDA(cudaMalloc(&q, (size_t)baked * 3 * sizeof(float4)));
+        ctx->dNrmSoup = (float4*)q;   // world normals in bake order, gathered into leaf order after the build
+    }
+    for (bool& u : ctx->typeUsed) u = false;
+    for (uint32_t i = 0; i < count; i++) {
+        InstanceRecords r;
+        const bool isBaked = ctx->bakeOffset[i] != ~0ull;
+        instanceRecords(ctx, i, isBaked, r);
+        shade[i] = r.sh;
+        small[i] = r.small;
+        handles[i] = ctx->instances[i].bsdf;
+        ctx->typeUsed[ctx->instances[i].bsdf >> 16] = true;
+        if (isBaked) { bakeInstance(ctx, i, r); continue; }
+        ctx->traceIndex[i] = (int32_t)ctx->hostTrace.size();
+        ctx->hostTrace.push_back(r.tr);
+        for (int a = 0; a < 3; a++) { ctx->hostWlo.push_back(r.wlo[a]); ctx->hostWhi.push_back(r.whi[a]); }
+    }
+    GSB_CUDA(cudaGetLastError());
+    cudaFree(ctx->dShade);
+    cudaFree(ctx->dInstBsdf);
+    ctx->dShade = uploadArray(shade.data(), count, ctx->stream);
+    ctx->dInstBsdf = uploadArray(handles.data(), count, ctx->stream);
+    cudaFree(ctx->dInstSmall);
+    ctx->dInstSmall = uploadArray(small.data(), count, ctx->stream);
+    freeBvh(ctx->world);
+    buildBlas(ctx->dWorldVerts, (uint32_t)baked, ctx->stream, ctx->world, true);
+    if (baked) k_gatherNormals<<<((uint32_t)baked + 127) / 128, 128, 0, ctx->stream>>>(ctx->world.leafPrim, (uint32_t)baked, ctx->dNrmSoup, ctx->dWorldNrm);
+    GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    freeBvh(ctx->tlas);
+    ctx->numTraceInstances = (uint32_t)ctx->hostTrace.size();
+    ctx->numBakedTriangles = (uint32_t)baked;
+    buildTlas(ctx->hostWlo.data(), ctx->hostWhi.data(), ctx->hostTrace.data(), ctx->numTraceInstances, ctx->stream, ctx->tlas);
+    GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->haveInstances = true;
+    choosePolicy(ctx);
+    double ms = ctx->tlas.buildMs + ctx->world.buildMs;
+    std::vector<bool> seen(ctx->meshes.size(), false);
+    for (uint32_t i = 0; i < count; i++) {
+        const uint32_t m = ctx->instances[i].mesh;
+        if (ctx->bakeOffset[i] == ~0ull && !seen[m]) { seen[m] = true; ms += ctx->meshes[m].blas.buildMs; }
+    }
+    ctx->lastBuildMs = ms;
+    ctx->lastRefitMs = 0.0;
+    ctx->refits = 0;
+}
+
 gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instances, uint32_t count) {
     if (!ctx || (count && !instances)) return fail(GSB_ERR_INVALID, "gsb_scene_set_instances: null argument");
     if (count > kMaxInstances) return fail(GSB_ERR_INVALID, "gsb_scene_set_instances: more than 2^27 - 1 instances");
@@ -583,136 +745,83 @@ gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instanc
         drain(ctx);
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
         ctx->instances.assign(instances, instances + count);
-        std::vector<ShadeInstance> shade(count);
-        std::vector<TraceInstance> trace;
-        std::vector<uint32_t> handles(count);
-        std::vector<float> wlo, whi;
-        // Bake rule (shared with the checker: kBakeMaxTris / kBakeBudget): in gl_InstanceID order, an instance
-        // whose mesh has at most kBakeMaxTris triangles goes to the world level while the baked total fits the budget.
-        std::vector<uint64_t> bakeOffset(count, ~0ull);   // first world-level triangle of a baked instance
-        uint64_t baked = 0;
-        for (uint32_t i = 0; i < count; i++) {
-            const uint32_t nt = ctx->meshes[instances[i].mesh].ntris;
-            if (nt > 0 && nt <= kBakeMaxTris && baked + nt <= kBakeBudget) { bakeOffset[i] = baked; baked += nt; }
-        }
-        cudaFree(ctx->dWorldVerts);
-        cudaFree(ctx->dWorldNrm);
-        ctx->dWorldVerts = nullptr;
-        ctx->dWorldNrm = nullptr;
-        float4* nrmSoup = nullptr;   // world normals in bake order, gathered into leaf order after the build
-        if (baked) {
-            void* q = nullptr;
-            GSB_CUDA(cudaMalloc(&q, (size_t)baked * 3 * sizeof(float4)));
-            ctx->dWorldVerts = (float4*)q;
-            GSB_CUDA(cudaMalloc(&q, (size_t)baked * 3 * sizeof(float4)));
-            ctx->dWorldNrm = (float4*)q;
-            GSB_CUDA(cudaMalloc(&q, (size_t)baked * 3 * sizeof(float4)));
-            nrmSoup = (float4*)q;
-        }
-        std::vector<float4> small(count);
-        for (bool& u : ctx->typeUsed) u = false;
-        for (uint32_t i = 0; i < count; i++) {
-            const gsb_instance& in = instances[i];
-            const MeshRec& mesh = ctx->meshes[in.mesh];
-            const float* T = in.transform;  // column-major: T[c*4 + r]
-            double M[3][4];
-            for (int r = 0; r < 3; r++)
-                for (int c = 0; c < 4; c++) M[r][c] = T[c * 4 + r];
-            // inverse of the linear part by cofactors, float64, rounded once to float32
-            const double c00 = M[1][1] * M[2][2] - M[1][2] * M[2][1], c01 = M[1][2] * M[2][0] - M[1][0] * M[2][2],
-                         c02 = M[1][0] * M[2][1] - M[1][1] * M[2][0];
-            const double det = M[0][0] * c00 + M[0][1] * c01 + M[0][2] * c02;
-            const double id = 1.0 / det;
-            double inv[3][3];
-            inv[0][0] = c00 * id;
-            inv[1][0] = c01 * id;
-            inv[2][0] = c02 * id;
-            inv[0][1] = (M[0][2] * M[2][1] - M[0][1] * M[2][2]) * id;
-            inv[1][1] = (M[0][0] * M[2][2] - M[0][2] * M[2][0]) * id;
-            inv[2][1] = (M[0][1] * M[2][0] - M[0][0] * M[2][1]) * id;
-            inv[0][2] = (M[0][1] * M[1][2] - M[0][2] * M[1][1]) * id;
-            inv[1][2] = (M[0][2] * M[1][0] - M[0][0] * M[1][2]) * id;
-            inv[2][2] = (M[0][0] * M[1][1] - M[0][1] * M[1][0]) * id;
-            // transformInvT = glm::inverse(glm::transpose(M)) in float32 as the reference's host computes it (PathTracer.cpp:62)
-            float nrm[3][3];
-            normalMatrixGlm(T, nrm);
-            ShadeInstance& sh = shade[i];
-            for (int r = 0; r < 3; r++) {
-                sh.o2w[r] = make_float4((float)M[r][0], (float)M[r][1], (float)M[r][2], (float)M[r][3]);
-                sh.nrm[r] = make_float4(nrm[r][0], nrm[r][1], nrm[r][2], in.emission[r]);
-            }
-            sh.vpos = mesh.vpos;
-            sh.vnrm = mesh.vnrm;
-            sh.bsdf = in.bsdf;
-            sh.twofaced = in.twofaced;
-            sh.pad[0] = sh.pad[1] = 0;
-            handles[i] = in.bsdf;
-            ctx->typeUsed[in.bsdf >> 16] = true;
-            const uint32_t smallBits = (in.bsdf & 0xffffu) | (std::min(in.twofaced, 0xffffu) << 16);
-            small[i] = make_float4(in.emission[0], in.emission[1], in.emission[2], 0.0f);
-            memcpy(&small[i].w, &smallBits, sizeof(float));
-            const uint32_t instWord = i | ((in.bsdf >> 16) << kInstTypeShift) | (bakeOffset[i] != ~0ull ? kInstBaked : 0u);
-            if (bakeOffset[i] != ~0ull) {
-                k_bakeInstance<<<(mesh.ntris + 127) / 128, 128, 0, ctx->stream>>>(mesh.vpos, mesh.vnrm, mesh.ntris, sh.o2w[0], sh.o2w[1], sh.o2w[2],
-                                                                                  sh.nrm[0], sh.nrm[1], sh.nrm[2], instWord,
-                                                                                  ctx->dWorldVerts + 3 * bakeOffset[i], nrmSoup + 3 * bakeOffset[i]);
-                continue;
-            }
-            TraceInstance tr;
-            for (int r = 0; r < 3; r++) {
-                const double tw = -(inv[r][0] * M[0][3] + inv[r][1] * M[1][3] + inv[r][2] * M[2][3]);
-                tr.w2o[r] = make_float4((float)inv[r][0], (float)inv[r][1], (float)inv[r][2], (float)tw);
-            }
-            tr.blas = mesh.blas.buffer;
-            // meshes of <= 4 triangles are traced without their (single) node: the TLAS box test already covered them
-            tr.triOffset16 = mesh.blas.leafOffset16 | ((mesh.ntris >= 1 && mesh.ntris <= 4) ? (mesh.ntris << kDirectShift) : 0u);
-            tr.instId = instWord;
-            trace.push_back(tr);
-            // padded world bounds of the padded object box
-            double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-            for (int corner = 0; corner < 8; corner++) {
-                const double p[3] = {(corner & 1) ? mesh.blas.hi[0] : mesh.blas.lo[0], (corner & 2) ? mesh.blas.hi[1] : mesh.blas.lo[1],
-                                     (corner & 4) ? mesh.blas.hi[2] : mesh.blas.lo[2]};
-                for (int r = 0; r < 3; r++) {
-                    const double w = M[r][0] * p[0] + M[r][1] * p[1] + M[r][2] * p[2] + M[r][3];
-                    lo[r] = std::fmin(lo[r], w);
-                    hi[r] = std::fmax(hi[r], w);
-                }
-            }
-            double scale = 0.0;
-            for (int a = 0; a < 3; a++) scale = std::fmax(scale, std::fmax(std::fabs(lo[a]), std::fabs(hi[a])));
-            const double pad = scale * (double)kBoxPadRel;
-            for (int a = 0; a < 3; a++) {
-                wlo.push_back(std::nextafter((float)(lo[a] - pad), -INFINITY));
-                whi.push_back(std::nextafter((float)(hi[a] + pad), INFINITY));
-            }
-        }
-        GSB_CUDA(cudaGetLastError());
-        cudaFree(ctx->dShade);
-        cudaFree(ctx->dInstBsdf);
-        ctx->dShade = uploadArray(shade.data(), count, ctx->stream);
-        ctx->dInstBsdf = uploadArray(handles.data(), count, ctx->stream);
-        cudaFree(ctx->dInstSmall);
-        ctx->dInstSmall = uploadArray(small.data(), count, ctx->stream);
-        freeBvh(ctx->world);
-        uint32_t* leafPrim = nullptr;
-        buildBlas(ctx->dWorldVerts, (uint32_t)baked, ctx->stream, ctx->world, true, &leafPrim);
-        if (baked) k_gatherNormals<<<((uint32_t)baked + 127) / 128, 128, 0, ctx->stream>>>(leafPrim, (uint32_t)baked, nrmSoup, ctx->dWorldNrm);
+        rebuildScene(ctx);
+        return GSB_OK;
+    });
+}
+
+// Moved instances (animated scenes; the reference rebuilds its TLAS from {blas, mat4} every frame, PathTracer.cpp:10-19):
+// the transforms of instances [first, first + count) are replaced, their records recomputed, baked ones re-baked into the
+// world level, and both levels REFIT over their existing topology (bvh.h: refitTriangles / refitTlas).  When the summed
+// node area of a refit level exceeds kRefitRebuildRatio x its value at build time the scene is rebuilt instead.
+gsb_status gsb_scene_update_transforms(gsb_context* ctx, uint32_t first, uint32_t count, const float* transforms) {
+    if (!ctx || (!transforms && count)) return fail(GSB_ERR_INVALID, "gsb_scene_update_transforms: null argument");
+    if (!ctx->haveInstances) return fail(GSB_ERR_STATE, "gsb_scene_update_transforms: no scene (call gsb_scene_set_instances first)");
+    if ((uint64_t)first + count > ctx->instances.size()) return fail(GSB_ERR_INVALID, "gsb_scene_update_transforms: instance range out of bounds");
+    if (count == 0) return GSB_OK;
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        drain(ctx);
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
-        cudaFree(leafPrim);
-        cudaFree(nrmSoup);
-        freeBvh(ctx->tlas);
-        ctx->numTraceInstances = (uint32_t)trace.size();
-        ctx->numBakedTriangles = (uint32_t)baked;
-        buildTlas(wlo.data(), whi.data(), trace.data(), (uint32_t)trace.size(), ctx->stream, ctx->tlas);
-        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
-        ctx->haveInstances = true;
-        choosePolicy(ctx);
-        double ms = ctx->tlas.buildMs + ctx->world.buildMs;
-        std::vector<bool> seen(ctx->meshes.size(), false);
-        for (uint32_t i = 0; i < count; i++)
-            if (bakeOffset[i] == ~0ull && !seen[instances[i].mesh]) { seen[instances[i].mesh] = true; ms += ctx->meshes[instances[i].mesh].blas.buildMs; }
-        ctx->lastBuildMs = ms;
+        constexpr double kRefitRebuildRatio = 2.0;
+        const char* force = getenv("GSB_REFIT");      // "0": always rebuild (A/B measurements)
+        if (force && atoi(force) == 0) {
+            for (uint32_t k = 0; k < count; k++) memcpy(ctx->instances[first + k].transform, transforms + 16 * (size_t)k, 16 * sizeof(float));
+            rebuildScene(ctx);
+            return GSB_OK;
+        }
+        // the yardstick of both levels, measured once on the trees as built
+        auto worldScale = [&]() {
+            float sc = 0.0f;
+            for (int a = 0; a < 3; a++) sc = std::fmax(sc, std::fmax(std::fabs(ctx->world.lo[a]), std::fabs(ctx->world.hi[a])));
+            return sc;
+        };
+        if (ctx->world.numPrims && ctx->world.areaAtBuild == 0.0) ctx->world.areaAtBuild = refitTriangles(ctx->world, worldScale(), ctx->stream, true);
+        if (ctx->numTraceInstances && ctx->tlas.areaAtBuild == 0.0)
+            ctx->tlas.areaAtBuild = refitTlas(ctx->tlas, ctx->hostWlo.data(), ctx->hostWhi.data(), ctx->hostTrace.data(), ctx->numTraceInstances, ctx->stream, true);
+        bool touchedWorld = false, touchedTlas = false;
+        for (uint32_t k = 0; k < count; k++) {
+            const uint32_t i = first + k;
+            memcpy(ctx->instances[i].transform, transforms + 16 * (size_t)k, 16 * sizeof(float));
+            InstanceRecords r;
+            const bool isBaked = ctx->bakeOffset[i] != ~0ull;
+            instanceRecords(ctx, i, isBaked, r);
+            GSB_CUDA(cudaMemcpyAsync(ctx->dShade + i, &r.sh, sizeof(ShadeInstance), cudaMemcpyHostToDevice, ctx->stream));
+            if (isBaked) {
+                bakeInstance(ctx, i, r);
+                touchedWorld = true;
+            } else {
+                const int32_t t = ctx->traceIndex[i];
+                ctx->hostTrace[t] = r.tr;
+                for (int a = 0; a < 3; a++) { ctx->hostWlo[3 * t + a] = r.wlo[a]; ctx->hostWhi[3 * t + a] = r.whi[a]; }
+                touchedTlas = true;
+            }
+        }
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));   // `r` lives on the stack: its copies must have left
+        double ms = 0.0;
+        bool degraded = false;
+        if (touchedWorld) {
+            // the baked triangles moved: leaf records and normals again from the soup (same leaf order), boxes bottom-up.
+            // The padding follows the largest coordinate of the level, like at build time.
+            const uint32_t n = ctx->world.numPrims;
+            repackTriangles(ctx->world, ctx->dWorldVerts, true, ctx->stream);
+            k_gatherNormals<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->world.leafPrim, n, ctx->dNrmSoup, ctx->dWorldNrm);
+            const float sc = soupScale(ctx->dWorldVerts, n * 3, ctx->stream);
+            const double area = refitTriangles(ctx->world, sc, ctx->stream);
+            ms += ctx->world.refitMs;
+            degraded = degraded || area > kRefitRebuildRatio * ctx->world.areaAtBuild;
+        }
+        if (touchedTlas) {
+            const double area = refitTlas(ctx->tlas, ctx->hostWlo.data(), ctx->hostWhi.data(), ctx->hostTrace.data(), ctx->numTraceInstances, ctx->stream);
+            ms += ctx->tlas.refitMs;
+            degraded = degraded || area > kRefitRebuildRatio * ctx->tlas.areaAtBuild;
+        }
+        if (degraded) {
+            rebuildScene(ctx);
+            return GSB_OK;
+        }
+        ctx->lastRefitMs = ms;
+        ctx->refits++;
         return GSB_OK;
     });
 }
@@ -774,6 +883,8 @@ gsb_status gsb_get_bvh_stats(gsb_context* ctx, gsb_bvh_stats* out) {
     out->sah_cost_before += ctx->world.sahBefore;
     out->sah_cost_after += ctx->world.sahAfter;
     out->build_ms = ctx->lastBuildMs;
+    out->refits = ctx->refits;
+    out->refit_ms = ctx->lastRefitMs;
     return GSB_OK;
 }
 

@@ -434,6 +434,7 @@ GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi,
     r.nodes = pool.get<uint4>((size_t)std::max<uint32_t>(n, 1) * 5);
     r.leafPrim = pool.get<uint32_t>(n);
     r.numNodes = 1;
+    out.levelEnd.assign(1, 1u);   // a single root unless the collapse below says otherwise
     if (n == 0) {
         k_emptyRoot<<<1, 1, 0, s>>>(r.nodes);
         return r;
@@ -515,10 +516,14 @@ GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi,
     GSB_CUDA(cudaMemcpyAsync(counters, initCounters, sizeof(initCounters), cudaMemcpyHostToDevice, s));
     uint32_t nItems = 1;
     uint32_t hostCounters[4];
+    out.levelEnd.clear();
+    uint32_t levelEnd = 1;
     while (nItems > 0) {
         k_collapse<<<(nItems + 127) / 128, 128, 0, s>>>(ca, itemsA, nItems, itemsB);
         GSB_CUDA(cudaMemcpyAsync(hostCounters, counters, sizeof(hostCounters), cudaMemcpyDeviceToHost, s));
         GSB_CUDA(cudaStreamSynchronize(s));
+        out.levelEnd.push_back(levelEnd);      // the nodes written by this launch end here; their children follow
+        levelEnd = hostCounters[0];
         nItems = hostCounters[2];
         GSB_CUDA(cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), s));
         std::swap(itemsA, itemsB);
@@ -542,6 +547,13 @@ void finishBuffer(const GenericResult& r, uint32_t n, size_t leafBytes, cudaStre
     GSB_CUDA(cudaMalloc(&buf, std::max<size_t>(out.bytes, 16)));
     out.buffer = (uint4*)buf;
     GSB_CUDA(cudaMemcpyAsync(out.buffer, r.nodes, nodeBytes, cudaMemcpyDeviceToDevice, s));
+    out.leafPrim = nullptr;
+    if (n > 0) {
+        void* q = nullptr;
+        GSB_CUDA(cudaMalloc(&q, (size_t)n * sizeof(uint32_t)));
+        GSB_CUDA(cudaMemcpyAsync(q, r.leafPrim, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+        out.leafPrim = (uint32_t*)q;
+    }
 }
 
 }  // namespace
@@ -550,10 +562,11 @@ void setTreeletRefinement(bool enabled) { g_treelets = enabled; }
 
 void freeBvh(DeviceBvh& bvh) {
     if (bvh.buffer) cudaFree(bvh.buffer);
+    if (bvh.leafPrim) cudaFree(bvh.leafPrim);
     bvh = DeviceBvh();
 }
 
-void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out, bool idsInVertices, uint32_t** outLeafPrim) {
+void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out, bool idsInVertices) {
     cudaEvent_t e0, e1;
     GSB_CUDA(cudaEventCreate(&e0));
     GSB_CUDA(cudaEventCreate(&e1));
@@ -587,15 +600,6 @@ void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBv
         if (ntris > 0)
             k_packTriangles<<<(ntris + B - 1) / B, B, 0, s>>>(r.leafPrim, ntris, dVertices,
                                                               reinterpret_cast<float4*>(out.buffer + out.leafOffset16), idsInVertices);
-        if (outLeafPrim) {
-            *outLeafPrim = nullptr;
-            if (ntris > 0) {
-                void* q = nullptr;
-                GSB_CUDA(cudaMalloc(&q, (size_t)ntris * sizeof(uint32_t)));
-                GSB_CUDA(cudaMemcpyAsync(q, r.leafPrim, (size_t)ntris * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
-                *outLeafPrim = (uint32_t*)q;
-            }
-        }
         GSB_CUDA(cudaGetLastError());
         for (int a = 0; a < 3; a++) { out.lo[a] = lo[a] - pad; out.hi[a] = hi[a] + pad; }
     }
@@ -604,6 +608,195 @@ void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBv
     GSB_CUDA(cudaEventElapsedTime(&out.buildMs, e0, e1));
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
+}
+
+// ---- refit ---------------------------------------------------------------------------------------------------------
+namespace {
+
+// leaf boxes of a triangle level from its own packed records (copy kz = 2 holds x, y, z in order), padded like k_triBoxes
+__global__ void k_leafTriBoxes(const float4* __restrict__ leaves, uint32_t n, float pad, float4* __restrict__ lo, float4* __restrict__ hi) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const float4 a = leaves[9 * (size_t)k + 6], b = leaves[9 * (size_t)k + 7], c = leaves[9 * (size_t)k + 8];
+    lo[k] = make_float4(fminf(a.x, fminf(b.x, c.x)) - pad, fminf(a.y, fminf(b.y, c.y)) - pad, fminf(a.z, fminf(b.z, c.z)) - pad, 0.0f);
+    hi[k] = make_float4(fmaxf(a.x, fmaxf(b.x, c.x)) + pad, fmaxf(a.y, fmaxf(b.y, c.y)) + pad, fmaxf(a.z, fmaxf(b.z, c.z)) + pad, 0.0f);
+}
+
+__global__ void k_gatherBoxes(const uint32_t* __restrict__ leafPrim, uint32_t n, const float4* __restrict__ inLo, const float4* __restrict__ inHi,
+                              float4* __restrict__ lo, float4* __restrict__ hi) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    lo[k] = inLo[leafPrim[k]];
+    hi[k] = inHi[leafPrim[k]];
+}
+
+// One level of the bottom-up refit: nodes [first, end).  The topology (child / leaf ranges, slot assignment, meta bytes)
+// stays; every node gets the union of its children's new boxes, a new quantisation frame and new quantised child boxes
+// (same outward rounding as emitNode).  nodeLo / nodeHi: per-node boxes, written here, read by the parents' launch.
+__global__ void k_refitLevel(uint4* __restrict__ nodes, uint32_t first, uint32_t end, const float4* __restrict__ leafLo,
+                             const float4* __restrict__ leafHi, float4* __restrict__ nodeLo, float4* __restrict__ nodeHi, double* area, bool dry) {
+    const uint32_t node = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (node >= end) return;
+    uint4* w = nodes + (size_t)node * 5;
+    const uint4 w0 = w[0], w1 = w[1];
+    const uint32_t imask = w0.w >> 24;
+    float clo[8][3], chi[8][3];
+    bool used[8];
+    float nlo[3] = {INFINITY, INFINITY, INFINITY}, nhi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int s = 0; s < 8; s++) {
+        const uint32_t m = ((s < 4 ? w1.z : w1.w) >> (8 * (s & 3))) & 0xffu;
+        used[s] = m != 0u;
+        if (!used[s]) continue;
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        if ((m & 0x1fu) >= 24u) {
+            const uint32_t c = w1.x + (uint32_t)__popc(imask & ((1u << s) - 1u));
+            const float4 a = nodeLo[c], b = nodeHi[c];
+            lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; hi[0] = b.x; hi[1] = b.y; hi[2] = b.z;
+        } else {
+            const uint32_t cnt = (uint32_t)__popc(m >> 5), off = m & 0x1fu;
+            for (uint32_t j = 0; j < cnt; j++) {
+                const float4 a = leafLo[w1.y + off + j], b = leafHi[w1.y + off + j];
+                lo[0] = fminf(lo[0], a.x); lo[1] = fminf(lo[1], a.y); lo[2] = fminf(lo[2], a.z);
+                hi[0] = fmaxf(hi[0], b.x); hi[1] = fmaxf(hi[1], b.y); hi[2] = fmaxf(hi[2], b.z);
+            }
+        }
+        for (int ax = 0; ax < 3; ax++) {
+            clo[s][ax] = lo[ax]; chi[s][ax] = hi[ax];
+            nlo[ax] = fminf(nlo[ax], lo[ax]); nhi[ax] = fmaxf(nhi[ax], hi[ax]);
+        }
+    }
+    if (!(nhi[0] >= nlo[0])) { nlo[0] = nlo[1] = nlo[2] = 0.0f; nhi[0] = nhi[1] = nhi[2] = 0.0f; }   // an empty root
+    uint32_t e[3];
+    double scale[3];
+    for (int ax = 0; ax < 3; ax++) {
+        const float ext = nhi[ax] - nlo[ax];
+        int ee = -126;
+        if (ext > 0.0f) {
+            ee = (int)ceil(log2((double)ext / 255.0));
+            while (ldexp(255.0, ee) < (double)ext) ee++;
+            ee = max(ee, -126);
+        }
+        e[ax] = (uint32_t)(ee + 127);
+        scale[ax] = ldexp(1.0, ee);
+    }
+    uint32_t qlo[3][8], qhi[3][8];
+    for (int s = 0; s < 8; s++)
+        for (int ax = 0; ax < 3; ax++) {
+            qlo[ax][s] = 0; qhi[ax][s] = 0;
+            if (!used[s]) continue;
+            double ql = floor(((double)clo[s][ax] - (double)nlo[ax]) / scale[ax]);
+            double qh = ceil(((double)chi[s][ax] - (double)nlo[ax]) / scale[ax]);
+            qlo[ax][s] = (uint32_t)fmin(fmax(ql, 0.0), 255.0);
+            qhi[ax][s] = (uint32_t)fmin(fmax(qh, 0.0), 255.0);
+        }
+    auto pack4 = [](const uint32_t* b) { return b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24); };
+    if (!dry) {
+        w[0] = make_uint4(__float_as_uint(nlo[0]), __float_as_uint(nlo[1]), __float_as_uint(nlo[2]), e[0] | (e[1] << 8) | (e[2] << 16) | (imask << 24));
+        w[2] = make_uint4(pack4(qlo[0]), pack4(qlo[0] + 4), pack4(qlo[1]), pack4(qlo[1] + 4));
+        w[3] = make_uint4(pack4(qlo[2]), pack4(qlo[2] + 4), pack4(qhi[0]), pack4(qhi[0] + 4));
+        w[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
+    }
+    // what the parents (and the area figure) see is the box the traversal will really test: the dequantised union
+    float dlo[3], dhi[3];
+    for (int ax = 0; ax < 3; ax++) {
+        uint32_t mx = 0;
+        for (int s = 0; s < 8; s++) mx = max(mx, used[s] ? qhi[ax][s] : 0u);
+        dlo[ax] = nlo[ax];
+        dhi[ax] = (float)((double)nlo[ax] + (double)mx * scale[ax]);
+        dhi[ax] = fmaxf(dhi[ax], nhi[ax]);
+    }
+    nodeLo[node] = make_float4(dlo[0], dlo[1], dlo[2], 0.0f);
+    nodeHi[node] = make_float4(dhi[0], dhi[1], dhi[2], 0.0f);
+    const double dx = (double)dhi[0] - dlo[0], dy = (double)dhi[1] - dlo[1], dz = (double)dhi[2] - dlo[2];
+    atomicAdd(area, 2.0 * (dx * dy + dy * dz + dz * dx));
+}
+
+double refitLevels(DeviceBvh& bvh, const float4* leafLo, const float4* leafHi, TempPool& pool, cudaStream_t s, bool dry) {
+    float4* nodeLo = pool.get<float4>(bvh.numNodes);
+    float4* nodeHi = pool.get<float4>(bvh.numNodes);
+    double* dArea = pool.get<double>(1);
+    GSB_CUDA(cudaMemsetAsync(dArea, 0, sizeof(double), s));
+    for (int l = (int)bvh.levelEnd.size() - 1; l >= 0; l--) {
+        const uint32_t first = l ? bvh.levelEnd[l - 1] : 0u, end = bvh.levelEnd[l];
+        if (end > first) k_refitLevel<<<(end - first + 127) / 128, 128, 0, s>>>(bvh.buffer, first, end, leafLo, leafHi, nodeLo, nodeHi, dArea, dry);
+    }
+    double area = 0.0;
+    float4 rootLo, rootHi;
+    GSB_CUDA(cudaMemcpyAsync(&area, dArea, sizeof(double), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA(cudaMemcpyAsync(&rootLo, nodeLo, sizeof(float4), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA(cudaMemcpyAsync(&rootHi, nodeHi, sizeof(float4), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA(cudaStreamSynchronize(s));
+    GSB_CUDA(cudaGetLastError());
+    if (!dry) {
+        bvh.lo[0] = rootLo.x; bvh.lo[1] = rootLo.y; bvh.lo[2] = rootLo.z;
+        bvh.hi[0] = rootHi.x; bvh.hi[1] = rootHi.y; bvh.hi[2] = rootHi.z;
+    }
+    return area;
+}
+
+struct ScopedTimer {
+    cudaEvent_t e0, e1;
+    cudaStream_t s;
+    float* out;
+    ScopedTimer(cudaStream_t st, float* o) : s(st), out(o) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, s); }
+    ~ScopedTimer() { cudaEventRecord(e1, s); cudaEventSynchronize(e1); cudaEventElapsedTime(out, e0, e1); cudaEventDestroy(e0); cudaEventDestroy(e1); }
+};
+
+}  // namespace
+
+float soupScale(const float4* dVertices, uint32_t nverts, cudaStream_t s) {
+    if (nverts == 0) return 0.0f;
+    TempPool pool(s);
+    BoundsAcc* acc = pool.get<BoundsAcc>(1);
+    k_initBounds<<<1, 32, 0, s>>>(acc);
+    k_vertexBounds<<<(int)std::min<uint32_t>((nverts + 255) / 256, 2048u), 256, 0, s>>>(dVertices, nverts, acc);
+    BoundsAcc h;
+    GSB_CUDA(cudaMemcpyAsync(&h, acc, sizeof(h), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA(cudaStreamSynchronize(s));
+    float scale = 0.0f;
+    for (int a = 0; a < 3; a++) scale = std::fmax(scale, std::fmax(std::fabs(floatFromOrdered(h.lo[a])), std::fabs(floatFromOrdered(h.hi[a]))));
+    return scale;
+}
+
+void repackTriangles(DeviceBvh& bvh, const float4* dVertices, bool idsInVertices, cudaStream_t s) {
+    if (bvh.numPrims == 0) return;
+    k_packTriangles<<<(bvh.numPrims + 255) / 256, 256, 0, s>>>(bvh.leafPrim, bvh.numPrims, dVertices,
+                                                               reinterpret_cast<float4*>(bvh.buffer + bvh.leafOffset16), idsInVertices);
+}
+
+double refitTriangles(DeviceBvh& bvh, float worldScale, cudaStream_t s, bool dry) {
+    if (bvh.numPrims == 0) return 0.0;
+    float scratch = 0.0f;
+    ScopedTimer timer(s, dry ? &scratch : &bvh.refitMs);
+    TempPool pool(s);
+    const uint32_t n = bvh.numPrims;
+    float4* lo = pool.get<float4>(n);
+    float4* hi = pool.get<float4>(n);
+    k_leafTriBoxes<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const float4*>(bvh.buffer + bvh.leafOffset16), n, worldScale * kBoxPadRel, lo, hi);
+    return refitLevels(bvh, lo, hi, pool, s, dry);
+}
+
+double refitTlas(DeviceBvh& bvh, const float* hostLo, const float* hostHi, const TraceInstance* hostRecords, uint32_t n, cudaStream_t s, bool dry) {
+    if (n == 0 || n != bvh.numPrims) return 0.0;
+    float scratch = 0.0f;
+    ScopedTimer timer(s, dry ? &scratch : &bvh.refitMs);
+    TempPool pool(s);
+    std::vector<float4> lo4(n), hi4(n);
+    for (uint32_t i = 0; i < n; i++) {
+        lo4[i] = make_float4(hostLo[3 * i], hostLo[3 * i + 1], hostLo[3 * i + 2], 0.0f);
+        hi4[i] = make_float4(hostHi[3 * i], hostHi[3 * i + 1], hostHi[3 * i + 2], 0.0f);
+    }
+    float4* inLo = pool.get<float4>(n);
+    float4* inHi = pool.get<float4>(n);
+    float4* lo = pool.get<float4>(n);
+    float4* hi = pool.get<float4>(n);
+    uint4* rec = pool.get<uint4>((size_t)n * 4);
+    GSB_CUDA(cudaMemcpyAsync(inLo, lo4.data(), (size_t)n * sizeof(float4), cudaMemcpyHostToDevice, s));
+    GSB_CUDA(cudaMemcpyAsync(inHi, hi4.data(), (size_t)n * sizeof(float4), cudaMemcpyHostToDevice, s));
+    GSB_CUDA(cudaMemcpyAsync(rec, hostRecords, (size_t)n * sizeof(TraceInstance), cudaMemcpyHostToDevice, s));
+    if (!dry) k_packInstances<<<(n + 255) / 256, 256, 0, s>>>(bvh.leafPrim, n, rec, bvh.buffer + bvh.leafOffset16);
+    k_gatherBoxes<<<(n + 255) / 256, 256, 0, s>>>(bvh.leafPrim, n, inLo, inHi, lo, hi);
+    return refitLevels(bvh, lo, hi, pool, s, dry);   // synchronises: the host vectors above outlive their copies
 }
 
 void buildTlas(const float* hostLo, const float* hostHi, const TraceInstance* hostRecords, uint32_t n, cudaStream_t s, DeviceBvh& out) {

@@ -77,6 +77,13 @@ struct gsb_context {
     float4* dWorldNrm = nullptr;       //   their vertex normals in world space, leaf order (shading reads them straight from here)
     float4* dInstSmall = nullptr;      // per instance: emission, bsdf index, twofaced (what a baked hit needs of its instance)
     uint32_t numBakedTriangles = 0;
+    float4* dNrmSoup = nullptr;        //   the same normals in bake order (kept: a moved baked instance is re-baked in place)
+    std::vector<uint64_t> bakeOffset;  // per instance: first world-level triangle (bake order), ~0 = not baked
+    std::vector<int32_t> traceIndex;   // per instance: its position in hostTrace, -1 = baked
+    std::vector<gsb::TraceInstance> hostTrace;   // trace records and padded world bounds of the TLAS instances (refit input)
+    std::vector<float> hostWlo, hostWhi;
+    double lastRefitMs = 0.0;
+    uint64_t refits = 0;
     gsb::DeviceBvh tlas;               // top level over the instances that are not baked
     uint32_t numTraceInstances = 0;
     gsb::ShadeInstance* dShade = nullptr;
@@ -97,12 +104,12 @@ struct gsb_context {
     float4* dAccum = nullptr;  // rgb = sum of samples, a = samples added
     gsb::WavefrontState wf;
     bool profiling = false;
-    uint32_t targetSlots = 1u << 23;  // paths in flight per wavefront (GSB_SLOTS overrides); 8 M x ~230 B = 1.9 GB of state.
-                                      // Measured: 4 M -> 8 M +3..4 % on all three scenes (shorter relative tail of the persistent launches), 16 M flat
+    uint32_t targetSlots = 1u << 24;  // paths in flight per wavefront (GSB_SLOTS overrides); 16 M x ~210 B = 3.5 GB of state.
+                                      // Measured (r2f, four launches per iteration): 4 M -> 8 M +4 %, 8 M -> 16 M +1.5 % (Cornell) .. +3.5 % (gallery, field)
     // control word of the persistent traversal kernels (traverse.cuh: traceStream): idle lanes that trigger a refill
     // (bits 0..7, GSB_REFILL), lanes that make a quorum for a traversal phase (8..15, GSB_VOTE; closest-hit kernel only,
     // the any-hit kernel measured best without a quorum), lanes that keep the triangle loop spinning (16..23, GSB_TRIMIN)
-    uint32_t refillMin = 24u | (4u << 8) | (2u << 16);
+    uint32_t refillMin = 24u | (4u << 8) | (4u << 16);
     uint32_t directRefill = 0u;    // idle lanes that trigger a refill straight from the source (GSB_REFILL); 0 = per-scene default (api.cu: choosePolicy)
     uint32_t shadowRefill = 0u;    // the same for the any-hit kernel (GSB_SHADOW_REFILL)
     uint32_t shadowControl = 24u;  // the any-hit kernel's control word (no phase quorum measured best)

@@ -141,6 +141,9 @@ typedef struct gsb_bvh_stats {
     /* world level: instances of small meshes are stored as world-space triangles under one BVH of their own (no ray
      * transform, no instance record on the way to them); the TLAS covers the remaining instances */
     uint64_t baked_instances, baked_triangles, world_nodes;
+    /* animated instances: refits since the last (re)build and the device time of the last one (gsb_scene_update_transforms) */
+    uint64_t refits;
+    double   refit_ms;
 } gsb_bvh_stats;
 
 /* ---- context ------------------------------------------------------------------- */
@@ -159,6 +162,11 @@ GSB_API gsb_status gsb_mesh_destroy(gsb_context* ctx, uint32_t mesh);
 /* Replaces the instance list and builds the top-level BVH once (the reference rebuilds
  * its TLAS every frame, PathTracer.cpp:10-19). */
 GSB_API gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instances, uint32_t count);
+/* Replaces the transforms (16 floats each, column-major, as gsb_instance::transform) of instances [first, first + count)
+ * and refits the acceleration structures over their existing topology; falls back to a rebuild when the refit tree has
+ * degraded (summed node area > 2x its value at build time).  Replaces: the per-frame TLAS rebuild from {blas, mat4} of
+ * renderer/PathTracer.cpp:10-19 / backend/vulkan/VulkanRays.cpp:92-118 for scenes whose instances move. */
+GSB_API gsb_status gsb_scene_update_transforms(gsb_context* ctx, uint32_t first, uint32_t count, const float* transforms);
 /* type in [0, GSB_BSDF_TYPE_COUNT); params = array of the matching gsb_*_bsdf record. */
 GSB_API gsb_status gsb_scene_set_bsdfs(gsb_context* ctx, uint32_t type, const void* params, uint32_t count);
 GSB_API gsb_status gsb_scene_set_lights(gsb_context* ctx, const gsb_triangle_light* lights, uint32_t count);

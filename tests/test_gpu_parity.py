@@ -431,10 +431,15 @@ def _record(name, **kv):
             f.write(json.dumps({"test": name, **kv}) + "\n")
 
 
-def _same_seed_image(gsb, ctx, o, w, h, spp, depth, name, min_close):
+def _same_seed_image(gsb, ctx, o, w, h, spp, depth, name, min_close, shadow_tol=2e-3):
     """Equal seeds, equal spp at a BASELINE frame size: per pixel against the oracle.  A path whose float32 rounding
-    differs between nvcc's and gcc's libm can take another branch; such paths are COUNTED (pixels outside the tolerance
-    bound them from above, the ray-count deltas from below) and bounded, not hidden in a loose image metric."""
+    differs between the two sides can take another branch; such paths are COUNTED (pixels outside the tolerance bound
+    them from above, the ray-count deltas from below) and bounded, not hidden in a loose image metric.
+    Where the differences come from (profiles/README.md, r2g: scripts/gpu_r2_fmad.sh): k_shade is compiled with FMA
+    contraction and the 2-ulp division / square root GLSL grants the reference's shaders.  With -fmad=false and IEEE
+    division the same tests leave 10 of 2 073 600 Cornell pixels outside the tolerance and the shadow-ray counts within
+    2e-6 of the oracle's; the product build casts 0.03 % (Cornell) to 0.15 % (field) more shadow rays, all at vertices
+    where dot(N, L) is zero up to rounding (NEE towards a light lying in the surface's own plane)."""
     import time
     ctx.set_params(max_depth=depth)
     o.set_params(max_depth=depth)
@@ -451,7 +456,7 @@ def _same_seed_image(gsb, ctx, o, w, h, spp, depth, name, min_close):
     assert gc["paths"] == w * h * spp == oc["paths"]
     d_ext = abs(gc["extension_rays"] - oc["extension_rays"]) / oc["extension_rays"]
     d_sh = abs(gc["shadow_rays"] - oc["shadow_rays"]) / oc["shadow_rays"]
-    assert d_ext <= 2e-3 and d_sh <= 2e-3, (d_ext, d_sh)
+    assert d_ext <= 2e-3 and d_sh <= shadow_tol, (d_ext, d_sh)
     assert not np.isnan(got).any() and np.all(got[..., 3] == 1.0)
     diff = np.abs(got[..., :3] - ref[..., :3]).max(axis=2)
     scale = np.maximum(ref[..., :3].max(axis=2), 0.05)
@@ -580,3 +585,63 @@ def test_staircase2_from_the_reference_scene_file(gsb, orc):
             assert np.array_equal(got[k], ref[k]), k
         assert (got["inst"] != gsb.NO_HIT).mean() > 0.5
         _same_seed_image(gsb, c, o, 360, 640, 8, 8, "staircase2_360x640", 0.995)
+
+
+# ---------------------------------------------------------------- animated instances
+def _moved(inst, i, angle_deg, shift=(0.0, 0.0, 0.0)):
+    """Instance i's transform (column-major float32[16]) rotated about the vertical axis through its own origin and shifted."""
+    M = np.array(list(inst[i].transform), np.float64).reshape(4, 4).T
+    a = np.radians(angle_deg)
+    R = np.eye(4)
+    R[0, 0], R[0, 2], R[2, 0], R[2, 2] = np.cos(a), np.sin(a), -np.sin(a), np.cos(a)
+    c = M[:3, 3].copy()
+    T0, T1 = np.eye(4), np.eye(4)
+    T0[:3, 3], T1[:3, 3] = -c, c + np.array(shift)
+    return (T1 @ R @ T0 @ M).T.astype(np.float32).reshape(16)
+
+
+@pytest.mark.parametrize("name,movers", [("cornell", [5, 6]), ("field_small", [3, 7, 2])])
+def test_moved_instances_refit_matches_the_oracle(gsb, orc, name, movers):
+    """gsb_scene_update_transforms over 8 frames (the tall and the short Cornell box turn: baked instances, world level
+    re-baked + refit; instanced blobs of the field turn and drift: TLAS refit): after every frame closest hits and
+    occlusion are bit-exact against the oracle, which is handed the same instance list from scratch; the final frame's
+    same-seed image agrees per pixel.  Refits are counted, and a far jump triggers the rebuild fallback."""
+    import ctypes as C
+    s = host_scene(name)
+    inst, ni = s.instances
+    o = orc.OracleScene.from_host_scene(s)
+    with gsb.Context(0) as c:
+        c.upload(s)
+        rays = random_rays(s, 60000, seed=5)
+        w, h = 320, 180
+        ys, xs = np.mgrid[0:h:2, 0:w:2]
+        rays = np.concatenate([rays, o.camera_rays(w, h, xs.ravel(), ys.ravel())])
+        for frame in range(1, 9):
+            for k, i in enumerate(movers):
+                T = _moved(inst, i, 11.0 * frame * (1 if k % 2 == 0 else -1), (0.02 * frame, 0.0, -0.015 * frame))
+                c.update_transforms(i, T[None])          # `inst` keeps the rest pose: _moved composes from it
+            # the oracle gets the whole instance list again
+            cur_inst, _ = s.instances
+            for k, i in enumerate(movers):
+                T = _moved(inst, i, 11.0 * frame * (1 if k % 2 == 0 else -1), (0.02 * frame, 0.0, -0.015 * frame))
+                C.memmove(cur_inst[i].transform, (C.c_float * 16)(*T), 64)
+            o.set_instances(cur_inst, ni)
+            got, ref = c.trace_batch(rays), o.trace_batch(rays, mode=1)
+            for key in ("inst", "prim", "t", "u", "v"):
+                assert np.array_equal(got[key], ref[key]), (frame, key)
+            occl = c.trace_batch(rays[:20000], any_hit=True)
+            assert np.array_equal(occl["inst"] != gsb.NO_HIT, ref["inst"][:20000] != gsb.NO_HIT)
+            st = c.bvh_stats()
+            assert st["refits"] == frame * len(movers) and st["refit_ms"] > 0.0
+        _same_seed_image(gsb, c, o, 320, 180, 8, 8, f"moved_{name}", 0.985, shadow_tol=6e-3)   # 460 K paths: the count is noisy
+        # a jump far outside the scene: the refit tree degrades past the threshold -> rebuilt (refit count starts over)
+        T = _moved(inst, movers[0], 0.0, (500.0, 0.0, 0.0))
+        c.update_transforms(movers[0], T[None])
+        assert c.bvh_stats()["refits"] == 0
+        C.memmove(cur_inst[movers[0]].transform, (C.c_float * 16)(*T), 64)
+        o.set_instances(cur_inst, ni)
+        got, ref = c.trace_batch(rays), o.trace_batch(rays, mode=1)
+        for key in ("inst", "prim", "t"):
+            assert np.array_equal(got[key], ref[key]), key
+        with pytest.raises(gsb.GsbError):
+            c.update_transforms(ni - 1, np.zeros((2, 16), np.float32))       # range runs past the last instance
