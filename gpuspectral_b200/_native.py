@@ -40,7 +40,7 @@ class Hit(C.Structure):
 
 
 class Params(C.Structure):
-    _fields_ = [("max_depth", C.c_int32), ("rr_start", C.c_int32), ("cutoff", C.c_float), ("nee", C.c_int32)]
+    _fields_ = [("max_depth", C.c_int32), ("rr_start", C.c_int32), ("cutoff", C.c_float), ("nee", C.c_int32), ("pixel_filter", C.c_int32)]
 
 
 class Counters(C.Structure):
@@ -138,6 +138,8 @@ HOST_API = {
     "gsbh_tracer_read_ldr": (C.c_int, [_P, C.POINTER(C.c_uint8)]),
     "gsbh_tracer_synchronize": (C.c_int, [_P]),
     "gsbh_write_pfm": (C.c_int, [C.c_char_p, _f32p, C.c_uint32, C.c_uint32]),
+    "gsbh_read_pfm": (C.c_int, [C.c_char_p, _f32p, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "gsbh_image_diff": (C.c_int, [_f32p, _f32p, C.c_uint32, C.c_uint32, C.POINTER(C.c_double)]),
     "gsbh_write_png": (C.c_int, [C.c_char_p, C.POINTER(C.c_uint8), C.c_uint32, C.c_uint32]),
 }
 

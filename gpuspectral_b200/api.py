@@ -209,8 +209,9 @@ class Context:
         N.core.gsb_default_params(C.byref(p))
         return p
 
-    def set_params(self, max_depth=50, rr_start=10, cutoff=20.0, nee=1):
-        p = N.Params(max_depth, rr_start, cutoff, nee)
+    def set_params(self, max_depth=50, rr_start=10, cutoff=20.0, nee=1, pixel_filter=0):
+        """pixel_filter: 0 none (the reference), 1 box jitter, 2 tent of radius 1 pixel."""
+        p = N.Params(max_depth, rr_start, cutoff, nee, pixel_filter)
         _check(N.core.gsb_set_params(self._c, C.byref(p)), "gsb_set_params")
 
     def upload(self, scene):
@@ -399,8 +400,9 @@ class PathTracer:
         self.width, self.height = width, height
         self.context._size = (width, height)
 
-    def set_params(self, max_depth=50, rr_start=10, cutoff=20.0, nee=1):
-        p = N.Params(max_depth, rr_start, cutoff, nee)
+    def set_params(self, max_depth=50, rr_start=10, cutoff=20.0, nee=1, pixel_filter=0):
+        """pixel_filter: 0 none (the reference), 1 box jitter, 2 tent of radius 1 pixel."""
+        p = N.Params(max_depth, rr_start, cutoff, nee, pixel_filter)
         self._hcheck(N.host.gsbh_tracer_set_params(self._t, C.byref(p)), "set_params")
 
     def set_timestamp(self, ts):
@@ -428,3 +430,31 @@ class PathTracer:
 
     def synchronize(self):
         self._hcheck(N.host.gsbh_tracer_synchronize(self._t), "synchronize")
+
+
+def read_pfm(path):
+    """PFM file -> (H, W, 4) float32, rows top-to-bottom (the host layer's reader; what `gsb_render --diff` uses)."""
+    w, h = C.c_uint32(), C.c_uint32()
+    if N.host.gsbh_read_pfm(str(path).encode(), None, 0, C.byref(w), C.byref(h)) != 0:
+        raise GsbError(N.host.gsbh_last_error().decode())
+    img = np.empty((h.value, w.value, 4), np.float32)
+    if N.host.gsbh_read_pfm(str(path).encode(), _fp(img), w.value * h.value, C.byref(w), C.byref(h)) != 0:
+        raise GsbError(N.host.gsbh_last_error().decode())
+    return img
+
+
+def write_pfm(path, rgba):
+    rgba = np.ascontiguousarray(rgba, np.float32)
+    if N.host.gsbh_write_pfm(str(path).encode(), _fp(rgba), rgba.shape[1], rgba.shape[0]) != 0:
+        raise GsbError(N.host.gsbh_last_error().decode())
+
+
+def image_diff(a, b):
+    """relMSE / RMSE / means / max |a - b| of two (H, W, 4) images over rgb; b is the reference (north_star check 3)."""
+    a, b = np.ascontiguousarray(a, np.float32), np.ascontiguousarray(b, np.float32)
+    if a.shape != b.shape:
+        raise ValueError("image sizes differ")
+    out = (C.c_double * 5)()
+    if N.host.gsbh_image_diff(_fp(a), _fp(b), a.shape[1], a.shape[0], out) != 0:
+        raise GsbError(N.host.gsbh_last_error().decode())
+    return dict(zip(("rel_mse", "rmse", "mean_a", "mean_b", "max_abs"), out))

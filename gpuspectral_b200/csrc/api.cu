@@ -840,12 +840,14 @@ gsb_status gsb_default_params(gsb_params* out) {
     out->rr_start = 10;
     out->cutoff = 20.0f;
     out->nee = 1;
+    out->pixel_filter = 0;
     return GSB_OK;
 }
 
 gsb_status gsb_set_params(gsb_context* ctx, const gsb_params* params) {
     if (!ctx || !params) return fail(GSB_ERR_INVALID, "gsb_set_params: null argument");
     if (params->max_depth < 0 || params->max_depth > 65000) return fail(GSB_ERR_INVALID, "gsb_set_params: max_depth out of range");
+    if (params->pixel_filter < 0 || params->pixel_filter > 2) return fail(GSB_ERR_INVALID, "gsb_set_params: pixel_filter must be 0 (none), 1 (box) or 2 (tent)");
     ctx->params = *params;
     return GSB_OK;
 }

@@ -96,7 +96,7 @@ struct gsb_context {
     float eye[3] = {0, 0, 0};
     float view[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
     float fov = 1.0f;
-    gsb_params params = {50, 10, 20.0f, 1};
+    gsb_params params = {50, 10, 20.0f, 1, 0};
     bool haveInstances = false;
     double lastBuildMs = 0.0;
 

@@ -108,6 +108,13 @@ GSB_D uint32_t sortKey(const SceneDev& sc, float3 o, float3 d) {
     return ((spreadBits3(cx) | (spreadBits3(cy) << 1) | (spreadBits3(cz) << 2)) << 3) | oct;
 }
 
+// Offset of the primary ray from the pixel's integer coordinate for one uniform draw u (gsb_params::pixel_filter):
+// box = u - 1/2; tent of radius 1 by inverting its CDF.  Individually rounded operations: the checker computes the same bits.
+GSB_D float filterOffset(int filter, float u) {
+    if (filter == 1) return __fsub_rn(u, 0.5f);
+    return u < 0.5f ? __fsub_rn(__fsqrt_rn(__fmul_rn(2.0f, u)), 1.0f) : __fsub_rn(1.0f, __fsqrt_rn(__fsub_rn(2.0f, __fmul_rn(2.0f, u))));
+}
+
 // raygen.rgen:20-48: seed + primary ray + payload initialisation for work item `work` (sample work / npix of
 // pixel work % npix); the new ray is also returned in registers
 GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderArgs& ra, uint32_t slot, unsigned long long work,
@@ -122,15 +129,23 @@ GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderA
     const uint32_t timestamp = ra.first + k * ra.stride;
     // rayDir(size, fragCoord, fov)
     const float sx = (float)ra.width, sy = (float)ra.height;
-    const float fx = (float)x - sx / 2.0f;
-    const float fy = (float)y - sy / 2.0f;
+    uint32_t rng = pcgHash(tea(ra.width * y + x, timestamp));                        // raygen.rgen:37
+    float px = (float)x, py = (float)y;
+    if (sc.params.pixel_filter) {
+        // extension (gsb_params::pixel_filter): the sample's first two draws place the ray inside the pixel's footprint
+        const float u0 = randUniform(rng), u1 = randUniform(rng);
+        px += filterOffset(sc.params.pixel_filter, u0);
+        py += filterOffset(sc.params.pixel_filter, u1);
+    }
+    const float fx = px - sx / 2.0f;
+    const float fy = py - sy / 2.0f;
     const float3 dir = normalize(f3(-fx, fy, ra.camZ));
     const float* V = sc.view;
     float3 d = f3(V[0] * dir.x + V[4] * dir.y + V[8] * dir.z, V[1] * dir.x + V[5] * dir.y + V[9] * dir.z,
                   V[2] * dir.x + V[6] * dir.y + V[10] * dir.z);
     d.y *= -1.0f;
     // .w: the path's RNG state (raygen.rgen:37)
-    o = make_float4(sc.eye[0], sc.eye[1], sc.eye[2], __uint_as_float(pcgHash(tea(ra.width * y + x, timestamp))));
+    o = make_float4(sc.eye[0], sc.eye[1], sc.eye[2], __uint_as_float(rng));
     dOut = make_float4(d.x, d.y, d.z, __uint_as_float(kFlagCountEmitted));   // .w: depth 0, wasDelta 0, countEmitted 1
     *rayOrigin(wf, slot) = o;
     *rayDirection(wf, slot) = dOut;

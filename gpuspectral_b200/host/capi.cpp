@@ -1,6 +1,7 @@
 // capi.cpp — extern "C" wrappers of the host layer (include/gpuspectral_b200_host.h).
 #include <cstring>
 #include <exception>
+#include <vector>
 #include <stdexcept>
 #include <string>
 
@@ -132,6 +133,25 @@ int gsbh_tracer_read_ldr(gsbh_tracer* t, uint8_t* out) {
 int gsbh_tracer_synchronize(gsbh_tracer* t) { return guarded([&] { t->tracer.synchronize(); }); }
 
 int gsbh_write_pfm(const char* path, const float* rgba, uint32_t w, uint32_t h) { return guarded([&] { gsbhost::writePFM(path, rgba, w, h); }); }
+int gsbh_read_pfm(const char* path, float* rgba, uint32_t capacity_pixels, uint32_t* w, uint32_t* h) {
+    return guarded([&] {
+        std::vector<float> img;
+        uint32_t ww = 0, hh = 0;
+        gsbhost::readPFM(path, img, ww, hh);
+        if (w) *w = ww;
+        if (h) *h = hh;
+        if (rgba) {
+            if ((uint64_t)ww * hh > capacity_pixels) throw std::runtime_error("gsbh_read_pfm: buffer too small");
+            std::memcpy(rgba, img.data(), img.size() * sizeof(float));
+        }
+    });
+}
+int gsbh_image_diff(const float* rgba_a, const float* rgba_b, uint32_t w, uint32_t h, double out5[5]) {
+    return guarded([&] {
+        const gsbhost::ImageDiff d = gsbhost::diffImages(rgba_a, rgba_b, w, h);
+        out5[0] = d.relMse; out5[1] = d.rmse; out5[2] = d.meanA; out5[3] = d.meanB; out5[4] = d.maxAbs;
+    });
+}
 int gsbh_write_png(const char* path, const uint8_t* rgba8, uint32_t w, uint32_t h) { return guarded([&] { gsbhost::writePNG(path, rgba8, w, h); }); }
 
 }  // extern "C"

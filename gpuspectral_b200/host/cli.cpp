@@ -15,17 +15,36 @@ using namespace gsbhost;
 static void usage() {
     std::fprintf(stderr,
                  "usage: gsb_render (<scene.xml | scene.gltf | scene.glb> | --builtin cornell|gallery|field) [--size WxH] [--spp N]\n"
-                 "                  [--max-depth D] [--device I] [--hdr out.pfm] [--ldr out.png]\n");
+                 "                  [--max-depth D] [--filter none|box|tent] [--device I] [--hdr out.pfm] [--ldr out.png]\n"
+                 "       gsb_render --diff a.pfm reference.pfm      (relMSE, RMSE, means, max |a - b|; no GPU needed)\n");
 }
 
 int main(int argc, char** argv) {
     std::string xml, builtin, hdrOut, ldrOut;
     uint32_t W = 0, H = 0, spp = 16;
-    int device = 0, maxDepth = -1;
+    int device = 0, maxDepth = -1, filter = 0;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
         auto next = [&]() -> const char* { return i + 1 < argc ? argv[++i] : ""; };
+        if (a == "--diff") {
+            // image comparison: the figures converged renders are judged by (north_star check 3)
+            const std::string fa = next(), fb = next();
+            try {
+                std::vector<float> ia, ib;
+                uint32_t wa, ha, wb, hb;
+                readPFM(fa, ia, wa, ha);
+                readPFM(fb, ib, wb, hb);
+                if (wa != wb || ha != hb) { std::fprintf(stderr, "error: image sizes differ (%ux%u vs %ux%u)\n", wa, ha, wb, hb); return 1; }
+                const ImageDiff d = diffImages(ia.data(), ib.data(), wa, ha);
+                std::printf("%ux%u relMSE %.6g RMSE %.6g mean %.6g vs %.6g max|a-b| %.6g\n", wa, ha, d.relMse, d.rmse, d.meanA, d.meanB, d.maxAbs);
+                return 0;
+            } catch (const std::exception& e) {
+                std::fprintf(stderr, "error: %s\n", e.what());
+                return 1;
+            }
+        }
         if (a == "--builtin") builtin = next();
+        else if (a == "--filter") { const std::string f = next(); filter = f == "box" ? 1 : (f == "tent" ? 2 : 0); }
         else if (a == "--size") { if (std::sscanf(next(), "%ux%u", &W, &H) != 2) { usage(); return 2; } }
         else if (a == "--spp") spp = (uint32_t)std::atoi(next());
         else if (a == "--max-depth") maxDepth = std::atoi(next());
@@ -45,10 +64,11 @@ int main(int argc, char** argv) {
         if (W == 0 || H == 0) { W = scene.filmWidth ? scene.filmWidth : 512; H = scene.filmHeight ? scene.filmHeight : 512; }
         PathTracer tracer(device);
         tracer.setup(W, H);
-        if (maxDepth >= 0) {
+        if (maxDepth >= 0 || filter) {
             gsb_params p;
             gsb_default_params(&p);
-            p.max_depth = maxDepth;
+            if (maxDepth >= 0) p.max_depth = maxDepth;
+            p.pixel_filter = filter;
             tracer.setParams(p);
         }
         tracer.render(scene, spp);

@@ -1,5 +1,7 @@
 #include "path_tracer.h"
 
+#include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
@@ -86,6 +88,61 @@ void writePFM(const std::string& path, const float* rgba, uint32_t width, uint32
         std::fwrite(row.data(), sizeof(float), row.size(), f);
     }
     std::fclose(f);
+}
+
+void readPFM(const std::string& path, std::vector<float>& rgba, uint32_t& width, uint32_t& height) {
+    FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) throw std::runtime_error("cannot read " + path);
+    char magic[3] = {0, 0, 0};
+    int w = 0, h = 0;
+    float scale = 0.0f;
+    if (std::fscanf(f, "%2s %d %d %f", magic, &w, &h, &scale) != 4 || (std::strcmp(magic, "PF") && std::strcmp(magic, "Pf")) || w <= 0 || h <= 0 || scale == 0.0f) {
+        std::fclose(f);
+        throw std::runtime_error(path + ": not a PFM file");
+    }
+    std::fgetc(f);   // the single whitespace byte after the scale
+    const int ch = magic[1] == 'F' ? 3 : 1;
+    std::vector<float> row((size_t)w * ch);
+    rgba.assign((size_t)w * h * 4, 1.0f);
+    const bool swap = scale > 0.0f;   // positive scale = big endian
+    for (int y = 0; y < h; y++) {
+        if (std::fread(row.data(), sizeof(float), row.size(), f) != row.size()) {
+            std::fclose(f);
+            throw std::runtime_error(path + ": truncated PFM file");
+        }
+        if (swap)
+            for (float& v : row) {
+                unsigned char* b = reinterpret_cast<unsigned char*>(&v);
+                std::swap(b[0], b[3]);
+                std::swap(b[1], b[2]);
+            }
+        float* dst = rgba.data() + (size_t)(h - 1 - y) * w * 4;   // PFM rows run bottom-up
+        for (int x = 0; x < w; x++)
+            for (int c = 0; c < 3; c++) dst[4 * x + c] = row[(size_t)x * ch + (ch == 3 ? c : 0)];
+    }
+    std::fclose(f);
+    width = (uint32_t)w;
+    height = (uint32_t)h;
+}
+
+ImageDiff diffImages(const float* a, const float* b, uint32_t width, uint32_t height) {
+    ImageDiff d = {0.0, 0.0, 0.0, 0.0, 0.0};
+    const size_t n = (size_t)width * height;
+    for (size_t i = 0; i < n; i++)
+        for (int c = 0; c < 3; c++) {
+            const double x = a[4 * i + c], y = b[4 * i + c], e = x - y;
+            d.relMse += e * e / (y * y + 1e-2);
+            d.rmse += e * e;
+            d.meanA += x;
+            d.meanB += y;
+            d.maxAbs = std::max(d.maxAbs, std::fabs(e));
+        }
+    const double m = (double)(n ? n * 3 : 1);
+    d.relMse /= m;
+    d.rmse = std::sqrt(d.rmse / m);
+    d.meanA /= m;
+    d.meanB /= m;
+    return d;
 }
 
 void writePPM(const std::string& path, const uint8_t* rgba8, uint32_t width, uint32_t height) {

@@ -58,6 +58,12 @@ class PathTracer {
 
 // Image writers for the headless framebuffer.
 void writePFM(const std::string& path, const float* rgba, uint32_t width, uint32_t height);
+// Reads a PFM ("PF" colour or "Pf" grey, either byte order) into RGBA32F rows top-to-bottom (alpha 1).
+void readPFM(const std::string& path, std::vector<float>& rgba, uint32_t& width, uint32_t& height);
+// Image comparison figures (the ones north_star asks converged images to be judged by): relMSE = mean((a-b)^2 / (b^2 + 1e-2)),
+// RMSE, mean of both images and the largest absolute difference, over the rgb channels; b is the reference image.
+struct ImageDiff { double relMse, rmse, meanA, meanB, maxAbs; };
+ImageDiff diffImages(const float* rgbaA, const float* rgbaB, uint32_t width, uint32_t height);
 void writePPM(const std::string& path, const uint8_t* rgba8, uint32_t width, uint32_t height);
 void writePNG(const std::string& path, const uint8_t* rgba8, uint32_t width, uint32_t height);
 

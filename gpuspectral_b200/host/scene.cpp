@@ -181,6 +181,24 @@ MeshData makeCube() {
     return m;
 }
 
+MeshData makeDisk(int segments) {
+    // Mitsuba's `disk`: the unit disk in the xy plane, normal +z.  engine/Loader.cpp:278-279 maps the plugin to
+    // "disk.obj", a file the reference never shipped; this fan of `segments` triangles (counter-clockwise seen from +z,
+    // the winding of rect.obj) stands in for it.
+    MeshData m;
+    m.name = "builtin:disk";
+    const float n[3] = {0, 0, 1}, c[3] = {0, 0, 0};
+    for (int k = 0; k < segments; k++) {
+        const double a0 = 2.0 * 3.14159265358979323846 * k / segments, a1 = 2.0 * 3.14159265358979323846 * (k + 1) / segments;
+        const float p0[3] = {(float)std::cos(a0), (float)std::sin(a0), 0.0f};
+        const float p1[3] = {k + 1 == segments ? 1.0f : (float)std::cos(a1), k + 1 == segments ? 0.0f : (float)std::sin(a1), 0.0f};
+        pushVertex(m, c, n);
+        pushVertex(m, p0, n);
+        pushVertex(m, p1, n);
+    }
+    return m;
+}
+
 MeshData makeUvSphere(int stacks, int slices) {
     MeshData m;
     m.name = "builtin:uvsphere:" + std::to_string(stacks) + "x" + std::to_string(slices);

@@ -95,7 +95,8 @@ MeshData loadObjMesh(const std::string& objPath);
 Scene loadGltfScene(const std::string& path);
 
 MeshData makeRectangle();                       // assets/rect.obj equivalent (2 triangles, z = 0, normal +z)
-MeshData makeCube();                            // assets/box.obj equivalent (12 triangles, [-1,1]^3)
+MeshData makeCube();
+MeshData makeDisk(int segments = 64);                            // assets/box.obj equivalent (12 triangles, [-1,1]^3)
 MeshData makeUvSphere(int stacks, int slices);  // unit sphere, smooth normals
 MeshData makeDisplacedSphere(int subdiv, uint32_t seed, float amplitude);  // icosphere, 20*4^subdiv triangles
 

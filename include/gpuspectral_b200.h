@@ -114,7 +114,11 @@ typedef struct gsb_hit { float t; float u; float v; uint32_t inst; uint32_t prim
 /* Integrator constants that are shader literals in the reference, with the
  * reference's values as defaults (gsb_default_params):
  *   max_depth 50 (raygen.rgen:27,73), rr_start 10 (:66), cutoff 20 (:60), nee 1 (rayhit.rchit:656). */
-typedef struct gsb_params { int32_t max_depth; int32_t rr_start; float cutoff; int32_t nee; } gsb_params;
+/* pixel_filter (extension; raygen.rgen:38 holds the sub-pixel jitter only as a comment): 0 = the reference's behaviour, one
+ * ray through every pixel's integer coordinate; 1 = box filter, the primary ray goes through a uniformly drawn point of the
+ * pixel's unit square; 2 = tent filter of radius 1 pixel (importance-sampled, so samples keep unit weight).  The two
+ * uniform draws are the first two of the pixel-sample's RNG stream, right after seeding (raygen.rgen:37). */
+typedef struct gsb_params { int32_t max_depth; int32_t rr_start; float cutoff; int32_t nee; int32_t pixel_filter; } gsb_params;
 
 /* Device-side statistics since the last gsb_clear / gsb_reset_counters. */
 typedef struct gsb_counters {

@@ -65,6 +65,10 @@ GSB_API int gsbh_tracer_read_ldr(gsbh_tracer* t, uint8_t* out_rgba8);
 GSB_API int gsbh_tracer_synchronize(gsbh_tracer* t);
 
 GSB_API int gsbh_write_pfm(const char* path, const float* rgba, uint32_t width, uint32_t height);
+/* Reads a PFM into RGBA32F rows top-to-bottom.  rgba may be NULL to query the size; capacity_pixels = pixels rgba can hold. */
+GSB_API int gsbh_read_pfm(const char* path, float* rgba, uint32_t capacity_pixels, uint32_t* out_width, uint32_t* out_height);
+/* out5 = relMSE (mean of (a-b)^2 / (b^2 + 1e-2)), RMSE, mean of a, mean of b, max |a-b| over rgb; b is the reference image. */
+GSB_API int gsbh_image_diff(const float* rgba_a, const float* rgba_b, uint32_t width, uint32_t height, double out5[5]);
 GSB_API int gsbh_write_png(const char* path, const uint8_t* rgba8, uint32_t width, uint32_t height);
 
 #ifdef __cplusplus

@@ -198,7 +198,7 @@ struct or_scene {
     float eye[3] = {0, 0, 0};
     float view[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
     float fov = 1.0f;
-    gsb_params params = {50, 10, 20.0f, 1};
+    gsb_params params = {50, 10, 20.0f, 1, 0};
 };
 
 namespace {
@@ -1147,10 +1147,17 @@ void closestHit(const or_scene& s, const Hit& hit, HitPayload& prd, PathStats& s
 }
 
 // rayDir + camera transform — raygen.rgen:20-35
-void primaryRay(const or_scene& s, uint32_t W, uint32_t H, uint32_t x, uint32_t y, vec3& origin, vec3& direction) {
+// gsb_params::pixel_filter (extension, no reference source): offset from the pixel's integer coordinate for one uniform draw
+inline float filterOffset(int filter, float u) {
+    if (filter == 1) return u - 0.5f;
+    return u < 0.5f ? std::sqrt(2.0f * u) - 1.0f : 1.0f - std::sqrt(2.0f - 2.0f * u);
+}
+
+void primaryRay(const or_scene& s, uint32_t W, uint32_t H, uint32_t x, uint32_t y, vec3& origin, vec3& direction, float offx = 0.0f,
+                float offy = 0.0f) {
     const float sx = (float)W, sy = (float)H;
-    const float fx = (float)x - sx / 2.0f;
-    const float fy = (float)y - sy / 2.0f;
+    const float fx = ((float)x + offx) - sx / 2.0f;
+    const float fy = ((float)y + offy) - sy / 2.0f;
     const float z = (gmax(sx, sy) / 2.0f) / std::tan(s.fov / 2.0f);
     vec3 dir = normalize(vec3(-fx, fy, z));
     const float* V = s.view;  // column-major
@@ -1165,8 +1172,18 @@ void primaryRay(const or_scene& s, uint32_t W, uint32_t H, uint32_t x, uint32_t 
 vec3 pathSample(const or_scene& s, uint32_t W, uint32_t H, uint32_t x, uint32_t y, uint32_t timestamp, PathStats& st,
                 or_bounce* bounces, uint32_t maxBounces, uint32_t* nBounces) {
     vec3 origin, direction;
-    primaryRay(s, W, H, x, y, origin, direction);
     uint32_t rngState = pcgHash(tea(W * y + x, timestamp));           // :37
+    float offx = 0.0f, offy = 0.0f;
+    if (s.params.pixel_filter) {
+        // extension: the first two draws of the stream place the ray inside the pixel's footprint (:38 is only a comment)
+        Rng jr(rngState);
+        const float u0 = jr.randUniform(), u1 = jr.randUniform();
+        offx = filterOffset(s.params.pixel_filter, u0);
+        offy = filterOffset(s.params.pixel_filter, u1);
+        rngState = jr.state;
+        st.draws += jr.draws;
+    }
+    primaryRay(s, W, H, x, y, origin, direction, offx, offy);
     vec3 result(0.0f);
     HitPayload prd;
     prd.weight = vec3(1.0f);

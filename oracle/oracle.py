@@ -20,7 +20,7 @@ NO_HIT = 0xFFFFFFFF
 
 
 class Params(C.Structure):
-    _fields_ = [("max_depth", C.c_int32), ("rr_start", C.c_int32), ("cutoff", C.c_float), ("nee", C.c_int32)]
+    _fields_ = [("max_depth", C.c_int32), ("rr_start", C.c_int32), ("cutoff", C.c_float), ("nee", C.c_int32), ("pixel_filter", C.c_int32)]
 
 
 class Counters(C.Structure):
@@ -172,8 +172,8 @@ class OracleScene:
         tw = np.ascontiguousarray(to_world, np.float32).reshape(16)
         lib().or_scene_set_camera(self._s, _fp(eye), _fp(tw), fov)
 
-    def set_params(self, max_depth=50, rr_start=10, cutoff=20.0, nee=1):
-        p = Params(max_depth, rr_start, cutoff, nee)
+    def set_params(self, max_depth=50, rr_start=10, cutoff=20.0, nee=1, pixel_filter=0):
+        p = Params(max_depth, rr_start, cutoff, nee, pixel_filter)
         lib().or_scene_set_params(self._s, C.byref(p))
 
     def render(self, width, height, first=0, n=1, stride=1, image=None, sum_mode=False, threads=0):

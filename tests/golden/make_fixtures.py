@@ -3,6 +3,7 @@
 tungsten_cornell_64.npy   64x64x3 float32 box-filtered copy of the reference repo's
                           src/GPUSpectral/assets/scenes/cornell-box/TungstenRender.exr (1024x1024, CC0 Bitterli scene,
                           rendered by Tungsten - an independent unbiased renderer, NOT by GPUSpectral): loose sanity only.
+tungsten_cornell_256_f16.npy   the same image box-filtered to 256x256, float16 (converged-render comparison on the GPU box).
 oracle_cornell_48x48_4spp_d8.npy   the oracle's own image for a fixed input: pins the oracle against accidental edits.
 oracle_paths.json         per-bounce records of a few fixed paths (instance, primitive, t bits, seed) from the oracle.
 rng_kat.json              RNG known answers derived from the GLSL text in SURVEY.md 8(c) (tea -> pcgHash -> draws).
@@ -27,6 +28,9 @@ def tungsten():
     assert img.shape[:2] == (1024, 1024)
     small = img.astype(np.float64).reshape(64, 16, 64, 16, 3).mean(axis=(1, 3)).astype(np.float32)
     np.save(os.path.join(HERE, "tungsten_cornell_64.npy"), small)
+    # 256 x 256 (4 x 4 box filter), float16: the yardstick of the converged-image figure (tests/test_gpu_parity.py)
+    quarter = img.astype(np.float64).reshape(256, 4, 256, 4, 3).mean(axis=(1, 3)).astype(np.float16)
+    np.save(os.path.join(HERE, "tungsten_cornell_256_f16.npy"), quarter)
 
 
 def oracle_fixtures():

@@ -40,7 +40,7 @@ def test_record_layouts_match_reference(gsb):
     assert gsb.BSDF_STRIDES[8] == 16 and gsb.BSDF_TYPE_COUNT == 9      # the rough dielectric extension
     from gpuspectral_b200 import _native as N
     assert C.sizeof(N.TriangleLight) == 64 and C.sizeof(N.Ray) == 32 and C.sizeof(N.Instance) == 88
-    assert C.sizeof(N.Params) == 16 and C.sizeof(N.Counters) == 72
+    assert C.sizeof(N.Params) == 20 and C.sizeof(N.Counters) == 72
     p = gsb.Context.default_params()
     assert (p.max_depth, p.rr_start, p.cutoff, p.nee) == (50, 10, 20.0, 1)   # raygen.rgen:27,60,66; rayhit.rchit:656
 
@@ -127,3 +127,40 @@ def test_builtin_shapes_equal_the_reference_obj_files(gsb, shape, obj):
     assert pa.shape == pb.shape and len(pa) in (6, 36)
     assert np.array_equal(pa, pb)
     assert np.array_equal(na, nb)
+
+
+def test_pfm_round_trip_image_diff_and_cli_diff(gsb, tmp_path):
+    """(f)2: HDR reader + image-diff tooling.  PFM written by the host layer reads back bit for bit (also a big-endian and
+    a grey file written by hand); relMSE / RMSE follow their definitions; `gsb_render --diff` prints the same figures."""
+    import subprocess
+    rng = np.random.default_rng(3)
+    a = rng.random((37, 53, 4)).astype(np.float32) * 4.0
+    a[..., 3] = 1.0
+    b = a.copy()
+    b[..., :3] += rng.normal(0.0, 0.05, (37, 53, 3)).astype(np.float32)
+    pa, pb = tmp_path / "a.pfm", tmp_path / "b.pfm"
+    gsb.write_pfm(pa, a)
+    gsb.write_pfm(pb, b)
+    assert np.array_equal(gsb.read_pfm(pa), a)
+    d = gsb.image_diff(a, b)
+    e = a[..., :3].astype(np.float64) - b[..., :3].astype(np.float64)
+    assert d["rel_mse"] == pytest.approx(np.mean(e ** 2 / (b[..., :3].astype(np.float64) ** 2 + 1e-2)), rel=1e-9)
+    assert d["rmse"] == pytest.approx(np.sqrt(np.mean(e ** 2)), rel=1e-9) and d["max_abs"] == pytest.approx(np.abs(e).max(), rel=1e-9)
+    # big-endian colour and little-endian grey, written by hand
+    be = tmp_path / "be.pfm"
+    be.write_bytes(b"PF\n53 37\n1.0\n" + a[::-1, :, :3].astype(">f4").tobytes())
+    assert np.array_equal(gsb.read_pfm(be), a)
+    grey = tmp_path / "g.pfm"
+    grey.write_bytes(b"Pf\n53 37\n-1.0\n" + a[::-1, :, 0].astype("<f4").tobytes())
+    g = gsb.read_pfm(grey)
+    assert np.array_equal(g[..., 0], a[..., 0]) and np.array_equal(g[..., 2], a[..., 0])
+    exe = os.path.join(ROOT, "gpuspectral_b200", "lib", "gsb_render")
+    r = subprocess.run([exe, "--diff", str(pa), str(pb)], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stderr
+    words = r.stdout.split()
+    assert float(words[words.index("relMSE") + 1]) == pytest.approx(d["rel_mse"], rel=1e-4)
+    assert float(words[words.index("RMSE") + 1]) == pytest.approx(d["rmse"], rel=1e-4)
+    r = subprocess.run([exe, "--diff", str(pa), str(tmp_path / "missing.pfm")], capture_output=True, text=True, timeout=60)
+    assert r.returncode != 0 and "error" in r.stderr.lower()
+    with pytest.raises(gsb.GsbError):
+        gsb.read_pfm(tmp_path / "missing.pfm")

@@ -225,3 +225,30 @@ def test_rough_dielectric_restatement_is_self_consistent(orc):
     for _ in range(3):
         st = (st * 747796405 + 2891336453) & 0xFFFFFFFF
     assert np.array_equal(s_out, st.astype(np.uint32))
+
+
+def test_pixel_filter_extension(orc):
+    """gsb_params::pixel_filter (extension; raygen.rgen:38 holds the jitter only as a comment).  Off = the reference: one ray
+    through the pixel's integer coordinate.  Box / tent: the first two draws of the sample's stream move the ray inside the
+    pixel's footprint; the stream then continues into the path, so the filtered render draws exactly 2 more numbers per
+    sample; the frame mean stays (a filter only redistributes), edges are anti-aliased."""
+    import gpuspectral_b200 as g
+    o = orc.OracleScene.from_host_scene(g.Scene.builtin("cornell"))
+    w, h, spp = 64, 64, 16
+    imgs, draws = {}, {}
+    for f in (0, 1, 2):
+        o.set_params(max_depth=4, pixel_filter=f)
+        imgs[f], c, _ = o.render(w, h, 0, spp)
+        draws[f] = c["rng_draws"]
+    o.set_params()
+    # the draw count differs by more than the 2 jitter draws (other pixels, other paths), but not by much
+    assert abs(draws[1] - draws[0] - 2 * w * h * spp) < 0.05 * draws[0]
+    for f in (1, 2):
+        assert not np.array_equal(imgs[f], imgs[0])
+        # away from the directly visible light (whose few pixels alias differently under point and area sampling)
+        dim = (imgs[0][..., :3].max(axis=2) < 2.0) & (imgs[f][..., :3].max(axis=2) < 2.0)
+        assert abs(imgs[f][dim][:, :3].mean() - imgs[0][dim][:, :3].mean()) < 0.03 * imgs[0][dim][:, :3].mean()
+    # offsets by construction: box in [-1/2, 1/2], tent in [-1, 1] with mean 0 (checked through the filter's own formula)
+    u = np.linspace(0.0, 1.0, 10001, dtype=np.float32)
+    tent = np.where(u < 0.5, np.sqrt(2 * u) - 1, 1 - np.sqrt(2 - 2 * u))
+    assert tent.min() >= -1 and tent.max() <= 1 and abs(tent.mean()) < 1e-3
