@@ -39,7 +39,10 @@ constexpr int kBlock = kTraceBlock;
 #define GSB_TRACE_MIN_BLOCKS 8   // resident blocks per SM the traversal kernels are compiled for
 #endif
 #ifndef GSB_SHADE_MIN_BLOCKS
-#define GSB_SHADE_MIN_BLOCKS 8   // resident blocks per SM the shading kernels are compiled for (register cap 80)
+#define GSB_SHADE_MIN_BLOCKS 8   // resident blocks per SM the shading kernels are compiled for (register cap 64)
+#endif
+#ifndef GSB_SHADE_MIN_BLOCKS_DIFFUSE
+#define GSB_SHADE_MIN_BLOCKS_DIFFUSE 6   // ... the diffuse kernel: 80 registers, no spills (r2i: 66.6 -> 61.5 ms per Cornell step with the state pipeline)
 #endif
 constexpr uint32_t kRetired = 0xffffffffu;   // sampleK: the slot has no path and will get none (the call's work is used up)
 // hitInst of a slot whose path has not been traced yet (k_generate): any word that is neither GSB_NO_HIT (= path ended)
@@ -318,12 +321,22 @@ __global__ void __launch_bounds__(kBlock, GSB_TRACE_MIN_BLOCKS) k_extend(SceneDe
 }
 
 // ---- shade ----------------------------------------------------------------------------------------
+GSB_D void cpAsync16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+GSB_D void cpAsync4(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+GSB_D void cpAsyncCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+GSB_D void cpAsyncWait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 // Material sorting without a global queue: every warp scans the slots 32 at a time in slot order and keeps those whose
 // hit carries a BSDF of this kernel's TYPE.  A tile with at least directMin matching lanes is shaded as it is — the
 // path-state streams are then read and written coalesced; sparser tiles are compacted through a 64-entry per-warp
 // buffer in shared memory and shaded 32 at a time (entries wait there across in-place tiles).
 template <int TYPE, bool HASINST>
-__global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t slots, uint32_t directMin) {
+__global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFUSE : GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t slots, uint32_t directMin) {
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
     __shared__ uint32_t s_buf[kBlock / 32][64];
     const uint32_t lane = threadIdx.x & 31u;
@@ -332,81 +345,88 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
     const uint32_t tiles = (slots + 31u) / 32u;
     uint32_t pendingCount = 0;
     uint32_t shaded = 0;   // warp-uniform: vertices this warp shaded (gsb_counters::shaded_vertices)
-    for (uint32_t tile = warpId;; tile += warpsTotal) {
-        const bool scanning = tile < tiles;
-        const uint32_t cand = tile * 32u + lane;
-        bool match = false;
-        if (scanning && cand < slots) {
-            match = (wf.hitInst[cand] >> kInstTypeShift) == (uint32_t)TYPE;   // the instance word carries the BSDF type; GSB_NO_HIT decodes to none
-        }
-        const uint32_t mm = __ballot_sync(0xffffffffu, match);
-#if GSB_SHADE_PREFETCH
-        {
-            // the tile this warp scans next is known (static stride): its state streams start their trip from DRAM
-            // while this tile is shaded
-            const uint32_t nxt = cand + warpsTotal * 32u;
-            if (nxt < slots) {
-#if GSB_SHADE_PREFETCH == 1
-#define GSB_PF prefetchL1
-#else
-#define GSB_PF prefetchL2
-#endif
-                GSB_PF(wf.hitInst + nxt);
-                GSB_PF(rayOrigin(wf, nxt));
-                GSB_PF(rayDirection(wf, nxt));
-                GSB_PF(wf.hitTUVP + nxt);
-                GSB_PF(wf.weightDW + nxt);
-#undef GSB_PF
+    // Software pipeline over batches of 32 vertices: the per-slot state of batch k (ray origin / direction, hit record,
+    // weight, instance word: 68 bytes per vertex) is fetched with cp.async into one of two shared-memory stages while batch
+    // k - 1 is shaded out of the other one, so the DRAM latency of the state streams overlaps the arithmetic and the
+    // dependent scene-record loads of the previous batch instead of stalling every warp at the top of its batch (r2h ncu:
+    // long-scoreboard 8.4 cycles per issue, 3.8 TB/s of DRAM with ~1/3 of the resident threads waiting on those loads).
+    __shared__ float4 s_state[kBlock / 32][2][4][32];     // [warp][stage][origin, direction, hit, weight][lane]
+    __shared__ uint32_t s_inst[kBlock / 32][2][32];
+    float4 (*st)[4][32] = s_state[threadIdx.x >> 5];
+    uint32_t (*sti)[32] = s_inst[threadIdx.x >> 5];
+    uint32_t tile = warpId;
+    bool scanDone = false, havePrev = false, prevActive = false;
+    uint32_t prevSlot = 0, stage = 0;
+    for (;;) {
+        // ---- scan until the next batch of vertices is known (or the slots are used up)
+        bool haveNew = false, newActive = false;
+        uint32_t newSlot = 0;
+        while (!scanDone) {
+            const bool scanning = tile < tiles;
+            const uint32_t cand = tile * 32u + lane;
+            tile += warpsTotal;
+            bool match = false;
+            if (scanning && cand < slots) {
+                match = (wf.hitInst[cand] >> kInstTypeShift) == (uint32_t)TYPE;   // the instance word carries the BSDF type; GSB_NO_HIT decodes to none
             }
-        }
-#endif
-        bool active;
-        uint32_t slot = 0;
-        if ((uint32_t)__popc(mm) >= directMin) {
-            // a tile that matches (almost) completely is shaded in place: coalesced state streams and no trip through
-            // the compaction buffer, at the price of its few non-matching lanes idling
-            active = match;
-            slot = cand;
-        } else {
+            const uint32_t mm = __ballot_sync(0xffffffffu, match);
+            if ((uint32_t)__popc(mm) >= directMin) {
+                // a tile that matches (almost) completely is shaded in place: coalesced state streams and no trip through
+                // the compaction buffer, at the price of its few non-matching lanes idling
+                newActive = match;
+                newSlot = cand;
+                haveNew = true;
+                break;
+            }
             if (match) buf[pendingCount + (uint32_t)__popc(mm & ((1u << lane) - 1u))] = cand;
             pendingCount += (uint32_t)__popc(mm);
             __syncwarp();
             if (pendingCount >= 32u || (!scanning && pendingCount > 0u)) {
                 const uint32_t n = pendingCount < 32u ? pendingCount : 32u;
-                active = lane < n;
-                if (active) slot = buf[pendingCount - n + lane];
+                newActive = lane < n;
+                if (newActive) newSlot = buf[pendingCount - n + lane];
                 pendingCount -= n;
                 __syncwarp();
-            } else if (!scanning) {
+                haveNew = true;
+                if (!scanning && pendingCount == 0u) scanDone = true;
                 break;
-            } else {
-                continue;
             }
+            if (!scanning) scanDone = true;
         }
+        // ---- its state starts its trip from DRAM
+        if (haveNew) {
+            if (newActive) {
+                cpAsync16(&st[stage][0][lane], rayOrigin(wf, newSlot));
+                cpAsync16(&st[stage][1][lane], rayDirection(wf, newSlot));
+                cpAsync16(&st[stage][2][lane], wf.hitTUVP + newSlot);
+                cpAsync16(&st[stage][3][lane], wf.weightDW + newSlot);
+                cpAsync4(&sti[stage][lane], wf.hitInst + newSlot);
+            }
+            cpAsyncCommit();
+        }
+        if (!havePrev) {
+            if (!haveNew) break;
+            havePrev = true; prevActive = newActive; prevSlot = newSlot; stage ^= 1u;
+            continue;
+        }
+        // ---- shade the previous batch out of the other stage
+        if (haveNew) cpAsyncWait<1>(); else cpAsyncWait<0>();
+        __syncwarp();
+        const uint32_t rs = stage ^ 1u;
+        const bool active = prevActive;
+        const uint32_t slot = prevSlot;
         bool terminate = false, needShadow = false, hasBase = false;
         float4 shO, shD, shBase, shNee;
         shaded += (uint32_t)__popc(__ballot_sync(0xffffffffu, active));
         if (active) {
-#if GSB_SHADE_STREAM
-            // read-once state streams go past L1 (evict-first), which then keeps the scene records the hit points to
-            const float4 ro = __ldcs(rayOrigin(wf, slot)), rd = __ldcs(rayDirection(wf, slot));
-            const float4 hit = __ldcs(wf.hitTUVP + slot);
-#else
-            const float4 ro = *rayOrigin(wf, slot), rd = *rayDirection(wf, slot);
-            const float4 hit = wf.hitTUVP[slot];
-#endif
-            const uint32_t instWord = wf.hitInst[slot];
-            uint32_t rng = __float_as_uint(ro.w);                                 // rayhit.rchit:668
+            const float4 ro = st[rs][0][lane], rd = st[rs][1][lane];
+            const float4 hit = st[rs][2][lane];
+            const uint32_t instWord = sti[rs][lane];
             uint32_t flags = __float_as_uint(rd.w);
             // weight and directWeight of a path's first vertex are 1 (raygen.rgen:42-47): nothing was stored for them
-            float4 wdw = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
-            if ((flags & 0xffffu) != 0u) {
-#if GSB_SHADE_STREAM
-                wdw = __ldcs(wf.weightDW + slot);
-#else
-                wdw = wf.weightDW[slot];
-#endif
-            }
+            float4 wdw = st[rs][3][lane];
+            if ((flags & 0xffffu) == 0u) wdw = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+            uint32_t rng = __float_as_uint(ro.w);                                 // rayhit.rchit:668
             float3 weight = xyz(wdw);
             const float directWeight = wdw.w;
             const uint32_t prim = __float_as_uint(hit.w);
@@ -555,7 +575,9 @@ __global__ void __launch_bounds__(kBlock, GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev
             if (hasBase) wf.shadowBase[sp] = shBase;
             wf.shadowNee[sp] = shNee;
         }
-        if (!scanning && pendingCount == 0u) break;
+        if (!haveNew) break;
+        prevActive = newActive; prevSlot = newSlot; stage ^= 1u;
+        __syncwarp();   // the stage just read is the next one to be filled
     }
     if (lane == 0u && shaded) atomicAdd(&wf.stats[ST_VERTICES], (unsigned long long)shaded);
 }

@@ -9,7 +9,7 @@ for v in "${VS[@]}"; do
   grep -A3 "k_extendILb0\|k_shadeILi0" gpuspectral_b200/build/wavefront.ptxas.log | grep "Used\|spill" | tr '\n' ' '; echo
   for sc in cornell ${SCENES}; do
     if [ $sc = field ]; then A="--steps 3 --spp-per-step 16"; elif [ $sc = gallery ]; then A="--steps 3 --spp-per-step 32"; else A="--steps 4 --spp-per-step 128"; fi
-    timeout 400 python bench.py --scene $sc $A --no-e2e --no-cpu-baseline --no-instrumented 2>&1 | python -c "
+    timeout 400 python bench.py --scene $sc $A --no-e2e --no-cpu-baseline --no-instrumented --no-extra 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):
