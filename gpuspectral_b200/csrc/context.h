@@ -33,9 +33,8 @@ struct WavefrontState {
     // sector instead of two; GSB_RAY_AOS=0 builds the two-stream layout for comparison
     float4* ray = nullptr;
     float4* weightDW = nullptr; // weight.xyz, directWeight
-    float4* result = nullptr;   // radiance of the current sample .xyz; only touched by vertices that add light
-    uint32_t* sampleK = nullptr;  // pixel the slot's current path belongs to; bit 31: path finished, add it to the image;
-                                  // 0xffffffff = slot retired (no work left)
+    float4* result = nullptr;   // radiance of the current sample .xyz (only touched by vertices that add light); .w = bits of the pixel
+                                // index the sample belongs to, 0xffffffff = slot retired (no work left)
     float4* hitTUVP = nullptr;    // t, u, v, primitive id bits
     uint32_t* hitInst = nullptr;
     float4* shadowO = nullptr;      // origin.xyz, tmax

@@ -44,7 +44,7 @@ constexpr int kBlock = kTraceBlock;
 #ifndef GSB_SHADE_MIN_BLOCKS_DIFFUSE
 #define GSB_SHADE_MIN_BLOCKS_DIFFUSE 6   // ... the diffuse kernel: 80 registers, no spills (r2i: 66.6 -> 61.5 ms per Cornell step with the state pipeline)
 #endif
-constexpr uint32_t kRetired = 0xffffffffu;   // sampleK: the slot has no path and will get none (the call's work is used up)
+constexpr uint32_t kRetired = 0xffffffffu;   // result.w (where the pixel index lives): the slot has no path and will get none (the call's work is used up)
 // hitInst of a slot whose path has not been traced yet (k_generate): any word that is neither GSB_NO_HIT (= path ended)
 // nor carries a valid BSDF type in bits 28..31
 constexpr uint32_t kInstFresh = 0xfffffffeu;
@@ -153,8 +153,7 @@ GSB_D void startPath(const SceneDev& sc, const WavefrontState& wf, const RenderA
     *rayOrigin(wf, slot) = o;
     *rayDirection(wf, slot) = dOut;
     // weight and directWeight start out as 1: k_shade knows that from depth 0 and does not read them (nothing is written here)
-    wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    wf.sampleK[slot] = pixel;
+    wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(pixel));   // .w: the pixel the sample belongs to
     if (wf.sortKey) wf.sortKey[slot] = sortKey(sc, xyz(o), d);
     pixelOut = pixel;
 }
@@ -183,7 +182,7 @@ __global__ void __launch_bounds__(kRegenBlock) k_regen(SceneDev sc, WavefrontSta
 #pragma unroll
     for (int k = 0; k < kRegenPer; k++) {
         const uint32_t slot = base + (uint32_t)k * kRegenBlock + tid;
-        if (slot < ra.slots && wf.hitInst[slot] == GSB_NO_HIT && wf.sampleK[slot] != kRetired) ended |= 1u << k;
+        if (slot < ra.slots && wf.hitInst[slot] == GSB_NO_HIT && __float_as_uint(wf.result[slot].w) != kRetired) ended |= 1u << k;
     }
     // exclusive prefix of the ended counts over the block
     const uint32_t n = (uint32_t)__popc(ended);
@@ -211,8 +210,8 @@ __global__ void __launch_bounds__(kRegenBlock) k_regen(SceneDev sc, WavefrontSta
     for (int k = 0; k < kRegenPer; k++) {
         if (!(ended & (1u << k))) continue;
         const uint32_t slot = base + (uint32_t)k * kRegenBlock + tid;
-        const uint32_t pixel = wf.sampleK[slot];
         const float4 res = wf.result[slot];
+        const uint32_t pixel = __float_as_uint(res.w);
         // raygen.rgen:106-108: a NaN sample leaves the image untouched
         if (!(isnan(res.x) || isnan(res.y) || isnan(res.z))) atomicAdd(&ra.accum[pixel], make_float4(res.x, res.y, res.z, 1.0f));
         if (work < ra.totalWork) {
@@ -220,7 +219,7 @@ __global__ void __launch_bounds__(kRegenBlock) k_regen(SceneDev sc, WavefrontSta
             uint32_t p;
             startPath(sc, wf, ra, slot, work, o, d, p);
         } else {
-            wf.sampleK[slot] = kRetired;
+            wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kRetired));
             *rayDirection(wf, slot) = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kFlagDead));
             if (wf.sortKey) wf.sortKey[slot] = 0xffffffffu;   // sorts behind every live ray
             retired++;
@@ -355,6 +354,8 @@ __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFU
     float4 (*st)[4][32] = s_state[threadIdx.x >> 5];
     uint32_t (*sti)[32] = s_inst[threadIdx.x >> 5];
     uint32_t tile = warpId;
+    // the instance word of the tile scanned next is loaded one scan ahead (its DRAM latency hides behind the batch in between)
+    uint32_t aheadWord = (tile < tiles && tile * 32u + lane < slots) ? wf.hitInst[tile * 32u + lane] : GSB_NO_HIT;
     bool scanDone = false, havePrev = false, prevActive = false;
     uint32_t prevSlot = 0, stage = 0;
     for (;;) {
@@ -365,10 +366,10 @@ __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFU
             const bool scanning = tile < tiles;
             const uint32_t cand = tile * 32u + lane;
             tile += warpsTotal;
-            bool match = false;
-            if (scanning && cand < slots) {
-                match = (wf.hitInst[cand] >> kInstTypeShift) == (uint32_t)TYPE;   // the instance word carries the BSDF type; GSB_NO_HIT decodes to none
-            }
+            const uint32_t word = aheadWord;
+            aheadWord = (tile < tiles && tile * 32u + lane < slots) ? wf.hitInst[tile * 32u + lane] : GSB_NO_HIT;
+            // the instance word carries the BSDF type; GSB_NO_HIT decodes to none
+            const bool match = scanning && cand < slots && (word >> kInstTypeShift) == (uint32_t)TYPE;
             const uint32_t mm = __ballot_sync(0xffffffffu, match);
             if ((uint32_t)__popc(mm) >= directMin) {
                 // a tile that matches (almost) completely is shaded in place: coalesced state streams and no trip through
@@ -701,7 +702,7 @@ void allocWavefront(gsb_context* ctx, uint32_t slots, bool sorting) {
     if (wf.capacity >= slots && wf.qCount) return;
     const size_t n = slots;
     ensure(wf.ray, 2 * n); ensure(wf.weightDW, n); ensure(wf.result, n);
-    ensure(wf.sampleK, n); ensure(wf.hitTUVP, n); ensure(wf.hitInst, n);
+    ensure(wf.hitTUVP, n); ensure(wf.hitInst, n);
 
     ensure(wf.shadowO, n); ensure(wf.shadowD, n); ensure(wf.shadowBase, n); ensure(wf.shadowNee, n);
     if (!wf.qCount) ensure(wf.qCount, (size_t)2 * Q_COUNT);
@@ -722,7 +723,7 @@ void launchShade(gsb_context* ctx, const SceneDev& sc, int grid, uint32_t parity
 
 void freeWavefront(gsb_context* ctx) {
     WavefrontState& wf = ctx->wf;
-    void* ptrs[] = {wf.ray, wf.weightDW, wf.result, wf.sampleK, wf.hitTUVP, wf.hitInst,
+    void* ptrs[] = {wf.ray, wf.weightDW, wf.result, wf.hitTUVP, wf.hitInst,
                     wf.shadowO, wf.shadowD, wf.shadowBase, wf.shadowNee, wf.qCount, wf.stats,
                     wf.sortKey, wf.sortKeyOut, wf.order, wf.iota, wf.sortTemp};
     for (void* p : ptrs)
