@@ -500,6 +500,39 @@ def run_ours(a, rank, world, local_rank):
                        "HDR frame resolved and copied to pinned host memory on rank 0"}
         if rank == 0:
             assert np.isfinite(host_np).all() and host_np[..., :3].mean() > 0.01
+        # the same per-frame loop for a scene whose instances MOVE: transforms from host memory through
+        # gsb_scene_update_transforms (re-bake + refit over the kept topology) instead of the full instance upload + rebuild
+        inst, ni = scene.instances
+        xf = np.array([list(inst[i].transform) for i in range(ni)], np.float32)
+
+        def refit_step(k):
+            ctx.update_transforms(0, xf)
+            ctx.set_camera(*scene.camera)
+            step(k)
+            if rank == 0:
+                ctx.read_hdr(out=host_np)
+
+        refit_step(100)
+        ctx.reset_counters()
+        barrier()
+        t0 = time.perf_counter()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record(stream)
+        for k in range(a.e2e_steps):
+            refit_step(101 + k)
+        g1.record(stream)
+        barrier()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        tt = torch.tensor([max(wall_ms, g0.elapsed_time(g1))], dtype=torch.float64, device=dev)
+        pp = torch.tensor([float(ctx.counters()["paths"])], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dist.all_reduce(pp, op=dist.ReduceOp.SUM)
+        st = ctx.bvh_stats()
+        e2e["moving_instances"] = {"value": float(pp.item()) / (float(tt.item()) * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": float(tt.item()) / a.e2e_steps,
+                                   "h2d_bytes_per_step": int(xf.nbytes) + 80, "refit_ms": st["refit_ms"], "rebuild_ms": bvh["build_ms"],
+                                   "what": "per step: every instance transform from host memory (gsb_scene_update_transforms: re-bake + "
+                                           "bottom-up refit), camera, render, reduce (N>1), HDR frame to pinned host memory on rank 0"}
 
     # ---- CPU baseline (rank 0, N = 1 only) ---------------------------------------------------------------------------------------
     cpu = None

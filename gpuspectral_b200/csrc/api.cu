@@ -295,12 +295,19 @@ void ensureStats(gsb_context* ctx) {
 bool sceneReady(gsb_context* ctx) { return ctx->haveInstances && ctx->tlas.buffer; }
 
 void checkOverflow(gsb_context* ctx) {
-    unsigned long long ov = 0;
+    unsigned long long ov = 0, live = 0;
     GSB_CUDA(cudaMemcpyAsync(&ov, &ctx->wf.stats[ST_OVERFLOW], sizeof(ov), cudaMemcpyDeviceToHost, ctx->stream));
+    GSB_CUDA(cudaMemcpyAsync(&live, &ctx->wf.stats[ST_LIVE], sizeof(live), cudaMemcpyDeviceToHost, ctx->stream));
     GSB_CUDA(cudaStreamSynchronize(ctx->stream));
     if (ov) {
         GSB_CUDA(cudaMemsetAsync(&ctx->wf.stats[ST_OVERFLOW], 0, sizeof(ov), ctx->stream));
         throw std::runtime_error("traversal stack overflow: BVH deeper than the traversal stack");
+    }
+    if (live) {
+        // the iteration bound of the render loop (a safety net against a hung device) stopped a frame whose paths were not all
+        // finished: samples are missing from the image, which must not pass for a completed render
+        GSB_CUDA(cudaMemsetAsync(&ctx->wf.stats[ST_LIVE], 0, sizeof(live), ctx->stream));
+        throw std::runtime_error("render stopped at its iteration bound with " + std::to_string(live) + " path slots still live: the frame is incomplete");
     }
 }
 

@@ -51,11 +51,18 @@ void PathTracer::uploadScene(const Scene& scene) {
     check(gsb_set_camera(ctx, eye, T, scene.camera.fov), "gsb_set_camera");
     uploaded = &scene;
     uploadedObjects = scene.renderObjects.size();
+    uploadedRevision = scene.revision;
 }
 
 void PathTracer::render(const Scene& scene, uint32_t spp, uint32_t stride) {
     if (w == 0 || h == 0) throw std::runtime_error("PathTracer::setup was not called");
-    if (uploaded != &scene || uploadedObjects != scene.renderObjects.size()) uploadScene(scene);
+    // The reference re-reads everything every frame (PathTracer.cpp:58-93).  Here the scene arrays are uploaded when the
+    // Scene object, its object count or its revision (Scene::touch(), to be called after editing transforms, materials or
+    // lights in place) changes; the camera is cheap host state and is set on every call.
+    if (uploaded != &scene || uploadedObjects != scene.renderObjects.size() || uploadedRevision != scene.revision) uploadScene(scene);
+    const float* T = scene.camera.toWorld;
+    const float eye[3] = {T[12], T[13], T[14]};  // Camera::getPosition = toWorld[3]
+    check(gsb_set_camera(ctx, eye, T, scene.camera.fov), "gsb_set_camera");
     check(gsb_render(ctx, w, h, (uint32_t)timestamp, spp, stride), "gsb_render");
     timestamp += (int)(spp * stride);
 }

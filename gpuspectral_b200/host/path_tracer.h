@@ -53,6 +53,7 @@ class PathTracer {
     uint32_t w = 0, h = 0;
     const Scene* uploaded = nullptr;
     size_t uploadedObjects = 0;
+    uint64_t uploadedRevision = 0;
     std::vector<uint32_t> meshHandles;
 };
 

@@ -44,6 +44,8 @@ struct Camera {  // Camera.h: toWorld + fov; eye = toWorld[3] (Camera.cpp:33-35)
 };
 
 struct Scene {
+    uint64_t revision = 0;   // bump (touch()) after editing transforms / materials / lights in place: PathTracer re-uploads
+    void touch() { revision++; }
     Camera camera;
     uint32_t filmWidth = 0, filmHeight = 0;  // from the XML film; the reference ignores it (frame size = window size)
     std::vector<MeshData> meshes;
