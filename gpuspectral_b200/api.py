@@ -94,6 +94,23 @@ class Scene:
         q = np.ctypeslib.as_array(N.host.gsbh_scene_mesh_normals(self._h, i), shape=(n, 3)).copy()
         return p, q
 
+    def mesh_uv(self, i):
+        """(n, 2) float32 texture coordinates of mesh i, or None when the mesh has none."""
+        n = N.host.gsbh_scene_mesh_vertex_count(self._h, i)
+        p = N.host.gsbh_scene_mesh_uvs(self._h, i)
+        if n == 0 or not p:
+            return None
+        return np.ctypeslib.as_array(p, shape=(n, 2)).copy()
+
+    @property
+    def textures(self):
+        """(gsb_texture array, count); bitmap texel pointers belong to this Scene."""
+        n = N.host.gsbh_scene_texture_count(self._h)
+        arr = (N.Texture * max(1, n))()
+        if n:
+            N.host.gsbh_scene_copy_textures(self._h, arr)
+        return arr, n
+
     def mesh_name(self, i):
         return N.host.gsbh_scene_mesh_name(self._h, i).decode()
 
@@ -173,12 +190,19 @@ class Context:
         self.close()
 
     # ---- scene ----------------------------------------------------------------------------
-    def mesh_create(self, positions, normals):
+    def mesh_create(self, positions, normals, uv=None):
         p = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
         q = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
         out = C.c_uint32()
-        _check(N.core.gsb_mesh_create(self._c, _fp(p), _fp(q), len(p), C.byref(out)), "gsb_mesh_create")
+        if uv is None:
+            _check(N.core.gsb_mesh_create(self._c, _fp(p), _fp(q), len(p), C.byref(out)), "gsb_mesh_create")
+        else:
+            t = np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
+            _check(N.core.gsb_mesh_create_uv(self._c, _fp(p), _fp(q), _fp(t), len(p), C.byref(out)), "gsb_mesh_create_uv")
         return out.value
+
+    def set_textures(self, textures, count):
+        _check(N.core.gsb_scene_set_textures(self._c, textures, count), "gsb_scene_set_textures")
 
     def mesh_destroy(self, mesh):
         _check(N.core.gsb_mesh_destroy(self._c, mesh), "gsb_mesh_destroy")
@@ -218,7 +242,11 @@ class Context:
         """Uploads a whole host Scene through the scene calls of the C ABI (meshes, BSDFs, lights, instances, camera)."""
         for m in self._mesh_map:
             N.core.gsb_mesh_destroy(self._c, m)
-        self._mesh_map = [self.mesh_create(*scene.mesh(i)) for i in range(scene.mesh_count)]
+        has_uv = hasattr(scene, "mesh_uv")
+        self._mesh_map = [self.mesh_create(*scene.mesh(i), uv=scene.mesh_uv(i) if has_uv else None) for i in range(scene.mesh_count)]
+        if hasattr(scene, "textures"):
+            tex, nt = scene.textures
+            self.set_textures(tex, nt)
         for t in range(N.BSDF_TYPE_COUNT):
             raw, n = scene.bsdfs(t)
             self.set_bsdfs(t, raw, n)

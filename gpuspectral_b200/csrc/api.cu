@@ -392,6 +392,8 @@ SceneDev gsb_context::sceneDev() const {
     for (int t = 0; t < GSB_BSDF_TYPE_COUNT; t++) sc.bsdf[t] = dBsdf[t];
     sc.lights = dLights;
     sc.numLights = numLights;
+    sc.textures = dTextures;
+    sc.numTextures = numTextures;
     sc.numInstances = (uint32_t)instances.size();
     memcpy(sc.eye, eye, sizeof(eye));
     memcpy(sc.view, view, sizeof(view));
@@ -408,6 +410,14 @@ SceneDev gsb_context::sceneDev() const {
         sc.sortScale[a] = (float)(1u << sortBits) / (hi - lo);
     }
     return sc;
+}
+
+static void freeTextures(gsb_context* ctx) {
+    for (float4* t : ctx->textureTexels) cudaFree(t);
+    ctx->textureTexels.clear();
+    cudaFree(ctx->dTextures);
+    ctx->dTextures = nullptr;
+    ctx->numTextures = 0;
 }
 
 extern "C" {
@@ -486,6 +496,7 @@ gsb_status gsb_destroy(gsb_context* ctx) {
         cudaFree(ctx->dWorldVerts);
         cudaFree(ctx->dWorldNrm);
         cudaFree(ctx->dNrmSoup);
+        freeTextures(ctx);
         cudaFree(ctx->dInstSmall);
         cudaFree(ctx->dShade);
         cudaFree(ctx->dInstBsdf);
@@ -500,6 +511,49 @@ gsb_status gsb_destroy(gsb_context* ctx) {
 }
 
 gsb_status gsb_mesh_create(gsb_context* ctx, const float* positions3, const float* normals3, uint32_t nverts, uint32_t* out_mesh) {
+    return gsb_mesh_create_uv(ctx, positions3, normals3, nullptr, nverts, out_mesh);
+}
+
+gsb_status gsb_scene_set_textures(gsb_context* ctx, const gsb_texture* textures, uint32_t count) {
+    if (!ctx || (count && !textures)) return fail(GSB_ERR_INVALID, "gsb_scene_set_textures: null argument");
+    for (uint32_t i = 0; i < count; i++) {
+        if (textures[i].type > GSB_TEXTURE_BITMAP) return fail(GSB_ERR_INVALID, "gsb_scene_set_textures: unknown texture type");
+        if (textures[i].type == GSB_TEXTURE_BITMAP && (!textures[i].texels || textures[i].width == 0 || textures[i].height == 0))
+            return fail(GSB_ERR_INVALID, "gsb_scene_set_textures: bitmap " + std::to_string(i) + " has no texels");
+    }
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        drain(ctx);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        freeTextures(ctx);
+        std::vector<TextureDev> recs(count);
+        for (uint32_t i = 0; i < count; i++) {
+            const gsb_texture& t = textures[i];
+            TextureDev& r = recs[i];
+            memset(&r, 0, sizeof(r));
+            r.type = t.type; r.width = t.width; r.height = t.height;
+            r.uscale = t.uscale; r.vscale = t.vscale; r.uoffset = t.uoffset; r.voffset = t.voffset;
+            r.color0 = make_float4(t.color0[0], t.color0[1], t.color0[2], 0.0f);
+            r.color1 = make_float4(t.color1[0], t.color1[1], t.color1[2], 0.0f);
+            if (t.type == GSB_TEXTURE_BITMAP) {
+                const size_t n = (size_t)t.width * t.height;
+                std::vector<float4> px(n);
+                for (size_t k = 0; k < n; k++) px[k] = make_float4(t.texels[3 * k], t.texels[3 * k + 1], t.texels[3 * k + 2], 0.0f);
+                float4* d = uploadArray(px.data(), (uint32_t)n, ctx->stream);
+                GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+                ctx->textureTexels.push_back(d);
+                r.texels = d;
+            }
+        }
+        ctx->dTextures = uploadArray(recs.data(), count, ctx->stream);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->numTextures = count;
+        return GSB_OK;
+    });
+}
+
+gsb_status gsb_mesh_create_uv(gsb_context* ctx, const float* positions3, const float* normals3, const float* uv2, uint32_t nverts,
+                              uint32_t* out_mesh) {
     if (!ctx || !out_mesh) return fail(GSB_ERR_INVALID, "gsb_mesh_create: null argument");
     if (nverts % 3 != 0) return fail(GSB_ERR_INVALID, "gsb_mesh_create: vertex count is not a multiple of 3");
     if (nverts && (!positions3 || !normals3)) return fail(GSB_ERR_INVALID, "gsb_mesh_create: null vertex arrays");
@@ -510,8 +564,9 @@ gsb_status gsb_mesh_create(gsb_context* ctx, const float* positions3, const floa
         m.ntris = nverts / 3;
         std::vector<float4> p4(nverts), n4(nverts);
         for (uint32_t i = 0; i < nverts; i++) {
-            p4[i] = make_float4(positions3[3 * (size_t)i], positions3[3 * (size_t)i + 1], positions3[3 * (size_t)i + 2], 0.0f);
-            n4[i] = make_float4(normals3[3 * (size_t)i], normals3[3 * (size_t)i + 1], normals3[3 * (size_t)i + 2], 0.0f);
+            // the texture coordinate rides in the two free .w components: u with the position, v with the normal
+            p4[i] = make_float4(positions3[3 * (size_t)i], positions3[3 * (size_t)i + 1], positions3[3 * (size_t)i + 2], uv2 ? uv2[2 * (size_t)i] : 0.0f);
+            n4[i] = make_float4(normals3[3 * (size_t)i], normals3[3 * (size_t)i + 1], normals3[3 * (size_t)i + 2], uv2 ? uv2[2 * (size_t)i + 1] : 0.0f);
         }
         m.vpos = uploadArray(p4.data(), nverts, ctx->stream);
         m.vnrm = uploadArray(n4.data(), nverts, ctx->stream);

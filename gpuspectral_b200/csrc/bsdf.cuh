@@ -474,6 +474,27 @@ GSB_D bool isTransmissionBSDF(uint32_t type) { return type == GSB_BSDF_SMOOTH_DI
 
 // Compile-time dispatch used by the material-sorted shade kernel (TYPE is uniform per block);
 // the runtime switch of :630-654 survives only in the diagnostic entry points.
+// ---- reflectance textures (extension; gsb_texture in the public header) -------------------------------------------------
+// checkerboard: Mitsuba's rule on the transformed coordinate; bitmap: bilinear over texel centres, repeat, v = 1 at row 0
+GSB_D float3 textureEval(const TextureDev& t, float u, float v) {
+    const float uu = u * t.uscale + t.uoffset, vv = v * t.vscale + t.voffset;
+    if (t.type == GSB_TEXTURE_CHECKERBOARD) {
+        const int ix = (int)floorf(2.0f * uu), iy = (int)floorf(2.0f * vv);
+        return ((ix + iy) & 1) == 0 ? xyz(t.color0) : xyz(t.color1);
+    }
+    const float w = (float)t.width, h = (float)t.height;
+    const float x = (uu - floorf(uu)) * w - 0.5f, y = (1.0f - (vv - floorf(vv))) * h - 0.5f;
+    const float fx = floorf(x), fy = floorf(y);
+    const float ax = x - fx, ay = y - fy;
+    int x0 = (int)fx, y0 = (int)fy;
+    const int W = (int)t.width, H = (int)t.height;
+    x0 = ((x0 % W) + W) % W; y0 = ((y0 % H) + H) % H;
+    const int x1 = (x0 + 1) % W, y1 = (y0 + 1) % H;
+    const float3 c00 = xyz(__ldg(t.texels + (size_t)y0 * W + x0)), c10 = xyz(__ldg(t.texels + (size_t)y0 * W + x1));
+    const float3 c01 = xyz(__ldg(t.texels + (size_t)y1 * W + x0)), c11 = xyz(__ldg(t.texels + (size_t)y1 * W + x1));
+    return (c00 * (1.0f - ax) + c10 * ax) * (1.0f - ay) + (c01 * (1.0f - ax) + c11 * ax) * ay;
+}
+
 template <int TYPE>
 GSB_D void sampleBSDFT(const SceneDev& sc, uint32_t index, uint32_t& rng, float3 wo, float3& wi, BSDFOutput& res) {
     if (TYPE == GSB_BSDF_DIFFUSE) diffuseSample(((const gsb_diffuse_bsdf*)sc.bsdf[TYPE])[index], rng, wo, wi, res);

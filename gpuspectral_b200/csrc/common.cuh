@@ -111,6 +111,16 @@ constexpr uint32_t kInstTypeShift = 28;
 constexpr uint32_t kMaxInstances = kInstMask;   // gsb_scene_set_instances rejects more
 constexpr uint32_t kNoLeaf = 0xffffffffu;
 
+// Device-side texture record (gsb_texture with the texels on the device, one float4 per texel).
+struct TextureDev {
+    uint32_t type, width, height, pad;
+    float uscale, vscale, uoffset, voffset;
+    float4 color0, color1;
+    const float4* texels;
+    uint64_t pad2;
+};
+static_assert(sizeof(TextureDev) == 80, "TextureDev layout");
+
 // Everything the kernels need to know about the scene; passed by value as a kernel parameter.
 struct SceneDev {
     const uint4* worldNodes;         // world level: 8-wide nodes over the triangles of all baked instances (world space)
@@ -123,8 +133,10 @@ struct SceneDev {
     const uint32_t* instBsdf;        // bsdf handle per instance (compact copy for queue binning)
     const void* bsdf[GSB_BSDF_TYPE_COUNT];
     const gsb_triangle_light* lights;
+    const TextureDev* textures;      // reflectance textures (diffuse records refer to them by hasTexture - 1)
     uint32_t numLights;
     uint32_t numInstances;
+    uint32_t numTextures;
     // camera: Camera of pt_common.glsl:16-21
     float eye[3];
     float view[16];  // column-major toWorld

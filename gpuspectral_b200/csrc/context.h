@@ -92,6 +92,9 @@ struct gsb_context {
     bool typeUsed[GSB_BSDF_TYPE_COUNT] = {};
     gsb_triangle_light* dLights = nullptr;
     uint32_t numLights = 0;
+    gsb::TextureDev* dTextures = nullptr;
+    std::vector<float4*> textureTexels;   // device texel arrays owned by the table
+    uint32_t numTextures = 0;
     float eye[3] = {0, 0, 0};
     float view[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
     float fov = 1.0f;

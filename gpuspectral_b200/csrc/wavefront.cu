@@ -497,6 +497,26 @@ __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFU
             BSDFOutput lightBsdfRes;
             lightBsdfRes.bsdf = f3(0.0f); lightBsdfRes.pdf = 0.0f; lightBsdfRes.isDelta = false;
             evalBSDFT<TYPE>(sc, handle & 0xffffu, wo, wL, lightBsdfRes);             // :729
+            if (TYPE == GSB_BSDF_DIFFUSE) {
+                // textured reflectance (extension): the diffuse value kD / pi with kD looked up at the hit's texture coordinate.
+                // A slow path taken by textured records only: the coordinates ride in the .w of the mesh's vertex arrays.
+                const int tex = ((const gsb_diffuse_bsdf*)sc.bsdf[GSB_BSDF_DIFFUSE])[handle & 0xffffu].hasTexture;
+                if (tex > 0 && (uint32_t)tex <= sc.numTextures) {
+                    uint32_t origPrim = prim;
+                    if (!HASINST || (instWord & kInstBaked)) origPrim = __float_as_uint(__ldg(sc.worldTris + 9 * (size_t)prim + 6).w);
+                    const ShadeInstance* sip = sc.shadeInst + inst;
+                    float tu = 0.0f, tv = 0.0f;
+#pragma unroll
+                    for (int k = 0; k < 3; k++) {
+                        const float bk = k == 0 ? bary.x : (k == 1 ? bary.y : bary.z);
+                        tu += bk * __ldg(sip->vpos + 3 * (size_t)origPrim + k).w;
+                        tv += bk * __ldg(sip->vnrm + 3 * (size_t)origPrim + k).w;
+                    }
+                    const float3 kd = textureEval(sc.textures[tex - 1], tu, tv);
+                    bsdfRes.bsdf = kd / GSB_PI;
+                    lightBsdfRes.bsdf = kd / GSB_PI;
+                }
+            }
 
             const bool transmissive = isTransmissionBSDF(TYPE);
             const float NdotV = dot(N, -rayDir);

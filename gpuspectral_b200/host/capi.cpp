@@ -57,6 +57,7 @@ gsbh_scene* gsbh_scene_builtin(const char* name, const int* params, int nparams)
         const std::string n = name ? name : "";
         auto par = [&](int i, int def) { return (params && i < nparams) ? params[i] : def; };
         if (n == "cornell") s = new gsbh_scene{gsbhost::makeCornellBox()};
+        else if (n == "cornell_textured") s = new gsbh_scene{gsbhost::makeTexturedCornellBox()};
         else if (n == "gallery") s = new gsbh_scene{gsbhost::makeBsdfGallery()};
         else if (n == "field") s = new gsbh_scene{gsbhost::makeInstancedField((uint32_t)par(0, 1234), par(1, 16), par(2, 7), par(3, 13))};
         else throw std::runtime_error("unknown built-in scene '" + n + "'");
@@ -70,6 +71,15 @@ uint32_t gsbh_scene_mesh_count(const gsbh_scene* s) { return (uint32_t)s->scene.
 uint32_t gsbh_scene_mesh_vertex_count(const gsbh_scene* s, uint32_t m) { return s->scene.meshes.at(m).vertexCount(); }
 const float* gsbh_scene_mesh_positions(const gsbh_scene* s, uint32_t m) { return s->scene.meshes.at(m).positions.data(); }
 const float* gsbh_scene_mesh_normals(const gsbh_scene* s, uint32_t m) { return s->scene.meshes.at(m).normals.data(); }
+const float* gsbh_scene_mesh_uvs(const gsbh_scene* s, uint32_t m) {
+    const auto& mesh = s->scene.meshes.at(m);
+    return mesh.uvs.size() == (size_t)mesh.vertexCount() * 2 ? mesh.uvs.data() : nullptr;
+}
+uint32_t gsbh_scene_texture_count(const gsbh_scene* s) { return (uint32_t)s->scene.textures.size(); }
+void gsbh_scene_copy_textures(const gsbh_scene* s, gsb_texture* out) {
+    const auto v = s->scene.textureRecords();   // texel pointers stay valid as long as the scene lives
+    if (!v.empty()) std::memcpy(out, v.data(), v.size() * sizeof(gsb_texture));
+}
 const char* gsbh_scene_mesh_name(const gsbh_scene* s, uint32_t m) { return s->scene.meshes.at(m).name.c_str(); }
 uint32_t gsbh_scene_instance_count(const gsbh_scene* s) { return (uint32_t)s->scene.renderObjects.size(); }
 void gsbh_scene_copy_instances(const gsbh_scene* s, gsb_instance* out) {

@@ -195,6 +195,41 @@ void parseTransform(const Ctx& c, const XmlNode* t, float* out) {
     }
 }
 
+// Reflectance textures (extension).  checkerboard: color0 / color1 / uscale / vscale / uoffset / voffset (Mitsuba's names);
+// bitmap: filename (PNG, binary PPM, PFM; 8-bit files are decoded from sRGB), uscale / vscale / uoffset / voffset.
+// Returns the texture index, or -1 (with a warning) when the texture cannot be used.
+int loadTexture(Ctx& c, const XmlNode& tex) {
+    const std::string type = tex.attrOr("type", "");
+    Scene::TextureData t;
+    std::memset(&t.desc, 0, sizeof(t.desc));
+    t.desc.uscale = t.desc.vscale = 1.0f;
+    c.number(tex, "uscale", t.desc.uscale);
+    c.number(tex, "vscale", t.desc.vscale);
+    c.number(tex, "uoffset", t.desc.uoffset);
+    c.number(tex, "voffset", t.desc.voffset);
+    if (type == "checkerboard") {
+        t.desc.type = GSB_TEXTURE_CHECKERBOARD;
+        const float c0[3] = {0.4f, 0.4f, 0.4f}, c1[3] = {0.2f, 0.2f, 0.2f};   // Mitsuba's defaults
+        std::memcpy(t.desc.color0, c0, sizeof(c0));
+        std::memcpy(t.desc.color1, c1, sizeof(c1));
+        c.color(tex, "color0", t.desc.color0);
+        c.color(tex, "color1", t.desc.color1);
+    } else if (type == "bitmap") {
+        const std::string file = c.str(tex, "filename");
+        try {
+            loadImageLinearRGB(c.baseDir + "/" + file, t.texels, t.desc.width, t.desc.height);
+        } catch (const std::exception& e) {
+            c.warn(std::string("diffuse: textured reflectance is not supported, using 0.5 (") + e.what() + ")");
+            return -1;
+        }
+        t.desc.type = GSB_TEXTURE_BITMAP;
+    } else {
+        c.warn("texture plugin '" + type + "' is not supported, using 0.5");
+        return -1;
+    }
+    return (int)c.scene->addTexture(std::move(t));
+}
+
 // Loader.cpp:145-234
 void loadMaterial(Ctx& c, Material& material, const XmlNode& obj) {
     Scene& scene = *c.scene;
@@ -211,8 +246,17 @@ void loadMaterial(Ctx& c, Material& material, const XmlNode& obj) {
     } else if (type == "diffuse") {
         gsb_diffuse_bsdf b = {{0.0f, 0.0f, 0.0f}, 0};
         if (!c.color(obj, "reflectance", b.reflectance)) {
-            if (c.prop(obj, "reflectance")) c.warn("diffuse: textured reflectance is not supported, using 0.5");
             b.reflectance[0] = b.reflectance[1] = b.reflectance[2] = 0.5f;
+            // extension: <texture type="checkerboard|bitmap" name="reflectance"> (commented-out code in the reference,
+            // Loader.cpp:122-143); the record refers to the texture by hasTexture = index + 1
+            const XmlNode* tp = c.prop(obj, "reflectance");
+            const XmlNode* tex = tp ? c.resolve(*tp) : nullptr;
+            if (tex && tex->tag == "texture") {
+                const int id = loadTexture(c, *tex);
+                if (id >= 0) b.hasTexture = id + 1;
+            } else if (tp) {
+                c.warn("diffuse: this kind of reflectance is not supported, using 0.5");
+            }
         }
         material.bsdf = scene.addDiffuseBSDF(b);
         material.hasBsdf = true;
@@ -393,16 +437,16 @@ Scene loadMitsubaScene(const std::string& xmlPath) {
     return loadMitsubaSceneFromString(readFile(xmlPath), dirOf(xmlPath));
 }
 
-// Wavefront OBJ: v / vn / f (vt accepted and ignored).  Faces are fan-triangulated and
+// Wavefront OBJ: v / vn / vt / f.  Faces are fan-triangulated and
 // un-indexed.  Where a corner has no normal the geometric face normal is used.
 MeshData loadObjMesh(const std::string& objPath) {
     std::ifstream f(objPath);
     if (!f) throw std::runtime_error("cannot open " + objPath);
     MeshData m;
     m.name = objPath;
-    std::vector<float> V, N;
+    std::vector<float> V, N, T;
     std::string line;
-    struct Corner { int v, n; };
+    struct Corner { int v, n, t; };
     std::vector<Corner> corners;
     while (std::getline(f, line)) {
         const char* p = line.c_str();
@@ -413,6 +457,9 @@ MeshData loadObjMesh(const std::string& objPath) {
         } else if (p[0] == 'v' && p[1] == 'n' && (p[2] == ' ' || p[2] == '\t')) {
             auto nums = parseNumbers(p + 3);
             if (nums.size() >= 3) N.insert(N.end(), nums.begin(), nums.begin() + 3);
+        } else if (p[0] == 'v' && p[1] == 't' && (p[2] == ' ' || p[2] == '\t')) {
+            auto nums = parseNumbers(p + 3);
+            if (nums.size() >= 2) T.insert(T.end(), nums.begin(), nums.begin() + 2);
         } else if (p[0] == 'f' && (p[1] == ' ' || p[1] == '\t')) {
             corners.clear();
             p += 2;
@@ -422,11 +469,11 @@ MeshData loadObjMesh(const std::string& objPath) {
                 char* end = nullptr;
                 long vi = std::strtol(p, &end, 10);
                 if (end == p) break;
-                long ni = 0;
+                long ni = 0, ti = 0;
                 p = end;
                 if (*p == '/') {
                     p++;
-                    if (*p != '/') { std::strtol(p, &end, 10); p = end; }  // vt
+                    if (*p != '/') { ti = std::strtol(p, &end, 10); p = end; }
                     if (*p == '/') {
                         p++;
                         ni = std::strtol(p, &end, 10);
@@ -437,6 +484,9 @@ MeshData loadObjMesh(const std::string& objPath) {
                 Corner c;
                 c.v = vi > 0 ? (int)vi - 1 : nv + (int)vi;
                 c.n = ni > 0 ? (int)ni - 1 : (ni < 0 ? nn + (int)ni : -1);
+                const int nt = (int)(T.size() / 2);
+                c.t = ti > 0 ? (int)ti - 1 : (ti < 0 ? nt + (int)ti : -1);
+                if (c.t >= nt) c.t = -1;
                 if (c.v < 0 || c.v >= nv) throw std::runtime_error(objPath + ": face references a missing vertex");
                 if (c.n >= nn) c.n = -1;
                 corners.push_back(c);
@@ -454,6 +504,8 @@ MeshData loadObjMesh(const std::string& objPath) {
                     m.positions.insert(m.positions.end(), &V[3 * (size_t)cr.v], &V[3 * (size_t)cr.v] + 3);
                     if (cr.n >= 0) m.normals.insert(m.normals.end(), &N[3 * (size_t)cr.n], &N[3 * (size_t)cr.n] + 3);
                     else m.normals.insert(m.normals.end(), fn, fn + 3);
+                    m.uvs.push_back(cr.t >= 0 ? T[2 * (size_t)cr.t] : 0.0f);
+                    m.uvs.push_back(cr.t >= 0 ? T[2 * (size_t)cr.t + 1] : 0.0f);
                 }
             }
         }

@@ -34,13 +34,18 @@ void PathTracer::uploadScene(const Scene& scene) {
     meshHandles.clear();
     for (const MeshData& m : scene.meshes) {
         uint32_t handle = 0;
-        check(gsb_mesh_create(ctx, m.positions.data(), m.normals.data(), m.vertexCount(), &handle), "gsb_mesh_create");
+        const float* uv = m.uvs.size() == (size_t)m.vertexCount() * 2 ? m.uvs.data() : nullptr;
+        check(gsb_mesh_create_uv(ctx, m.positions.data(), m.normals.data(), uv, m.vertexCount(), &handle), "gsb_mesh_create_uv");
         meshHandles.push_back(handle);
     }
     for (uint32_t type = 0; type < GSB_BSDF_TYPE_COUNT; type++) {
         uint32_t count = 0, stride = 0;
         const void* data = scene.bsdfData(type, &count, &stride);
         check(gsb_scene_set_bsdfs(ctx, type, data, count), "gsb_scene_set_bsdfs");
+    }
+    {
+        const std::vector<gsb_texture> tex = scene.textureRecords();
+        check(gsb_scene_set_textures(ctx, tex.data(), (uint32_t)tex.size()), "gsb_scene_set_textures");
     }
     check(gsb_scene_set_lights(ctx, scene.triangleLights.data(), (uint32_t)scene.triangleLights.size()), "gsb_scene_set_lights");
     std::vector<gsb_instance> inst = scene.instanceRecords();

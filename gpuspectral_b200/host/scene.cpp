@@ -143,9 +143,11 @@ uint64_t Scene::instancedTriangles() const {
 }
 
 // ---- built-in meshes -----------------------------------------------------------------------
-static void pushVertex(MeshData& m, const float* p, const float* n) {
+static void pushVertex(MeshData& m, const float* p, const float* n, float u = 0.0f, float v = 0.0f) {
     m.positions.insert(m.positions.end(), p, p + 3);
     m.normals.insert(m.normals.end(), n, n + 3);
+    m.uvs.push_back(u);
+    m.uvs.push_back(v);
 }
 
 MeshData makeRectangle() {
@@ -155,8 +157,9 @@ MeshData makeRectangle() {
     const float v[4][3] = {{-1, 1, 0}, {1, 1, 0}, {-1, -1, 0}, {1, -1, 0}};
     const float n[3] = {0, 0, 1};
     const int f[2][3] = {{0, 2, 1}, {2, 3, 1}};
+    const float uv[4][2] = {{0, 1}, {1, 1}, {0, 0}, {1, 0}};   // the vt lines of assets/rect.obj
     for (auto& tri : f)
-        for (int k : tri) pushVertex(m, v[k], n);
+        for (int k : tri) pushVertex(m, v[k], n, uv[k][0], uv[k][1]);
     return m;
 }
 
@@ -175,9 +178,10 @@ MeshData makeCube() {
     };
     const float n[6][3] = {{1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
     const int f[2][3] = {{0, 2, 1}, {2, 3, 1}};
+    const float uv[4][2] = {{0, 1}, {1, 1}, {0, 0}, {1, 0}};   // every face carries the unit square
     for (int s = 0; s < 6; s++)
         for (auto& tri : f)
-            for (int k : tri) pushVertex(m, q[s][k], n[s]);
+            for (int k : tri) pushVertex(m, q[s][k], n[s], uv[k][0], uv[k][1]);
     return m;
 }
 
@@ -192,9 +196,9 @@ MeshData makeDisk(int segments) {
         const double a0 = 2.0 * 3.14159265358979323846 * k / segments, a1 = 2.0 * 3.14159265358979323846 * (k + 1) / segments;
         const float p0[3] = {(float)std::cos(a0), (float)std::sin(a0), 0.0f};
         const float p1[3] = {k + 1 == segments ? 1.0f : (float)std::cos(a1), k + 1 == segments ? 0.0f : (float)std::sin(a1), 0.0f};
-        pushVertex(m, c, n);
-        pushVertex(m, p0, n);
-        pushVertex(m, p1, n);
+        pushVertex(m, c, n, 0.5f, 0.5f);
+        pushVertex(m, p0, n, 0.5f + 0.5f * p0[0], 0.5f + 0.5f * p0[1]);
+        pushVertex(m, p1, n, 0.5f + 0.5f * p1[0], 0.5f + 0.5f * p1[1]);
     }
     return m;
 }
@@ -435,6 +439,46 @@ Scene makeBsdfGallery() {
         o.mesh = 1;
         o.material = s.addMaterial(m);
         s.addRenderObject(o);
+    }
+    return s;
+}
+
+// The Cornell box with textured reflectances (extension, see gsb_texture): the walls are instances of the rectangle mesh
+// (texture coordinates = the vt lines of assets/rect.obj) and the boxes instances of the cube mesh.  Records 0 (floor),
+// 2 (back wall) and 6 (tall box) of the diffuse table — the order cornell-box/scene.xml lists its shapes in — get a
+// checkerboard, a procedurally painted bitmap and a finer checkerboard.
+Scene makeTexturedCornellBox() {
+    Scene s = makeCornellBox();
+    Scene::TextureData floorTex;
+    std::memset(&floorTex.desc, 0, sizeof(floorTex.desc));
+    floorTex.desc.type = GSB_TEXTURE_CHECKERBOARD;
+    const float a0[3] = {0.75f, 0.72f, 0.68f}, a1[3] = {0.15f, 0.2f, 0.35f};
+    std::memcpy(floorTex.desc.color0, a0, sizeof(a0));
+    std::memcpy(floorTex.desc.color1, a1, sizeof(a1));
+    floorTex.desc.uscale = floorTex.desc.vscale = 4.0f;
+    Scene::TextureData wall;
+    std::memset(&wall.desc, 0, sizeof(wall.desc));
+    wall.desc.type = GSB_TEXTURE_BITMAP;
+    wall.desc.width = 96; wall.desc.height = 64;
+    wall.desc.uscale = wall.desc.vscale = 1.0f;
+    wall.texels.resize((size_t)96 * 64 * 3);
+    for (int y = 0; y < 64; y++)
+        for (int x = 0; x < 96; x++) {
+            const float u = (x + 0.5f) / 96.0f, v = (y + 0.5f) / 64.0f;
+            const float ring = 0.5f + 0.5f * std::sin(40.0f * std::sqrt((u - 0.5f) * (u - 0.5f) * 2.25f + (v - 0.5f) * (v - 0.5f)));
+            float* p = &wall.texels[3 * ((size_t)y * 96 + x)];
+            p[0] = 0.15f + 0.7f * u; p[1] = 0.15f + 0.6f * ring; p[2] = 0.8f - 0.6f * v;
+        }
+    Scene::TextureData boxTex = floorTex;
+    const float b0[3] = {0.8f, 0.3f, 0.2f}, b1[3] = {0.9f, 0.85f, 0.6f};
+    std::memcpy(boxTex.desc.color0, b0, sizeof(b0));
+    std::memcpy(boxTex.desc.color1, b1, sizeof(b1));
+    boxTex.desc.uscale = 3.0f; boxTex.desc.vscale = 6.0f; boxTex.desc.uoffset = 0.25f;
+    const uint32_t t0 = s.addTexture(std::move(floorTex)), t1 = s.addTexture(std::move(wall)), t2 = s.addTexture(std::move(boxTex));
+    if (s.diffuseBSDFs.size() >= 7) {
+        s.diffuseBSDFs[0].hasTexture = (int32_t)t0 + 1;
+        s.diffuseBSDFs[2].hasTexture = (int32_t)t1 + 1;
+        s.diffuseBSDFs[6].hasTexture = (int32_t)t2 + 1;
     }
     return s;
 }

@@ -20,6 +20,7 @@ struct MeshData {
     std::string name;
     std::vector<float> positions;  // 3 floats per vertex
     std::vector<float> normals;    // 3 floats per vertex
+    std::vector<float> uvs;        // 2 floats per vertex, or empty (Mesh::Vertex::uv, renderer/Mesh.h:17)
     uint32_t vertexCount() const { return (uint32_t)(positions.size() / 3); }
     uint32_t triangleCount() const { return vertexCount() / 3; }
 };
@@ -62,6 +63,15 @@ struct Scene {
     std::vector<gsb_rough_plastic_bsdf> roughPlasticBSDFs;
     std::vector<gsb_rough_dielectric_bsdf> roughDielectricBSDFs;   // extension (no reference counterpart)
     std::vector<std::string> warnings;
+    // reflectance textures (extension): descriptors as the C ABI takes them, texels owned here
+    struct TextureData { gsb_texture desc; std::vector<float> texels; };
+    std::vector<TextureData> textures;
+    uint32_t addTexture(TextureData&& t) { textures.push_back(std::move(t)); return (uint32_t)textures.size() - 1; }
+    std::vector<gsb_texture> textureRecords() const {
+        std::vector<gsb_texture> out;
+        for (const TextureData& t : textures) { gsb_texture d = t.desc; d.texels = t.texels.empty() ? nullptr : t.texels.data(); out.push_back(d); }
+        return out;
+    }
 
     int addMaterial(const Material& m) { materials.push_back(m); return (int)materials.size() - 1; }
     uint32_t addMesh(MeshData&& m) { meshes.push_back(std::move(m)); return (uint32_t)meshes.size() - 1; }
@@ -93,9 +103,13 @@ struct Scene {
 // Throws std::runtime_error on unreadable input.
 Scene loadMitsubaScene(const std::string& xmlPath);
 MeshData loadObjMesh(const std::string& objPath);
+// Image files for bitmap textures: PFM, binary PPM (P6) and PNG (8-bit, non-interlaced; own inflate).  Returns linear RGB
+// (8-bit sources go through the sRGB decoding curve), rows top to bottom.  Throws std::runtime_error.
+void loadImageLinearRGB(const std::string& path, std::vector<float>& rgb, uint32_t& width, uint32_t& height);
 // glTF 2.0 (.gltf / .glb), see gltf.cpp.  Throws std::runtime_error on unreadable input.
 Scene loadGltfScene(const std::string& path);
 
+Scene makeTexturedCornellBox();                 // the Cornell box with a checkerboard floor, a bitmap back wall and a checkerboard tall box (texture extension)
 MeshData makeRectangle();                       // assets/rect.obj equivalent (2 triangles, z = 0, normal +z)
 MeshData makeCube();
 MeshData makeDisk(int segments = 64);                            // assets/box.obj equivalent (12 triangles, [-1,1]^3)

@@ -150,6 +150,19 @@ typedef struct gsb_bvh_stats {
     double   refit_ms;
 } gsb_bvh_stats;
 
+/* Reflectance textures (extension: the reference's loader keeps `bitmap` and `checkerboard` only as commented-out code,
+ * engine/Loader.cpp:122-143, and its shaders pass a `uv` to every BSDF that none of them uses, rayhit.rchit:341-654;
+ * Mitsuba semantics).  A diffuse BSDF record refers to texture i by hasTexture = i + 1 (0 = the constant reflectance). */
+#define GSB_TEXTURE_CHECKERBOARD 0u  /* color0 where floor(2 u') + floor(2 v') is even, color1 elsewhere; (u', v') = (u * uscale + uoffset, v * vscale + voffset) */
+#define GSB_TEXTURE_BITMAP 1u        /* width x height linear-RGB texels, row 0 = top of the image (v = 1), bilinear, repeat */
+typedef struct gsb_texture {
+    uint32_t type;
+    uint32_t width, height;      /* bitmap only */
+    const float* texels;         /* bitmap only: width * height * 3 floats, copied by gsb_scene_set_textures */
+    float color0[3], color1[3];  /* checkerboard only */
+    float uscale, vscale, uoffset, voffset;
+} gsb_texture;
+
 /* ---- context ------------------------------------------------------------------- */
 GSB_API gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx);
 GSB_API gsb_status gsb_destroy(gsb_context* ctx);
@@ -165,6 +178,12 @@ GSB_API gsb_status gsb_mesh_create(gsb_context* ctx, const float* positions3, co
 GSB_API gsb_status gsb_mesh_destroy(gsb_context* ctx, uint32_t mesh);
 /* Replaces the instance list and builds the top-level BVH once (the reference rebuilds
  * its TLAS every frame, PathTracer.cpp:10-19). */
+/* gsb_mesh_create with texture coordinates (2 floats per vertex; NULL = all zero).  Replaces: Mesh::Mesh's `texcoord`
+ * attribute (renderer/Mesh.cpp:7-22,37,50), which the reference uploads and never reads. */
+GSB_API gsb_status gsb_mesh_create_uv(gsb_context* ctx, const float* positions3, const float* normals3, const float* uv2,
+                                      uint32_t num_vertices, uint32_t* out_mesh);
+/* Replaces the scene's texture table (may be called before or after gsb_scene_set_instances). */
+GSB_API gsb_status gsb_scene_set_textures(gsb_context* ctx, const gsb_texture* textures, uint32_t count);
 GSB_API gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instances, uint32_t count);
 /* Replaces the transforms (16 floats each, column-major, as gsb_instance::transform) of instances [first, first + count)
  * and refits the acceleration structures over their existing topology; falls back to a rebuild when the refit tree has

@@ -158,6 +158,7 @@ struct BvhNode {           // oracle's own CPU BVH (binary, object space)
 struct Mesh {
     std::vector<float> pos;   // 3 floats / vertex
     std::vector<float> nrm;
+    std::vector<float> uv;    // 2 floats / vertex; empty = all zero (texture extension)
     uint32_t ntris = 0;
     std::vector<BvhNode> nodes;
     std::vector<uint32_t> order;
@@ -195,6 +196,9 @@ struct or_scene {
     std::vector<gsb_rough_plastic_bsdf> roughPlastic;
     std::vector<gsb_rough_dielectric_bsdf> roughDielectric;   // extension, see roughDielectricSample
     std::vector<gsb_triangle_light> lights;
+    // reflectance textures (extension; gsb_texture of the public header with the texels copied)
+    struct Texture { gsb_texture desc; std::vector<float> texels; };
+    std::vector<Texture> textures;
     float eye[3] = {0, 0, 0};
     float view[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
     float fov = 1.0f;
@@ -1050,6 +1054,27 @@ inline bool isvalid(vec3 v) { return isvalid(v.x) && isvalid(v.y) && isvalid(v.z
 
 struct PathStats { uint64_t ext = 0, shadow = 0, draws = 0; };
 
+// Reflectance textures (extension, no reference source: engine/Loader.cpp:122-143 holds them as commented-out code).
+// checkerboard: Mitsuba's rule on the transformed coordinate; bitmap: bilinear over texel centres, repeat, v = 1 at row 0.
+vec3 textureEval(const or_scene::Texture& t, float u, float v) {
+    const gsb_texture& d = t.desc;
+    const float uu = u * d.uscale + d.uoffset, vv = v * d.vscale + d.voffset;
+    if (d.type == GSB_TEXTURE_CHECKERBOARD) {
+        const int ix = (int)std::floor(2.0f * uu), iy = (int)std::floor(2.0f * vv);
+        return ((ix + iy) & 1) == 0 ? v3(d.color0) : v3(d.color1);
+    }
+    const float w = (float)d.width, h = (float)d.height;
+    const float x = (uu - std::floor(uu)) * w - 0.5f, y = (1.0f - (vv - std::floor(vv))) * h - 0.5f;
+    const float fx = std::floor(x), fy = std::floor(y);
+    const float ax = x - fx, ay = y - fy;
+    const int W = (int)d.width, H = (int)d.height;
+    int x0 = (int)fx, y0 = (int)fy;
+    x0 = ((x0 % W) + W) % W; y0 = ((y0 % H) + H) % H;
+    const int x1 = (x0 + 1) % W, y1 = (y0 + 1) % H;
+    auto px = [&](int xx, int yy) { const float* p = &t.texels[3 * ((size_t)yy * W + xx)]; return vec3(p[0], p[1], p[2]); };
+    return (px(x0, y0) * (1.0f - ax) + px(x1, y0) * ax) * (1.0f - ay) + (px(x0, y1) * (1.0f - ax) + px(x1, y1) * ax) * ay;
+}
+
 void closestHit(const or_scene& s, const Hit& hit, HitPayload& prd, PathStats& st, or_bounce* rec) {
     Rng rng(prd.seed);  // :668
     const Instance& instance = s.instances[hit.inst];
@@ -1104,6 +1129,22 @@ void closestHit(const or_scene& s, const Hit& hit, HitPayload& prd, PathStats& s
     BSDFOutput lightBsdfRes;
     lightBsdfRes.bsdf = vec3(0.0f); lightBsdfRes.pdf = 0.0f; lightBsdfRes.isDelta = false;
     evalBSDF(s, handle, wo, wL, lightBsdfRes);                         // :729
+    if ((handle >> 16) == GSB_BSDF_DIFFUSE) {
+        // textured reflectance (extension): kD / pi with kD looked up at the hit's interpolated texture coordinate
+        const int tex = s.diffuse[handle & 0xffffu].hasTexture;
+        if (tex > 0 && (size_t)tex <= s.textures.size()) {
+            float tu = 0.0f, tv = 0.0f;
+            for (int k = 0; k < 3; k++) {
+                const float bk = k == 0 ? bary.x : (k == 1 ? bary.y : bary.z);
+                const size_t vi = 3 * (size_t)hit.prim + k;
+                tu += bk * (mesh.uv.empty() ? 0.0f : mesh.uv[2 * vi]);
+                tv += bk * (mesh.uv.empty() ? 0.0f : mesh.uv[2 * vi + 1]);
+            }
+            const vec3 kd = textureEval(s.textures[tex - 1], tu, tv);
+            bsdfRes.bsdf = kd / kPi;
+            lightBsdfRes.bsdf = kd / kPi;
+        }
+    }
 
     const bool transmissive = isTransmission(handle >> 16);
     bool neeDone = false;                                              // :732
@@ -1315,9 +1356,29 @@ or_scene* or_scene_create(void) { return new or_scene(); }
 void or_scene_destroy(or_scene* s) { delete s; }
 
 uint32_t or_scene_add_mesh(or_scene* s, const float* positions3, const float* normals3, uint32_t nverts) {
+    return or_scene_add_mesh_uv(s, positions3, normals3, nullptr, nverts);
+}
+
+int or_scene_set_textures(or_scene* s, const gsb_texture* textures, uint32_t count) {
+    s->textures.clear();
+    for (uint32_t i = 0; i < count; i++) {
+        or_scene::Texture t;
+        t.desc = textures[i];
+        if (t.desc.type == GSB_TEXTURE_BITMAP) {
+            if (!t.desc.texels || !t.desc.width || !t.desc.height) return 1;
+            t.texels.assign(t.desc.texels, t.desc.texels + (size_t)t.desc.width * t.desc.height * 3);
+        }
+        t.desc.texels = nullptr;
+        s->textures.push_back(std::move(t));
+    }
+    return 0;
+}
+
+uint32_t or_scene_add_mesh_uv(or_scene* s, const float* positions3, const float* normals3, const float* uv2, uint32_t nverts) {
     Mesh m;
     m.pos.assign(positions3, positions3 + 3 * (size_t)nverts);
     m.nrm.assign(normals3, normals3 + 3 * (size_t)nverts);
+    if (uv2) m.uv.assign(uv2, uv2 + 2 * (size_t)nverts);
     m.ntris = nverts / 3;
     buildMeshBvh(m);
     s->meshes.push_back(std::move(m));

@@ -41,6 +41,9 @@ typedef struct or_bounce {
 or_scene* or_scene_create(void);
 void or_scene_destroy(or_scene* s);
 uint32_t or_scene_add_mesh(or_scene* s, const float* positions3, const float* normals3, uint32_t nverts);
+/* texture extension: texture coordinates per vertex (NULL = zero) and the texture table, as gsb_mesh_create_uv / gsb_scene_set_textures */
+uint32_t or_scene_add_mesh_uv(or_scene* s, const float* positions3, const float* normals3, const float* uv2, uint32_t nverts);
+int or_scene_set_textures(or_scene* s, const gsb_texture* textures, uint32_t count);
 int or_scene_set_instances(or_scene* s, const gsb_instance* instances, uint32_t count);
 /* number of instances whose triangles are stored in world space (the bake rule of oracle.cpp: kBakeMaxTris / kBakeBudget) */
 uint32_t or_scene_baked_instances(const or_scene* s);

@@ -51,6 +51,8 @@ def lib():
             "or_scene_create": (P, []),
             "or_scene_destroy": (None, [P]),
             "or_scene_add_mesh": (C.c_uint32, [P, f32p, f32p, C.c_uint32]),
+            "or_scene_add_mesh_uv": (C.c_uint32, [P, f32p, f32p, f32p, C.c_uint32]),
+            "or_scene_set_textures": (C.c_int, [P, P, C.c_uint32]),
             "or_scene_set_instances": (C.c_int, [P, P, C.c_uint32]),
             "or_scene_set_bsdfs": (C.c_int, [P, C.c_uint32, P, C.c_uint32]),
             "or_scene_set_lights": (C.c_int, [P, P, C.c_uint32]),
@@ -101,8 +103,12 @@ class OracleScene:
     def from_host_scene(scene):
         """scene: gpuspectral_b200.Scene (the host layer's flat arrays; no product compute involved)."""
         o = OracleScene()
+        has_uv = hasattr(scene, "mesh_uv")
         for i in range(scene.mesh_count):
-            o.add_mesh(*scene.mesh(i))
+            o.add_mesh(*scene.mesh(i), uv=scene.mesh_uv(i) if has_uv else None)
+        if hasattr(scene, "textures"):
+            tex, nt = scene.textures
+            o.set_textures(tex, nt)
         for t in range(9):   # 8 reference types + the rough dielectric extension
             raw, n = scene.bsdfs(t)
             o.set_bsdfs(t, raw, n)
@@ -151,10 +157,18 @@ class OracleScene:
         o.set_camera(z["eye"], z["to_world"], float(z["fov"][0]))
         return o
 
-    def add_mesh(self, positions, normals):
+    def add_mesh(self, positions, normals, uv=None):
         p = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
         q = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
-        return lib().or_scene_add_mesh(self._s, _fp(p), _fp(q), len(p))
+        if uv is None:
+            return lib().or_scene_add_mesh(self._s, _fp(p), _fp(q), len(p))
+        t = np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
+        return lib().or_scene_add_mesh_uv(self._s, _fp(p), _fp(q), _fp(t), len(p))
+
+    def set_textures(self, textures, count):
+        """textures: ctypes array of gsb_texture records (gpuspectral_b200._native.Texture layout)."""
+        if lib().or_scene_set_textures(self._s, C.cast(textures, C.c_void_p), count) != 0:
+            raise ValueError("oracle: a bitmap texture has no texels")
 
     def set_instances(self, instances, count):
         if lib().or_scene_set_instances(self._s, C.cast(instances, C.c_void_p), count) != 0:

@@ -693,3 +693,21 @@ def test_converged_cornell_against_the_tungsten_render(gsb, ctx):
         assert d["rel_mse"] < 0.1, (k, d)
         assert 0.85 < d["mean_a"] / d["mean_b"] < 1.2, (k, d)
     assert out["tent_filter"]["rel_mse"] <= out["no_filter"]["rel_mse"]     # Tungsten filters its pixels too
+
+
+def test_textured_cornell_same_seeds(gsb, orc):
+    """Reflectance textures (extension): checkerboard floor and tall box, bitmap back wall (bilinear, repeat), texture
+    coordinates through gsb_mesh_create_uv, baked instances fetching them through their original primitive id.  Same
+    seeds: per pixel against the oracle; and the frame differs from the untextured box."""
+    s = gsb.Scene.builtin("cornell_textured")
+    o = orc.OracleScene.from_host_scene(s)
+    with gsb.Context(0) as c:
+        c.upload(s)
+        _same_seed_image(gsb, c, o, 480, 480, 8, 8, "cornell_textured_480", 0.995)
+        c.set_params(max_depth=8)
+        c.render(240, 240, 0, 0); c.clear(); c.render(240, 240, 0, 8)
+        tex_img = c.read_hdr().copy()
+        c.set_textures(None, 0)            # records point past the (now empty) table: the constant reflectance applies
+        c.clear(); c.render(240, 240, 0, 8)
+        plain = c.read_hdr()
+        assert _rel_mse(tex_img, plain) > 1e-2
