@@ -37,6 +37,11 @@ class Texture(C.Structure):
                 ("uscale", C.c_float), ("vscale", C.c_float), ("uoffset", C.c_float), ("voffset", C.c_float)]
 
 
+class Environment(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("width", C.c_uint32), ("height", C.c_uint32), ("texels", C.POINTER(C.c_float)),
+                ("scale", C.c_float * 3), ("to_world", C.c_float * 9)]
+
+
 class Ray(C.Structure):
     _fields_ = [("origin", C.c_float * 3), ("tmin", C.c_float), ("dir", C.c_float * 3), ("tmax", C.c_float)]
 
@@ -77,6 +82,7 @@ CORE_API = {
     "gsb_scene_set_instances": (C.c_int, [_P, C.POINTER(Instance), C.c_uint32]),
     "gsb_mesh_create_uv": (C.c_int, [_P, _f32p, _f32p, _f32p, C.c_uint32, C.POINTER(C.c_uint32)]),
     "gsb_scene_set_textures": (C.c_int, [_P, C.POINTER(Texture), C.c_uint32]),
+    "gsb_scene_set_environment": (C.c_int, [_P, C.POINTER(Environment)]),
     "gsb_scene_update_transforms": (C.c_int, [_P, C.c_uint32, C.c_uint32, C.POINTER(C.c_float)]),
     "gsb_scene_set_bsdfs": (C.c_int, [_P, C.c_uint32, _P, C.c_uint32]),
     "gsb_scene_set_lights": (C.c_int, [_P, C.POINTER(TriangleLight), C.c_uint32]),
@@ -122,6 +128,7 @@ HOST_API = {
     "gsbh_scene_mesh_normals": (_f32p, [_P, C.c_uint32]),
     "gsbh_scene_mesh_uvs": (_f32p, [_P, C.c_uint32]),
     "gsbh_scene_texture_count": (C.c_uint32, [_P]),
+    "gsbh_scene_environment": (None, [_P, C.POINTER(Environment)]),
     "gsbh_scene_copy_textures": (None, [_P, C.POINTER(Texture)]),
     "gsbh_scene_mesh_name": (C.c_char_p, [_P, C.c_uint32]),
     "gsbh_scene_instance_count": (C.c_uint32, [_P]),

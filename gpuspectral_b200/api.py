@@ -111,6 +111,13 @@ class Scene:
             N.host.gsbh_scene_copy_textures(self._h, arr)
         return arr, n
 
+    @property
+    def environment(self):
+        """gsb_environment record (type 0 = none); the texel pointer belongs to this Scene."""
+        e = N.Environment()
+        N.host.gsbh_scene_environment(self._h, C.byref(e))
+        return e
+
     def mesh_name(self, i):
         return N.host.gsbh_scene_mesh_name(self._h, i).decode()
 
@@ -201,6 +208,10 @@ class Context:
             _check(N.core.gsb_mesh_create_uv(self._c, _fp(p), _fp(q), _fp(t), len(p), C.byref(out)), "gsb_mesh_create_uv")
         return out.value
 
+    def set_environment(self, env=None):
+        """env: _native.Environment record or None (no environment emitter)."""
+        _check(N.core.gsb_scene_set_environment(self._c, C.byref(env) if env is not None else None), "gsb_scene_set_environment")
+
     def set_textures(self, textures, count):
         _check(N.core.gsb_scene_set_textures(self._c, textures, count), "gsb_scene_set_textures")
 
@@ -247,6 +258,7 @@ class Context:
         if hasattr(scene, "textures"):
             tex, nt = scene.textures
             self.set_textures(tex, nt)
+        self.set_environment(scene.environment if hasattr(scene, "environment") else None)
         for t in range(N.BSDF_TYPE_COUNT):
             raw, n = scene.bsdfs(t)
             self.set_bsdfs(t, raw, n)

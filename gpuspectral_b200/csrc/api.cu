@@ -394,6 +394,7 @@ SceneDev gsb_context::sceneDev() const {
     sc.numLights = numLights;
     sc.textures = dTextures;
     sc.numTextures = numTextures;
+    sc.env = env;
     sc.numInstances = (uint32_t)instances.size();
     memcpy(sc.eye, eye, sizeof(eye));
     memcpy(sc.view, view, sizeof(view));
@@ -410,6 +411,44 @@ SceneDev gsb_context::sceneDev() const {
         sc.sortScale[a] = (float)(1u << sortBits) / (hi - lo);
     }
     return sc;
+}
+
+// Sampling tables of a latitude-longitude environment (shared rule with the checker): per row the running sum of the texel
+// luminances (Rec. 709 weights, after the per-channel scale), normalised; over the rows the running sum of
+// row total x sin(theta at the row centre), normalised.  Accumulated in double, stored as float.
+static void buildEnvironmentTables(const gsb_environment& e, std::vector<float>& rowCdf, std::vector<float>& colCdf) {
+    const uint32_t W = e.width, H = e.height;
+    rowCdf.assign((size_t)H + 1, 0.0f);
+    colCdf.assign((size_t)H * (W + 1), 0.0f);
+    std::vector<double> rowW(H);
+    double total = 0.0;
+    for (uint32_t y = 0; y < H; y++) {
+        std::vector<double> c((size_t)W + 1, 0.0);
+        for (uint32_t x = 0; x < W; x++) {
+            const float* p = e.texels + 3 * ((size_t)y * W + x);
+            const double lum = 0.2126 * (double)(p[0] * e.scale[0]) + 0.7152 * (double)(p[1] * e.scale[1]) + 0.0722 * (double)(p[2] * e.scale[2]);
+            c[x + 1] = c[x] + (lum > 0.0 ? lum : 0.0);
+        }
+        for (uint32_t x = 0; x <= W; x++) colCdf[(size_t)y * (W + 1) + x] = (float)(c[W] > 0.0 ? c[x] / c[W] : (double)x / W);
+        colCdf[(size_t)y * (W + 1) + W] = 1.0f;
+        rowW[y] = c[W] * std::sin(3.14159265358979323846 * (y + 0.5) / H);
+        total += rowW[y];
+    }
+    double acc = 0.0;
+    for (uint32_t y = 0; y < H; y++) {
+        acc += rowW[y];
+        rowCdf[y + 1] = (float)(total > 0.0 ? acc / total : (double)(y + 1) / H);
+    }
+    rowCdf[H] = 1.0f;
+}
+
+static void freeEnvironment(gsb_context* ctx) {
+    cudaFree(ctx->dEnvTexels);
+    cudaFree(ctx->dEnvRowCdf);
+    cudaFree(ctx->dEnvColCdf);
+    ctx->dEnvTexels = nullptr;
+    ctx->dEnvRowCdf = ctx->dEnvColCdf = nullptr;
+    memset(&ctx->env, 0, sizeof(ctx->env));
 }
 
 static void freeTextures(gsb_context* ctx) {
@@ -497,6 +536,7 @@ gsb_status gsb_destroy(gsb_context* ctx) {
         cudaFree(ctx->dWorldNrm);
         cudaFree(ctx->dNrmSoup);
         freeTextures(ctx);
+        freeEnvironment(ctx);
         cudaFree(ctx->dInstSmall);
         cudaFree(ctx->dShade);
         cudaFree(ctx->dInstBsdf);
@@ -512,6 +552,38 @@ gsb_status gsb_destroy(gsb_context* ctx) {
 
 gsb_status gsb_mesh_create(gsb_context* ctx, const float* positions3, const float* normals3, uint32_t nverts, uint32_t* out_mesh) {
     return gsb_mesh_create_uv(ctx, positions3, normals3, nullptr, nverts, out_mesh);
+}
+
+gsb_status gsb_scene_set_environment(gsb_context* ctx, const gsb_environment* env) {
+    if (!ctx) return fail(GSB_ERR_INVALID, "gsb_scene_set_environment: null context");
+    if (env && env->type > GSB_ENVIRONMENT_LATLONG) return fail(GSB_ERR_INVALID, "gsb_scene_set_environment: unknown environment type");
+    if (env && env->type == GSB_ENVIRONMENT_LATLONG && (!env->texels || env->width == 0 || env->height == 0))
+        return fail(GSB_ERR_INVALID, "gsb_scene_set_environment: the latitude-longitude image has no texels");
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        drain(ctx);
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        freeEnvironment(ctx);
+        if (!env || env->type == GSB_ENVIRONMENT_NONE) return GSB_OK;
+        EnvDev& d = ctx->env;
+        d.type = env->type; d.width = env->width; d.height = env->height;
+        for (int k = 0; k < 3; k++) d.scale[k] = env->scale[k];
+        for (int k = 0; k < 9; k++) d.rot[k] = env->to_world[k];
+        d.distance = 1.0e5f;
+        if (env->type == GSB_ENVIRONMENT_LATLONG) {
+            const size_t n = (size_t)env->width * env->height;
+            std::vector<float4> px(n);
+            for (size_t k = 0; k < n; k++) px[k] = make_float4(env->texels[3 * k], env->texels[3 * k + 1], env->texels[3 * k + 2], 0.0f);
+            std::vector<float> rowCdf, colCdf;
+            buildEnvironmentTables(*env, rowCdf, colCdf);
+            ctx->dEnvTexels = uploadArray(px.data(), n, ctx->stream);
+            ctx->dEnvRowCdf = uploadArray(rowCdf.data(), rowCdf.size(), ctx->stream);
+            ctx->dEnvColCdf = uploadArray(colCdf.data(), colCdf.size(), ctx->stream);
+            GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+            d.texels = ctx->dEnvTexels; d.rowCdf = ctx->dEnvRowCdf; d.colCdf = ctx->dEnvColCdf;
+        }
+        return GSB_OK;
+    });
 }
 
 gsb_status gsb_scene_set_textures(gsb_context* ctx, const gsb_texture* textures, uint32_t count) {

@@ -558,11 +558,67 @@ struct LightOutput {
 };
 
 // sampleLight + sampleTrangleLight.  One raw draw picks the light, two uniform draws the point.
+// ---- environment emitter (extension; gsb_environment in the public header) ----------------------------------------------
+GSB_D float3 envRotate(const float* R, float3 d) {
+    return f3(R[0] * d.x + R[1] * d.y + R[2] * d.z, R[3] * d.x + R[4] * d.y + R[5] * d.z, R[6] * d.x + R[7] * d.y + R[8] * d.z);
+}
+GSB_D float3 envRotateInv(const float* R, float3 d) {
+    return f3(R[0] * d.x + R[3] * d.y + R[6] * d.z, R[1] * d.x + R[4] * d.y + R[7] * d.z, R[2] * d.x + R[5] * d.y + R[8] * d.z);
+}
+// radiance arriving from world direction d
+GSB_D float3 envRadiance(const EnvDev& e, float3 d) {
+    const float3 sc = f3(e.scale[0], e.scale[1], e.scale[2]);
+    if (e.type == GSB_ENVIRONMENT_CONSTANT) return sc;
+    const float3 l = envRotateInv(e.rot, d);
+    const float th = acosf(fminf(fmaxf(l.y, -1.0f), 1.0f));
+    const float ph = atan2f(l.x, -l.z);
+    const float u = ph * (0.5f / GSB_PI) + 0.5f, v = th * (1.0f / GSB_PI);
+    const int x = min((int)(u * (float)e.width), (int)e.width - 1), y = min((int)(v * (float)e.height), (int)e.height - 1);
+    return xyz(__ldg(e.texels + (size_t)max(y, 0) * e.width + max(x, 0))) * sc;
+}
+// largest i in [0, n) with cdf[i] <= x
+GSB_D int envSearch(const float* cdf, int n, float x) {
+    int lo = 0, hi = n;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(cdf + mid) <= x) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+// direction towards the environment for two uniform draws, its radiance and solid-angle density
+GSB_D float3 envSample(const EnvDev& e, float e1, float e2, float3& radiance, float& pdf) {
+    if (e.type == GSB_ENVIRONMENT_CONSTANT) {
+        const float z = 1.0f - 2.0f * e1, r = sqrtf(fmaxf(0.0f, 1.0f - z * z)), ph = 2.0f * GSB_PI * e2;
+        radiance = f3(e.scale[0], e.scale[1], e.scale[2]);
+        pdf = 1.0f / (4.0f * GSB_PI);
+        return f3(r * cosf(ph), z, r * sinf(ph));
+    }
+    const int W = (int)e.width, H = (int)e.height;
+    const float a = fminf(e1, 0.99999994f), b = fminf(e2, 0.99999994f);
+    const int y = envSearch(e.rowCdf, H, a);
+    const float r0 = __ldg(e.rowCdf + y), r1 = __ldg(e.rowCdf + y + 1);
+    const float* cc = e.colCdf + (size_t)y * (W + 1);
+    const int x = envSearch(cc, W, b);
+    const float c0 = __ldg(cc + x), c1 = __ldg(cc + x + 1);
+    const float fv = r1 > r0 ? (a - r0) / (r1 - r0) : 0.5f, fu = c1 > c0 ? (b - c0) / (c1 - c0) : 0.5f;
+    const float u = ((float)x + fu) / (float)W, v = ((float)y + fv) / (float)H;
+    const float th = v * GSB_PI, ph = (u - 0.5f) * (2.0f * GSB_PI);
+    const float st = sinf(th);
+    const float3 l = f3(st * sinf(ph), cosf(th), -st * cosf(ph));
+    radiance = xyz(__ldg(e.texels + (size_t)y * W + x)) * f3(e.scale[0], e.scale[1], e.scale[2]);
+    pdf = st > 0.0f ? (r1 - r0) * (c1 - c0) * (float)W * (float)H / (2.0f * GSB_PI * GSB_PI * st) : 0.0f;
+    return envRotate(e.rot, l);
+}
+
 // numLights == 0 (a modulo by zero in the shader) is defined as: the three draws are still
 // consumed, pdf = 0, no emission, `haveLight` false (no shadow ray is cast).
+// EXT = false compiles the reference's light set only (scenes without an environment emitter pay nothing for the extension).
+template <bool EXT = true>
 GSB_D LightOutput sampleLight(const SceneDev& sc, uint32_t& rng, float3 pos, bool& haveLight) {
     LightOutput res;
-    if (sc.numLights == 0) {
+    // the environment emitter (extension) counts as one more light behind the triangle lights
+    const uint32_t numLights = sc.numLights + ((EXT && sc.env.type) ? 1u : 0u);
+    if (numLights == 0) {
         randPcg(rng); randPcg(rng); randPcg(rng);
         haveLight = false;
         res.position = pos + f3(0.0f, 1.0f, 0.0f);
@@ -571,7 +627,15 @@ GSB_D LightOutput sampleLight(const SceneDev& sc, uint32_t& rng, float3 pos, boo
         return res;
     }
     haveLight = true;
-    const uint32_t lightIdx = randPcg(rng) % sc.numLights;
+    const uint32_t lightIdx = randPcg(rng) % numLights;
+    if (EXT && lightIdx == sc.numLights) {
+        const float e1 = randUniform(rng);
+        const float e2 = randUniform(rng);
+        const float3 d = envSample(sc.env, e1, e2, res.emission, res.pdf);
+        res.position = pos + d * sc.env.distance;
+        res.pdf *= 1.0f / (float)numLights;
+        return res;
+    }
     const float4* lp = reinterpret_cast<const float4*>(sc.lights + lightIdx);
     const float4 p0 = __ldg(lp), p1 = __ldg(lp + 1), p2 = __ldg(lp + 2), rad = __ldg(lp + 3);
     const float e1 = randUniform(rng);
@@ -588,7 +652,7 @@ GSB_D LightOutput sampleLight(const SceneDev& sc, uint32_t& rng, float3 pos, boo
     res.position = lightPos;
     res.emission = xyz(rad) * (dot(-l, normal) > 0.0f ? 1.0f : 0.0f);
     res.pdf = ldist * ldist / (fabsf(dot(-l, normal)) * A);
-    res.pdf *= 1.0f / (float)sc.numLights;
+    res.pdf *= 1.0f / (float)numLights;
     return res;
 }
 

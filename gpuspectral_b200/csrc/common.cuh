@@ -121,6 +121,20 @@ struct TextureDev {
 };
 static_assert(sizeof(TextureDev) == 80, "TextureDev layout");
 
+// Environment emitter on the device: texels (float4) + the sampling tables built by buildEnvironmentTables (api.cu):
+// rowCdf[h + 1] over rows (weight = sum of the row's luminances x sin(theta) at the row centre), colCdf[h][w + 1] per row.
+struct EnvDev {
+    uint32_t type, width, height, pad;
+    float scale[3];
+    float distance;          // how far away a sampled point of the environment is placed (beyond the scene)
+    float rot[9];            // local -> world
+    float pad2[3];
+    const float4* texels;
+    const float* rowCdf;
+    const float* colCdf;
+    uint64_t pad3;
+};
+
 // Everything the kernels need to know about the scene; passed by value as a kernel parameter.
 struct SceneDev {
     const uint4* worldNodes;         // world level: 8-wide nodes over the triangles of all baked instances (world space)
@@ -134,6 +148,7 @@ struct SceneDev {
     const void* bsdf[GSB_BSDF_TYPE_COUNT];
     const gsb_triangle_light* lights;
     const TextureDev* textures;      // reflectance textures (diffuse records refer to them by hasTexture - 1)
+    EnvDev env;                      // environment emitter (type 0 = none)
     uint32_t numLights;
     uint32_t numInstances;
     uint32_t numTextures;

@@ -92,6 +92,10 @@ struct gsb_context {
     bool typeUsed[GSB_BSDF_TYPE_COUNT] = {};
     gsb_triangle_light* dLights = nullptr;
     uint32_t numLights = 0;
+    gsb::EnvDev env = {};                  // environment emitter; its device arrays:
+    float4* dEnvTexels = nullptr;
+    float* dEnvRowCdf = nullptr;
+    float* dEnvColCdf = nullptr;
     gsb::TextureDev* dTextures = nullptr;
     std::vector<float4*> textureTexels;   // device texel arrays owned by the table
     uint32_t numTextures = 0;

@@ -291,6 +291,22 @@ struct ExtendSource {
     GSB_D void commit(bool have, const HitRecord& hit, uint32_t slot, uint32_t) {
         if (!have) return;
         wf.hitInst[slot] = hit.inst;
+        if (hit.inst == GSB_NO_HIT && sc.env.type) {
+            // the ray left the scene: radiance of the environment emitter (extension), weighted like a surface emitter
+            // that a BSDF sample reaches (rayhit.rchit:760-768) and subject to the per-bounce cutoff (raygen.rgen:60-63)
+            const float4 rd = *rayDirection(wf, slot);
+            const uint32_t flags = __float_as_uint(rd.w);
+            float4 wdw = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+            if ((flags & 0xffffu) != 0u) wdw = wf.weightDW[slot];
+            const bool plain = !sc.params.nee || (flags & kFlagCountEmitted) || (flags & kFlagWasDelta);
+            const float3 e = envRadiance(sc.env, xyz(rd)) * xyz(wdw) * (plain ? 1.0f : wdw.w);
+            const float cutoff = sc.params.cutoff;
+            if ((e.x != 0.0f || e.y != 0.0f || e.z != 0.0f) && e.x < cutoff && e.y < cutoff && e.z < cutoff) {
+                float4 res = wf.result[slot];
+                res.x += e.x; res.y += e.y; res.z += e.z;
+                wf.result[slot] = res;
+            }
+        }
         // a baked hit is shaded from the world level's own records: it carries its leaf position instead of gl_PrimitiveID
         if (hit.inst != GSB_NO_HIT) wf.hitTUVP[slot] = make_float4(hit.t, hit.u, hit.v, __uint_as_float((hit.inst & kInstBaked) ? hit.leaf : hit.prim));
     }
@@ -334,7 +350,9 @@ GSB_D void cpAsyncWait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "me
 // hit carries a BSDF of this kernel's TYPE.  A tile with at least directMin matching lanes is shaded as it is — the
 // path-state streams are then read and written coalesced; sparser tiles are compacted through a 64-entry per-warp
 // buffer in shared memory and shaded 32 at a time (entries wait there across in-place tiles).
-template <int TYPE, bool HASINST>
+// EXT: the scene uses an extension that shading has to know about (reflectance textures, environment emitter); the plain
+// instantiation carries none of that code (r2m: the texture branch alone cost the diffuse kernel 11 % when compiled in).
+template <int TYPE, bool HASINST, bool EXT>
 __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFUSE : GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t slots, uint32_t directMin) {
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
     __shared__ uint32_t s_buf[kBlock / 32][64];
@@ -488,7 +506,7 @@ __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFU
             wi = onbUntransform(onb, wi);                                            // :718
 
             bool haveLight;
-            const LightOutput lightRes = sampleLight(sc, rng, position, haveLight);  // :720
+            const LightOutput lightRes = sampleLight<EXT>(sc, rng, position, haveLight);  // :720
             const float3 L = normalize(lightRes.position - position);                // :722
             const float3 wL = onbTransform(onb, L);                                  // :723
             const float Ldist = length(lightRes.position - position);                // :724
@@ -497,7 +515,7 @@ __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFU
             BSDFOutput lightBsdfRes;
             lightBsdfRes.bsdf = f3(0.0f); lightBsdfRes.pdf = 0.0f; lightBsdfRes.isDelta = false;
             evalBSDFT<TYPE>(sc, handle & 0xffffu, wo, wL, lightBsdfRes);             // :729
-            if (TYPE == GSB_BSDF_DIFFUSE) {
+            if (EXT && TYPE == GSB_BSDF_DIFFUSE) {
                 // textured reflectance (extension): the diffuse value kD / pi with kD looked up at the hit's texture coordinate.
                 // A slow path taken by textured records only: the coordinates ride in the .w of the mesh's vertex arrays.
                 const int tex = ((const gsb_diffuse_bsdf*)sc.bsdf[GSB_BSDF_DIFFUSE])[handle & 0xffffu].hasTexture;
@@ -735,8 +753,14 @@ void allocWavefront(gsb_context* ctx, uint32_t slots, bool sorting) {
 
 template <int TYPE>
 void launchShade(gsb_context* ctx, const SceneDev& sc, int grid, uint32_t parity, uint32_t slots) {
-    if (ctx->numTraceInstances > 0) k_shade<TYPE, true><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots, ctx->shadeDirectMin);
-    else k_shade<TYPE, false><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots, ctx->shadeDirectMin);
+    const bool ext = ctx->numTextures > 0 || ctx->env.type != 0;
+    if (ctx->numTraceInstances > 0) {
+        if (ext) k_shade<TYPE, true, true><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots, ctx->shadeDirectMin);
+        else k_shade<TYPE, true, false><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots, ctx->shadeDirectMin);
+    } else {
+        if (ext) k_shade<TYPE, false, true><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots, ctx->shadeDirectMin);
+        else k_shade<TYPE, false, false><<<grid, kBlock, 0, ctx->stream>>>(sc, ctx->wf, parity, slots, ctx->shadeDirectMin);
+    }
 }
 
 }  // namespace

@@ -57,6 +57,7 @@ gsbh_scene* gsbh_scene_builtin(const char* name, const int* params, int nparams)
         const std::string n = name ? name : "";
         auto par = [&](int i, int def) { return (params && i < nparams) ? params[i] : def; };
         if (n == "cornell") s = new gsbh_scene{gsbhost::makeCornellBox()};
+        else if (n == "field_env") s = new gsbh_scene{gsbhost::makeFieldUnderSky((uint32_t)par(0, 1234), par(1, 3), par(2, 3), par(3, 3))};
         else if (n == "cornell_textured") s = new gsbh_scene{gsbhost::makeTexturedCornellBox()};
         else if (n == "gallery") s = new gsbh_scene{gsbhost::makeBsdfGallery()};
         else if (n == "field") s = new gsbh_scene{gsbhost::makeInstancedField((uint32_t)par(0, 1234), par(1, 16), par(2, 7), par(3, 13))};
@@ -75,6 +76,7 @@ const float* gsbh_scene_mesh_uvs(const gsbh_scene* s, uint32_t m) {
     const auto& mesh = s->scene.meshes.at(m);
     return mesh.uvs.size() == (size_t)mesh.vertexCount() * 2 ? mesh.uvs.data() : nullptr;
 }
+void gsbh_scene_environment(const gsbh_scene* s, gsb_environment* out) { *out = s->scene.environmentRecord(); }
 uint32_t gsbh_scene_texture_count(const gsbh_scene* s) { return (uint32_t)s->scene.textures.size(); }
 void gsbh_scene_copy_textures(const gsbh_scene* s, gsb_texture* out) {
     const auto v = s->scene.textureRecords();   // texel pointers stay valid as long as the scene lives

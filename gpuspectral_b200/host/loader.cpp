@@ -420,7 +420,35 @@ Scene buildScene(const XmlNode& root, const std::string& baseDir) {
                     if (c.number(*child, "height", h)) scene.filmHeight = (uint32_t)h;
                 }
         } else if (n->tag == "emitter") {
-            c.warn("scene-level emitter '" + n->attrOr("type", "") + "' ignored (the reference has no environment light)");
+            // extension (Loader.cpp:338-346 holds the envmap branch as commented-out code): Mitsuba's `constant` and `envmap`
+            const std::string et = n->attrOr("type", "");
+            gsb_environment env;
+            std::memset(&env, 0, sizeof(env));
+            env.to_world[0] = env.to_world[4] = env.to_world[8] = 1.0f;
+            env.scale[0] = env.scale[1] = env.scale[2] = 1.0f;
+            if (et == "constant") {
+                env.type = GSB_ENVIRONMENT_CONSTANT;
+                c.color(*n, "radiance", env.scale);
+                scene.environment = env;
+            } else if (et == "envmap") {
+                float sc = 1.0f;
+                c.number(*n, "scale", sc);
+                env.scale[0] = env.scale[1] = env.scale[2] = sc;
+                float M[16];
+                const XmlNode* tw = c.prop(*n, "to_world");
+                parseTransform(c, (tw && tw->tag == "transform") ? tw : nullptr, M);   // column-major; its rotation part
+                for (int r = 0; r < 3; r++)
+                    for (int k = 0; k < 3; k++) env.to_world[3 * r + k] = M[4 * k + r];
+                try {
+                    loadImageLinearRGB(baseDir + "/" + c.str(*n, "filename"), scene.environmentTexels, env.width, env.height);
+                    env.type = GSB_ENVIRONMENT_LATLONG;
+                    scene.environment = env;
+                } catch (const std::exception& e) {
+                    c.warn(std::string("envmap emitter ignored: ") + e.what());
+                }
+            } else {
+                c.warn("scene-level emitter '" + et + "' ignored (constant and envmap are supported)");
+            }
         }
     }
     return scene;

@@ -47,6 +47,10 @@ void PathTracer::uploadScene(const Scene& scene) {
         const std::vector<gsb_texture> tex = scene.textureRecords();
         check(gsb_scene_set_textures(ctx, tex.data(), (uint32_t)tex.size()), "gsb_scene_set_textures");
     }
+    {
+        const gsb_environment env = scene.environmentRecord();
+        check(gsb_scene_set_environment(ctx, &env), "gsb_scene_set_environment");
+    }
     check(gsb_scene_set_lights(ctx, scene.triangleLights.data(), (uint32_t)scene.triangleLights.size()), "gsb_scene_set_lights");
     std::vector<gsb_instance> inst = scene.instanceRecords();
     for (gsb_instance& i : inst) i.mesh = meshHandles.at(i.mesh);

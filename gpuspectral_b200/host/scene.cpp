@@ -567,4 +567,37 @@ Scene makeInstancedField(uint32_t seed, int uniqueMeshes, int subdiv, int gridN)
     return s;
 }
 
+// The instanced field under a procedural sky (environment emitter extension): a 128 x 64 latitude-longitude image — blue
+// gradient above the horizon, dim ground colour below, and a small very bright sun 35 degrees up — rotated a little about the
+// vertical axis.  The quad light of the field stays (dimmed), so light sampling chooses between triangle lights and the sky.
+Scene makeFieldUnderSky(uint32_t seed, int uniqueMeshes, int subdiv, int gridN) {
+    Scene s = makeInstancedField(seed, uniqueMeshes, subdiv, gridN);
+    const uint32_t W = 128, H = 64;
+    s.environmentTexels.resize((size_t)W * H * 3);
+    const float kPi = 3.14159265358979323846f;
+    const float sunTheta = (90.0f - 35.0f) * kPi / 180.0f, sunPhi = 0.6f;
+    for (uint32_t y = 0; y < H; y++)
+        for (uint32_t x = 0; x < W; x++) {
+            const float th = (y + 0.5f) / H * kPi, ph = ((x + 0.5f) / W - 0.5f) * 2.0f * kPi;
+            float* p = &s.environmentTexels[3 * ((size_t)y * W + x)];
+            if (th < 0.5f * kPi) {
+                const float t = th / (0.5f * kPi);
+                p[0] = 0.25f + 0.45f * t; p[1] = 0.45f + 0.35f * t; p[2] = 0.9f;
+            } else {
+                p[0] = 0.12f; p[1] = 0.1f; p[2] = 0.08f;
+            }
+            const float dth = th - sunTheta, dph = std::remainder(ph - sunPhi, 2.0f * kPi) * std::sin(sunTheta);
+            if (dth * dth + dph * dph < 0.05f * 0.05f) { p[0] = 900.0f; p[1] = 800.0f; p[2] = 600.0f; }
+        }
+    std::memset(&s.environment, 0, sizeof(s.environment));
+    s.environment.type = GSB_ENVIRONMENT_LATLONG;
+    s.environment.width = W;
+    s.environment.height = H;
+    s.environment.scale[0] = s.environment.scale[1] = s.environment.scale[2] = 1.0f;
+    const float a = 0.4f, ca = std::cos(a), sa = std::sin(a);
+    const float Rm[9] = {ca, 0, sa, 0, 1, 0, -sa, 0, ca};
+    std::memcpy(s.environment.to_world, Rm, sizeof(Rm));
+    return s;
+}
+
 }  // namespace gsbhost

@@ -66,6 +66,10 @@ struct Scene {
     // reflectance textures (extension): descriptors as the C ABI takes them, texels owned here
     struct TextureData { gsb_texture desc; std::vector<float> texels; };
     std::vector<TextureData> textures;
+    // environment emitter (extension): descriptor as the C ABI takes it, texels owned here; type 0 = none
+    gsb_environment environment = {};
+    std::vector<float> environmentTexels;
+    gsb_environment environmentRecord() const { gsb_environment e = environment; e.texels = environmentTexels.empty() ? nullptr : environmentTexels.data(); return e; }
     uint32_t addTexture(TextureData&& t) { textures.push_back(std::move(t)); return (uint32_t)textures.size() - 1; }
     std::vector<gsb_texture> textureRecords() const {
         std::vector<gsb_texture> out;
@@ -109,6 +113,7 @@ void loadImageLinearRGB(const std::string& path, std::vector<float>& rgb, uint32
 // glTF 2.0 (.gltf / .glb), see gltf.cpp.  Throws std::runtime_error on unreadable input.
 Scene loadGltfScene(const std::string& path);
 
+Scene makeFieldUnderSky(uint32_t seed, int uniqueMeshes, int subdiv, int gridN);   // the instanced field lit by a latitude-longitude sky with a sun (environment extension)
 Scene makeTexturedCornellBox();                 // the Cornell box with a checkerboard floor, a bitmap back wall and a checkerboard tall box (texture extension)
 MeshData makeRectangle();                       // assets/rect.obj equivalent (2 triangles, z = 0, normal +z)
 MeshData makeCube();

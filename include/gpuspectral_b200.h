@@ -163,6 +163,23 @@ typedef struct gsb_texture {
     float uscale, vscale, uoffset, voffset;
 } gsb_texture;
 
+/* Environment emitter (extension: engine/Loader.cpp:338-346 holds `envmap` only as commented-out code; Mitsuba's
+ * `constant` and `envmap` emitters).  Rays that leave the scene gather its radiance — weighted by the path's directWeight
+ * exactly like a surface emitter reached by a BSDF sample (rayhit.rchit:760-768) — and light sampling treats it as one more
+ * light next to the triangle lights: chosen with the same raw draw, its direction drawn with the same two uniform draws.
+ * Bitmap: latitude-longitude image, row 0 = +Y pole, u = atan2(x, -z) / 2 pi + 1/2; piecewise-constant radiance per texel,
+ * importance-sampled proportionally to texel luminance x sin(theta).  to_world: row-major 3x3 rotation, local -> world. */
+#define GSB_ENVIRONMENT_NONE 0u
+#define GSB_ENVIRONMENT_CONSTANT 1u
+#define GSB_ENVIRONMENT_LATLONG 2u
+typedef struct gsb_environment {
+    uint32_t type;
+    uint32_t width, height;   /* latlong only */
+    const float* texels;      /* latlong only: width * height * 3 floats of linear RGB, copied */
+    float scale[3];           /* constant: the radiance; latlong: factor per channel */
+    float to_world[9];
+} gsb_environment;
+
 /* ---- context ------------------------------------------------------------------- */
 GSB_API gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx);
 GSB_API gsb_status gsb_destroy(gsb_context* ctx);
@@ -182,6 +199,8 @@ GSB_API gsb_status gsb_mesh_destroy(gsb_context* ctx, uint32_t mesh);
  * attribute (renderer/Mesh.cpp:7-22,37,50), which the reference uploads and never reads. */
 GSB_API gsb_status gsb_mesh_create_uv(gsb_context* ctx, const float* positions3, const float* normals3, const float* uv2,
                                       uint32_t num_vertices, uint32_t* out_mesh);
+/* Sets (or, with NULL / type NONE, removes) the environment emitter. */
+GSB_API gsb_status gsb_scene_set_environment(gsb_context* ctx, const gsb_environment* env);
 /* Replaces the scene's texture table (may be called before or after gsb_scene_set_instances). */
 GSB_API gsb_status gsb_scene_set_textures(gsb_context* ctx, const gsb_texture* textures, uint32_t count);
 GSB_API gsb_status gsb_scene_set_instances(gsb_context* ctx, const gsb_instance* instances, uint32_t count);

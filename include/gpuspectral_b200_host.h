@@ -37,6 +37,7 @@ GSB_API uint32_t gsbh_scene_mesh_vertex_count(const gsbh_scene* s, uint32_t mesh
 GSB_API const float* gsbh_scene_mesh_positions(const gsbh_scene* s, uint32_t mesh);
 GSB_API const float* gsbh_scene_mesh_normals(const gsbh_scene* s, uint32_t mesh);
 GSB_API const float* gsbh_scene_mesh_uvs(const gsbh_scene* s, uint32_t mesh);   /* 2 floats per vertex, or NULL */
+GSB_API void gsbh_scene_environment(const gsbh_scene* s, gsb_environment* out);  /* type 0 = none; texel pointer belongs to the scene */
 GSB_API uint32_t gsbh_scene_texture_count(const gsbh_scene* s);
 GSB_API void gsbh_scene_copy_textures(const gsbh_scene* s, gsb_texture* out);   /* texel pointers belong to the scene */
 GSB_API const char* gsbh_scene_mesh_name(const gsbh_scene* s, uint32_t mesh);

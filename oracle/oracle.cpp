@@ -199,6 +199,12 @@ struct or_scene {
     // reflectance textures (extension; gsb_texture of the public header with the texels copied)
     struct Texture { gsb_texture desc; std::vector<float> texels; };
     std::vector<Texture> textures;
+    // environment emitter (extension; gsb_environment of the public header with the texels copied and the sampling tables)
+    struct Environment {
+        gsb_environment desc = {};
+        std::vector<float> texels, rowCdf, colCdf;
+        float distance = 1.0e5f;
+    } env;
     float eye[3] = {0, 0, 0};
     float view[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
     float fov = 1.0f;
@@ -1019,10 +1025,61 @@ LightOutput sampleTriangleLight(const gsb_triangle_light& light, Rng& rng, vec3 
     return res;
 }
 
+// ---- environment emitter (extension, no reference source: engine/Loader.cpp:338-346 holds it as commented-out code) ----
+inline vec3 envRotate(const float* R, vec3 d) {
+    return vec3(R[0] * d.x + R[1] * d.y + R[2] * d.z, R[3] * d.x + R[4] * d.y + R[5] * d.z, R[6] * d.x + R[7] * d.y + R[8] * d.z);
+}
+inline vec3 envRotateInv(const float* R, vec3 d) {
+    return vec3(R[0] * d.x + R[3] * d.y + R[6] * d.z, R[1] * d.x + R[4] * d.y + R[7] * d.z, R[2] * d.x + R[5] * d.y + R[8] * d.z);
+}
+vec3 envRadiance(const or_scene::Environment& e, vec3 d) {
+    const vec3 sc = v3(e.desc.scale);
+    if (e.desc.type == GSB_ENVIRONMENT_CONSTANT) return sc;
+    const vec3 l = envRotateInv(e.desc.to_world, d);
+    const float th = std::acos(std::fmin(std::fmax(l.y, -1.0f), 1.0f));
+    const float ph = std::atan2(l.x, -l.z);
+    const float u = ph * (0.5f / kPi) + 0.5f, v = th * (1.0f / kPi);
+    const int W = (int)e.desc.width, H = (int)e.desc.height;
+    const int x = std::max(std::min((int)(u * (float)W), W - 1), 0), y = std::max(std::min((int)(v * (float)H), H - 1), 0);
+    return v3(&e.texels[3 * ((size_t)y * W + x)]) * sc;
+}
+inline int envSearch(const float* cdf, int n, float x) {   // largest i in [0, n) with cdf[i] <= x
+    int lo = 0, hi = n;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (cdf[mid] <= x) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+vec3 envSample(const or_scene::Environment& e, float e1, float e2, vec3& radiance, float& pdf) {
+    if (e.desc.type == GSB_ENVIRONMENT_CONSTANT) {
+        const float z = 1.0f - 2.0f * e1, r = std::sqrt(std::fmax(0.0f, 1.0f - z * z)), ph = 2.0f * kPi * e2;
+        radiance = v3(e.desc.scale);
+        pdf = 1.0f / (4.0f * kPi);
+        return vec3(r * std::cos(ph), z, r * std::sin(ph));
+    }
+    const int W = (int)e.desc.width, H = (int)e.desc.height;
+    const float a = std::fmin(e1, 0.99999994f), b = std::fmin(e2, 0.99999994f);
+    const int y = envSearch(e.rowCdf.data(), H, a);
+    const float r0 = e.rowCdf[y], r1 = e.rowCdf[y + 1];
+    const float* cc = &e.colCdf[(size_t)y * (W + 1)];
+    const int x = envSearch(cc, W, b);
+    const float c0 = cc[x], c1 = cc[x + 1];
+    const float fv = r1 > r0 ? (a - r0) / (r1 - r0) : 0.5f, fu = c1 > c0 ? (b - c0) / (c1 - c0) : 0.5f;
+    const float u = ((float)x + fu) / (float)W, v = ((float)y + fv) / (float)H;
+    const float th = v * kPi, ph = (u - 0.5f) * (2.0f * kPi);
+    const float st = std::sin(th);
+    const vec3 l(st * std::sin(ph), std::cos(th), -st * std::cos(ph));
+    radiance = v3(&e.texels[3 * ((size_t)y * W + x)]) * v3(e.desc.scale);
+    pdf = st > 0.0f ? (r1 - r0) * (c1 - c0) * (float)W * (float)H / (2.0f * kPi * kPi * st) : 0.0f;
+    return envRotate(e.desc.to_world, l);
+}
+
 // sampleLight, :147-153.  numLights == 0 is a division by zero in the shader; the oracle
 // defines it as: the three draws are still consumed, pdf = 0, no emission.
 LightOutput sampleLight(const or_scene& s, Rng& rng, vec3 pos, bool& haveLight) {
-    const uint32_t numLights = (uint32_t)s.lights.size();
+    // the environment emitter (extension) counts as one more light behind the triangle lights
+    const uint32_t numLights = (uint32_t)s.lights.size() + (s.env.desc.type ? 1u : 0u);
     if (numLights == 0) {
         rng.randPcg(); rng.randPcg(); rng.randPcg();
         haveLight = false;
@@ -1034,6 +1091,15 @@ LightOutput sampleLight(const or_scene& s, Rng& rng, vec3 pos, bool& haveLight) 
     }
     haveLight = true;
     uint32_t lightIdx = rng.randPcg() % numLights;
+    if (lightIdx == s.lights.size()) {
+        LightOutput res;
+        const float e1 = rng.randUniform();
+        const float e2 = rng.randUniform();
+        const vec3 d = envSample(s.env, e1, e2, res.emission, res.pdf);
+        res.position = pos + d * s.env.distance;
+        res.pdf *= 1.0f / (float)numLights;
+        return res;
+    }
     LightOutput res = sampleTriangleLight(s.lights[lightIdx], rng, pos);
     res.pdf *= 1.0f / (float)numLights;
     return res;
@@ -1245,7 +1311,14 @@ vec3 pathSample(const or_scene& s, uint32_t W, uint32_t H, uint32_t x, uint32_t 
         st.ext++;
         or_bounce* rec = (bounces && nb < maxBounces) ? &bounces[nb] : nullptr;
         if (rec) { std::memset(rec, 0, sizeof(*rec)); rec->inst = hit.inst; rec->prim = hit.prim; rec->t = hit.t; }
-        if (hit.inst == GSB_NO_HIT) prd.done = 1;                      // miss.rmiss:15-18
+        if (hit.inst == GSB_NO_HIT) {
+            prd.done = 1;                                              // miss.rmiss:15-18
+            if (s.env.desc.type) {
+                // environment emitter (extension): weighted like a surface emitter a BSDF sample reaches, :760-768
+                const bool plain = !s.params.nee || prd.countEmitted != 0 || prd.wasDelta != 0;
+                prd.emitted = envRadiance(s.env, prd.direction) * prd.weight * (plain ? 1.0f : prd.directWeight);
+            }
+        }
         else closestHit(s, hit, prd, st, rec);
         if (rec) {
             rec->emitted[0] = prd.emitted.x; rec->emitted[1] = prd.emitted.y; rec->emitted[2] = prd.emitted.z;
@@ -1357,6 +1430,60 @@ void or_scene_destroy(or_scene* s) { delete s; }
 
 uint32_t or_scene_add_mesh(or_scene* s, const float* positions3, const float* normals3, uint32_t nverts) {
     return or_scene_add_mesh_uv(s, positions3, normals3, nullptr, nverts);
+}
+
+int or_scene_set_environment(or_scene* s, const gsb_environment* env) {
+    s->env = or_scene::Environment();
+    if (!env || env->type == GSB_ENVIRONMENT_NONE) return 0;
+    s->env.desc = *env;
+    s->env.desc.texels = nullptr;
+    if (env->type != GSB_ENVIRONMENT_LATLONG) return 0;
+    if (!env->texels || !env->width || !env->height) return 1;
+    const uint32_t W = env->width, H = env->height;
+    s->env.texels.assign(env->texels, env->texels + (size_t)W * H * 3);
+    // the sampling tables, by the rule stated at buildEnvironmentTables (gpuspectral_b200/csrc/api.cu): double sums, float tables
+    s->env.rowCdf.assign((size_t)H + 1, 0.0f);
+    s->env.colCdf.assign((size_t)H * (W + 1), 0.0f);
+    std::vector<double> rowW(H);
+    double total = 0.0;
+    for (uint32_t y = 0; y < H; y++) {
+        std::vector<double> c((size_t)W + 1, 0.0);
+        for (uint32_t x = 0; x < W; x++) {
+            const float* p = env->texels + 3 * ((size_t)y * W + x);
+            const double lum = 0.2126 * (double)(p[0] * env->scale[0]) + 0.7152 * (double)(p[1] * env->scale[1]) + 0.0722 * (double)(p[2] * env->scale[2]);
+            c[x + 1] = c[x] + (lum > 0.0 ? lum : 0.0);
+        }
+        for (uint32_t x = 0; x <= W; x++) s->env.colCdf[(size_t)y * (W + 1) + x] = (float)(c[W] > 0.0 ? c[x] / c[W] : (double)x / W);
+        s->env.colCdf[(size_t)y * (W + 1) + W] = 1.0f;
+        rowW[y] = c[W] * std::sin(3.14159265358979323846 * (y + 0.5) / H);
+        total += rowW[y];
+    }
+    double acc = 0.0;
+    for (uint32_t y = 0; y < H; y++) {
+        acc += rowW[y];
+        s->env.rowCdf[y + 1] = (float)(total > 0.0 ? acc / total : (double)(y + 1) / H);
+    }
+    s->env.rowCdf[H] = 1.0f;
+    return 0;
+}
+
+// probes of the environment emitter: direction / radiance / solid-angle density for pairs of uniform numbers, and the
+// radiance looked up for given directions
+void or_env_sample(const or_scene* s, const float* e1, const float* e2, uint32_t n, float* dirs3, float* radiance3, float* pdf) {
+    for (uint32_t i = 0; i < n; i++) {
+        vec3 rad;
+        float p = 0.0f;
+        const vec3 d = envSample(s->env, e1[i], e2[i], rad, p);
+        dirs3[3 * i] = d.x; dirs3[3 * i + 1] = d.y; dirs3[3 * i + 2] = d.z;
+        radiance3[3 * i] = rad.x; radiance3[3 * i + 1] = rad.y; radiance3[3 * i + 2] = rad.z;
+        pdf[i] = p;
+    }
+}
+void or_env_radiance(const or_scene* s, const float* dirs3, uint32_t n, float* radiance3) {
+    for (uint32_t i = 0; i < n; i++) {
+        const vec3 r = envRadiance(s->env, vec3(dirs3[3 * i], dirs3[3 * i + 1], dirs3[3 * i + 2]));
+        radiance3[3 * i] = r.x; radiance3[3 * i + 1] = r.y; radiance3[3 * i + 2] = r.z;
+    }
 }
 
 int or_scene_set_textures(or_scene* s, const gsb_texture* textures, uint32_t count) {

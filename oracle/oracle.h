@@ -44,6 +44,9 @@ uint32_t or_scene_add_mesh(or_scene* s, const float* positions3, const float* no
 /* texture extension: texture coordinates per vertex (NULL = zero) and the texture table, as gsb_mesh_create_uv / gsb_scene_set_textures */
 uint32_t or_scene_add_mesh_uv(or_scene* s, const float* positions3, const float* normals3, const float* uv2, uint32_t nverts);
 int or_scene_set_textures(or_scene* s, const gsb_texture* textures, uint32_t count);
+int or_scene_set_environment(or_scene* s, const gsb_environment* env);   /* NULL / type 0 removes it */
+void or_env_sample(const or_scene* s, const float* e1, const float* e2, uint32_t n, float* dirs3, float* radiance3, float* pdf);
+void or_env_radiance(const or_scene* s, const float* dirs3, uint32_t n, float* radiance3);
 int or_scene_set_instances(or_scene* s, const gsb_instance* instances, uint32_t count);
 /* number of instances whose triangles are stored in world space (the bake rule of oracle.cpp: kBakeMaxTris / kBakeBudget) */
 uint32_t or_scene_baked_instances(const or_scene* s);

@@ -53,6 +53,9 @@ def lib():
             "or_scene_add_mesh": (C.c_uint32, [P, f32p, f32p, C.c_uint32]),
             "or_scene_add_mesh_uv": (C.c_uint32, [P, f32p, f32p, f32p, C.c_uint32]),
             "or_scene_set_textures": (C.c_int, [P, P, C.c_uint32]),
+            "or_scene_set_environment": (C.c_int, [P, P]),
+            "or_env_sample": (None, [P, f32p, f32p, C.c_uint32, f32p, f32p, f32p]),
+            "or_env_radiance": (None, [P, f32p, C.c_uint32, f32p]),
             "or_scene_set_instances": (C.c_int, [P, P, C.c_uint32]),
             "or_scene_set_bsdfs": (C.c_int, [P, C.c_uint32, P, C.c_uint32]),
             "or_scene_set_lights": (C.c_int, [P, P, C.c_uint32]),
@@ -109,6 +112,8 @@ class OracleScene:
         if hasattr(scene, "textures"):
             tex, nt = scene.textures
             o.set_textures(tex, nt)
+        if hasattr(scene, "environment"):
+            o.set_environment(scene.environment)
         for t in range(9):   # 8 reference types + the rough dielectric extension
             raw, n = scene.bsdfs(t)
             o.set_bsdfs(t, raw, n)
@@ -164,6 +169,24 @@ class OracleScene:
             return lib().or_scene_add_mesh(self._s, _fp(p), _fp(q), len(p))
         t = np.ascontiguousarray(uv, np.float32).reshape(-1, 2)
         return lib().or_scene_add_mesh_uv(self._s, _fp(p), _fp(q), _fp(t), len(p))
+
+    def set_environment(self, env=None):
+        """env: ctypes gsb_environment record (gpuspectral_b200._native.Environment layout) or None."""
+        if lib().or_scene_set_environment(self._s, C.cast(C.pointer(env), C.c_void_p) if env is not None else None) != 0:
+            raise ValueError("oracle: the environment image has no texels")
+
+    def env_sample(self, e1, e2):
+        e1, e2 = np.ascontiguousarray(e1, np.float32), np.ascontiguousarray(e2, np.float32)
+        n = len(e1)
+        d, r, p = np.zeros((n, 3), np.float32), np.zeros((n, 3), np.float32), np.zeros(n, np.float32)
+        lib().or_env_sample(self._s, _fp(e1), _fp(e2), n, _fp(d), _fp(r), _fp(p))
+        return d, r, p
+
+    def env_radiance(self, dirs):
+        dirs = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+        out = np.zeros((len(dirs), 3), np.float32)
+        lib().or_env_radiance(self._s, _fp(dirs), len(dirs), _fp(out))
+        return out
 
     def set_textures(self, textures, count):
         """textures: ctypes array of gsb_texture records (gpuspectral_b200._native.Texture layout)."""
