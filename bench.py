@@ -301,6 +301,20 @@ def traversal_roofline(bvh, peaks, ext_fetch, sh_fetch, stage, iters, ext_rays, 
     return roof, shade
 
 
+def build_roofline(bvh, peaks):
+    """BVH build against the HBM roofline: per unique triangle 48 B of vertices in, 144 B of leaf records
+    out, ~10 B of 8-wide nodes, and the (key, index) radix sort's four passes over 12 B in + 12 B out; build_ms is the
+    device-event time of all BLAS + TLAS builds of the scene, host synchronisation between levels included."""
+    tris = bvh.get("unique_triangles", 0) + bvh.get("baked_triangles", 0)
+    ms = bvh.get("build_ms", 0.0)
+    if not tris or ms <= 0:
+        return None
+    nbytes = tris * (48 + 144 + 10 + 4 * 24)
+    gbs = nbytes / (ms * 1e-3) / 1e9
+    return {"bound": "hbm", "bytes_per_triangle": 298, "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s", "frac": gbs / peaks["hbm"],
+            "mtris_per_s": tris / (ms * 1e-3) / 1e6}
+
+
 def short_run(g, torch, dev, stream, name, scene, W, H, S, max_depth, peaks, steps=2, warmup=2):
     """A short driver-run measurement of another BASELINE.json configuration on this GPU: value, stage times, fetch counts,
     roofline fractions (same method as the main line, fewer steps; no e2e / CPU legs)."""
@@ -345,7 +359,7 @@ def short_run(g, torch, dev, stream, name, scene, W, H, S, max_depth, peaks, ste
             "ms_per_step": ms / steps, "stage_ms_per_step": stage, "image_ok": ok, "setup_s": t_build,
             "rays_per_path": {"extension": c["extension_rays"] / c["paths"], "shadow": c["shadow_rays"] / c["paths"]},
             "roofline": {k: roof[k] for k in ("bound", "achieved", "peak", "frac", "frac_of_hbm_peak", "frac_of_l2_peak", "bytes_per_ray", "fetch_per_ray", "ms_per_launch")},
-            "shade_gbs": shade["achieved_gbs"], "bvh": bvh}
+            "shade_gbs": shade["achieved_gbs"], "bvh": bvh, "bvh_roofline": build_roofline(bvh, peaks)}
 
 
 def run_ours(a, rank, world, local_rank):
@@ -571,7 +585,7 @@ def run_ours(a, rank, world, local_rank):
                            "l2": "path state streams of a step (up to 4.2 M slots x ~230 B) exceed the 126 MB L2; scene data is meant to be cache resident"},
                 "e2e": e2e, "roofline": roofline, "roofline_shade": roofline_shade, "cpu_baseline": cpu, "clocks": clocks, "gpu_launches": int(launches),
                 "stage_ms_per_step": {k: v / prof_steps for k, v in stage.items()},
-                "device_ms_per_step": device_ms / a.steps, "bvh": bvh, "extra_workloads": extra}
+                "device_ms_per_step": device_ms / a.steps, "bvh": bvh, "bvh_roofline": build_roofline(bvh, peaks), "extra_workloads": extra}
         print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:

@@ -194,13 +194,15 @@ __global__ void k_testRng(const uint32_t* idx, const uint32_t* ts, uint32_t n, u
     for (uint32_t k = 0; k < nDraws; k++) o[1 + k] = randPcg(rng);
 }
 
-__global__ void k_testCamera(SceneDev sc, uint32_t W, uint32_t H, const uint32_t* px, const uint32_t* py, uint32_t n, gsb_ray* out) {
+// the primary ray exactly as startPath (wavefront.cu) forms it: camZ evaluated once on the host, same expression order,
+// same compile flags (the Makefile gives this translation unit the shading kernels' division / square-root precision)
+__global__ void k_testCamera(SceneDev sc, uint32_t W, uint32_t H, float camZ, const uint32_t* px, const uint32_t* py, uint32_t n, gsb_ray* out) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float sx = (float)W, sy = (float)H;
     const float fx = (float)px[i] - sx / 2.0f;
     const float fy = (float)py[i] - sy / 2.0f;
-    const float z = (fmaxf(sx, sy) / 2.0f) / tanf(sc.fov / 2.0f);
+    const float z = camZ;
     const float3 dir = normalize(f3(-fx, fy, z));
     const float* V = sc.view;
     float3 d = f3(V[0] * dir.x + V[4] * dir.y + V[8] * dir.z, V[1] * dir.x + V[5] * dir.y + V[9] * dir.z,
@@ -1290,7 +1292,8 @@ gsb_status gsb_test_camera_rays(gsb_context* ctx, uint32_t width, uint32_t heigh
         uint32_t* dx = scr.upload(px, n, ctx->stream);
         uint32_t* dy = scr.upload(py, n, ctx->stream);
         gsb_ray* dOut = scr.alloc<gsb_ray>(n);
-        k_testCamera<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->sceneDev(), width, height, dx, dy, n, dOut);
+        const float camZ = (std::fmax((float)width, (float)height) / 2.0f) / std::tan(ctx->fov / 2.0f);   // as renderImpl
+        k_testCamera<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->sceneDev(), width, height, camZ, dx, dy, n, dOut);
         GSB_CUDA(cudaMemcpyAsync(out, dOut, (size_t)n * sizeof(gsb_ray), cudaMemcpyDeviceToHost, ctx->stream));
         GSB_CUDA(cudaStreamSynchronize(ctx->stream));
         return GSB_OK;
