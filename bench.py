@@ -322,8 +322,11 @@ def short_run(g, torch, dev, stream, name, scene, W, H, S, max_depth, peaks, ste
     ctx = g.Context(dev.index)
     ctx.set_stream(stream.cuda_stream)
     ctx.upload(scene)
+    first_build_ms = ctx.bvh_stats()["build_ms"]
+    ctx.upload(scene)           # built twice: the second build does not pay for the growth of the allocation pools
     ctx.set_params(max_depth=max_depth)
     bvh = ctx.bvh_stats()
+    bvh["first_build_ms"] = first_build_ms
     ctx.render(W, H, 0, 0)
     ctx.clear()
     torch.cuda.synchronize()
@@ -382,8 +385,11 @@ def run_ours(a, rank, world, local_rank):
     torch.cuda.set_stream(stream)
     ctx.set_stream(stream.cuda_stream)
     ctx.upload(scene)
+    first_build_ms = ctx.bvh_stats()["build_ms"]
+    ctx.upload(scene)           # built twice: the second build does not pay for the growth of the allocation pools
     ctx.set_params(max_depth=a.max_depth)
     bvh = ctx.bvh_stats()       # device time of the BLAS + TLAS builds, node / triangle counts, SAH before / after refinement
+    bvh["first_build_ms"] = first_build_ms
     ctx.render(W, H, 0, 0)      # allocate the frame
     ctx.clear()
     ptr, nbytes = ctx.device_sum_ptr()
