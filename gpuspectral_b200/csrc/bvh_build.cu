@@ -15,6 +15,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
+#include <stdexcept>
 #include <vector>
 
 #include "bvh.h"
@@ -227,7 +228,8 @@ struct CollapseArgs {
     const uint32_t* sorted;
     uint4* nodes;          // output nodes, 5 x uint4 each
     uint32_t* leafPrim;    // output: primitive index per leaf position
-    uint32_t* counters;    // [0] nodes allocated, [1] leaf positions allocated, [2] next-level item count
+    uint32_t* counters;    // [0] nodes allocated, [1] leaf positions allocated
+    uint32_t* levelCount;  // items per level: a launch reads its own entry and appends to the next one
     uint32_t maxLeaf;      // primitives per leaf child (one box per leaf child): 1..3
 };
 
@@ -278,7 +280,7 @@ __device__ void emitNode(const CollapseArgs& a, uint32_t outNode, float4 nlo, fl
     }
     const uint32_t childBase = nInternal ? atomicAdd(&a.counters[0], nInternal) : 0u;
     const uint32_t leafBase = nLeafPrims ? atomicAdd(&a.counters[1], nLeafPrims) : 0u;
-    const uint32_t itemBase = nInternal ? atomicAdd(&a.counters[2], nInternal) : 0u;
+    const uint32_t itemBase = nInternal ? atomicAdd(a.levelCount + 1, nInternal) : 0u;
 
     // quantisation frame
     const float p[3] = {nlo.x, nlo.y, nlo.z};
@@ -334,9 +336,11 @@ __device__ void emitNode(const CollapseArgs& a, uint32_t outNode, float4 nlo, fl
     out[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
 }
 
-__global__ void k_collapse(CollapseArgs a, const CollapseItem* __restrict__ items, uint32_t nItems, CollapseItem* next) {
+// One level of the collapse.  The launch is sized for the most items the level can hold (min(8^level, n)); how many it
+// really holds is read from a.levelCount[0] on the device, so consecutive levels need no host synchronisation in between.
+__global__ void k_collapse(CollapseArgs a, const CollapseItem* __restrict__ items, CollapseItem* next) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nItems) return;
+    if (i >= a.levelCount[0]) return;
     const CollapseItem it = items[i];
     const int b = it.binNode;
     int child[8];
@@ -514,19 +518,41 @@ GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi,
     GSB_CUDA(cudaMemcpyAsync(itemsA, &rootItem, sizeof(rootItem), cudaMemcpyHostToDevice, s));
     const uint32_t initCounters[4] = {1u, 0u, 0u, 0u};
     GSB_CUDA(cudaMemcpyAsync(counters, initCounters, sizeof(initCounters), cudaMemcpyHostToDevice, s));
-    uint32_t nItems = 1;
-    uint32_t hostCounters[4];
+    // Levels are launched in batches without waiting for the host: each launch is sized for the most items its level can
+    // hold and reads the real count on the device; after a batch the per-level counts come back and say whether the tree
+    // has ended (round 1 synchronised once per level: 117 times for the 17 meshes of the field scene).
+    constexpr int kMaxLevels = 64, kBatch = 6;
+    uint32_t* levelCount = pool.get<uint32_t>(kMaxLevels + 2);
+    GSB_CUDA(cudaMemsetAsync(levelCount, 0, (kMaxLevels + 2) * sizeof(uint32_t), s));
+    const uint32_t one = 1u;
+    GSB_CUDA(cudaMemcpyAsync(levelCount, &one, sizeof(one), cudaMemcpyHostToDevice, s));
+    uint32_t hostCounters[4] = {1u, 0u, 0u, 0u};
+    uint32_t hostLevels[kMaxLevels + 2] = {0};
     out.levelEnd.clear();
-    uint32_t levelEnd = 1;
-    while (nItems > 0) {
-        k_collapse<<<(nItems + 127) / 128, 128, 0, s>>>(ca, itemsA, nItems, itemsB);
+    int level = 0;
+    bool ended = false;
+    while (!ended && level < kMaxLevels) {
+        const int stop = std::min(level + kBatch, kMaxLevels);
+        for (int l = level; l < stop; l++) {
+            double cap = 1.0;
+            for (int k = 0; k < l && cap < (double)n; k++) cap *= 8.0;
+            const uint32_t most = (uint32_t)std::min<double>(cap, (double)n);
+            ca.levelCount = levelCount + l;
+            k_collapse<<<(most + 127) / 128, 128, 0, s>>>(ca, itemsA, itemsB);
+            std::swap(itemsA, itemsB);
+        }
+        GSB_CUDA(cudaMemcpyAsync(hostLevels, levelCount, sizeof(hostLevels), cudaMemcpyDeviceToHost, s));
         GSB_CUDA(cudaMemcpyAsync(hostCounters, counters, sizeof(hostCounters), cudaMemcpyDeviceToHost, s));
         GSB_CUDA(cudaStreamSynchronize(s));
-        out.levelEnd.push_back(levelEnd);      // the nodes written by this launch end here; their children follow
-        levelEnd = hostCounters[0];
-        nItems = hostCounters[2];
-        GSB_CUDA(cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), s));
-        std::swap(itemsA, itemsB);
+        level = stop;
+        ended = hostLevels[stop] == 0u;
+    }
+    if (!ended) throw std::runtime_error("BVH collapse: tree deeper than 64 levels of 8-wide nodes");
+    // node index ranges of the levels: one node per item, levels emitted one after the other
+    uint32_t levelEnd = 0;
+    for (int l = 0; l < kMaxLevels && hostLevels[l] > 0u; l++) {
+        levelEnd += hostLevels[l];
+        out.levelEnd.push_back(levelEnd);
     }
     r.numNodes = hostCounters[0];
     double hostCost[2] = {0, 0};
