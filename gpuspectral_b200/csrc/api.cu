@@ -403,6 +403,8 @@ SceneDev gsb_context::sceneDev() const {
     sc.fov = fov;
     sc.params = params;
     sc.sortBits = sortBits;
+    sc.sortMode = 0u;
+    if (const char* e = getenv("GSB_SORT_MODE")) sc.sortMode = (uint32_t)std::min(2, std::max(0, atoi(e)));
     for (int a = 0; a < 3; a++) {
         // bounds of everything a ray can hit: the world level and the top level
         float lo = 1e30f, hi = -1e30f;

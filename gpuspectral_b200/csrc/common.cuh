@@ -160,6 +160,7 @@ struct SceneDev {
     // ray sorting: origin cell = (o - sortLo) * sortScale per axis, clamped to [0, 2^sortBits); sortBits = 0: no sorting
     float sortLo[3], sortScale[3];
     uint32_t sortBits;
+    uint32_t sortMode;   // 0: cell, then octant; 1: octant, then cell; 2: cell, then 2 bits of direction per axis (A/B knob GSB_SORT_MODE)
 };
 
 }  // namespace gsb

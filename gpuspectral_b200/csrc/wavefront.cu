@@ -108,7 +108,15 @@ GSB_D uint32_t sortKey(const SceneDev& sc, float3 o, float3 d) {
     const uint32_t cy = (uint32_t)fminf(fmaxf((o.y - sc.sortLo[1]) * sc.sortScale[1], 0.0f), top);
     const uint32_t cz = (uint32_t)fminf(fmaxf((o.z - sc.sortLo[2]) * sc.sortScale[2], 0.0f), top);
     const uint32_t oct = (d.x < 0.0f ? 0u : 4u) | (d.y < 0.0f ? 0u : 2u) | (d.z < 0.0f ? 0u : 1u);
-    return ((spreadBits3(cx) | (spreadBits3(cy) << 1) | (spreadBits3(cz) << 2)) << 3) | oct;
+    const uint32_t cell = spreadBits3(cx) | (spreadBits3(cy) << 1) | (spreadBits3(cz) << 2);
+    if (sc.sortMode == 1u) return (oct << (3u * sc.sortBits)) | cell;      // octant major
+    if (sc.sortMode == 2u) {
+        // 2 bits of direction per axis below the cell
+        const uint32_t qx = (uint32_t)fminf(fmaxf((d.x * 0.5f + 0.5f) * 4.0f, 0.0f), 3.0f), qy = (uint32_t)fminf(fmaxf((d.y * 0.5f + 0.5f) * 4.0f, 0.0f), 3.0f),
+                       qz = (uint32_t)fminf(fmaxf((d.z * 0.5f + 0.5f) * 4.0f, 0.0f), 3.0f);
+        return (cell << 6) | spreadBits3(qx) | (spreadBits3(qy) << 1) | (spreadBits3(qz) << 2);
+    }
+    return (cell << 3) | oct;
 }
 
 // Offset of the primary ray from the pixel's integer coordinate for one uniform draw u (gsb_params::pixel_filter):
@@ -882,7 +890,7 @@ void renderImpl(gsb_context* ctx, uint32_t width, uint32_t height, uint32_t firs
     uint32_t parity = 0;
     const int regenGrid = (int)((slots + kRegenSpan - 1) / kRegenSpan);
     // key bits that matter: 3 per grid level + the octant
-    const int sortEndBit = (int)std::min(32u, 3u * sc.sortBits + 3u);
+    const int sortEndBit = (int)std::min(32u, 3u * sc.sortBits + (sc.sortMode == 2u ? 6u : 3u));
     auto iteration = [&]() {
         mark();
         k_regen<<<regenGrid, kRegenBlock, 0, s>>>(sc, wf, ra);
