@@ -33,7 +33,14 @@ def build(force=False):
     srcs.append(os.path.join(_HERE, "..", "include", "gpuspectral_b200.h"))
     stale = force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs)
     if stale:
-        subprocess.run(["make", "-C", _HERE, "-B", "liboracle.so"], check=True, capture_output=True)
+        r = subprocess.run(["make", "-C", _HERE, "-B", "liboracle.so"], capture_output=True, text=True)
+        if r.returncode != 0:
+            if force or not os.path.exists(_SO):
+                raise RuntimeError("oracle: make failed\n" + r.stdout[-2000:] + r.stderr[-2000:])
+            # a prebuilt library travels with the repository snapshot; file times on the receiving box say nothing about
+            # staleness, and a box without a host compiler must still be able to run the checker
+            import warnings
+            warnings.warn("oracle: rebuild failed, using the existing liboracle.so")
     return _SO
 
 

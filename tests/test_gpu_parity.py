@@ -747,3 +747,43 @@ def test_environment_emitter_same_seeds(gsb, orc):
         c.clear(); c.render(240, 135, 0, 2)
         assert (c.read_hdr()[..., :3].max(axis=2) == 0.0).sum() > 200   # the reference's behaviour: a miss adds nothing
         o.set_params()
+
+
+def test_degenerate_tree_shapes_trace_exactly(gsb, orc):
+    """The deepest trees an LBVH can produce: triangles whose sizes and positions fall off geometrically towards a corner
+    (every Morton split separates one of them: a chain), and thousands of coincident triangles (equal codes).  The 8-wide
+    collapse folds a binary chain 7 to 1, so the traversal stack (32 / 48 entries, ST_OVERFLOW when exceeded) is not
+    reached: the batches trace without an overflow error, ids / t exact against the oracle."""
+    rng = np.random.default_rng(2)
+    tris = []
+    for k in range(60):
+        s = 2.0 ** -k
+        tris.append([[s, s, s], [s * 1.5, s, s], [s, s * 1.5, s * 1.2]])
+    chain = np.array(tris, np.float32).reshape(-1, 3)
+    same = np.tile(np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32), (3000, 1)) + 5.0
+    for name, pos in (("chain", chain), ("coincident", same), ("both, as a large mesh", np.concatenate([chain, same] * 3))):
+        nrm = np.tile(np.array([[0, 0, 1]], np.float32), (len(pos), 1))
+        import gpuspectral_b200._native as N
+        inst = (N.Instance * 1)()
+        inst[0].transform[:] = [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1]
+        inst[0].mesh = 0
+        inst[0].bsdf = 0
+        o = orc.OracleScene()
+        o.add_mesh(pos, nrm)
+        o.set_bsdfs(0, bytes(16), 1)
+        o.set_instances(inst, 1)
+        with gsb.Context(0) as c:
+            inst[0].mesh = c.mesh_create(pos, nrm)
+            c.set_bsdfs(0, bytes(16), 1)
+            c.set_instances(inst, 1)
+            n = 40000
+            org = (rng.random((n, 3)) * 8 - 1).astype(np.float32)
+            tgt = pos[rng.integers(0, len(pos), n)] + rng.normal(0, 0.02, (n, 3)).astype(np.float32)
+            d = tgt - org
+            d /= np.linalg.norm(d, axis=1, keepdims=True)
+            rays = gsb.make_rays(org, d.astype(np.float32), 0.0, 1e10)
+            got = c.trace_batch(rays)                    # raises GsbError on ST_OVERFLOW
+            ref = o.trace_batch(rays, mode=1)
+            assert np.array_equal(got["inst"], ref["inst"]) and np.array_equal(got["prim"], ref["prim"]), name
+            assert np.array_equal(got["t"], ref["t"]), name
+            assert (got["inst"] != gsb.NO_HIT).mean() > 0.02, name     # the chain's triangles shrink to 2^-59: most aimed rays pass by
