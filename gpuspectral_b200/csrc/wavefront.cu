@@ -509,24 +509,16 @@ __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFU
             BSDFOutput bsdfRes;
             bsdfRes.bsdf = f3(0.0f); bsdfRes.pdf = 0.0f; bsdfRes.isDelta = false;
             float3 wi = f3(0.0f);
-            sampleBSDFT<TYPE>(sc, handle & 0xffffu, rng, wo, wi, bsdfRes);            // :716
-            const float NoW = fabsf(wi.z);                                           // :717
-            wi = onbUntransform(onb, wi);                                            // :718
-
-            bool haveLight;
-            const LightOutput lightRes = sampleLight<EXT>(sc, rng, position, haveLight);  // :720
-            const float3 L = normalize(lightRes.position - position);                // :722
-            const float3 wL = onbTransform(onb, L);                                  // :723
-            const float Ldist = length(lightRes.position - position);                // :724
-            const float NoL = fabsf(dot(SN, L));                                     // :725
-            const float lightPdf = lightRes.pdf;                                     // :726
-            BSDFOutput lightBsdfRes;
-            lightBsdfRes.bsdf = f3(0.0f); lightBsdfRes.pdf = 0.0f; lightBsdfRes.isDelta = false;
-            evalBSDFT<TYPE>(sc, handle & 0xffffu, wo, wL, lightBsdfRes);             // :729
-            if (EXT && TYPE == GSB_BSDF_DIFFUSE) {
-                // textured reflectance (extension): the diffuse value kD / pi with kD looked up at the hit's texture coordinate.
-                // A slow path taken by textured records only: the coordinates ride in the .w of the mesh's vertex arrays.
-                const int tex = ((const gsb_diffuse_bsdf*)sc.bsdf[GSB_BSDF_DIFFUSE])[handle & 0xffffu].hasTexture;
+            // textured reflectance (extension; the diffuse and the rough-plastic records carry a hasTexture field the reference
+            // never uses): the colour looked up at the hit's interpolated texture coordinate stands in for the record's constant
+            // one.  A slow path taken by textured records only: the coordinates ride in the .w of the mesh's vertex arrays.
+            bool textured = false;
+            gsb_diffuse_bsdf texDiffuse;
+            gsb_rough_plastic_bsdf texPlastic;
+            if (EXT && (TYPE == GSB_BSDF_DIFFUSE || TYPE == GSB_BSDF_ROUGH_PLASTIC)) {
+                const uint32_t bidx = handle & 0xffffu;
+                const int tex = TYPE == GSB_BSDF_DIFFUSE ? ((const gsb_diffuse_bsdf*)sc.bsdf[GSB_BSDF_DIFFUSE])[bidx].hasTexture
+                                                         : ((const gsb_rough_plastic_bsdf*)sc.bsdf[GSB_BSDF_ROUGH_PLASTIC])[bidx].hasTexture;
                 if (tex > 0 && (uint32_t)tex <= sc.numTextures) {
                     uint32_t origPrim = prim;
                     if (!HASINST || (instWord & kInstBaked)) origPrim = __float_as_uint(__ldg(sc.worldTris + 9 * (size_t)prim + 6).w);
@@ -539,11 +531,34 @@ __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFU
                         tv += bk * __ldg(sip->vnrm + 3 * (size_t)origPrim + k).w;
                     }
                     const float3 kd = textureEval(sc.textures[tex - 1], tu, tv);
-                    bsdfRes.bsdf = kd / GSB_PI;
-                    lightBsdfRes.bsdf = kd / GSB_PI;
+                    textured = true;
+                    if (TYPE == GSB_BSDF_DIFFUSE) {
+                        texDiffuse = ((const gsb_diffuse_bsdf*)sc.bsdf[GSB_BSDF_DIFFUSE])[bidx];
+                        texDiffuse.reflectance[0] = kd.x; texDiffuse.reflectance[1] = kd.y; texDiffuse.reflectance[2] = kd.z;
+                    } else {
+                        texPlastic = ((const gsb_rough_plastic_bsdf*)sc.bsdf[GSB_BSDF_ROUGH_PLASTIC])[bidx];
+                        texPlastic.diffuse[0] = kd.x; texPlastic.diffuse[1] = kd.y; texPlastic.diffuse[2] = kd.z;
+                    }
                 }
             }
+            if (!(EXT && textured)) sampleBSDFT<TYPE>(sc, handle & 0xffffu, rng, wo, wi, bsdfRes);            // :716
+            else if (TYPE == GSB_BSDF_DIFFUSE) diffuseSample(texDiffuse, rng, wo, wi, bsdfRes);
+            else roughPlasticSample(texPlastic, rng, wo, wi, bsdfRes);
+            const float NoW = fabsf(wi.z);                                           // :717
+            wi = onbUntransform(onb, wi);                                            // :718
 
+            bool haveLight;
+            const LightOutput lightRes = sampleLight<EXT>(sc, rng, position, haveLight);  // :720
+            const float3 L = normalize(lightRes.position - position);                // :722
+            const float3 wL = onbTransform(onb, L);                                  // :723
+            const float Ldist = length(lightRes.position - position);                // :724
+            const float NoL = fabsf(dot(SN, L));                                     // :725
+            const float lightPdf = lightRes.pdf;                                     // :726
+            BSDFOutput lightBsdfRes;
+            lightBsdfRes.bsdf = f3(0.0f); lightBsdfRes.pdf = 0.0f; lightBsdfRes.isDelta = false;
+            if (!(EXT && textured)) evalBSDFT<TYPE>(sc, handle & 0xffffu, wo, wL, lightBsdfRes);             // :729
+            else if (TYPE == GSB_BSDF_DIFFUSE) diffuseEval(texDiffuse, wo, wL, lightBsdfRes);
+            else roughPlasticEval(texPlastic, wo, wL, lightBsdfRes);
             const bool transmissive = isTransmissionBSDF(TYPE);
             const float NdotV = dot(N, -rayDir);
             float3 nee = f3(0.0f);

@@ -1,7 +1,8 @@
-// image.cpp — image files for bitmap reflectance textures: PFM, binary PPM and PNG, decoded here (no third-party code:
+// image.cpp — image files for bitmap reflectance textures: PFM, binary PPM, PNG and baseline JPEG, decoded here (no third-party code:
 // the reference reads textures through stb_image, engine/Loader.cpp:66-86, in a path it never enables).
 // PNG: 8-bit grey / grey+alpha / RGB / RGBA / palette, non-interlaced; zlib stream inflated by the decoder below
 // (stored, fixed and dynamic Huffman blocks, RFC 1950 / 1951), the five scanline filters of the PNG specification.
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -210,6 +211,216 @@ void decodePng(const std::vector<uint8_t>& file, std::vector<float>& rgb, uint32
     }
 }
 
+// ---- baseline JPEG (ITU T.81 sequential DCT, Huffman, 8 bit; grey or YCbCr with any sampling factors, restart intervals) ------
+// What the reference's own textured scene needs (staircase2/textures/*.jpg are baseline files).  Progressive files are refused.
+struct JpegHuff {
+    uint8_t bits[17] = {0};
+    uint8_t vals[256] = {0};
+    int mincode[17], maxcode[18], valptr[17];
+    bool present = false;
+    void build() {
+        int code = 0, k = 0;
+        for (int l = 1; l <= 16; l++) {
+            valptr[l] = k;
+            mincode[l] = code;
+            code += bits[l];
+            k += bits[l];
+            maxcode[l] = bits[l] ? code - 1 : -1;
+            code <<= 1;
+        }
+        maxcode[17] = 0x7fffffff;
+        present = true;
+    }
+};
+
+struct JpegBits {
+    const uint8_t* p;
+    size_t n, pos;
+    uint32_t acc = 0;
+    int cnt = 0;
+    int bit() {
+        if (cnt == 0) {
+            uint8_t b = 0;
+            if (pos < n) {
+                b = p[pos++];
+                if (b == 0xff) {
+                    if (pos < n && p[pos] == 0x00) pos++;          // stuffed zero
+                    else { pos--; b = 0; }                          // a marker: feed zeros, the caller handles it
+                }
+            }
+            acc = b;
+            cnt = 8;
+        }
+        cnt--;
+        return (int)((acc >> cnt) & 1u);
+    }
+    int receive(int s) {
+        int v = 0;
+        for (int i = 0; i < s; i++) v = (v << 1) | bit();
+        return v;
+    }
+    int decode(const JpegHuff& h) {
+        int code = 0;
+        for (int l = 1; l <= 16; l++) {
+            code = (code << 1) | bit();
+            if (h.maxcode[l] >= 0 && code <= h.maxcode[l] && code >= h.mincode[l]) return h.vals[h.valptr[l] + code - h.mincode[l]];
+        }
+        throw std::runtime_error("jpeg: bad Huffman code");
+    }
+    void restart() {
+        cnt = 0;
+        // skip to just behind the RSTn marker
+        while (pos + 1 < n && !(p[pos] == 0xff && p[pos + 1] >= 0xd0 && p[pos + 1] <= 0xd7)) pos++;
+        if (pos + 1 < n) pos += 2;
+    }
+};
+
+void decodeJpeg(const std::vector<uint8_t>& f, std::vector<float>& rgb, uint32_t& W, uint32_t& H) {
+    static const uint8_t zigzag[64] = {0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
+                                       35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+    uint16_t quant[4][64] = {{0}};
+    JpegHuff dc[4], ac[4];
+    struct Comp { int id = 0, h = 1, v = 1, tq = 0, td = 0, ta = 0, pred = 0, stride = 0; std::vector<uint8_t> plane; } comp[3];
+    int ncomp = 0, restartInterval = 0;
+    W = H = 0;
+    size_t pos = 2;
+    auto be16 = [&](size_t o) { return (int)((f[o] << 8) | f[o + 1]); };
+    size_t scanStart = 0;
+    while (pos + 4 <= f.size()) {
+        if (f[pos] != 0xff) { pos++; continue; }
+        const uint8_t m = f[pos + 1];
+        if (m == 0xd8 || m == 0x01 || (m >= 0xd0 && m <= 0xd7) || m == 0xff) { pos += (m == 0xff) ? 1 : 2; continue; }
+        const size_t len = (size_t)be16(pos + 2), body = pos + 4, end = pos + 2 + len;
+        if (end > f.size()) throw std::runtime_error("jpeg: truncated segment");
+        if (m == 0xdb) {
+            for (size_t q = body; q < end;) {
+                const int pq = f[q] >> 4, tq = f[q] & 15;
+                q++;
+                if (tq > 3) throw std::runtime_error("jpeg: bad quantisation table");
+                for (int i = 0; i < 64; i++) { quant[tq][zigzag[i]] = (uint16_t)(pq ? be16(q) : f[q]); q += pq ? 2 : 1; }
+            }
+        } else if (m == 0xc4) {
+            for (size_t q = body; q < end;) {
+                const int tc = f[q] >> 4, th = f[q] & 15;
+                q++;
+                if (th > 3) throw std::runtime_error("jpeg: bad Huffman table");
+                JpegHuff& h = tc ? ac[th] : dc[th];
+                int total = 0;
+                for (int l = 1; l <= 16; l++) { h.bits[l] = f[q++]; total += h.bits[l]; }
+                if (total > 256 || q + total > end) throw std::runtime_error("jpeg: bad Huffman table");
+                for (int i = 0; i < total; i++) h.vals[i] = f[q++];
+                h.build();
+            }
+        } else if (m == 0xc0 || m == 0xc1) {
+            if (f[body] != 8) throw std::runtime_error("jpeg: only 8-bit samples are supported");
+            H = (uint32_t)be16(body + 1);
+            W = (uint32_t)be16(body + 3);
+            ncomp = f[body + 5];
+            if (ncomp != 1 && ncomp != 3) throw std::runtime_error("jpeg: only grey and three-component images are supported");
+            for (int c = 0; c < ncomp; c++) {
+                comp[c].id = f[body + 6 + 3 * c];
+                comp[c].h = f[body + 7 + 3 * c] >> 4;
+                comp[c].v = f[body + 7 + 3 * c] & 15;
+                comp[c].tq = f[body + 8 + 3 * c] & 3;
+                if (comp[c].h < 1 || comp[c].h > 4 || comp[c].v < 1 || comp[c].v > 4) throw std::runtime_error("jpeg: bad sampling factors");
+            }
+        } else if (m == 0xc2 || (m >= 0xc3 && m <= 0xcf && m != 0xc4 && m != 0xc8 && m != 0xcc)) {
+            throw std::runtime_error("jpeg: only baseline (sequential Huffman) files are supported");
+        } else if (m == 0xdd) {
+            restartInterval = be16(body);
+        } else if (m == 0xda) {
+            const int ns = f[body];
+            if (ns != ncomp) throw std::runtime_error("jpeg: non-interleaved scans are not supported");
+            for (int k = 0; k < ns; k++) {
+                const int id = f[body + 1 + 2 * k];
+                for (int c = 0; c < ncomp; c++)
+                    if (comp[c].id == id) { comp[c].td = f[body + 2 + 2 * k] >> 4; comp[c].ta = f[body + 2 + 2 * k] & 15; }
+            }
+            scanStart = end;
+            break;
+        }
+        pos = end;
+    }
+    if (!W || !H || !scanStart) throw std::runtime_error("jpeg: no image data");
+    int hmax = 1, vmax = 1;
+    for (int c = 0; c < ncomp; c++) { hmax = std::max(hmax, comp[c].h); vmax = std::max(vmax, comp[c].v); }
+    const int mcusX = (int)((W + 8 * hmax - 1) / (8 * hmax)), mcusY = (int)((H + 8 * vmax - 1) / (8 * vmax));
+    for (int c = 0; c < ncomp; c++) {
+        comp[c].stride = mcusX * comp[c].h * 8;
+        comp[c].plane.assign((size_t)comp[c].stride * mcusY * comp[c].v * 8, 0);
+        if (!dc[comp[c].td & 3].present || !ac[comp[c].ta & 3].present) throw std::runtime_error("jpeg: missing Huffman table");
+    }
+    float cosT[8][8];
+    for (int x = 0; x < 8; x++)
+        for (int u = 0; u < 8; u++) cosT[x][u] = (u == 0 ? 0.70710678f : 1.0f) * std::cos((2 * x + 1) * u * 3.14159265358979f / 16.0f) * 0.5f;
+    JpegBits br{f.data(), f.size(), scanStart};
+    int sinceRestart = 0;
+    for (int my = 0; my < mcusY; my++)
+        for (int mx = 0; mx < mcusX; mx++) {
+            if (restartInterval && sinceRestart == restartInterval) {
+                br.restart();
+                for (int c = 0; c < ncomp; c++) comp[c].pred = 0;
+                sinceRestart = 0;
+            }
+            sinceRestart++;
+            for (int c = 0; c < ncomp; c++)
+                for (int by = 0; by < comp[c].v; by++)
+                    for (int bx = 0; bx < comp[c].h; bx++) {
+                        float F[64] = {0.0f};
+                        const int t = br.decode(dc[comp[c].td & 3]);
+                        int diff = t ? br.receive(t) : 0;
+                        if (t && diff < (1 << (t - 1))) diff -= (1 << t) - 1;
+                        comp[c].pred += diff;
+                        F[0] = (float)(comp[c].pred * quant[comp[c].tq][0]);
+                        for (int k = 1; k < 64;) {
+                            const int rs = br.decode(ac[comp[c].ta & 3]), r = rs >> 4, sbits = rs & 15;
+                            if (sbits == 0) {
+                                if (r == 15) { k += 16; continue; }
+                                break;
+                            }
+                            k += r;
+                            if (k > 63) throw std::runtime_error("jpeg: bad coefficient run");
+                            int v = br.receive(sbits);
+                            if (v < (1 << (sbits - 1))) v -= (1 << sbits) - 1;
+                            F[zigzag[k]] = (float)(v * quant[comp[c].tq][zigzag[k]]);
+                            k++;
+                        }
+                        float tmp[64];
+                        for (int v = 0; v < 8; v++)
+                            for (int x = 0; x < 8; x++) {
+                                float a = 0.0f;
+                                for (int u = 0; u < 8; u++) a += F[8 * v + u] * cosT[x][u];
+                                tmp[8 * v + x] = a;
+                            }
+                        uint8_t* dst = &comp[c].plane[(size_t)((my * comp[c].v + by) * 8) * comp[c].stride + (size_t)(mx * comp[c].h + bx) * 8];
+                        for (int y = 0; y < 8; y++)
+                            for (int x = 0; x < 8; x++) {
+                                float a = 0.0f;
+                                for (int v = 0; v < 8; v++) a += tmp[8 * v + x] * cosT[y][v];
+                                const int q = (int)std::floor(a + 128.5f);
+                                dst[(size_t)y * comp[c].stride + x] = (uint8_t)std::min(std::max(q, 0), 255);
+                            }
+                    }
+        }
+    rgb.resize((size_t)W * H * 3);
+    for (uint32_t y = 0; y < H; y++)
+        for (uint32_t x = 0; x < W; x++) {
+            float s[3] = {0, 128, 128};
+            for (int c = 0; c < ncomp; c++)   // chroma planes: nearest sample (no filtering)
+                s[c] = comp[c].plane[(size_t)(y * comp[c].v / vmax) * comp[c].stride + (size_t)(x * comp[c].h / hmax)];
+            float r = s[0], g = s[0], b = s[0];
+            if (ncomp == 3) {
+                r = s[0] + 1.402f * (s[2] - 128.0f);
+                g = s[0] - 0.344136f * (s[1] - 128.0f) - 0.714136f * (s[2] - 128.0f);
+                b = s[0] + 1.772f * (s[1] - 128.0f);
+            }
+            float* o = &rgb[3 * ((size_t)y * W + x)];
+            o[0] = srgbToLinear((uint8_t)std::min(std::max((int)std::floor(r + 0.5f), 0), 255));
+            o[1] = srgbToLinear((uint8_t)std::min(std::max((int)std::floor(g + 0.5f), 0), 255));
+            o[2] = srgbToLinear((uint8_t)std::min(std::max((int)std::floor(b + 0.5f), 0), 255));
+        }
+}
+
 void decodePpm(const std::vector<uint8_t>& file, std::vector<float>& rgb, uint32_t& W, uint32_t& H) {
     size_t pos = 2;
     auto number = [&]() {
@@ -239,6 +450,7 @@ void loadImageLinearRGB(const std::string& path, std::vector<float>& rgb, uint32
     static const uint8_t pngMagic[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
     if (file.size() > 8 && !std::memcmp(file.data(), pngMagic, 8)) return decodePng(file, rgb, width, height);
     if (file.size() > 2 && file[0] == 'P' && file[1] == '6') return decodePpm(file, rgb, width, height);
+    if (file.size() > 3 && file[0] == 0xff && file[1] == 0xd8 && file[2] == 0xff) return decodeJpeg(file, rgb, width, height);
     if (file.size() > 2 && file[0] == 'P' && (file[1] == 'F' || file[1] == 'f')) {
         std::vector<float> rgba;
         readPFM(path, rgba, width, height);   // linear already
@@ -247,7 +459,7 @@ void loadImageLinearRGB(const std::string& path, std::vector<float>& rgb, uint32
             for (int c = 0; c < 3; c++) rgb[3 * i + c] = rgba[4 * i + c];
         return;
     }
-    throw std::runtime_error(path + ": unsupported image format (PNG, binary PPM and PFM are read)");
+    throw std::runtime_error(path + ": unsupported image format (PNG, baseline JPEG, binary PPM and PFM are read)");
 }
 
 }  // namespace gsbhost

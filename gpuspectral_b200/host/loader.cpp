@@ -76,6 +76,7 @@ struct Ctx {
     std::map<std::string, std::string> defaults;
     std::map<std::string, const XmlNode*> ids;
     std::map<std::string, uint32_t> meshCache;
+    std::map<const XmlNode*, int> textureCache;   // a texture element referenced by several shapes is loaded once
     Scene* scene = nullptr;
 
     std::string subst(const std::string& v) const {
@@ -198,7 +199,15 @@ void parseTransform(const Ctx& c, const XmlNode* t, float* out) {
 // Reflectance textures (extension).  checkerboard: color0 / color1 / uscale / vscale / uoffset / voffset (Mitsuba's names);
 // bitmap: filename (PNG, binary PPM, PFM; 8-bit files are decoded from sRGB), uscale / vscale / uoffset / voffset.
 // Returns the texture index, or -1 (with a warning) when the texture cannot be used.
+int loadTextureUncached(Ctx& c, const XmlNode& tex);
 int loadTexture(Ctx& c, const XmlNode& tex) {
+    auto it = c.textureCache.find(&tex);
+    if (it != c.textureCache.end()) return it->second;
+    const int id = loadTextureUncached(c, tex);
+    c.textureCache.emplace(&tex, id);
+    return id;
+}
+int loadTextureUncached(Ctx& c, const XmlNode& tex) {
     const std::string type = tex.attrOr("type", "");
     Scene::TextureData t;
     std::memset(&t.desc, 0, sizeof(t.desc));
@@ -230,6 +239,19 @@ int loadTexture(Ctx& c, const XmlNode& tex) {
     return (int)c.scene->addTexture(std::move(t));
 }
 
+// extension: <texture type="checkerboard|bitmap" name="..."> where the reference expects a colour (commented-out code there,
+// Loader.cpp:122-143); returns the record's hasTexture value = texture index + 1, or 0 (constant 0.5, with a warning)
+int texturedProperty(Ctx& c, const XmlNode& obj, const char* name, const char* plugin) {
+    const XmlNode* tp = c.prop(obj, name);
+    const XmlNode* tex = tp ? c.resolve(*tp) : nullptr;
+    if (tex && tex->tag == "texture") {
+        const int id = loadTexture(c, *tex);
+        return id >= 0 ? id + 1 : 0;
+    }
+    if (tp) c.warn(std::string(plugin) + ": this kind of " + name + " is not supported, using 0.5");
+    return 0;
+}
+
 // Loader.cpp:145-234
 void loadMaterial(Ctx& c, Material& material, const XmlNode& obj) {
     Scene& scene = *c.scene;
@@ -247,23 +269,17 @@ void loadMaterial(Ctx& c, Material& material, const XmlNode& obj) {
         gsb_diffuse_bsdf b = {{0.0f, 0.0f, 0.0f}, 0};
         if (!c.color(obj, "reflectance", b.reflectance)) {
             b.reflectance[0] = b.reflectance[1] = b.reflectance[2] = 0.5f;
-            // extension: <texture type="checkerboard|bitmap" name="reflectance"> (commented-out code in the reference,
-            // Loader.cpp:122-143); the record refers to the texture by hasTexture = index + 1
-            const XmlNode* tp = c.prop(obj, "reflectance");
-            const XmlNode* tex = tp ? c.resolve(*tp) : nullptr;
-            if (tex && tex->tag == "texture") {
-                const int id = loadTexture(c, *tex);
-                if (id >= 0) b.hasTexture = id + 1;
-            } else if (tp) {
-                c.warn("diffuse: this kind of reflectance is not supported, using 0.5");
-            }
+            b.hasTexture = texturedProperty(c, obj, "reflectance", "diffuse");
         }
         material.bsdf = scene.addDiffuseBSDF(b);
         material.hasBsdf = true;
     } else if (type == "roughplastic") {
         gsb_rough_plastic_bsdf b;
         std::memset(&b, 0, sizeof(b));
-        if (!c.color(obj, "diffuse_reflectance", b.diffuse)) b.diffuse[0] = b.diffuse[1] = b.diffuse[2] = 0.5f;
+        if (!c.color(obj, "diffuse_reflectance", b.diffuse)) {
+            b.diffuse[0] = b.diffuse[1] = b.diffuse[2] = 0.5f;
+            b.hasTexture = texturedProperty(c, obj, "diffuse_reflectance", "roughplastic");
+        }
         float alpha = 0.1f;
         c.number(obj, "alpha", alpha);
         iorAndR0(b.iorIn, b.R0);

@@ -1180,7 +1180,31 @@ void closestHit(const or_scene& s, const Hit& hit, HitPayload& prd, PathStats& s
     bsdfRes.bsdf = vec3(0.0f); bsdfRes.pdf = 0.0f; bsdfRes.isDelta = false;
     vec3 wi;
     const uint32_t handle = instance.src.bsdf;
-    sampleBSDF(s, handle, rng, wo, wi, bsdfRes);                       // :716
+    // textured reflectance (extension; the diffuse and the rough-plastic records carry a hasTexture field the reference never
+    // uses): the colour looked up at the hit's interpolated texture coordinate stands in for the record's constant one
+    const uint32_t btype = handle >> 16, bidx = handle & 0xffffu;
+    bool textured = false;
+    gsb_diffuse_bsdf texDiffuse = {};
+    gsb_rough_plastic_bsdf texPlastic = {};
+    if (btype == GSB_BSDF_DIFFUSE || btype == GSB_BSDF_ROUGH_PLASTIC) {
+        const int tex = btype == GSB_BSDF_DIFFUSE ? s.diffuse[bidx].hasTexture : s.roughPlastic[bidx].hasTexture;
+        if (tex > 0 && (size_t)tex <= s.textures.size()) {
+            float tu = 0.0f, tv = 0.0f;
+            for (int k = 0; k < 3; k++) {
+                const float bk = k == 0 ? bary.x : (k == 1 ? bary.y : bary.z);
+                const size_t vi = 3 * (size_t)hit.prim + k;
+                tu += bk * (mesh.uv.empty() ? 0.0f : mesh.uv[2 * vi]);
+                tv += bk * (mesh.uv.empty() ? 0.0f : mesh.uv[2 * vi + 1]);
+            }
+            const vec3 kd = textureEval(s.textures[tex - 1], tu, tv);
+            textured = true;
+            if (btype == GSB_BSDF_DIFFUSE) { texDiffuse = s.diffuse[bidx]; texDiffuse.reflectance[0] = kd.x; texDiffuse.reflectance[1] = kd.y; texDiffuse.reflectance[2] = kd.z; }
+            else { texPlastic = s.roughPlastic[bidx]; texPlastic.diffuse[0] = kd.x; texPlastic.diffuse[1] = kd.y; texPlastic.diffuse[2] = kd.z; }
+        }
+    }
+    if (!textured) sampleBSDF(s, handle, rng, wo, wi, bsdfRes);        // :716
+    else if (btype == GSB_BSDF_DIFFUSE) diffuseSample(texDiffuse, rng, wo, wi, bsdfRes);
+    else roughPlasticSample(texPlastic, rng, wo, wi, bsdfRes);
     float NoW = std::fabs(wi.z);                                       // :717
     wi = onbUntransform(onb, wi);                                      // :718
 
@@ -1194,24 +1218,9 @@ void closestHit(const or_scene& s, const Hit& hit, HitPayload& prd, PathStats& s
 
     BSDFOutput lightBsdfRes;
     lightBsdfRes.bsdf = vec3(0.0f); lightBsdfRes.pdf = 0.0f; lightBsdfRes.isDelta = false;
-    evalBSDF(s, handle, wo, wL, lightBsdfRes);                         // :729
-    if ((handle >> 16) == GSB_BSDF_DIFFUSE) {
-        // textured reflectance (extension): kD / pi with kD looked up at the hit's interpolated texture coordinate
-        const int tex = s.diffuse[handle & 0xffffu].hasTexture;
-        if (tex > 0 && (size_t)tex <= s.textures.size()) {
-            float tu = 0.0f, tv = 0.0f;
-            for (int k = 0; k < 3; k++) {
-                const float bk = k == 0 ? bary.x : (k == 1 ? bary.y : bary.z);
-                const size_t vi = 3 * (size_t)hit.prim + k;
-                tu += bk * (mesh.uv.empty() ? 0.0f : mesh.uv[2 * vi]);
-                tv += bk * (mesh.uv.empty() ? 0.0f : mesh.uv[2 * vi + 1]);
-            }
-            const vec3 kd = textureEval(s.textures[tex - 1], tu, tv);
-            bsdfRes.bsdf = kd / kPi;
-            lightBsdfRes.bsdf = kd / kPi;
-        }
-    }
-
+    if (!textured) evalBSDF(s, handle, wo, wL, lightBsdfRes);          // :729
+    else if (btype == GSB_BSDF_DIFFUSE) diffuseEval(texDiffuse, wo, wL, lightBsdfRes);
+    else roughPlasticEval(texPlastic, wo, wL, lightBsdfRes);
     const bool transmissive = isTransmission(handle >> 16);
     bool neeDone = false;                                              // :732
     if (s.params.nee && haveLight) {                                   // :734

@@ -134,12 +134,30 @@ class OracleScene:
     # ---- scene archives: the flat records of a host scene as one .npz, so that the CPU arm of bench.py can run without the
     # product package (tests/golden/make_scene_npz.py writes them; tests/test_oracle_cpu.py checks archive == host scene)
     @staticmethod
-    def dump_host_scene(scene, path):
+    def dump_host_scene(scene, path, max_texture=0):
+        """max_texture > 0: bitmap textures are box-filtered down until neither side exceeds it (keeps archives small)."""
         import ctypes
         arrays = {"mesh_count": np.array([scene.mesh_count], np.uint32)}
+        tex, nt = scene.textures if hasattr(scene, "textures") else (None, 0)
+        arrays["texture_count"] = np.array([nt], np.uint32)
+        for t in range(nt):
+            d = tex[t]
+            arrays[f"tex{t}_desc"] = np.array([d.type, d.uscale, d.vscale, d.uoffset, d.voffset, *d.color0, *d.color1], np.float64)
+            if d.type == 1:
+                px = np.ctypeslib.as_array(d.texels, shape=(d.height, d.width, 3)).astype(np.float32)
+                f = 1
+                while max_texture and max(d.width, d.height) // f > max_texture:
+                    f *= 2
+                if f > 1:
+                    h, w = d.height // f * f, d.width // f * f
+                    px = px[:h, :w].reshape(h // f, f, w // f, f, 3).mean(axis=(1, 3)).astype(np.float32)
+                arrays[f"tex{t}_px"] = px.astype(np.float16)
         for i in range(scene.mesh_count):
             p, q = scene.mesh(i)
             arrays[f"mesh{i}_p"], arrays[f"mesh{i}_n"] = p, q
+            uv = scene.mesh_uv(i) if (nt and hasattr(scene, "mesh_uv")) else None
+            if uv is not None:
+                arrays[f"mesh{i}_uv"] = uv
         for t in range(9):
             raw, n = scene.bsdfs(t)
             arrays[f"bsdf{t}"] = np.frombuffer(raw, np.uint8)
@@ -159,7 +177,10 @@ class OracleScene:
         z = np.load(path)
         o = OracleScene()
         for i in range(int(z["mesh_count"][0])):
-            o.add_mesh(z[f"mesh{i}_p"], z[f"mesh{i}_n"])
+            o.add_mesh(z[f"mesh{i}_p"], z[f"mesh{i}_n"], uv=z[f"mesh{i}_uv"] if f"mesh{i}_uv" in z else None)
+        tex, nt, _keep = archive_textures(z)
+        if nt:
+            o.set_textures(tex, nt)
         for t in range(9):
             o.set_bsdfs(t, z[f"bsdf{t}"].tobytes(), int(z[f"bsdf{t}_count"][0]))
         lights = C.create_string_buffer(z["lights"].tobytes(), max(1, z["lights"].size))
@@ -197,7 +218,7 @@ class OracleScene:
 
     def set_textures(self, textures, count):
         """textures: ctypes array of gsb_texture records (gpuspectral_b200._native.Texture layout)."""
-        if lib().or_scene_set_textures(self._s, C.cast(textures, C.c_void_p), count) != 0:
+        if lib().or_scene_set_textures(self._s, C.cast(textures, C.c_void_p) if textures is not None else None, count) != 0:
             raise ValueError("oracle: a bitmap texture has no texels")
 
     def set_instances(self, instances, count):
@@ -275,6 +296,31 @@ class OracleScene:
         pdf, seed_out = np.zeros(n, np.float32), np.zeros(n, np.uint32)
         lib().or_sample_light(self._s, _fp(pos), _up(seed), n, _fp(lpos), _fp(em), _fp(pdf), _up(seed_out))
         return lpos, em, pdf, seed_out
+
+
+class _Texture(C.Structure):     # gsb_texture (include/gpuspectral_b200.h), declared here so that the archive reader needs no product import
+    _fields_ = [("type", C.c_uint32), ("width", C.c_uint32), ("height", C.c_uint32), ("texels", C.POINTER(C.c_float)),
+                ("color0", C.c_float * 3), ("color1", C.c_float * 3),
+                ("uscale", C.c_float), ("vscale", C.c_float), ("uoffset", C.c_float), ("voffset", C.c_float)]
+
+
+def archive_textures(z):
+    """(gsb_texture array, count, texel arrays to keep alive) of a scene archive."""
+    nt = int(z["texture_count"][0]) if "texture_count" in z else 0
+    arr = (_Texture * max(1, nt))()
+    keep = []
+    for t in range(nt):
+        d = z[f"tex{t}_desc"]
+        arr[t].type = int(d[0])
+        arr[t].uscale, arr[t].vscale, arr[t].uoffset, arr[t].voffset = (float(x) for x in d[1:5])
+        arr[t].color0[:] = [float(x) for x in d[5:8]]
+        arr[t].color1[:] = [float(x) for x in d[8:11]]
+        if arr[t].type == 1:
+            px = np.ascontiguousarray(z[f"tex{t}_px"], np.float32)
+            keep.append(px)
+            arr[t].height, arr[t].width = px.shape[:2]
+            arr[t].texels = px.ctypes.data_as(C.POINTER(C.c_float))
+    return arr, nt, keep
 
 
 def rng(idx, timestamp, n_draws):

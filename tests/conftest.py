@@ -112,9 +112,21 @@ class ArchiveScene:
         self._lights = (N.TriangleLight * max(1, nl))()
         C.memmove(self._lights, z["lights"].tobytes(), nl * C.sizeof(N.TriangleLight))
         self._nl = nl
+        from oracle import oracle as orc
+        self._tex, self._nt, self._tex_keep = orc.archive_textures(z)
 
     def mesh(self, i):
         return self._z[f"mesh{i}_p"], self._z[f"mesh{i}_n"]
+
+    def mesh_uv(self, i):
+        return self._z[f"mesh{i}_uv"] if f"mesh{i}_uv" in self._z else None
+
+    @property
+    def textures(self):
+        import ctypes as C
+
+        import gpuspectral_b200._native as N
+        return C.cast(self._tex, C.POINTER(N.Texture)), self._nt
 
     def bsdfs(self, t):
         return self._z[f"bsdf{t}"].tobytes(), int(self._z[f"bsdf{t}_count"][0])

@@ -23,5 +23,5 @@ if __name__ == "__main__":
     if os.path.exists(xml):
         sc = g.Scene.load_xml(xml)
         out = os.path.join(ROOT, "tests", "golden", "scene_staircase2.npz")
-        orc.OracleScene.dump_host_scene(sc, out)
+        orc.OracleScene.dump_host_scene(sc, out, max_texture=256)     # its three JPEG textures box-filtered to <= 256 pixels
         print(out, os.path.getsize(out), "bytes;", sc.instanced_triangles, "triangles; loader warnings:", sc.warnings)

@@ -73,7 +73,7 @@ def test_png_ppm_pfm_bitmaps_and_checkerboard_from_xml(gsb, tmp_path):
     s = gsb.Scene.from_xml_string(_XML % shapes, str(tmp_path))
     tex, nt = s.textures
     assert nt == 4                                   # the jpeg is refused with a warning, its record keeps 0.5
-    assert any("d.jpg" in w or "unsupported" in w for w in s.warnings)
+    assert any("jpeg" in w or "unsupported" in w for w in s.warnings)
     want = _srgb_to_linear(img)
     assert np.allclose(_texels(tex[0]), want, atol=2e-6) and np.allclose(_texels(tex[1]), want, atol=2e-6)
     assert np.array_equal(_texels(tex[2]), hdr[..., :3])
@@ -138,3 +138,37 @@ def test_oracle_texture_lookup_through_a_rendered_quad(gsb, orc):
     # indirect share of the pixel: a few per cent; a flipped or transposed lookup is off by integer factors)
     assert np.allclose(ratio, want, rtol=0.1, atol=0.03)
     assert np.corrcoef(ratio.ravel(), want.ravel())[0, 1] > 0.995
+
+
+def test_baseline_jpeg_decoder_against_opencv(gsb, tmp_path):
+    """Own baseline-JPEG decoder (the format of the reference's staircase2 textures) against OpenCV's libjpeg on files
+    written here: 4:4:4 within a level of libjpeg's integer IDCT, 4:2:0 apart only by the chroma upsampling filter
+    (nearest here, interpolating there); grey; a progressive file is refused with a warning."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(6)
+    yy, xx = np.mgrid[0:75, 0:101]
+    img = np.stack([127 + 120 * np.sin(xx / 9.0), 127 + 120 * np.cos(yy / 7.0), (xx * 2 + yy) % 256], 2)
+    img = np.clip(img + rng.normal(0, 6, img.shape), 0, 255).astype(np.uint8)
+    cases = {"a444.jpg": [cv2.IMWRITE_JPEG_QUALITY, 92, cv2.IMWRITE_JPEG_SAMPLING_FACTOR, cv2.IMWRITE_JPEG_SAMPLING_FACTOR_444],
+             "a420.jpg": [cv2.IMWRITE_JPEG_QUALITY, 85, cv2.IMWRITE_JPEG_SAMPLING_FACTOR, cv2.IMWRITE_JPEG_SAMPLING_FACTOR_420, cv2.IMWRITE_JPEG_RST_INTERVAL, 3],
+             "prog.jpg": [cv2.IMWRITE_JPEG_PROGRESSIVE, 1]}
+    for name, flags in cases.items():
+        assert cv2.imwrite(str(tmp_path / name), img[..., ::-1], flags)
+    assert cv2.imwrite(str(tmp_path / "grey.jpg"), img[..., 0])
+    shapes = "".join(f'<shape type="rectangle"><bsdf type="diffuse"><texture name="reflectance" type="bitmap">'
+                     f'<string name="filename" value="{n}"/></texture></bsdf></shape>' for n in ("a444.jpg", "a420.jpg", "grey.jpg", "prog.jpg"))
+    s = gsb.Scene.from_xml_string(_XML % shapes, str(tmp_path))
+    tex, nt = s.textures
+    assert nt == 3 and any("baseline" in w for w in s.warnings)
+
+    def levels(t):      # back to 8-bit sRGB levels
+        a = _texels(t).astype(np.float64)
+        return np.where(a <= 0.0031308, a * 12.92, 1.055 * np.maximum(a, 1e-12) ** (1 / 2.4) - 0.055) * 255
+    for t, name, mean_tol, p99_tol in ((tex[0], "a444.jpg", 0.3, 2.0), (tex[1], "a420.jpg", 5.0, 40.0)):
+        ref = cv2.imread(str(tmp_path / name), cv2.IMREAD_COLOR)[..., ::-1].astype(np.float64)
+        d = np.abs(levels(t) - ref)
+        assert (t.width, t.height) == (101, 75)
+        assert d.mean() < mean_tol and np.percentile(d, 99) <= p99_tol, (name, d.mean(), np.percentile(d, 99))
+    g = cv2.imread(str(tmp_path / "grey.jpg"), cv2.IMREAD_GRAYSCALE).astype(np.float64)
+    d = np.abs(levels(tex[2])[..., 1] - g)
+    assert d.mean() < 0.3 and d.max() <= 2.0
