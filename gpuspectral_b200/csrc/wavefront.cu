@@ -48,6 +48,12 @@ constexpr uint32_t kRetired = 0xffffffffu;   // result.w (where the pixel index 
 // hitInst of a slot whose path has not been traced yet (k_generate): any word that is neither GSB_NO_HIT (= path ended)
 // nor carries a valid BSDF type in bits 28..31
 constexpr uint32_t kInstFresh = 0xfffffffeu;
+// hitInst of a slot whose path left the scene and whose sample k_extend has already added to the image (GSB_MISS_DELIVERS):
+// k_regen only has to start the slot's next path.  Like kInstFresh it decodes to no BSDF type.
+constexpr uint32_t kInstDelivered = 0xfffffffdu;
+#ifndef GSB_MISS_DELIVERS
+#define GSB_MISS_DELIVERS 1
+#endif
 #ifndef GSB_SHADE_PREFETCH
 #define GSB_SHADE_PREFETCH 0  // k_shade prefetches its next tile's state: 1 into L1, 2 into L2
 #endif
@@ -186,11 +192,15 @@ __global__ void __launch_bounds__(kRegenBlock) k_regen(SceneDev sc, WavefrontSta
     __shared__ unsigned long long s_base;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t base = blockIdx.x * (uint32_t)kRegenSpan;
-    uint32_t ended = 0;   // bit k: slot base + k * kRegenBlock + tid holds an ended path
+    uint32_t ended = 0, delivered = 0;   // bit k: slot base + k * kRegenBlock + tid holds an ended path / one whose sample k_extend delivered
 #pragma unroll
     for (int k = 0; k < kRegenPer; k++) {
         const uint32_t slot = base + (uint32_t)k * kRegenBlock + tid;
-        if (slot < ra.slots && wf.hitInst[slot] == GSB_NO_HIT && __float_as_uint(wf.result[slot].w) != kRetired) ended |= 1u << k;
+        if (slot < ra.slots) {
+            const uint32_t hi = wf.hitInst[slot];
+            if (hi == kInstDelivered) { ended |= 1u << k; delivered |= 1u << k; }
+            else if (hi == GSB_NO_HIT && __float_as_uint(wf.result[slot].w) != kRetired) ended |= 1u << k;
+        }
     }
     // exclusive prefix of the ended counts over the block
     const uint32_t n = (uint32_t)__popc(ended);
@@ -210,29 +220,39 @@ __global__ void __launch_bounds__(kRegenBlock) k_regen(SceneDev sc, WavefrontSta
         total += c;
     }
     if (total == 0u) return;
+    // the block's ended slots, compacted: entry i of the list gets work item s_base + i, and the list is then processed by
+    // all threads side by side (r2q: with every thread working through its own eight slots the path start — hash, camera
+    // ray — ran with 5.6 of 32 lanes, 1572 instructions per warp; it was 103 M of the kernel's instructions)
+    __shared__ uint32_t s_list[kRegenSpan];
+    {
+        uint32_t at = before + (incl - n);
+#pragma unroll
+        for (int k = 0; k < kRegenPer; k++)
+            if (ended & (1u << k)) s_list[at++] = (base + (uint32_t)k * kRegenBlock + tid) | (delivered & (1u << k) ? 0x80000000u : 0u);
+    }
     if (tid == 0u) s_base = atomicAdd(&wf.stats[ST_NEXTWORK], (unsigned long long)total);
     __syncthreads();
-    unsigned long long work = s_base + before + (incl - n);
     uint32_t retired = 0;
-#pragma unroll
-    for (int k = 0; k < kRegenPer; k++) {
-        if (!(ended & (1u << k))) continue;
-        const uint32_t slot = base + (uint32_t)k * kRegenBlock + tid;
-        const float4 res = wf.result[slot];
-        const uint32_t pixel = __float_as_uint(res.w);
-        // raygen.rgen:106-108: a NaN sample leaves the image untouched
-        if (!(isnan(res.x) || isnan(res.y) || isnan(res.z))) atomicAdd(&ra.accum[pixel], make_float4(res.x, res.y, res.z, 1.0f));
+    for (uint32_t i = tid; i < total; i += kRegenBlock) {
+        const uint32_t entry = s_list[i], slot = entry & 0x7fffffffu;
+        const unsigned long long work = s_base + i;
+        if (!(entry & 0x80000000u)) {      // (a path that left the scene was delivered by k_extend)
+            const float4 res = wf.result[slot];
+            const uint32_t pixel = __float_as_uint(res.w);
+            // raygen.rgen:106-108: a NaN sample leaves the image untouched
+            if (!(isnan(res.x) || isnan(res.y) || isnan(res.z))) atomicAdd(&ra.accum[pixel], make_float4(res.x, res.y, res.z, 1.0f));
+        }
         if (work < ra.totalWork) {
             float4 o, d;
             uint32_t p;
             startPath(sc, wf, ra, slot, work, o, d, p);
         } else {
             wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kRetired));
+            wf.hitInst[slot] = GSB_NO_HIT;   // (not kInstDelivered any more: a retired slot must not be taken for an ended path again)
             *rayDirection(wf, slot) = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kFlagDead));
             if (wf.sortKey) wf.sortKey[slot] = 0xffffffffu;   // sorts behind every live ray
             retired++;
         }
-        work++;
     }
     // live-slot count: one atomic per warp that retired something
     for (int o = 16; o > 0; o >>= 1) retired += __shfl_xor_sync(0xffffffffu, retired, o);
@@ -285,6 +305,9 @@ struct ExtendSource {
         if (idx == kNoTag) return false;
         const float4 o = *rayOrigin(wf, slot), d = *rayDirection(wf, slot);
         if (__float_as_uint(d.w) & kFlagDead) return false;
+#if GSB_MISS_DELIVERS
+        prefetchL2(wf.result + slot);   // should the ray leave the scene, its sample is read at hand-in: have it in L2 by then
+#endif
         job.ox = o.x; job.oy = o.y; job.oz = o.z;
         job.dx = d.x; job.dy = d.y; job.dz = d.z;
         job.tmin = 0.0f; job.tmax = 1e10f;                              // raygen.rgen:54-58
@@ -298,6 +321,27 @@ struct ExtendSource {
     // added) is also what k_regen reads as "this path has ended"
     GSB_D void commit(bool have, const HitRecord& hit, uint32_t slot, uint32_t) {
         if (!have) return;
+#if GSB_MISS_DELIVERS
+        if (hit.inst == GSB_NO_HIT) {
+            // miss.rmiss: the path has ended, and nothing is pending for it (its last shadow ray was resolved before this
+            // launch): the sample goes to the image right here (raygen.rgen:84-108) — k_regen then only starts the slot's
+            // next path and touches neither the sample nor the image.  With an environment emitter its radiance joins first.
+            float4 res = wf.result[slot];
+            if (sc.env.type) {
+                const float4 rd = *rayDirection(wf, slot);
+                const uint32_t flags = __float_as_uint(rd.w);
+                float4 wdw = make_float4(1.0f, 1.0f, 1.0f, 1.0f);
+                if ((flags & 0xffffu) != 0u) wdw = wf.weightDW[slot];
+                const bool plain = !sc.params.nee || (flags & kFlagCountEmitted) || (flags & kFlagWasDelta);
+                const float3 e = envRadiance(sc.env, xyz(rd)) * xyz(wdw) * (plain ? 1.0f : wdw.w);
+                const float cutoff = sc.params.cutoff;
+                if ((e.x != 0.0f || e.y != 0.0f || e.z != 0.0f) && e.x < cutoff && e.y < cutoff && e.z < cutoff) { res.x += e.x; res.y += e.y; res.z += e.z; }
+            }
+            if (!(isnan(res.x) || isnan(res.y) || isnan(res.z))) atomicAdd(&ra.accum[__float_as_uint(res.w)], make_float4(res.x, res.y, res.z, 1.0f));
+            wf.hitInst[slot] = kInstDelivered;
+            return;
+        }
+#endif
         wf.hitInst[slot] = hit.inst;
         if (hit.inst == GSB_NO_HIT && sc.env.type) {
             // the ray left the scene: radiance of the environment emitter (extension), weighted like a surface emitter
