@@ -266,7 +266,9 @@ def traversal_roofline(bvh, peaks, ext_fetch, sh_fetch, stage, iters, ext_rays, 
     """`roofline` of the dominant kernel (k_extend) + the side figures of k_shadow and k_shade, from per-stage CUDA-event
     times on the render stream.  Bound: L2 when the BVH fits the 126 MB L2 with room to spare (configs[1], [2]), HBM
     otherwise (configs[3]) — SURVEY 8(d)."""
-    ext_b, sh_b = ray_bytes(ext_fetch, 32 + 24), ray_bytes(sh_fetch, 32 + 4)
+    # a ray that leaves the scene also reads its path's sample (16 B) and adds it to the image (16 B read-modify-write) in k_extend
+    miss_frac = max(0.0, 1.0 - vertices / ext_rays) if ext_rays else 0.0
+    ext_b, sh_b = ray_bytes(ext_fetch, 32 + 24 + miss_frac * 48), ray_bytes(sh_fetch, 32 + 4)
     ext_ms, sh_ms, shade_ms = stage["extend"] / max(iters, 1), stage["shadow"] / max(iters, 1), stage["shade"] / max(iters, 1)
     achieved = ext_b * (ext_rays / max(iters, 1)) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
     sh_achieved = sh_b * (sh_rays / max(iters, 1)) / (sh_ms * 1e-3) / 1e9 if sh_ms > 0 else 0.0
@@ -285,7 +287,7 @@ def traversal_roofline(bvh, peaks, ext_fetch, sh_fetch, stage, iters, ext_rays, 
             "frac_of_hbm_peak": achieved / peaks["hbm"], "hbm_peak": peaks["hbm"], "l2_peak": peaks["l2"],
             "frac_of_l2_peak": (achieved / peaks["l2"]) if peaks["l2"] else None,
             "bytes_per_ray": ext_b, "rays_per_launch": ext_rays / max(iters, 1), "ms_per_launch": ext_ms,
-            "fetch_per_ray": ext_fetch, "launches": iters,
+            "fetch_per_ray": ext_fetch, "miss_fraction": miss_frac, "launches": iters,
             "share_of_step": {k: v / total for k, v in stage.items()} if total > 0 else None,
             "shadow": {"bytes_per_ray": sh_b, "fetch_per_ray": sh_fetch, "achieved": sh_achieved, "ms_per_launch": sh_ms,
                        "frac": sh_achieved / peak if peak else None},
