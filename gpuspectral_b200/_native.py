@@ -108,6 +108,7 @@ CORE_API = {
     "gsb_trace_batch": (C.c_int, [_P, C.POINTER(Ray), C.c_uint32, C.POINTER(Hit), C.c_int]),
     "gsb_trace_batch_stats": (C.c_int, [_P, C.POINTER(Ray), C.c_uint32, C.POINTER(Hit), C.c_int]),
     "gsb_trace_batch_timed": (C.c_int, [_P, C.POINTER(Ray), C.c_uint32, C.c_int, C.c_int, C.POINTER(C.c_double)]),
+    "gsb_trace_batch_static": (C.c_int, [_P, C.POINTER(Ray), C.c_uint32, C.POINTER(Hit), C.c_int]),
     "gsb_test_rng": (C.c_int, [_P, _u32p, _u32p, C.c_uint32, C.c_uint32, _u32p]),
     "gsb_test_camera_rays": (C.c_int, [_P, C.c_uint32, C.c_uint32, _u32p, _u32p, C.c_uint32, C.POINTER(Ray)]),
     "gsb_test_bsdf_sample": (C.c_int, [_P, C.c_uint32, _f32p, _u32p, C.c_uint32, _f32p, _f32p, _f32p, _u32p, _u32p]),

@@ -360,6 +360,17 @@ class Context:
                "gsb_trace_batch")
         return hits
 
+    STATIC_BATCH_MAX_RAYS = 65536
+
+    def trace_batch_static(self, rays, any_hit=False):
+        """gsb_trace_batch_static: the same hits as trace_batch with no device allocation (scratch in a static
+        device array of the library, at most STATIC_BATCH_MAX_RAYS rays per call; calls on one device must not overlap)."""
+        rays = np.ascontiguousarray(rays, RAY_DTYPE)
+        hits = np.zeros(len(rays), HIT_DTYPE)
+        _check(N.core.gsb_trace_batch_static(self._c, rays.ctypes.data_as(C.POINTER(N.Ray)), len(rays),
+                                             hits.ctypes.data_as(C.POINTER(N.Hit)), int(any_hit)), "gsb_trace_batch_static")
+        return hits
+
     def trace_batch_timed(self, rays, any_hit=False, repeats=10):
         rays = np.ascontiguousarray(rays, RAY_DTYPE)
         ms = C.c_double()

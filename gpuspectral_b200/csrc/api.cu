@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -324,6 +325,35 @@ void drain(gsb_context* ctx) {
 }  // namespace gsb
 
 using namespace gsb;
+
+// ---- gsb_trace_batch_static: the ray-batch entry for callers that may not allocate ---------------------
+// Scratch of that entry, held by every GPU that loads this library until the process exits: a control block (the
+// kernel's work counter and traversal-stack overflow flag, the ST_* words k_traceBatch touches), then the device
+// copies of the caller's rays and of the hits.  In HOST code the name below is only a stand-in for the symbol, not a
+// device address: a kernel is given the pointer cudaGetSymbolAddress returns for the device that is current.
+constexpr size_t kStaticControlBytes = 256;
+static_assert(ST_COUNT * sizeof(unsigned long long) <= kStaticControlBytes, "control block too small");
+constexpr size_t kStaticRaysOffset = kStaticControlBytes;
+constexpr size_t kStaticHitsOffset = kStaticRaysOffset + (size_t)GSB_STATIC_BATCH_MAX_RAYS * sizeof(gsb_ray);
+constexpr size_t kStaticScratchBytes = kStaticHitsOffset + (size_t)GSB_STATIC_BATCH_MAX_RAYS * sizeof(gsb_hit);
+static_assert(kStaticHitsOffset % 16 == 0, "hit array must keep 16-byte alignment");
+static __device__ __align__(256) unsigned char g_staticBatchScratch[kStaticScratchBytes];
+
+// Device address of the scratch on `device`, which must be the current device: resolved once per device.
+static unsigned char* staticBatchScratch(int device) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex lock;
+    static unsigned char* address[kMaxDevices] = {};
+    if (device < 0 || device >= kMaxDevices) throw std::runtime_error("gsb_trace_batch_static: device ordinal out of range");
+    std::lock_guard<std::mutex> hold(lock);
+    if (!address[device]) {
+        void* p = nullptr;
+        GSB_CUDA(cudaGetSymbolAddress(&p, g_staticBatchScratch));
+        if (!p) throw std::runtime_error("gsb_trace_batch_static: cudaGetSymbolAddress returned no address");
+        address[device] = static_cast<unsigned char*>(p);
+    }
+    return address[device];
+}
 
 // transformInvT = glm::inverse(glm::transpose(M)) (PathTracer.cpp:62) in float32: glm's 4x4 inverse is the cofactor
 // expansion of external/glm/glm/detail/func_matrix.inl:294-352; restated operation for operation so that the normal
@@ -1268,6 +1298,52 @@ gsb_status gsb_trace_batch_stats(gsb_context* ctx, const gsb_ray* rays, uint32_t
 gsb_status gsb_trace_batch_timed(gsb_context* ctx, const gsb_ray* rays, uint32_t count, int any_hit, int repeats, double* out_ms_per_launch) {
     if (!out_ms_per_launch || repeats < 1) return fail(GSB_ERR_INVALID, "gsb_trace_batch_timed: bad argument");
     return traceBatch(ctx, rays, count, nullptr, any_hit, false, repeats, out_ms_per_launch);
+}
+
+// No counterpart in the reference.  gsb_trace_batch with its scratch
+// (device rays, device hits, work counter) in g_staticBatchScratch instead of cudaMalloc'ed memory: no cudaMalloc /
+// cudaFree / cudaMallocAsync, no event or stream creation, no allocating library call.  All calls on a device share
+// the array, so calls that overlap on the GPU (two contexts on different streams, two threads) race; the control block
+// is cleared at the start of every call, rays and hits are fully overwritten for the `count` entries used.
+gsb_status gsb_trace_batch_static(gsb_context* ctx, const gsb_ray* rays, uint32_t count, gsb_hit* out_hits, int any_hit) {
+    if (!ctx || (count && (!rays || !out_hits))) return fail(GSB_ERR_INVALID, "gsb_trace_batch_static: null argument");
+    if (count > GSB_STATIC_BATCH_MAX_RAYS)
+        return fail(GSB_ERR_INVALID, "gsb_trace_batch_static: " + std::to_string(count) + " rays exceed the static scratch of " +
+                                         std::to_string((unsigned)GSB_STATIC_BATCH_MAX_RAYS) + " rays (GSB_STATIC_BATCH_MAX_RAYS); split the batch or use gsb_trace_batch");
+    if (!sceneReady(ctx)) return fail(GSB_ERR_STATE, "gsb_trace_batch_static: no scene (call gsb_scene_set_instances first)");
+    if (!ctx->pending.empty())
+        return fail(GSB_ERR_STATE, "gsb_trace_batch_static: an asynchronous gsb_render is pending (call gsb_synchronize first)");
+    if (count == 0) return GSB_OK;
+    return guarded([&]() -> gsb_status {
+        Bind bind(ctx->device);
+        unsigned char* base = staticBatchScratch(ctx->device);
+        unsigned long long* control = reinterpret_cast<unsigned long long*>(base);
+        gsb_ray* dRays = reinterpret_cast<gsb_ray*>(base + kStaticRaysOffset);
+        gsb_hit* dHits = reinterpret_cast<gsb_hit*>(base + kStaticHitsOffset);
+        cudaStream_t s = ctx->stream;
+        GSB_CUDA(cudaMemsetAsync(control, 0, kStaticControlBytes, s));   // work counter and overflow flag start at zero
+        GSB_CUDA(cudaMemcpyAsync(dRays, rays, (size_t)count * sizeof(gsb_ray), cudaMemcpyHostToDevice, s));
+        const SceneDev sc = ctx->sceneDev();
+        const bool hasInst = ctx->numTraceInstances > 0;
+        const bool pool = any_hit ? ctx->poolShadow : ctx->poolExtend;   // the traversal variant the render kernels of this scene use
+        using BatchKernel = void (*)(SceneDev, const gsb_ray*, uint32_t, gsb_hit*, unsigned long long*, uint32_t);
+        static const BatchKernel kernels[8] = {
+            k_traceBatch<false, false, false, false>, k_traceBatch<false, false, true, false>, k_traceBatch<true, false, false, false>, k_traceBatch<true, false, true, false>,
+            k_traceBatch<false, false, false, true>,  k_traceBatch<false, false, true, true>,  k_traceBatch<true, false, false, true>,  k_traceBatch<true, false, true, true>};
+        const BatchKernel kernel = kernels[(pool ? 4 : 0) | (any_hit ? 2 : 0) | (hasInst ? 1 : 0)];
+        int sms = 148, perSm = 4;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, (const void*)kernel, kTraceBlock, 0);
+        const int grid = std::max(1, std::min((int)((count + kTraceBlock - 1) / kTraceBlock), sms * std::max(perSm, 1)));
+        kernel<<<grid, kTraceBlock, 0, s>>>(sc, dRays, count, dHits, control, any_hit ? ctx->shadowControl : ctx->refillMin);
+        GSB_CUDA(cudaGetLastError());
+        unsigned long long overflow = 0;
+        GSB_CUDA(cudaMemcpyAsync(out_hits, dHits, (size_t)count * sizeof(gsb_hit), cudaMemcpyDeviceToHost, s));
+        GSB_CUDA(cudaMemcpyAsync(&overflow, control + ST_OVERFLOW, sizeof(overflow), cudaMemcpyDeviceToHost, s));
+        GSB_CUDA(cudaStreamSynchronize(s));
+        if (overflow) throw std::runtime_error("traversal stack overflow: BVH deeper than the traversal stack");
+        return GSB_OK;
+    });
 }
 
 // ---- diagnostics ------------------------------------------------------------------------------------

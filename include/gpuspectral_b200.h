@@ -275,6 +275,21 @@ GSB_API gsb_status gsb_trace_batch_stats(gsb_context* ctx, const gsb_ray* rays, 
  * traversal kernel `repeats` times and reports the mean kernel time in ms. */
 GSB_API gsb_status gsb_trace_batch_timed(gsb_context* ctx, const gsb_ray* rays, uint32_t count,
                                          int any_hit, int repeats, double* out_ms_per_launch);
+/* No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same rays in, same hits out as gsb_trace_batch, but the device copies of the rays and hits
+ * and the kernel's work counter live in a file-scope `static __device__` array of the library
+ * (256 B + GSB_STATIC_BATCH_MAX_RAYS * (32 + 20) B = 3.25 MiB, held by every GPU that loads the
+ * library until the process exits): the call makes no cudaMalloc / cudaFree / cudaMallocAsync and
+ * no other allocating CUDA or library call.  count > GSB_STATIC_BATCH_MAX_RAYS is rejected with
+ * GSB_ERR_INVALID (split the batch, or use gsb_trace_batch); a pending asynchronous gsb_render is
+ * rejected with GSB_ERR_STATE (call gsb_synchronize first).  Every call on a device shares the
+ * array and finds the previous call's contents in it (the control words are cleared per call, the
+ * used ray/hit entries are overwritten): calls that overlap on the GPU - two contexts or two host
+ * threads on the same device - race and must be serialised by the caller. */
+#define GSB_STATIC_BATCH_MAX_RAYS 65536u
+GSB_API gsb_status gsb_trace_batch_static(gsb_context* ctx, const gsb_ray* rays, uint32_t count,
+                                          gsb_hit* out_hits, int any_hit);
 
 /* ---- diagnostic entry points (unit parity against the oracle) ---------------------- */
 /* Seeds exactly as raygen.rgen:37 for pixel-linear index idx and frame `timestamp`, then
