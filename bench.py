@@ -306,7 +306,7 @@ def traversal_roofline(bvh, peaks, ext_fetch, sh_fetch, stage, iters, ext_rays, 
 def build_roofline(bvh, peaks):
     """BVH build against the HBM roofline: per unique triangle 48 B of vertices in, 144 B of leaf records
     out, ~10 B of 8-wide nodes, and the (key, index) radix sort's four passes over 12 B in + 12 B out; build_ms is the
-    device-event time of all BLAS + TLAS builds of the scene, host synchronisation between levels included."""
+    device-event time of the batched BLAS build + world level + TLAS of the scene (queueing by the host included)."""
     tris = bvh.get("unique_triangles", 0) + bvh.get("baked_triangles", 0)
     ms = bvh.get("build_ms", 0.0)
     if not tris or ms <= 0:

@@ -676,8 +676,9 @@ gsb_status gsb_mesh_create_uv(gsb_context* ctx, const float* positions3, const f
         }
         m.vpos = uploadArray(p4.data(), nverts, ctx->stream);
         m.vnrm = uploadArray(n4.data(), nverts, ctx->stream);
-        buildBlas(m.vpos, m.ntris, ctx->stream, m.blas);
-        GSB_CUDA(cudaStreamSynchronize(ctx->stream));
+        // The bottom level is built when the instance list first needs it (gsb_scene_set_instances): the meshes of a scene
+        // are then built side by side in one batch, and a mesh that is only ever baked into the world level needs none.
+        GSB_CUDA(cudaStreamSynchronize(ctx->stream));   // p4 / n4 go out of scope
         uint32_t id = (uint32_t)ctx->meshes.size();
         for (uint32_t k = 0; k < ctx->meshes.size(); k++)
             if (!ctx->meshes[k].alive) { id = k; break; }
@@ -842,6 +843,18 @@ static void rebuildScene(gsb_context* ctx) {
     for (uint32_t i = 0; i < count; i++) {
         const uint32_t nt = ctx->meshes[ctx->instances[i].mesh].ntris;
         if (nt > 0 && nt <= kBakeMaxTris && baked + nt <= kBakeBudget) { ctx->bakeOffset[i] = baked; baked += nt; }
+    }
+    {   // bottom levels still missing for the meshes that are traced through one: all of them in one batch
+        std::vector<BlasBuildRequest> todo;
+        std::vector<bool> queued(ctx->meshes.size(), false);
+        for (uint32_t i = 0; i < count; i++) {
+            const uint32_t mi = ctx->instances[i].mesh;
+            MeshRec& m = ctx->meshes[mi];
+            if (ctx->bakeOffset[i] != ~0ull || m.blas.buffer || queued[mi]) continue;
+            queued[mi] = true;
+            todo.push_back(BlasBuildRequest{m.vpos, m.ntris, &m.blas, false});
+        }
+        if (!todo.empty()) buildBlasBatch(todo.data(), todo.size(), ctx->stream);
     }
     cudaFree(ctx->dWorldVerts);
     cudaFree(ctx->dWorldNrm);

@@ -44,6 +44,10 @@ constexpr float kBoxPadRel = 1.0f / 32768.0f;
 // every baked triangle) instead of the position of the triangle in the soup.
 // out.leafPrim keeps the input triangle index of every leaf position.
 void buildBlas(const float4* dVertices, uint32_t numTriangles, cudaStream_t stream, DeviceBvh& out, bool idsInVertices = false);
+// The bottom levels of several meshes in one call: the builds run side by side on a few streams and the host waits once
+// per phase instead of several times per mesh.  buildMs of every `out` = its share (by triangle count) of the batch time.
+struct BlasBuildRequest { const float4* vertices; uint32_t ntris; DeviceBvh* out; bool idsInVertices; };
+void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t stream);
 
 // Bake rule (shared with the checker): in gl_InstanceID order an instance whose mesh has at most
 // kBakeMaxTris triangles is stored in world space at the world level, while the baked total stays within kBakeBudget.

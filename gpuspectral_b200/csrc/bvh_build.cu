@@ -13,8 +13,12 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <memory>
 #include <stdexcept>
 #include <vector>
 
@@ -56,6 +60,42 @@ __global__ void k_initBounds(BoundsAcc* b) {
     }
 }
 
+// Everything one build keeps on the device for the host to read ONCE, when the build has run: the build itself never
+// waits for the host (round 2 synchronised 6 times per mesh: bounds, two collapse batches, SAH cost, final sizes, timer).
+constexpr int kMaxLevels = 64;   // of 8-wide nodes
+struct BuildFrame {
+    float cmin[3], cinv[3];   // Morton frame: centroid -> [0, 1)
+    float pad;                // absolute padding of the primitive boxes
+    float lo[3], hi[3];       // padded bounds of the level
+};
+struct BuildControl {
+    uint32_t counters[4];     // [0] nodes allocated, [1] leaf positions allocated, [2] blocks of the running wide launch that have ended
+    uint32_t level;           // the level the next collapse launch works on
+    uint32_t reserved;
+    double cost[2];           // SAH cost of the binary tree before / after the treelet passes
+    BuildFrame frame;
+    uint32_t levelCount[kMaxLevels + 2];   // items (= nodes) per level
+};
+
+// the frame of a triangle level from its vertex bounds, with the float operations the host used to do
+__global__ void k_blasFrame(const BoundsAcc* acc, BuildFrame* f) {
+    float scale = 0.0f;
+    float lo[3], hi[3];
+    for (int a = 0; a < 3; a++) {
+        lo[a] = floatFromOrdered(acc->lo[a]);
+        hi[a] = floatFromOrdered(acc->hi[a]);
+        scale = fmaxf(scale, fmaxf(fabsf(lo[a]), fabsf(hi[a])));
+    }
+    const float pad = __fmul_rn(scale, kBoxPadRel);
+    f->pad = pad;
+    for (int a = 0; a < 3; a++) {
+        f->cmin[a] = lo[a];
+        f->cinv[a] = hi[a] > lo[a] ? __fdiv_rn(1.0f, __fsub_rn(hi[a], lo[a])) : 0.0f;
+        f->lo[a] = __fsub_rn(lo[a], pad);
+        f->hi[a] = __fadd_rn(hi[a], pad);
+    }
+}
+
 // bounds of all vertices of a triangle soup
 __global__ void k_vertexBounds(const float4* __restrict__ v, uint32_t nverts, BoundsAcc* acc) {
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
@@ -82,9 +122,11 @@ __global__ void k_vertexBounds(const float4* __restrict__ v, uint32_t nverts, Bo
 }
 
 // padded primitive boxes of triangles
-__global__ void k_triBoxes(const float4* __restrict__ v, uint32_t ntris, float pad, float4* __restrict__ plo, float4* __restrict__ phi) {
+__global__ void k_triBoxes(const float4* __restrict__ v, uint32_t ntris, const BuildFrame* __restrict__ frame, float4* __restrict__ plo,
+                           float4* __restrict__ phi) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= ntris) return;
+    const float pad = frame->pad;
     const float4 a = __ldg(v + 3 * (size_t)i), b = __ldg(v + 3 * (size_t)i + 1), c = __ldg(v + 3 * (size_t)i + 2);
     plo[i] = make_float4(fminf(a.x, fminf(b.x, c.x)) - pad, fminf(a.y, fminf(b.y, c.y)) - pad, fminf(a.z, fminf(b.z, c.z)) - pad, 0.0f);
     phi[i] = make_float4(fmaxf(a.x, fmaxf(b.x, c.x)) + pad, fmaxf(a.y, fmaxf(b.y, c.y)) + pad, fmaxf(a.z, fmaxf(b.z, c.z)) + pad, 0.0f);
@@ -100,10 +142,12 @@ __device__ inline uint64_t spread21(uint32_t x) {
     return v;
 }
 
-__global__ void k_morton(const float4* __restrict__ plo, const float4* __restrict__ phi, uint32_t n, float3 cmin, float3 cinv,
+__global__ void k_morton(const float4* __restrict__ plo, const float4* __restrict__ phi, uint32_t n, const BuildFrame* __restrict__ frame,
                          uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    const float3 cmin = make_float3(frame->cmin[0], frame->cmin[1], frame->cmin[2]);
+    const float3 cinv = make_float3(frame->cinv[0], frame->cinv[1], frame->cinv[2]);
     const float4 lo = plo[i], hi = phi[i];
     const float cx = (0.5f * (lo.x + hi.x) - cmin.x) * cinv.x;
     const float cy = (0.5f * (lo.y + hi.y) - cmin.y) * cinv.y;
@@ -228,15 +272,14 @@ struct CollapseArgs {
     const uint32_t* sorted;
     uint4* nodes;          // output nodes, 5 x uint4 each
     uint32_t* leafPrim;    // output: primitive index per leaf position
-    uint32_t* counters;    // [0] nodes allocated, [1] leaf positions allocated
-    uint32_t* levelCount;  // items per level: a launch reads its own entry and appends to the next one
+    BuildControl* ctl;     // node / leaf allocation counters, the current level and the items per level
     uint32_t maxLeaf;      // primitives per leaf child (one box per leaf child): 1..3
 };
 
 __device__ inline uint32_t refCount(const BinTree& t, int ref) { return ref >= 0 ? t.last[ref] - t.first[ref] + 1u : 1u; }
 __device__ inline uint32_t refFirst(const BinTree& t, int ref) { return ref >= 0 ? t.first[ref] : (uint32_t)~ref; }
 
-__device__ void emitNode(const CollapseArgs& a, uint32_t outNode, float4 nlo, float4 nhi, const int* child, int nc,
+__device__ void emitNode(const CollapseArgs& a, uint32_t level, uint32_t outNode, float4 nlo, float4 nhi, const int* child, int nc,
                          CollapseItem* next) {
     // classify + boxes
     float4 clo[8], chi[8];
@@ -278,9 +321,9 @@ __device__ void emitNode(const CollapseArgs& a, uint32_t outNode, float4 nlo, fl
         if (internal[k]) nInternal++;
         else nLeafPrims += refCount(a.t, child[k]);
     }
-    const uint32_t childBase = nInternal ? atomicAdd(&a.counters[0], nInternal) : 0u;
-    const uint32_t leafBase = nLeafPrims ? atomicAdd(&a.counters[1], nLeafPrims) : 0u;
-    const uint32_t itemBase = nInternal ? atomicAdd(a.levelCount + 1, nInternal) : 0u;
+    const uint32_t childBase = nInternal ? atomicAdd(&a.ctl->counters[0], nInternal) : 0u;
+    const uint32_t leafBase = nLeafPrims ? atomicAdd(&a.ctl->counters[1], nLeafPrims) : 0u;
+    const uint32_t itemBase = nInternal ? atomicAdd(&a.ctl->levelCount[level + 1], nInternal) : 0u;
 
     // quantisation frame
     const float p[3] = {nlo.x, nlo.y, nlo.z};
@@ -336,18 +379,14 @@ __device__ void emitNode(const CollapseArgs& a, uint32_t outNode, float4 nlo, fl
     out[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
 }
 
-// One level of the collapse.  The launch is sized for the most items the level can hold (min(8^level, n)); how many it
-// really holds is read from a.levelCount[0] on the device, so consecutive levels need no host synchronisation in between.
-__global__ void k_collapse(CollapseArgs a, const CollapseItem* __restrict__ items, CollapseItem* next) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.levelCount[0]) return;
-    const CollapseItem it = items[i];
+// One item of a level: the binary node it stands for is opened greedily (the internal child with the largest surface
+// area first) until 8 slots are used, and the 8-wide node is emitted.
+__device__ void collapseItem(const CollapseArgs& a, uint32_t level, const CollapseItem it, CollapseItem* next) {
     const int b = it.binNode;
     int child[8];
     int nc = 2;
     child[0] = a.t.left[b];
     child[1] = a.t.right[b];
-    // greedily open the internal child with the largest surface area until 8 slots are used
     while (nc < 8) {
         float bestArea = -1.0f;
         int bk = -1;
@@ -361,14 +400,73 @@ __global__ void k_collapse(CollapseArgs a, const CollapseItem* __restrict__ item
         child[bk] = a.t.left[x];
         child[nc++] = a.t.right[x];
     }
-    emitNode(a, it.outNode, a.t.lo[b], a.t.hi[b], child, nc, next);
+    emitNode(a, level, it.outNode, a.t.lo[b], a.t.hi[b], child, nc, next);
+}
+
+// The collapse runs level by level (node indices of a level are contiguous: the refit walks them bottom-up), and the host
+// does not know how many items a level holds or how deep the tree is.  Two kernels read both from the control block:
+// k_collapseNarrow, ONE block, works through consecutive levels while they hold at most `limit` items (limit 0: to the end
+// of the tree) - the first levels (1, 8, 64, 512 items) and whatever a deep, thin tree has left; k_collapseWide, a fixed
+// grid, does one level with a grid-stride loop, and the last of its blocks to end moves the control block to the next level.
+// The items of level l are read from buffer l & 1 and those of level l + 1 appended to the other one.
+__global__ void __launch_bounds__(256) k_collapseNarrow(CollapseArgs a, CollapseItem* bufA, CollapseItem* bufB, uint32_t limit) {
+    for (;;) {
+        const uint32_t level = *(volatile uint32_t*)&a.ctl->level;
+        if (level >= (uint32_t)kMaxLevels) return;
+        const uint32_t cnt = *(volatile uint32_t*)&a.ctl->levelCount[level];
+        if (cnt == 0u || (limit != 0u && cnt > limit)) return;
+        const CollapseItem* items = (level & 1u) ? bufB : bufA;
+        CollapseItem* next = (level & 1u) ? bufA : bufB;
+        for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) {
+            CollapseItem it;
+            it.binNode = __ldcg(&items[i].binNode);     // written by this kernel one level earlier: not through the read-only path
+            it.outNode = __ldcg(&items[i].outNode);
+            collapseItem(a, level, it, next);
+        }
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) *(volatile uint32_t*)&a.ctl->level = level + 1u;
+        __threadfence();
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(128) k_collapseWide(CollapseArgs a, CollapseItem* bufA, CollapseItem* bufB) {
+    // every block reads the same level: it only changes when all blocks of this launch have ended
+    const uint32_t level = *(volatile uint32_t*)&a.ctl->level;
+    const uint32_t cnt = level < (uint32_t)kMaxLevels ? *(volatile uint32_t*)&a.ctl->levelCount[level] : 0u;
+    const CollapseItem* items = (level & 1u) ? bufB : bufA;
+    CollapseItem* next = (level & 1u) ? bufA : bufB;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < cnt; i += gridDim.x * blockDim.x) collapseItem(a, level, items[i], next);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t ended = atomicAdd(&a.ctl->counters[2], 1u);
+        if (ended == gridDim.x - 1u) {
+            a.ctl->counters[2] = 0u;
+            if (cnt) a.ctl->level = level + 1u;
+            __threadfence();
+        }
+    }
+}
+
+// start of a collapse: the root item, one node allocated, one item on level 0
+__global__ void k_collapseStart(BuildControl* ctl, CollapseItem* bufA) {
+    ctl->counters[0] = 1u;
+    ctl->counters[1] = 0u;
+    ctl->counters[2] = 0u;
+    ctl->level = 0u;
+    ctl->levelCount[0] = 1u;
+    bufA[0] = CollapseItem{0, 0u};
 }
 
 // n == 1: a root with a single leaf slot
 __global__ void k_singleLeafRoot(CollapseArgs a) {
     const int child[1] = {~0};
-    a.counters[1] = 0;
-    emitNode(a, 0u, a.plo[a.sorted[0]], a.phi[a.sorted[0]], child, 1, nullptr);
+    a.ctl->counters[0] = 1u;
+    a.ctl->counters[1] = 0u;
+    a.ctl->levelCount[0] = 1u;
+    emitNode(a, 0u, 0u, a.plo[a.sorted[0]], a.phi[a.sorted[0]], child, 1, nullptr);
 }
 
 __global__ void k_emptyRoot(uint4* nodes) {
@@ -409,12 +507,28 @@ T* dalloc(size_t count, cudaStream_t s) {
     return (T*)p;
 }
 
+// Temporaries of a build, stream-ordered.  With a capacity the pool is ONE cudaMallocAsync block that get() carves up
+// (a build makes ~30 requests, and at ~20 us each the requests of the 17 meshes of the field scene cost more host time
+// than the GPU needs for the builds); what does not fit, and every request of a pool without capacity, is its own block.
 struct TempPool {
     cudaStream_t s;
     std::vector<void*> ptrs;
-    explicit TempPool(cudaStream_t st) : s(st) {}
+    uint8_t* arena = nullptr;
+    size_t capacity = 0, used = 0;
+    explicit TempPool(cudaStream_t st, size_t arenaBytes = 0) : s(st), capacity(arenaBytes) {
+        if (capacity) {
+            arena = dalloc<uint8_t>(capacity, s);
+            ptrs.push_back(arena);
+        }
+    }
     template <class T>
     T* get(size_t count) {
+        const size_t bytes = (std::max<size_t>(count, 1) * sizeof(T) + 255) & ~(size_t)255;
+        if (used + bytes <= capacity) {
+            T* p = reinterpret_cast<T*>(arena + used);
+            used += bytes;
+            return p;
+        }
         T* p = dalloc<T>(count, s);
         ptrs.push_back(p);
         return p;
@@ -424,50 +538,61 @@ struct TempPool {
     }
 };
 
-// Generic build over padded primitive boxes already on the device.  Produces the node array
-// (temp, worst-case sized) and the primitive order of the leaves.
-struct GenericResult {
-    uint4* nodes;        // temp, from pool
-    uint32_t numNodes;
-    uint32_t* leafPrim;  // temp, from pool
+// One build in flight.  start() queues the whole pipeline on the job's stream without waiting for the host; collect()
+// reads the control block back (the one wait of a build); finish() allocates the final buffer and copies the nodes.
+struct BuildJob {
+    TempPool pool;
+    cudaStream_t s;
+    uint32_t n = 0;
+    bool topLevel = false;
+    bool refine = false;
+    uint4* nodes = nullptr;        // temp, worst-case sized
+    uint32_t* leafPrim = nullptr;  // temp: primitive index per leaf position
+    uint32_t numNodes = 1;
+    BuildControl* ctl = nullptr;   // device
+    BuildControl host;             // its copy after collect()
+    // 16 + 16 primitive boxes, 80 nodes, 4 leaf order, 24 keys / values twice, 60 binary tree, 16 collapse items, 16 + 32 treelet
+    // arrays per primitive, the sort's own temporaries (a second key / value buffer, 12 per primitive, and its histograms)
+    // and the 256-byte rounding of ~35 requests; a request that does not fit falls back to a block of its own
+    static size_t arenaBytes(uint32_t n) { return (size_t)std::max<uint32_t>(n, 1) * 292 + (128u << 10); }
+    BuildJob(cudaStream_t st, uint32_t count) : pool(st, arenaBytes(count)), s(st) { memset(&host, 0, sizeof(host)); }
+
+    // the control block, zeroed; the caller then fills ctl->frame (k_blasFrame, or a copy of a host frame)
+    void begin(uint32_t count, bool top) {
+        n = count;
+        topLevel = top;
+        ctl = pool.get<BuildControl>(1);
+        GSB_CUDA(cudaMemsetAsync(ctl, 0, sizeof(BuildControl), s));
+    }
+    void start(const float4* plo, const float4* phi);
+    void collect(DeviceBvh& out);
 };
 
-GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi, uint32_t n, const float cmin[3], const float cmax[3],
-                           cudaStream_t s, DeviceBvh& out, bool topLevel) {
-    GenericResult r;
-    r.nodes = pool.get<uint4>((size_t)std::max<uint32_t>(n, 1) * 5);
-    r.leafPrim = pool.get<uint32_t>(n);
-    r.numNodes = 1;
-    out.levelEnd.assign(1, 1u);   // a single root unless the collapse below says otherwise
+void BuildJob::start(const float4* plo, const float4* phi) {
+    nodes = pool.get<uint4>((size_t)std::max<uint32_t>(n, 1) * 5);
+    leafPrim = pool.get<uint32_t>(n);
     if (n == 0) {
-        k_emptyRoot<<<1, 1, 0, s>>>(r.nodes);
-        return r;
+        k_emptyRoot<<<1, 1, 0, s>>>(nodes);
+        return;
     }
     const int B = 256;
     uint64_t* keys = pool.get<uint64_t>(n);
     uint64_t* keysSorted = pool.get<uint64_t>(n);
     uint32_t* vals = pool.get<uint32_t>(n);
     uint32_t* sorted = pool.get<uint32_t>(n);
-    float3 cm = make_float3(cmin[0], cmin[1], cmin[2]);
-    float3 ci;
-    ci.x = cmax[0] > cmin[0] ? 1.0f / (cmax[0] - cmin[0]) : 0.0f;
-    ci.y = cmax[1] > cmin[1] ? 1.0f / (cmax[1] - cmin[1]) : 0.0f;
-    ci.z = cmax[2] > cmin[2] ? 1.0f / (cmax[2] - cmin[2]) : 0.0f;
-    k_morton<<<(n + B - 1) / B, B, 0, s>>>(plo, phi, n, cm, ci, keys, vals);
+    k_morton<<<(n + B - 1) / B, B, 0, s>>>(plo, phi, n, &ctl->frame, keys, vals);
     size_t tempBytes = 0;
     GSB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tempBytes, keys, keysSorted, vals, sorted, (int)n, 0, 63, s));
     void* temp = pool.get<uint8_t>(tempBytes);
     GSB_CUDA(cub::DeviceRadixSort::SortPairs(temp, tempBytes, keys, keysSorted, vals, sorted, (int)n, 0, 63, s));
 
-    uint32_t* counters = pool.get<uint32_t>(4);
-    GSB_CUDA(cudaMemsetAsync(counters, 0, 4 * sizeof(uint32_t), s));
     CollapseArgs ca;
     ca.plo = plo;
     ca.phi = phi;
     ca.sorted = sorted;
-    ca.nodes = r.nodes;
-    ca.leafPrim = r.leafPrim;
-    ca.counters = counters;
+    ca.nodes = nodes;
+    ca.leafPrim = leafPrim;
+    ca.ctl = ctl;
     // Top level: one instance per leaf child, so that every instance is culled by a box of its own before the ray pays
     // for its transform and root fetch (with 3 per leaf the gallery entered 5.8 and the field 4.7 - 6.9 instances per ray).
     // Bottom level: up to GSB_MAX_LEAF (default 3) triangles share a leaf box.
@@ -477,7 +602,7 @@ GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi,
         memset(&ca.t, 0, sizeof(ca.t));
         k_singleLeafRoot<<<1, 1, 0, s>>>(ca);
         GSB_CUDA(cudaGetLastError());
-        return r;
+        return;
     }
     BinTree t;
     t.left = pool.get<int>(n - 1);
@@ -494,91 +619,96 @@ GenericResult buildGeneric(TempPool& pool, const float4* plo, const float4* phi,
     k_fitBoxes<<<(n + B - 1) / B, B, 0, s>>>(t, plo, phi, sorted, (int)n);
     GSB_CUDA(cudaGetLastError());
 
-    double* dCost = pool.get<double>(2);
-    GSB_CUDA(cudaMemsetAsync(dCost, 0, 2 * sizeof(double), s));
     const int costBlocks = (int)std::min<uint32_t>((n + B - 1) / B, 1024u);
-    k_sahCost<<<costBlocks, B, 0, s>>>(t, plo, phi, (int)n, dCost);
-    // Bottom level: two passes.  Top level: off by default — on the instanced test scene the refined TLAS lowered the SAH
+    k_sahCost<<<costBlocks, B, 0, s>>>(t, plo, phi, (int)n, &ctl->cost[0]);
+    // Bottom level: one pass (on one B200 the first pass buys the gallery +10 % paths/s and the field +1 %, a second one
+    // +-0.5 % on both at 4 ms of build time for the field's 5.2 M triangles: profiles/README.md, r2w; GSB_TREELET_PASSES=2
+    // brings it back).  Top level: off by default — on the instanced test scene the refined TLAS lowered the SAH
     // cost but raised the instances entered per ray (4.7 -> 6.1): the Morton order of the instance centroids gives a
     // better front-to-back visiting order than the SAH-optimal grouping (profiles/README.md, r1g).
-    int passes = (g_treelets && !topLevel) ? 2 : 0;
+    int passes = (g_treelets && !topLevel) ? 1 : 0;
     if (const char* e = getenv(topLevel ? "GSB_TREELET_PASSES_TLAS" : "GSB_TREELET_PASSES")) passes = atoi(e);
-    const bool refine = passes > 0 && n >= 16;
+    refine = passes > 0 && n >= 16;
     if (refine) {
-        refineTreelets(pool.s, t, plo, phi, sorted, (int)n, passes, [&](size_t bytes) { return (void*)pool.get<uint8_t>(bytes); });
+        refineTreelets(s, t, plo, phi, sorted, (int)n, passes, [&](size_t bytes) { return (void*)pool.get<uint8_t>(bytes); });
         ca.sorted = sorted;  // the refinement re-derives the leaf order
-        k_sahCost<<<costBlocks, B, 0, s>>>(t, plo, phi, (int)n, dCost + 1);
+        k_sahCost<<<costBlocks, B, 0, s>>>(t, plo, phi, (int)n, &ctl->cost[1]);
     }
 
-    // level-synchronous collapse
+    // collapse: the first levels in one block, the wide ones one launch each, the rest (if any) in one block again
     CollapseItem* itemsA = pool.get<CollapseItem>(n);
     CollapseItem* itemsB = pool.get<CollapseItem>(n);
     ca.t = t;
-    const CollapseItem rootItem = {0, 0u};
-    GSB_CUDA(cudaMemcpyAsync(itemsA, &rootItem, sizeof(rootItem), cudaMemcpyHostToDevice, s));
-    const uint32_t initCounters[4] = {1u, 0u, 0u, 0u};
-    GSB_CUDA(cudaMemcpyAsync(counters, initCounters, sizeof(initCounters), cudaMemcpyHostToDevice, s));
-    // Levels are launched in batches without waiting for the host: each launch is sized for the most items its level can
-    // hold and reads the real count on the device; after a batch the per-level counts come back and say whether the tree
-    // has ended (round 1 synchronised once per level: 117 times for the 17 meshes of the field scene).
-    constexpr int kMaxLevels = 64, kBatch = 6;
-    uint32_t* levelCount = pool.get<uint32_t>(kMaxLevels + 2);
-    GSB_CUDA(cudaMemsetAsync(levelCount, 0, (kMaxLevels + 2) * sizeof(uint32_t), s));
-    const uint32_t one = 1u;
-    GSB_CUDA(cudaMemcpyAsync(levelCount, &one, sizeof(one), cudaMemcpyHostToDevice, s));
-    uint32_t hostCounters[4] = {1u, 0u, 0u, 0u};
-    uint32_t hostLevels[kMaxLevels + 2] = {0};
-    out.levelEnd.clear();
-    int level = 0;
-    bool ended = false;
-    while (!ended && level < kMaxLevels) {
-        const int stop = std::min(level + kBatch, kMaxLevels);
-        for (int l = level; l < stop; l++) {
-            double cap = 1.0;
-            for (int k = 0; k < l && cap < (double)n; k++) cap *= 8.0;
-            const uint32_t most = (uint32_t)std::min<double>(cap, (double)n);
-            ca.levelCount = levelCount + l;
-            k_collapse<<<(most + 127) / 128, 128, 0, s>>>(ca, itemsA, itemsB);
-            std::swap(itemsA, itemsB);
+    k_collapseStart<<<1, 1, 0, s>>>(ctl, itemsA);
+    constexpr uint32_t kNarrowLimit = 512;
+    k_collapseNarrow<<<1, 256, 0, s>>>(ca, itemsA, itemsB, kNarrowLimit);
+    if (n > kNarrowLimit) {
+        int wide = 4;   // levels past the narrow ones that a balanced tree of n leaves needs, and a margin of four
+        for (double cap = (double)kNarrowLimit; cap < (double)n; cap *= 8.0) wide++;
+        static int maxBlocks = 0;
+        if (!maxBlocks) {
+            int dev = 0, sms = 148, perSm = 4;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, (const void*)k_collapseWide, 128, 0);
+            maxBlocks = sms * std::max(perSm, 1);
         }
-        GSB_CUDA(cudaMemcpyAsync(hostLevels, levelCount, sizeof(hostLevels), cudaMemcpyDeviceToHost, s));
-        GSB_CUDA(cudaMemcpyAsync(hostCounters, counters, sizeof(hostCounters), cudaMemcpyDeviceToHost, s));
-        GSB_CUDA(cudaStreamSynchronize(s));
-        level = stop;
-        ended = hostLevels[stop] == 0u;
+        const int blocks = (int)std::min<uint32_t>((n + 127) / 128, (uint32_t)maxBlocks);
+        for (int k = 0; k < wide; k++) k_collapseWide<<<blocks, 128, 0, s>>>(ca, itemsA, itemsB);
+        k_collapseNarrow<<<1, 256, 0, s>>>(ca, itemsA, itemsB, 0u);
     }
-    if (!ended) throw std::runtime_error("BVH collapse: tree deeper than 64 levels of 8-wide nodes");
-    // node index ranges of the levels: one node per item, levels emitted one after the other
-    uint32_t levelEnd = 0;
-    for (int l = 0; l < kMaxLevels && hostLevels[l] > 0u; l++) {
-        levelEnd += hostLevels[l];
-        out.levelEnd.push_back(levelEnd);
-    }
-    r.numNodes = hostCounters[0];
-    double hostCost[2] = {0, 0};
-    GSB_CUDA(cudaMemcpyAsync(hostCost, dCost, sizeof(hostCost), cudaMemcpyDeviceToHost, s));
-    GSB_CUDA(cudaStreamSynchronize(s));
-    out.sahBefore = hostCost[0];
-    out.sahAfter = refine ? hostCost[1] : hostCost[0];
-    return r;
+    GSB_CUDA(cudaGetLastError());
 }
 
+// Waits for the build and takes what the host needs from its control block: node count, level ranges, bounds, SAH cost.
+void BuildJob::collect(DeviceBvh& out) {
+    GSB_CUDA(cudaMemcpyAsync(&host, ctl, sizeof(BuildControl), cudaMemcpyDeviceToHost, s));
+    GSB_CUDA(cudaStreamSynchronize(s));
+    out.levelEnd.clear();
+    numNodes = 1;
+    if (n <= 1) {
+        out.levelEnd.assign(1, 1u);
+        out.sahBefore = out.sahAfter = 0.0;
+        return;
+    }
+    if (host.level >= (uint32_t)kMaxLevels || host.levelCount[host.level] != 0u)
+        throw std::runtime_error("BVH collapse: tree deeper than 64 levels of 8-wide nodes");
+    // node index ranges of the levels: one node per item, levels emitted one after the other
+    uint32_t levelEnd = 0;
+    for (int l = 0; l < kMaxLevels && host.levelCount[l] > 0u; l++) {
+        levelEnd += host.levelCount[l];
+        out.levelEnd.push_back(levelEnd);
+    }
+    numNodes = host.counters[0];
+    if (levelEnd != numNodes) throw std::runtime_error("BVH collapse: level counts do not add up to the node count");
+    out.sahBefore = host.cost[0];
+    out.sahAfter = refine ? host.cost[1] : host.cost[0];
+}
+
+struct GenericResult {
+    uint4* nodes;
+    uint32_t numNodes;
+    uint32_t* leafPrim;
+};
+
+// The final buffer: nodes, leaf records and, behind them, the leaf order (kept for the refit) in ONE block from the
+// stream-ordered pool (two cudaMalloc calls per mesh cost 0.6 ms of host time each on the field scene, with outliers of
+// tens of ms when the driver went to the OS); freeBvh returns it with cudaFree, which waits for the device as before.
 void finishBuffer(const GenericResult& r, uint32_t n, size_t leafBytes, cudaStream_t s, DeviceBvh& out) {
     const size_t nodeBytes = (size_t)r.numNodes * 80;
     out.numNodes = r.numNodes;
     out.numPrims = n;
     out.leafOffset16 = (uint32_t)(nodeBytes / 16);
     out.bytes = nodeBytes + (size_t)n * leafBytes;
+    const size_t orderOffset = (out.bytes + 255) & ~(size_t)255;
     void* buf = nullptr;
-    GSB_CUDA(cudaMalloc(&buf, std::max<size_t>(out.bytes, 16)));
+    GSB_CUDA(cudaMallocAsync(&buf, std::max<size_t>(orderOffset + (size_t)n * sizeof(uint32_t), 16), s));
     out.buffer = (uint4*)buf;
     GSB_CUDA(cudaMemcpyAsync(out.buffer, r.nodes, nodeBytes, cudaMemcpyDeviceToDevice, s));
     out.leafPrim = nullptr;
     if (n > 0) {
-        void* q = nullptr;
-        GSB_CUDA(cudaMalloc(&q, (size_t)n * sizeof(uint32_t)));
-        GSB_CUDA(cudaMemcpyAsync(q, r.leafPrim, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
-        out.leafPrim = (uint32_t*)q;
+        out.leafPrim = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(buf) + orderOffset);
+        GSB_CUDA(cudaMemcpyAsync(out.leafPrim, r.leafPrim, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
     }
 }
 
@@ -587,53 +717,112 @@ void finishBuffer(const GenericResult& r, uint32_t n, size_t leafBytes, cudaStre
 void setTreeletRefinement(bool enabled) { g_treelets = enabled; }
 
 void freeBvh(DeviceBvh& bvh) {
-    if (bvh.buffer) cudaFree(bvh.buffer);
-    if (bvh.leafPrim) cudaFree(bvh.leafPrim);
+    if (bvh.buffer) cudaFree(bvh.buffer);   // leafPrim lives in the same block
     bvh = DeviceBvh();
 }
 
-void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out, bool idsInVertices) {
+// Bottom levels of several meshes at once.  Every build is a chain of dependent launches whose tail (the last levels of the
+// bottom-up treelet and box passes, the first levels of the collapse) leaves most of the GPU idle, so the builds of a batch
+// run on up to kBuildStreams streams side by side and the host waits once per phase, not per mesh:
+//   phase 1  every job queued on its stream: bounds, boxes, Morton codes, sort, tree, treelets, collapse
+//   phase 2  control blocks read back (node counts), final buffers allocated, nodes copied, triangles packed
+// Jobs are taken in waves of at most kWaveTriangles so that the temporaries (~230 B per triangle) stay bounded.
+void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t s) {
+    if (count == 0) return;
+    size_t kBuildStreams = 8;
+    if (const char* e = getenv("GSB_BUILD_STREAMS")) kBuildStreams = (size_t)std::max(1, atoi(e));
+    constexpr uint64_t kWaveTriangles = 48ull << 20;
     cudaEvent_t e0, e1;
     GSB_CUDA(cudaEventCreate(&e0));
     GSB_CUDA(cudaEventCreate(&e1));
     GSB_CUDA(cudaEventRecord(e0, s));
-    {
-        TempPool pool(s);
-        const int B = 256;
-        float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
-        float pad = 0.0f;
-        float4* plo = pool.get<float4>(ntris);
-        float4* phi = pool.get<float4>(ntris);
-        if (ntris > 0) {
-            BoundsAcc* acc = pool.get<BoundsAcc>(1);
-            k_initBounds<<<1, 32, 0, s>>>(acc);
-            const uint32_t nverts = ntris * 3;
-            k_vertexBounds<<<(int)std::min<uint32_t>((nverts + B - 1) / B, 2048u), B, 0, s>>>(dVertices, nverts, acc);
-            BoundsAcc h;
-            GSB_CUDA(cudaMemcpyAsync(&h, acc, sizeof(h), cudaMemcpyDeviceToHost, s));
-            GSB_CUDA(cudaStreamSynchronize(s));
-            float scale = 0.0f;
-            for (int a = 0; a < 3; a++) {
-                lo[a] = floatFromOrdered(h.lo[a]);
-                hi[a] = floatFromOrdered(h.hi[a]);
-                scale = std::fmax(scale, std::fmax(std::fabs(lo[a]), std::fabs(hi[a])));
-            }
-            pad = scale * kBoxPadRel;
-            k_triBoxes<<<(ntris + B - 1) / B, B, 0, s>>>(dVertices, ntris, pad, plo, phi);
+    std::vector<cudaStream_t> streams;
+    cudaEvent_t joined = nullptr;
+    if (count > 1) {
+        streams.resize(std::min(count, kBuildStreams));
+        for (cudaStream_t& st : streams) {
+            GSB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+            GSB_CUDA(cudaStreamWaitEvent(st, e0, 0));
         }
-        GenericResult r = buildGeneric(pool, plo, phi, ntris, lo, hi, s, out, false);
-        finishBuffer(r, ntris, 144, s, out);
-        if (ntris > 0)
-            k_packTriangles<<<(ntris + B - 1) / B, B, 0, s>>>(r.leafPrim, ntris, dVertices,
-                                                              reinterpret_cast<float4*>(out.buffer + out.leafOffset16), idsInVertices);
-        GSB_CUDA(cudaGetLastError());
-        for (int a = 0; a < 3; a++) { out.lo[a] = lo[a] - pad; out.hi[a] = hi[a] + pad; }
+        GSB_CUDA(cudaEventCreateWithFlags(&joined, cudaEventDisableTiming));
+    }
+    const int B = 256;
+    const bool trace = getenv("GSB_BUILD_TRACE") != nullptr;
+    uint64_t totalTris = 0;
+    for (size_t i = 0; i < count; i++) totalTris += requests[i].ntris;
+    size_t first = 0;
+    while (first < count) {
+        size_t end = first;
+        uint64_t waveTris = 0;
+        while (end < count && (end == first || waveTris + requests[end].ntris <= kWaveTriangles)) waveTris += requests[end++].ntris;
+        std::vector<std::unique_ptr<BuildJob>> jobs;
+        const auto tWave = std::chrono::steady_clock::now();
+        for (size_t i = first; i < end; i++) {
+            const BlasBuildRequest& q = requests[i];
+            cudaStream_t js = streams.empty() ? s : streams[(i - first) % streams.size()];
+            jobs.emplace_back(new BuildJob(js, q.ntris));
+            BuildJob& j = *jobs.back();
+            j.begin(q.ntris, false);
+            float4* plo = j.pool.get<float4>(q.ntris);
+            float4* phi = j.pool.get<float4>(q.ntris);
+            if (q.ntris > 0) {
+                BoundsAcc* acc = j.pool.get<BoundsAcc>(1);
+                k_initBounds<<<1, 32, 0, js>>>(acc);
+                const uint32_t nverts = q.ntris * 3;
+                k_vertexBounds<<<(int)std::min<uint32_t>((nverts + B - 1) / B, 296u), B, 0, js>>>(q.vertices, nverts, acc);
+                k_blasFrame<<<1, 1, 0, js>>>(acc, &j.ctl->frame);
+                k_triBoxes<<<(q.ntris + B - 1) / B, B, 0, js>>>(q.vertices, q.ntris, &j.ctl->frame, plo, phi);
+            }
+            j.start(plo, phi);
+        }
+        const auto tIssued = std::chrono::steady_clock::now();
+        double msCollect = 0.0, msFinish = 0.0;
+        for (size_t i = first; i < end; i++) {
+            const BlasBuildRequest& q = requests[i];
+            BuildJob& j = *jobs[i - first];
+            DeviceBvh& out = *q.out;
+            const auto tc0 = std::chrono::steady_clock::now();
+            j.collect(out);
+            const auto tc1 = std::chrono::steady_clock::now();
+            msCollect += std::chrono::duration<double, std::milli>(tc1 - tc0).count();
+            const GenericResult r = {j.nodes, j.numNodes, j.leafPrim};
+            finishBuffer(r, q.ntris, 144, j.s, out);
+            if (q.ntris > 0)
+                k_packTriangles<<<(q.ntris + B - 1) / B, B, 0, j.s>>>(j.leafPrim, q.ntris, q.vertices,
+                                                                       reinterpret_cast<float4*>(out.buffer + out.leafOffset16), q.idsInVertices);
+            GSB_CUDA(cudaGetLastError());
+            for (int a = 0; a < 3; a++) {
+                out.lo[a] = q.ntris ? j.host.frame.lo[a] : 0.0f;
+                out.hi[a] = q.ntris ? j.host.frame.hi[a] : 0.0f;
+            }
+            msFinish += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tc1).count();
+        }
+        if (trace)
+            fprintf(stderr, "[gsb build] wave of %zu meshes, %llu triangles: queued in %.2f ms, waited %.2f ms for the control blocks, %.2f ms in allocation + pack launches\n",
+                    end - first, (unsigned long long)waveTris, std::chrono::duration<double, std::milli>(tIssued - tWave).count(), msCollect, msFinish);
+        jobs.clear();   // the temporaries go back to the pool in stream order
+        first = end;
+    }
+    for (cudaStream_t st : streams) {
+        GSB_CUDA(cudaEventRecord(joined, st));
+        GSB_CUDA(cudaStreamWaitEvent(s, joined, 0));
     }
     GSB_CUDA(cudaEventRecord(e1, s));
     GSB_CUDA(cudaEventSynchronize(e1));
-    GSB_CUDA(cudaEventElapsedTime(&out.buildMs, e0, e1));
+    float ms = 0.0f;
+    GSB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    // the batch time is shared out by triangle count, so that the per-mesh figures still add up to the time that passed
+    for (size_t i = 0; i < count; i++)
+        requests[i].out->buildMs = count == 1 ? ms : (totalTris ? ms * (float)((double)requests[i].ntris / (double)totalTris) : ms / (float)count);
+    for (cudaStream_t st : streams) cudaStreamDestroy(st);
+    if (joined) cudaEventDestroy(joined);
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
+}
+
+void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out, bool idsInVertices) {
+    const BlasBuildRequest q = {dVertices, ntris, &out, idsInVertices};
+    buildBlasBatch(&q, 1, s);
 }
 
 // ---- refit ---------------------------------------------------------------------------------------------------------
@@ -853,7 +1042,18 @@ void buildTlas(const float* hostLo, const float* hostHi, const TraceInstance* ho
             GSB_CUDA(cudaMemcpyAsync(phi, hi4.data(), (size_t)n * sizeof(float4), cudaMemcpyHostToDevice, s));
             GSB_CUDA(cudaMemcpyAsync(rec, hostRecords, (size_t)n * sizeof(TraceInstance), cudaMemcpyHostToDevice, s));
         }
-        GenericResult r = buildGeneric(pool, plo, phi, n, clo, chi, s, out, true);
+        BuildJob job(s, n);
+        job.begin(n, true);
+        BuildFrame frame;
+        memset(&frame, 0, sizeof(frame));
+        for (int a = 0; a < 3; a++) {
+            frame.cmin[a] = clo[a];
+            frame.cinv[a] = chi[a] > clo[a] ? 1.0f / (chi[a] - clo[a]) : 0.0f;
+        }
+        GSB_CUDA(cudaMemcpyAsync(&job.ctl->frame, &frame, sizeof(frame), cudaMemcpyHostToDevice, s));
+        job.start(plo, phi);
+        job.collect(out);
+        const GenericResult r = {job.nodes, job.numNodes, job.leafPrim};
         finishBuffer(r, n, sizeof(TraceInstance), s, out);
         if (n > 0) k_packInstances<<<(n + 255) / 256, 256, 0, s>>>(r.leafPrim, n, rec, out.buffer + out.leafOffset16);
         GSB_CUDA(cudaGetLastError());

@@ -33,28 +33,43 @@ struct TreeletScratch {   // per warp
     uint8_t subsetOf[6];
 };
 
-__device__ inline void treeletRefBox(const BinTree& t, const float4* __restrict__ plo, const float4* __restrict__ phi,
-                                     const uint32_t* __restrict__ sorted, int ref, float4& lo, float4& hi) {
+// slo / shi: the primitive boxes in sorted order (k_sortedBoxes), so that the box of a leaf reference is one load away
+__device__ inline void treeletRefBox(const BinTree& t, const float4* __restrict__ slo, const float4* __restrict__ shi, int ref, float4& lo,
+                                     float4& hi) {
     if (ref >= 0) {
         lo = __ldcg(t.lo + ref);
         hi = __ldcg(t.hi + ref);
     } else {
-        const uint32_t p = sorted[~ref];
-        lo = plo[p];
-        hi = phi[p];
+        lo = __ldg(slo + ~ref);
+        hi = __ldg(shi + ~ref);
     }
 }
 
-__device__ void optimiseTreelet(const BinTree& t, uint32_t* cnt, const float4* __restrict__ plo, const float4* __restrict__ phi,
-                                const uint32_t* __restrict__ sorted, int root, TreeletScratch& S, int lane,
-                                const uint8_t* __restrict__ subsetsBySize, uint32_t* stats) {
+__global__ void k_sortedBoxes(const float4* __restrict__ plo, const float4* __restrict__ phi, const uint32_t* __restrict__ sorted, int n,
+                              float4* __restrict__ slo, float4* __restrict__ shi) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t p = sorted[i];
+    slo[i] = plo[p];
+    shi[i] = phi[p];
+}
+
+__device__ void optimiseTreelet(const BinTree& t, uint32_t* cnt, const float4* __restrict__ slo, const float4* __restrict__ shi, int root,
+                                TreeletScratch& S, int lane, const uint8_t* __restrict__ subsetsBySize, uint32_t* stats) {
     // ---- 1. grow the treelet: lanes 0..6 each hold one treelet leaf -------------------------------------
-    int myRef = 0;
+    // A lane that holds an internal node also fetches that node's two child references at once (myL / myR): when the node
+    // is the one expanded next, its children's boxes are one load away instead of two dependent ones.  The whole pass is
+    // bound by these chains of dependent L2 loads, not by arithmetic.
+    int myRef = 0, myL = 0, myR = 0;
     float myArea = -2.0f;  // -2: unused lane, -1: primitive leaf (cannot be expanded)
     float4 mylo = make_float4(0, 0, 0, 0), myhi = mylo;
     if (lane < 2) {
         myRef = lane == 0 ? __ldcg(t.left + root) : __ldcg(t.right + root);
-        treeletRefBox(t, plo, phi, sorted, myRef, mylo, myhi);
+        if (myRef >= 0) {
+            myL = __ldcg(t.left + myRef);
+            myR = __ldcg(t.right + myRef);
+        }
+        treeletRefBox(t, slo, shi, myRef, mylo, myhi);
         myArea = myRef >= 0 ? boxArea(mylo, myhi) : -1.0f;
     }
     if (lane == 0) S.nodeId[0] = root;
@@ -72,11 +87,16 @@ __device__ void optimiseTreelet(const BinTree& t, uint32_t* cnt, const float4* _
         bl = __shfl_sync(kFullMask, bl, 0);
         if (best < 0.0f) return;  // fewer than 7 leaves below the root (cannot happen while cnt >= 7); warp-uniform
         const int x = __shfl_sync(kFullMask, myRef, bl);
+        const int xl = __shfl_sync(kFullMask, myL, bl), xr = __shfl_sync(kFullMask, myR, bl);
         curCost += best;
         if (lane == 0) S.nodeId[nLeaves - 1] = x;
         if (lane == bl || lane == nLeaves) {
-            myRef = lane == bl ? __ldcg(t.left + x) : __ldcg(t.right + x);
-            treeletRefBox(t, plo, phi, sorted, myRef, mylo, myhi);
+            myRef = lane == bl ? xl : xr;
+            if (myRef >= 0) {
+                myL = __ldcg(t.left + myRef);
+                myR = __ldcg(t.right + myRef);
+            }
+            treeletRefBox(t, slo, shi, myRef, mylo, myhi);
             myArea = myRef >= 0 ? boxArea(mylo, myhi) : -1.0f;
         }
     }
@@ -196,9 +216,9 @@ __device__ void optimiseTreelet(const BinTree& t, uint32_t* cnt, const float4* _
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(32 * kTreeletWarps)
-k_treeletPass(BinTree t, uint32_t* cnt, const float4* __restrict__ plo, const float4* __restrict__ phi,
-              const uint32_t* __restrict__ sorted, int n, uint32_t gamma, uint32_t* stats) {
+__global__ void __launch_bounds__(32 * kTreeletWarps, 16)
+k_treeletPass(BinTree t, uint32_t* cnt, const float4* __restrict__ slo, const float4* __restrict__ shi, int n, uint32_t gamma,
+              uint32_t* stats) {
     __shared__ TreeletScratch scratch[kTreeletWarps];
     __shared__ uint8_t subsetsBySize[128];  // the 127 non-empty subsets ordered by leaf count
     for (int s = threadIdx.x + 1; s < 128; s += blockDim.x) {
@@ -225,7 +245,7 @@ k_treeletPass(BinTree t, uint32_t* cnt, const float4* __restrict__ plo, const fl
         while (m) {
             const int src = __ffs(m) - 1;
             m &= m - 1;
-            optimiseTreelet(t, cnt, plo, phi, sorted, __shfl_sync(kFullMask, node, src), S, lane, subsetsBySize, stats);
+            optimiseTreelet(t, cnt, slo, shi, __shfl_sync(kFullMask, node, src), S, lane, subsetsBySize, stats);
         }
         if (active) {
             node = __ldcg(t.parent + node);
@@ -290,10 +310,13 @@ void refineTreelets(cudaStream_t s, BinTree& t, const float4* plo, const float4*
     uint32_t* stats = (uint32_t*)alloc(2 * sizeof(uint32_t));
     GSB_CUDA(cudaMemsetAsync(stats, 0, 2 * sizeof(uint32_t), s));
     k_initCounts<<<(n + B - 1) / B, B, 0, s>>>(t, cnt, n);
+    float4* slo = (float4*)alloc((size_t)n * sizeof(float4));
+    float4* shi = (float4*)alloc((size_t)n * sizeof(float4));
+    k_sortedBoxes<<<(n + B - 1) / B, B, 0, s>>>(plo, phi, sorted, n, slo, shi);
     const int TB = 32 * kTreeletWarps;
     for (int p = 0; p < passes; p++) {
         GSB_CUDA(cudaMemsetAsync(t.flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
-        k_treeletPass<<<(n + TB - 1) / TB, TB, 0, s>>>(t, cnt, plo, phi, sorted, n, 7u, stats);
+        k_treeletPass<<<(n + TB - 1) / TB, TB, 0, s>>>(t, cnt, slo, shi, n, 7u, stats);
     }
     uint32_t* newSorted = (uint32_t*)alloc((size_t)n * sizeof(uint32_t));
     uint32_t* newPos = (uint32_t*)alloc((size_t)n * sizeof(uint32_t));

@@ -189,7 +189,10 @@ GSB_API const char* gsb_version(void);
 /* ---- scene (replaces Mesh uploads + createBLAS/createTLAS + prepareScene) -------- */
 /* Non-indexed triangle soup, 3 consecutive vertices per triangle, tightly packed float3
  * positions and normals (renderer/Mesh.cpp:7-22; VulkanRays.cpp:17-35).  nverts % 3 == 0.
- * Builds the mesh's bottom-level BVH on the device. */
+ * Uploads the mesh; its bottom-level BVH is built by the first gsb_scene_set_instances that
+ * needs it, together with those of the scene's other meshes (one batched build, like a
+ * vkCmdBuildAccelerationStructuresKHR with several infos; a mesh that is only baked into the
+ * world level gets none). */
 GSB_API gsb_status gsb_mesh_create(gsb_context* ctx, const float* positions3, const float* normals3,
                                    uint32_t nverts, uint32_t* out_mesh);
 GSB_API gsb_status gsb_mesh_destroy(gsb_context* ctx, uint32_t mesh);
