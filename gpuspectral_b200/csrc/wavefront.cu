@@ -404,6 +404,9 @@ GSB_D void cpAsyncWait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "me
 // buffer in shared memory and shaded 32 at a time (entries wait there across in-place tiles).
 // EXT: the scene uses an extension that shading has to know about (reflectance textures, environment emitter); the plain
 // instantiation carries none of that code (r2m: the texture branch alone cost the diffuse kernel 11 % when compiled in).
+#ifndef GSB_SHADE_DEFER_SHADOW
+#define GSB_SHADE_DEFER_SHADOW 1
+#endif
 template <int TYPE, bool HASINST, bool EXT>
 __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFUSE : GSB_SHADE_MIN_BLOCKS) k_shade(SceneDev sc, WavefrontState wf, uint32_t parity, uint32_t slots, uint32_t directMin) {
     uint32_t* qc = wf.qCount + parity * Q_COUNT;
@@ -423,6 +426,28 @@ __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFU
     __shared__ uint32_t s_inst[kBlock / 32][2][32];
     float4 (*st)[4][32] = s_state[threadIdx.x >> 5];
     uint32_t (*sti)[32] = s_inst[threadIdx.x >> 5];
+    // Deferred shadow-queue writes (below) for the diffuse kernel of world-only scenes: there it buys 4.5 % of the kernel
+    // (Cornell); on the field and on the gallery's 8-blocks-per-SM kernels the 2 KB per warp it takes from L1 cost more
+    // than the hidden atomic gives back (r2x: field shade 14.0 -> 14.7 ms with it on everywhere).
+    constexpr bool kDefer = GSB_SHADE_DEFER_SHADOW && TYPE == 0 && !HASINST;
+    __shared__ float4 s_shadow[kDefer ? kBlock / 32 : 1][kDefer ? 4 : 1][kDefer ? 32 : 1];   // [warp][origin, direction, nee, base][lane]
+    float4 (*sh)[kDefer ? 32 : 1] = s_shadow[kDefer ? (threadIdx.x >> 5) : 0];
+    uint32_t pendMask = 0u, pendBase = 0u, pendRank = 0u;
+    bool pendNeed = false, pendHasBase = false;
+    auto flushShadow = [&]() {
+        if constexpr (kDefer) {
+            if (pendMask) {                               // warp-uniform
+                const uint32_t sp = __shfl_sync(0xffffffffu, pendBase, 0) + pendRank;
+                if (pendNeed) {
+                    wf.shadowO[sp] = sh[0][lane];
+                    wf.shadowD[sp] = sh[1][lane];
+                    wf.shadowNee[sp] = sh[2][lane];
+                    if (pendHasBase) wf.shadowBase[sp] = sh[3][lane];
+                }
+                pendMask = 0u;
+            }
+        }
+    };
     uint32_t tile = warpId;
     // the instance word of the tile scanned next is loaded one scan ahead (its DRAM latency hides behind the batch in between)
     uint32_t aheadWord = (tile < tiles && tile * 32u + lane < slots) ? wf.hitInst[tile * 32u + lane] : GSB_NO_HIT;
@@ -437,10 +462,14 @@ __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFU
             const uint32_t cand = tile * 32u + lane;
             tile += warpsTotal;
             const uint32_t word = aheadWord;
-            aheadWord = (tile < tiles && tile * 32u + lane < slots) ? wf.hitInst[tile * 32u + lane] : GSB_NO_HIT;
             // the instance word carries the BSDF type; GSB_NO_HIT decodes to none
             const bool match = scanning && cand < slots && (word >> kInstTypeShift) == (uint32_t)TYPE;
             const uint32_t mm = __ballot_sync(0xffffffffu, match);
+            // The next tile's word is requested only now, AFTER this tile's word has been used: issued before the vote (r2w
+            // ncu, SASS: LDG three instructions ahead of the ISETP on `word`) the test waited on the scoreboard the new load
+            // had just taken - a full DRAM round trip at the head of every batch, 18.7 % of the kernel's stall samples.
+            asm volatile("" ::: "memory");
+            aheadWord = (tile < tiles && tile * 32u + lane < slots) ? wf.hitInst[tile * 32u + lane] : GSB_NO_HIT;
             if ((uint32_t)__popc(mm) >= directMin) {
                 // a tile that matches (almost) completely is shaded in place: coalesced state streams and no trip through
                 // the compaction buffer, at the price of its few non-matching lanes idling
@@ -674,17 +703,37 @@ __global__ void __launch_bounds__(kBlock, TYPE == 0 ? GSB_SHADE_MIN_BLOCKS_DIFFU
             }
         }
         if (terminate) wf.hitInst[slot] = GSB_NO_HIT;   // the path has ended: k_regen adds the sample to the image next iteration
-        const uint32_t sp = queueSlot(qc, Q_SHADOW, needShadow);
-        if (needShadow) {
-            wf.shadowO[sp] = shO;
-            wf.shadowD[sp] = shD;
-            if (hasBase) wf.shadowBase[sp] = shBase;
-            wf.shadowNee[sp] = shNee;
+        if constexpr (kDefer) {
+            // The batch's place in the shadow queue is asked for here and used one batch later: the entries wait in shared
+            // memory meanwhile.  Used at once, the atomic's round trip to L2 stalled every warp at the end of every batch
+            // (r2w ncu: 10.5 % of the kernel's stall samples on the shuffle that broadcasts its result).
+            flushShadow();
+            const uint32_t mask = __ballot_sync(0xffffffffu, needShadow);
+            pendMask = mask;
+            pendNeed = needShadow;
+            pendHasBase = needShadow && hasBase;
+            pendRank = (uint32_t)__popc(mask & ((1u << lane) - 1u));
+            if (mask) {
+                if (lane == 0u) pendBase = atomicAdd(&qc[Q_SHADOW], (uint32_t)__popc(mask));
+                if (needShadow) {
+                    sh[0][lane] = shO; sh[1][lane] = shD; sh[2][lane] = shNee;
+                    if (hasBase) sh[3][lane] = shBase;
+                }
+            }
+        } else {
+            const uint32_t sp = queueSlot(qc, Q_SHADOW, needShadow);
+            if (needShadow) {
+                wf.shadowO[sp] = shO;
+                wf.shadowD[sp] = shD;
+                if (hasBase) wf.shadowBase[sp] = shBase;
+                wf.shadowNee[sp] = shNee;
+            }
         }
         if (!haveNew) break;
         prevActive = newActive; prevSlot = newSlot; stage ^= 1u;
         __syncwarp();   // the stage just read is the next one to be filled
     }
+    flushShadow();
     if (lane == 0u && shaded) atomicAdd(&wf.stats[ST_VERTICES], (unsigned long long)shaded);
 }
 
