@@ -51,6 +51,9 @@ constexpr uint32_t kInstFresh = 0xfffffffeu;
 // hitInst of a slot whose path left the scene and whose sample k_extend has already added to the image (GSB_MISS_DELIVERS):
 // k_regen only has to start the slot's next path.  Like kInstFresh it decodes to no BSDF type.
 constexpr uint32_t kInstDelivered = 0xfffffffdu;
+// hitInst of a slot that has no path and will get none (the call's work is used up): k_regen tells it from an ended path
+// by this word alone (it used to read result.w of every GSB_NO_HIT slot for that: a second, dependent DRAM round trip)
+constexpr uint32_t kInstRetired = 0xfffffffcu;
 #ifndef GSB_MISS_DELIVERS
 #define GSB_MISS_DELIVERS 1
 #endif
@@ -186,21 +189,39 @@ __global__ void k_generate(SceneDev sc, WavefrontState wf, RenderArgs ra) {
 // or k_shade ended it).  One block owns kRegenSpan consecutive slots: it counts its ended slots, reserves that many
 // consecutive work items with ONE atomic (work item w = sample w / npix of pixel w % npix, so a block's new paths are
 // neighbouring pixels of one sample), and starts them.  A slot that finds no work left is retired.
-constexpr int kRegenBlock = 256, kRegenPer = 8, kRegenSpan = kRegenBlock * kRegenPer;
-__global__ void __launch_bounds__(kRegenBlock) k_regen(SceneDev sc, WavefrontState wf, RenderArgs ra) {
+#ifndef GSB_REGEN_PER
+#define GSB_REGEN_PER 8
+#endif
+constexpr int kRegenBlock = 256, kRegenPer = GSB_REGEN_PER, kRegenSpan = kRegenBlock * kRegenPer;
+static_assert(kRegenPer % 4 == 0, "k_regen reads the instance words four at a time");
+// slot k (0 .. kRegenPer - 1) of thread tid in the block that starts at `base`
+GSB_D uint32_t regenSlot(uint32_t base, uint32_t tid, int k) { return base + (uint32_t)(k >> 2) * (4u * kRegenBlock) + 4u * tid + (uint32_t)(k & 3); }
+__global__ void __launch_bounds__(kRegenBlock, 8) k_regen(SceneDev sc, WavefrontState wf, RenderArgs ra) {
     __shared__ uint32_t s_warp[kRegenBlock / 32];
     __shared__ unsigned long long s_base;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     const uint32_t base = blockIdx.x * (uint32_t)kRegenSpan;
     uint32_t ended = 0, delivered = 0;   // bit k: slot base + k * kRegenBlock + tid holds an ended path / one whose sample k_extend delivered
+    // The scan is the kernel's floor (64 MB of instance words per launch at 16 M slots): 16-byte loads, all of a thread's
+    // in flight before the first word is looked at.  Thread tid owns slots base + 4 tid + 1024 j + {0..3}; slot k of the
+    // masks is j * 4 + c.
+    uint32_t hi[kRegenPer];
+#pragma unroll
+    for (int j = 0; j < kRegenPer / 4; j++) {
+        const uint32_t slot = regenSlot(base, tid, 4 * j);
+        uint4 w = make_uint4(kInstRetired, kInstRetired, kInstRetired, kInstRetired);
+        if (slot + 3u < ra.slots) w = __ldcs(reinterpret_cast<const uint4*>(wf.hitInst + slot));
+        else {
+            if (slot < ra.slots) w.x = wf.hitInst[slot];
+            if (slot + 1u < ra.slots) w.y = wf.hitInst[slot + 1u];
+            if (slot + 2u < ra.slots) w.z = wf.hitInst[slot + 2u];
+        }
+        hi[4 * j] = w.x; hi[4 * j + 1] = w.y; hi[4 * j + 2] = w.z; hi[4 * j + 3] = w.w;
+    }
 #pragma unroll
     for (int k = 0; k < kRegenPer; k++) {
-        const uint32_t slot = base + (uint32_t)k * kRegenBlock + tid;
-        if (slot < ra.slots) {
-            const uint32_t hi = wf.hitInst[slot];
-            if (hi == kInstDelivered) { ended |= 1u << k; delivered |= 1u << k; }
-            else if (hi == GSB_NO_HIT && __float_as_uint(wf.result[slot].w) != kRetired) ended |= 1u << k;
-        }
+        if (hi[k] == kInstDelivered) { ended |= 1u << k; delivered |= 1u << k; }
+        else if (hi[k] == GSB_NO_HIT) ended |= 1u << k;
     }
     // exclusive prefix of the ended counts over the block
     const uint32_t n = (uint32_t)__popc(ended);
@@ -220,6 +241,10 @@ __global__ void __launch_bounds__(kRegenBlock) k_regen(SceneDev sc, WavefrontSta
         total += c;
     }
     if (total == 0u) return;
+    // the block's work items are reserved now and the answer is looked at after the list is built and the first samples
+    // are requested: the atomic's round trip overlaps both
+    unsigned long long reserved = 0ull;
+    if (tid == 0u) reserved = atomicAdd(&wf.stats[ST_NEXTWORK], (unsigned long long)total);
     // the block's ended slots, compacted: entry i of the list gets work item s_base + i, and the list is then processed by
     // all threads side by side (r2q: with every thread working through its own eight slots the path start — hash, camera
     // ray — ran with 5.6 of 32 lanes, 1572 instructions per warp; it was 103 M of the kernel's instructions)
@@ -228,16 +253,27 @@ __global__ void __launch_bounds__(kRegenBlock) k_regen(SceneDev sc, WavefrontSta
         uint32_t at = before + (incl - n);
 #pragma unroll
         for (int k = 0; k < kRegenPer; k++)
-            if (ended & (1u << k)) s_list[at++] = (base + (uint32_t)k * kRegenBlock + tid) | (delivered & (1u << k) ? 0x80000000u : 0u);
+            if (ended & (1u << k)) s_list[at++] = regenSlot(base, tid, k) | (delivered & (1u << k) ? 0x80000000u : 0u);
     }
-    if (tid == 0u) s_base = atomicAdd(&wf.stats[ST_NEXTWORK], (unsigned long long)total);
+    __syncthreads();
+    // A thread's first entry and that path's sample are requested BEFORE the reservation's answer is waited for: the
+    // atomic's round trip (thread 0, then the barrier everybody waits at) and the sample's trip from DRAM overlap instead
+    // of following one another (r2w ncu: 16 % of the stall samples on the sample load, 10 per issue at the barrier).
+    uint32_t firstEntry = 0x80000000u;
+    float4 firstRes = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (tid < total) {
+        firstEntry = s_list[tid];
+        if (!(firstEntry & 0x80000000u)) firstRes = wf.result[firstEntry & 0x7fffffffu];
+    }
+    asm volatile("" ::: "memory");
+    if (tid == 0u) s_base = reserved;
     __syncthreads();
     uint32_t retired = 0;
     for (uint32_t i = tid; i < total; i += kRegenBlock) {
-        const uint32_t entry = s_list[i], slot = entry & 0x7fffffffu;
+        const uint32_t entry = i == tid ? firstEntry : s_list[i], slot = entry & 0x7fffffffu;
         const unsigned long long work = s_base + i;
         if (!(entry & 0x80000000u)) {      // (a path that left the scene was delivered by k_extend)
-            const float4 res = wf.result[slot];
+            const float4 res = i == tid ? firstRes : wf.result[slot];
             const uint32_t pixel = __float_as_uint(res.w);
             // raygen.rgen:106-108: a NaN sample leaves the image untouched
             if (!(isnan(res.x) || isnan(res.y) || isnan(res.z))) atomicAdd(&ra.accum[pixel], make_float4(res.x, res.y, res.z, 1.0f));
@@ -248,7 +284,7 @@ __global__ void __launch_bounds__(kRegenBlock) k_regen(SceneDev sc, WavefrontSta
             startPath(sc, wf, ra, slot, work, o, d, p);
         } else {
             wf.result[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kRetired));
-            wf.hitInst[slot] = GSB_NO_HIT;   // (not kInstDelivered any more: a retired slot must not be taken for an ended path again)
+            wf.hitInst[slot] = kInstRetired;   // neither an ended path nor one with a BSDF type: nobody picks the slot up again
             *rayDirection(wf, slot) = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(kFlagDead));
             if (wf.sortKey) wf.sortKey[slot] = 0xffffffffu;   // sorts behind every live ray
             retired++;
