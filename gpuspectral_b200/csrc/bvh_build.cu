@@ -73,6 +73,8 @@ struct BuildControl {
     uint32_t level;           // the level the next collapse launch works on
     uint32_t reserved;
     double cost[2];           // SAH cost of the binary tree before / after the treelet passes
+    float wideCost;           // SAH cost of the 8-wide tree the cut tables promise (root entry of k_collapseCost), 0 without them
+    float reserved2;
     BuildFrame frame;
     uint32_t levelCount[kMaxLevels + 2];   // items (= nodes) per level
 };
@@ -274,19 +276,42 @@ struct CollapseArgs {
     uint32_t* leafPrim;    // output: primitive index per leaf position
     BuildControl* ctl;     // node / leaf allocation counters, the current level and the items per level
     uint32_t maxLeaf;      // primitives per leaf child (one box per leaf child): 1..3
+    // SAH-aware cut (k_collapseCost): per binary node, cd[i-1] = least cost of standing for its subtree with at most i
+    // children of an 8-wide node, ch[i-1] = how (see k_collapseCost); nullptr = greedy cut by surface area
+    const float* cutCost;  // [n-1][7]
+    const uint8_t* cutHow; // [n-1][8]
+    float costNode, costPrim;
 };
+
+// Quantisation frame of one axis: the smallest exponent e with 255 * 2^e >= ext (e >= -126), from the float's own exponent
+// and mantissa (ext = m * 2^x, m in [0.5, 1): e = x - 8, one more when m > 255/256) - it used to be ceil(log2(ext / 255)) in
+// double plus a fix-up loop, ~150 instructions per axis.  inv = 2^-e: the grid coordinates are (v - origin) * inv, exact like
+// the division by 2^e they replace (48 double divisions per node, the bulk of the collapse and refit kernels).
+__device__ inline int quantExponent(float ext, double& scale, double& inv) {
+    int e = -126;
+    if (ext > 0.0f) {
+        int x;
+        const float m = frexpf(ext, &x);
+        e = max(x - 8 + (m > 0.99609375f ? 1 : 0), -126);
+    }
+    scale = __hiloint2double((1023 + e) << 20, 0);
+    inv = __hiloint2double((1023 - e) << 20, 0);
+    return e;
+}
 
 __device__ inline uint32_t refCount(const BinTree& t, int ref) { return ref >= 0 ? t.last[ref] - t.first[ref] + 1u : 1u; }
 __device__ inline uint32_t refFirst(const BinTree& t, int ref) { return ref >= 0 ? t.first[ref] : (uint32_t)~ref; }
 
+// leafMask: bit k set = child k becomes a leaf slot (its primitives tested in place) even though it is a binary node;
+// single primitives always are, and without the cost tables every reference of at most maxLeaf primitives is.
 __device__ void emitNode(const CollapseArgs& a, uint32_t level, uint32_t outNode, float4 nlo, float4 nhi, const int* child, int nc,
-                         CollapseItem* next) {
+                         CollapseItem* next, uint32_t leafMask = 0xffu) {
     // classify + boxes
     float4 clo[8], chi[8];
     bool internal[8];
     for (int k = 0; k < nc; k++) {
         refBox(a.t, a.plo, a.phi, a.sorted, child[k], clo[k], chi[k]);
-        internal[k] = refCount(a.t, child[k]) > a.maxLeaf;
+        internal[k] = child[k] >= 0 && (refCount(a.t, child[k]) > a.maxLeaf || !(leafMask >> k & 1u));
     }
     // octant slot assignment: slot s (bits x,y,z = 4,2,1) should hold the child lying furthest
     // towards (+ if bit set, - if clear) on each axis; traversal visits slot^octant in descending order.
@@ -329,17 +354,8 @@ __device__ void emitNode(const CollapseArgs& a, uint32_t level, uint32_t outNode
     const float p[3] = {nlo.x, nlo.y, nlo.z};
     const float ext[3] = {nhi.x - nlo.x, nhi.y - nlo.y, nhi.z - nlo.z};
     int e[3];
-    double scale[3];
-    for (int ax = 0; ax < 3; ax++) {
-        int ee = -126;
-        if (ext[ax] > 0.0f) {
-            ee = (int)ceil(log2((double)ext[ax] / 255.0));
-            while (ldexp(255.0, ee) < (double)ext[ax]) ee++;
-            ee = max(ee, -126);
-        }
-        e[ax] = ee;
-        scale[ax] = ldexp(1.0, ee);
-    }
+    double scale[3], inv[3];
+    for (int ax = 0; ax < 3; ax++) e[ax] = quantExponent(ext[ax], scale[ax], inv[ax]);
     uint32_t meta[8], qlo[3][8], qhi[3][8];
     uint32_t imask = 0, rank = 0, leafOff = 0;
     for (int s = 0; s < 8; s++) {
@@ -349,8 +365,8 @@ __device__ void emitNode(const CollapseArgs& a, uint32_t level, uint32_t outNode
         if (k < 0) continue;
         const float lo3[3] = {clo[k].x, clo[k].y, clo[k].z}, hi3[3] = {chi[k].x, chi[k].y, chi[k].z};
         for (int ax = 0; ax < 3; ax++) {
-            double ql = floor(((double)lo3[ax] - (double)p[ax]) / scale[ax]);
-            double qh = ceil(((double)hi3[ax] - (double)p[ax]) / scale[ax]);
+            double ql = floor(((double)lo3[ax] - (double)p[ax]) * inv[ax]);
+            double qh = ceil(((double)hi3[ax] - (double)p[ax]) * inv[ax]);
             ql = fmin(fmax(ql, 0.0), 255.0);
             qh = fmin(fmax(qh, 0.0), 255.0);
             qlo[ax][s] = (uint32_t)ql;
@@ -379,11 +395,125 @@ __device__ void emitNode(const CollapseArgs& a, uint32_t level, uint32_t outNode
     out[4] = make_uint4(pack4(qhi[1]), pack4(qhi[1] + 4), pack4(qhi[2]), pack4(qhi[2] + 4));
 }
 
-// One item of a level: the binary node it stands for is opened greedily (the internal child with the largest surface
-// area first) until 8 slots are used, and the 8-wide node is emitted.
+// SAH cost tables for the cut (Ylitie, Karras & Laine 2017, section 3.1, on the binary tree the treelet pass left).
+// For a binary node b with P primitives and box area A:
+//   cd[0] = min( A * P * costPrim  if P <= maxLeaf            (b is a leaf slot),
+//                A * costNode + min_k L[k] + R[8 - k] )        (b is an 8-wide node; k children come from its left subtree)
+//   cd[i] = min( cd[i - 1], min_k L[k] + R[i + 1 - k] )        (b's subtree shows up as at most i + 1 children of an ancestor)
+// with L / R the tables of its two children (a single primitive: its area * costPrim for every i).  ch[0] = 0 for the leaf
+// slot, else the k of the 8-way split; ch[i] = 0 for "as with one child fewer", else the k of the split.
+// Bottom-up with arrival counters like k_fitBoxes: the second thread to reach a node finds both tables written.
+__global__ void k_collapseCost(BinTree t, const float4* __restrict__ plo, const float4* __restrict__ phi, const uint32_t* __restrict__ sorted,
+                               int n, uint32_t maxLeaf, float costNode, float costPrim, float* cd, uint8_t* ch) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int node = t.leafParent[i];
+    while (node >= 0) {
+        __threadfence();
+        if (atomicAdd(&t.flags[node], 1u) == 0u) return;
+        float tab[2][8];
+        const int refs[2] = {t.left[node], t.right[node]};
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+            if (refs[c] >= 0) {
+#pragma unroll
+                for (int k = 0; k < 7; k++) tab[c][k + 1] = __ldcg(cd + 7 * (size_t)refs[c] + k);
+            } else {
+                const uint32_t p = sorted[~refs[c]];
+                const float leaf = boxArea(plo[p], phi[p]) * costPrim;
+#pragma unroll
+                for (int k = 1; k < 8; k++) tab[c][k] = leaf;
+            }
+        }
+        const float area = boxArea(t.lo[node], t.hi[node]);
+        const uint32_t prims = t.last[node] - t.first[node] + 1u;
+        float best = INFINITY;
+        int how = 1;
+#pragma unroll
+        for (int k = 1; k < 8; k++) {
+            const float c = tab[0][k] + tab[1][8 - k];
+            if (c < best) { best = c; how = k; }
+        }
+        best += area * costNode;
+        if (prims <= maxLeaf) {
+            const float leaf = area * (float)prims * costPrim;
+            if (leaf <= best) { best = leaf; how = 0; }
+        }
+        float out[7];
+        uint8_t outHow[8];
+        out[0] = best;
+        outHow[0] = (uint8_t)how;
+#pragma unroll
+        for (int m = 2; m < 8; m++) {      // at most m children
+            float bm = out[m - 2];
+            int hm = 0;
+#pragma unroll
+            for (int k = 1; k < m; k++) {
+                const float c = tab[0][k] + tab[1][m - k];
+                if (c < bm) { bm = c; hm = k; }
+            }
+            out[m - 1] = bm;
+            outHow[m - 1] = (uint8_t)hm;
+        }
+        outHow[7] = 0;
+#pragma unroll
+        for (int k = 0; k < 7; k++) __stcg(cd + 7 * (size_t)node + k, out[k]);
+        uint2 packed;
+        packed.x = outHow[0] | (outHow[1] << 8) | (outHow[2] << 16) | ((uint32_t)outHow[3] << 24);
+        packed.y = outHow[4] | (outHow[5] << 8) | (outHow[6] << 16);
+        __stcg(reinterpret_cast<uint2*>(ch + 8 * (size_t)node), packed);
+        node = t.parent[node];
+    }
+}
+
+// The children of the 8-wide node that stands for binary node b, by the cost tables: `budget` children for the subtree of
+// `ref`, split as the tables say until a piece has a budget of one (or is a single primitive).
+__device__ int cutBySah(const CollapseArgs& a, int b, int* child, uint32_t& leafMask) {
+    // a node's eight "how" bytes come in one load, together with its two child references: a piece of the cut costs one
+    // round trip to L2, not one per byte looked at
+    auto howOf = [&](int ref) {
+        const uint2 h = __ldg(reinterpret_cast<const uint2*>(a.cutHow + 8 * (size_t)ref));
+        return (unsigned long long)h.x | ((unsigned long long)h.y << 32);
+    };
+    int stackRef[8], stackBudget[8];
+    int sp = 0, nc = 0;
+    leafMask = 0u;
+    int k8 = (int)(howOf(b) & 0xffull);
+    if (k8 == 0) k8 = 1;   // the root of a tree of at most maxLeaf primitives still becomes a node: one child per side
+    stackRef[sp] = a.t.right[b]; stackBudget[sp++] = 8 - k8;
+    stackRef[sp] = a.t.left[b]; stackBudget[sp++] = k8;
+    while (sp > 0) {
+        int ref = stackRef[--sp], budget = stackBudget[sp];
+        for (;;) {
+            if (ref < 0) { child[nc++] = ref; break; }
+            const unsigned long long how = howOf(ref);
+            const int l = a.t.left[ref], r = a.t.right[ref];   // asked for with the bytes: used when the piece is split
+            while (budget > 1 && ((how >> (8 * (budget - 1))) & 0xffull) == 0ull) budget--;
+            if (budget == 1) {
+                if ((how & 0xffull) == 0ull) leafMask |= 1u << nc;
+                child[nc++] = ref;
+                break;
+            }
+            const int k = (int)((how >> (8 * (budget - 1))) & 0xffull);
+            stackRef[sp] = r; stackBudget[sp++] = budget - k;
+            ref = l;
+            budget = k;
+        }
+    }
+    return nc;
+}
+
+// One item of a level: the binary node it stands for is opened - by the SAH cost tables when the build made them, else
+// greedily (the internal child with the largest surface area first) until 8 slots are used - and the 8-wide node is emitted.
 __device__ void collapseItem(const CollapseArgs& a, uint32_t level, const CollapseItem it, CollapseItem* next) {
     const int b = it.binNode;
     int child[8];
+    if (a.cutHow) {
+        uint32_t leafMask;
+        const int n = cutBySah(a, b, child, leafMask);
+        emitNode(a, level, it.outNode, a.t.lo[b], a.t.hi[b], child, n, next, leafMask);
+        return;
+    }
     int nc = 2;
     child[0] = a.t.left[b];
     child[1] = a.t.right[b];
@@ -451,7 +581,8 @@ __global__ void __launch_bounds__(128) k_collapseWide(CollapseArgs a, CollapseIt
 }
 
 // start of a collapse: the root item, one node allocated, one item on level 0
-__global__ void k_collapseStart(BuildControl* ctl, CollapseItem* bufA) {
+__global__ void k_collapseStart(BuildControl* ctl, CollapseItem* bufA, const float* cutCost) {
+    ctl->wideCost = cutCost ? cutCost[0] : 0.0f;
     ctl->counters[0] = 1u;
     ctl->counters[1] = 0u;
     ctl->counters[2] = 0u;
@@ -551,10 +682,11 @@ struct BuildJob {
     uint32_t numNodes = 1;
     BuildControl* ctl = nullptr;   // device
     BuildControl host;             // its copy after collect()
-    // 16 + 16 primitive boxes, 80 nodes, 4 leaf order, 24 keys / values twice, 60 binary tree, 16 collapse items, 16 + 32 treelet
+    int passesOverride = -1, gammaOverride = 0;   // a candidate build (buildBlasBatch): treelet settings of its own
+    // 16 + 16 primitive boxes, 80 nodes, 4 leaf order, 24 keys / values twice, 60 binary tree, 16 collapse items, 36 cut tables, 16 + 32 treelet
     // arrays per primitive, the sort's own temporaries (a second key / value buffer, 12 per primitive, and its histograms)
     // and the 256-byte rounding of ~35 requests; a request that does not fit falls back to a block of its own
-    static size_t arenaBytes(uint32_t n) { return (size_t)std::max<uint32_t>(n, 1) * 292 + (128u << 10); }
+    static size_t arenaBytes(uint32_t n) { return (size_t)std::max<uint32_t>(n, 1) * 328 + (128u << 10); }
     BuildJob(cudaStream_t st, uint32_t count) : pool(st, arenaBytes(count)), s(st) { memset(&host, 0, sizeof(host)); }
 
     // the control block, zeroed; the caller then fills ctl->frame (k_blasFrame, or a copy of a host frame)
@@ -628,9 +760,10 @@ void BuildJob::start(const float4* plo, const float4* phi) {
     // better front-to-back visiting order than the SAH-optimal grouping (profiles/README.md, r1g).
     int passes = (g_treelets && !topLevel) ? 1 : 0;
     if (const char* e = getenv(topLevel ? "GSB_TREELET_PASSES_TLAS" : "GSB_TREELET_PASSES")) passes = atoi(e);
+    if (passesOverride >= 0) passes = passesOverride;
     refine = passes > 0 && n >= 16;
     if (refine) {
-        refineTreelets(s, t, plo, phi, sorted, (int)n, passes, [&](size_t bytes) { return (void*)pool.get<uint8_t>(bytes); });
+        refineTreelets(s, t, plo, phi, sorted, (int)n, passes, [&](size_t bytes) { return (void*)pool.get<uint8_t>(bytes); }, nullptr, gammaOverride);
         ca.sorted = sorted;  // the refinement re-derives the leaf order
         k_sahCost<<<costBlocks, B, 0, s>>>(t, plo, phi, (int)n, &ctl->cost[1]);
     }
@@ -639,7 +772,25 @@ void BuildJob::start(const float4* plo, const float4* phi) {
     CollapseItem* itemsA = pool.get<CollapseItem>(n);
     CollapseItem* itemsB = pool.get<CollapseItem>(n);
     ca.t = t;
-    k_collapseStart<<<1, 1, 0, s>>>(ctl, itemsA);
+    // Which binary nodes become 8-wide nodes, which leaf slots: by SAH cost tables over the binary tree (default), or
+    // greedily by surface area (GSB_COLLAPSE_SAH=0; top level: GSB_COLLAPSE_SAH_TLAS).  costNode : costPrim = what one
+    // 8-wide node test costs against one triangle test (top level: one instance entry).
+    ca.cutCost = nullptr;
+    ca.cutHow = nullptr;
+    ca.costNode = 1.0f;
+    ca.costPrim = topLevel ? 2.0f : 1.0f;
+    bool sahCut = true;
+    if (const char* e = getenv(topLevel ? "GSB_COLLAPSE_SAH_TLAS" : "GSB_COLLAPSE_SAH")) sahCut = atoi(e) != 0;
+    if (const char* e = getenv(topLevel ? "GSB_SAH_COST_INST" : "GSB_SAH_COST_PRIM")) ca.costPrim = (float)atof(e);
+    if (sahCut) {
+        float* cd = pool.get<float>((size_t)(n - 1) * 7);
+        uint8_t* ch = pool.get<uint8_t>((size_t)(n - 1) * 8);
+        GSB_CUDA(cudaMemsetAsync(t.flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
+        k_collapseCost<<<(n + B - 1) / B, B, 0, s>>>(t, plo, phi, ca.sorted, (int)n, ca.maxLeaf, ca.costNode, ca.costPrim, cd, ch);
+        ca.cutCost = cd;
+        ca.cutHow = ch;
+    }
+    k_collapseStart<<<1, 1, 0, s>>>(ctl, itemsA, ca.cutCost);
     constexpr uint32_t kNarrowLimit = 512;
     k_collapseNarrow<<<1, 256, 0, s>>>(ca, itemsA, itemsB, kNarrowLimit);
     if (n > kNarrowLimit) {
@@ -683,6 +834,9 @@ void BuildJob::collect(DeviceBvh& out) {
     if (levelEnd != numNodes) throw std::runtime_error("BVH collapse: level counts do not add up to the node count");
     out.sahBefore = host.cost[0];
     out.sahAfter = refine ? host.cost[1] : host.cost[0];
+    if (getenv("GSB_BUILD_TRACE") && n <= 100000)
+        fprintf(stderr, "[gsb build] %u primitives: %u nodes on %zu levels, binary SAH %.1f -> %.1f, wide SAH (cut tables) %.2f\n", n, numNodes,
+                out.levelEnd.size(), out.sahBefore, out.sahAfter, (double)host.wideCost);
 }
 
 struct GenericResult {
@@ -729,6 +883,12 @@ void freeBvh(DeviceBvh& bvh) {
 // Jobs are taken in waves of at most kWaveTriangles so that the temporaries (~230 B per triangle) stay bounded.
 void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t s) {
     if (count == 0) return;
+    // candidate treelet settings {passes, gamma} of small levels, beside the default build
+    static const int kCandidates[5][2] = {{1, 7}, {1, 10}, {1, 24}, {2, 14}, {2, 7}};
+    constexpr uint32_t kCandidateMaxTris = 16384;
+    bool candidates = true;
+    if (const char* e = getenv("GSB_BUILD_CANDIDATES")) candidates = atoi(e) != 0;
+    if (getenv("GSB_TREELET_PASSES") || getenv("GSB_TREELET_GAMMA") || getenv("GSB_COLLAPSE_SAH") || !g_treelets) candidates = false;   // explicit settings are taken as given
     size_t kBuildStreams = 8;
     if (const char* e = getenv("GSB_BUILD_STREAMS")) kBuildStreams = (size_t)std::max(1, atoi(e));
     constexpr uint64_t kWaveTriangles = 48ull << 20;
@@ -738,8 +898,10 @@ void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t
     GSB_CUDA(cudaEventRecord(e0, s));
     std::vector<cudaStream_t> streams;
     cudaEvent_t joined = nullptr;
-    if (count > 1) {
-        streams.resize(std::min(count, kBuildStreams));
+    bool anySmall = false;
+    for (size_t i = 0; i < count; i++) anySmall = anySmall || (requests[i].ntris >= 16 && requests[i].ntris <= kCandidateMaxTris);
+    if (count > 1 || (candidates && anySmall)) {
+        streams.resize(candidates && anySmall ? kBuildStreams : std::min(count, kBuildStreams));
         for (cudaStream_t& st : streams) {
             GSB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
             GSB_CUDA(cudaStreamWaitEvent(st, e0, 0));
@@ -756,33 +918,59 @@ void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t
         uint64_t waveTris = 0;
         while (end < count && (end == first || waveTris + requests[end].ntris <= kWaveTriangles)) waveTris += requests[end++].ntris;
         std::vector<std::unique_ptr<BuildJob>> jobs;
+        std::vector<std::vector<std::unique_ptr<BuildJob>>> rivals(end - first);   // candidate builds of small levels
         const auto tWave = std::chrono::steady_clock::now();
         for (size_t i = first; i < end; i++) {
             const BlasBuildRequest& q = requests[i];
-            cudaStream_t js = streams.empty() ? s : streams[(i - first) % streams.size()];
-            jobs.emplace_back(new BuildJob(js, q.ntris));
-            BuildJob& j = *jobs.back();
-            j.begin(q.ntris, false);
-            float4* plo = j.pool.get<float4>(q.ntris);
-            float4* phi = j.pool.get<float4>(q.ntris);
-            if (q.ntris > 0) {
-                BoundsAcc* acc = j.pool.get<BoundsAcc>(1);
-                k_initBounds<<<1, 32, 0, js>>>(acc);
-                const uint32_t nverts = q.ntris * 3;
-                k_vertexBounds<<<(int)std::min<uint32_t>((nverts + B - 1) / B, 296u), B, 0, js>>>(q.vertices, nverts, acc);
-                k_blasFrame<<<1, 1, 0, js>>>(acc, &j.ctl->frame);
-                k_triBoxes<<<(q.ntris + B - 1) / B, B, 0, js>>>(q.vertices, q.ntris, &j.ctl->frame, plo, phi);
-            }
-            j.start(plo, phi);
+            size_t turn = i - first;
+            auto launch = [&](int passes, int gamma) {
+                cudaStream_t js = streams.empty() ? s : streams[turn++ % streams.size()];   // candidates of a level side by side
+                std::unique_ptr<BuildJob> job(new BuildJob(js, q.ntris));
+                BuildJob& j = *job;
+                j.passesOverride = passes;
+                j.gammaOverride = gamma;
+                j.begin(q.ntris, false);
+                float4* plo = j.pool.get<float4>(q.ntris);
+                float4* phi = j.pool.get<float4>(q.ntris);
+                if (q.ntris > 0) {
+                    BoundsAcc* acc = j.pool.get<BoundsAcc>(1);
+                    k_initBounds<<<1, 32, 0, js>>>(acc);
+                    const uint32_t nverts = q.ntris * 3;
+                    k_vertexBounds<<<(int)std::min<uint32_t>((nverts + B - 1) / B, 296u), B, 0, js>>>(q.vertices, nverts, acc);
+                    k_blasFrame<<<1, 1, 0, js>>>(acc, &j.ctl->frame);
+                    k_triBoxes<<<(q.ntris + B - 1) / B, B, 0, js>>>(q.vertices, q.ntris, &j.ctl->frame, plo, phi);
+                }
+                j.start(plo, phi);
+                return job;
+            };
+            jobs.push_back(launch(-1, 0));
+            // A small level is built several times, with different treelet settings, and the tree with the least SAH cost
+            // AS AN 8-WIDE TREE (the root entry of the cut tables) is kept: on a few dozen triangles which treelets happen
+            // to be formed decides whether the level has three nodes or four, and the binary SAH cost does not see it
+            // (Cornell box, r3c: 386.3 against 386.8, but 144.7 against 149.1 as wide trees, 1096 against 1003 Mpaths/s).
+            if (candidates && q.ntris >= 16 && q.ntris <= kCandidateMaxTris)
+                for (const int* c : {kCandidates[0], kCandidates[1], kCandidates[2], kCandidates[3], kCandidates[4]})
+                    rivals[i - first].push_back(launch(c[0], c[1]));
         }
         const auto tIssued = std::chrono::steady_clock::now();
         double msCollect = 0.0, msFinish = 0.0;
         for (size_t i = first; i < end; i++) {
             const BlasBuildRequest& q = requests[i];
-            BuildJob& j = *jobs[i - first];
             DeviceBvh& out = *q.out;
             const auto tc0 = std::chrono::steady_clock::now();
-            j.collect(out);
+            jobs[i - first]->collect(out);
+            for (std::unique_ptr<BuildJob>& r : rivals[i - first]) {
+                DeviceBvh other;
+                r->collect(other);
+                if (r->host.wideCost > 0.0f && jobs[i - first]->host.wideCost > 0.0f && r->host.wideCost < jobs[i - first]->host.wideCost) {
+                    out.levelEnd = other.levelEnd;
+                    out.sahBefore = other.sahBefore;
+                    out.sahAfter = other.sahAfter;
+                    jobs[i - first].swap(r);
+                }
+            }
+            rivals[i - first].clear();
+            BuildJob& j = *jobs[i - first];
             const auto tc1 = std::chrono::steady_clock::now();
             msCollect += std::chrono::duration<double, std::milli>(tc1 - tc0).count();
             const GenericResult r = {j.nodes, j.numNodes, j.leafPrim};
@@ -882,25 +1070,15 @@ __global__ void k_refitLevel(uint4* __restrict__ nodes, uint32_t first, uint32_t
     }
     if (!(nhi[0] >= nlo[0])) { nlo[0] = nlo[1] = nlo[2] = 0.0f; nhi[0] = nhi[1] = nhi[2] = 0.0f; }   // an empty root
     uint32_t e[3];
-    double scale[3];
-    for (int ax = 0; ax < 3; ax++) {
-        const float ext = nhi[ax] - nlo[ax];
-        int ee = -126;
-        if (ext > 0.0f) {
-            ee = (int)ceil(log2((double)ext / 255.0));
-            while (ldexp(255.0, ee) < (double)ext) ee++;
-            ee = max(ee, -126);
-        }
-        e[ax] = (uint32_t)(ee + 127);
-        scale[ax] = ldexp(1.0, ee);
-    }
+    double scale[3], inv[3];
+    for (int ax = 0; ax < 3; ax++) e[ax] = (uint32_t)(quantExponent(nhi[ax] - nlo[ax], scale[ax], inv[ax]) + 127);
     uint32_t qlo[3][8], qhi[3][8];
     for (int s = 0; s < 8; s++)
         for (int ax = 0; ax < 3; ax++) {
             qlo[ax][s] = 0; qhi[ax][s] = 0;
             if (!used[s]) continue;
-            double ql = floor(((double)clo[s][ax] - (double)nlo[ax]) / scale[ax]);
-            double qh = ceil(((double)chi[s][ax] - (double)nlo[ax]) / scale[ax]);
+            double ql = floor(((double)clo[s][ax] - (double)nlo[ax]) * inv[ax]);
+            double qh = ceil(((double)chi[s][ax] - (double)nlo[ax]) * inv[ax]);
             qlo[ax][s] = (uint32_t)fmin(fmax(ql, 0.0), 255.0);
             qhi[ax][s] = (uint32_t)fmin(fmax(qh, 0.0), 255.0);
         }

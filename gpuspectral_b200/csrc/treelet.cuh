@@ -304,7 +304,7 @@ __global__ void k_remapLeafRefs(BinTree t, const uint32_t* __restrict__ newPos, 
 // examined / rewritten over all passes.
 template <class Alloc>
 void refineTreelets(cudaStream_t s, BinTree& t, const float4* plo, const float4* phi, uint32_t*& sorted, int n, int passes,
-                    Alloc alloc, uint32_t* hostStats = nullptr) {
+                    Alloc alloc, uint32_t* hostStats = nullptr, int gammaOverride = 0) {
     const int B = 256;
     uint32_t* cnt = (uint32_t*)alloc((size_t)n * sizeof(uint32_t));
     uint32_t* stats = (uint32_t*)alloc(2 * sizeof(uint32_t));
@@ -314,9 +314,16 @@ void refineTreelets(cudaStream_t s, BinTree& t, const float4* plo, const float4*
     float4* shi = (float4*)alloc((size_t)n * sizeof(float4));
     k_sortedBoxes<<<(n + B - 1) / B, B, 0, s>>>(plo, phi, sorted, n, slo, shi);
     const int TB = 32 * kTreeletWarps;
+    // gamma: a node becomes a treelet root when its subtree holds at least that many leaves (7 = every node a treelet can
+    // be grown under; larger values skip the small subtrees, which the treelets of their ancestors still reach into)
+    // Default 14: on the field scene the pass costs 2.4 ms instead of 4 and the SAH cost ends 0.4 % higher (66 982 against
+    // 66 726; paths/s equal within noise on field and gallery, profiles/README.md r3c).
+    uint32_t gamma = 14u;
+    if (const char* e = getenv("GSB_TREELET_GAMMA")) gamma = (uint32_t)std::max(7, atoi(e));
+    if (gammaOverride >= 7) gamma = (uint32_t)gammaOverride;   // a candidate build of a small level (bvh_build.cu: kCandidates)
     for (int p = 0; p < passes; p++) {
         GSB_CUDA(cudaMemsetAsync(t.flags, 0, (size_t)(n - 1) * sizeof(uint32_t), s));
-        k_treeletPass<<<(n + TB - 1) / TB, TB, 0, s>>>(t, cnt, slo, shi, n, 7u, stats);
+        k_treeletPass<<<(n + TB - 1) / TB, TB, 0, s>>>(t, cnt, slo, shi, n, gamma, stats);
     }
     uint32_t* newSorted = (uint32_t*)alloc((size_t)n * sizeof(uint32_t));
     uint32_t* newPos = (uint32_t*)alloc((size_t)n * sizeof(uint32_t));

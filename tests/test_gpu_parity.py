@@ -74,6 +74,7 @@ def test_treelet_refinement_keeps_hits_and_lowers_sah(gsb, orc, monkeypatch):
     s = host_scene("field_medium")
     rays = random_rays(s, 30000, seed=11)
     results, stats = [], []
+    monkeypatch.setenv("GSB_TREELET_GAMMA", "7")      # every node a treelet root (the default skips subtrees of fewer than 14 leaves)
     for blas, tlas in [(0, 0), (1, 0), (2, 0), (3, 2)]:
         monkeypatch.setenv("GSB_TREELET_PASSES", str(blas))
         monkeypatch.setenv("GSB_TREELET_PASSES_TLAS", str(tlas))
