@@ -891,7 +891,9 @@ static void rebuildScene(gsb_context* ctx) {
     cudaFree(ctx->dInstSmall);
     ctx->dInstSmall = uploadArray(small.data(), count, ctx->stream);
     freeBvh(ctx->world);
-    buildBlas(ctx->dWorldVerts, (uint32_t)baked, ctx->stream, ctx->world, true);
+    // the treelet setting that won the world level's comparison is kept while the level keeps its size
+    if (ctx->worldSettingTris != baked) { ctx->worldSetting = -1; ctx->worldSettingTris = baked; }
+    buildBlas(ctx->dWorldVerts, (uint32_t)baked, ctx->stream, ctx->world, true, &ctx->worldSetting);
     if (baked) k_gatherNormals<<<((uint32_t)baked + 127) / 128, 128, 0, ctx->stream>>>(ctx->world.leafPrim, (uint32_t)baked, ctx->dNrmSoup, ctx->dWorldNrm);
     GSB_CUDA(cudaStreamSynchronize(ctx->stream));
     freeBvh(ctx->tlas);

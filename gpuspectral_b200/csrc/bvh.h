@@ -43,10 +43,13 @@ constexpr float kBoxPadRel = 1.0f / 32768.0f;
 // idsInVertices: the leaf records take v0.w / v1.w from the input vertices (world level: primitive and instance id of
 // every baked triangle) instead of the position of the triangle in the soup.
 // out.leafPrim keeps the input triangle index of every leaf position.
-void buildBlas(const float4* dVertices, uint32_t numTriangles, cudaStream_t stream, DeviceBvh& out, bool idsInVertices = false);
+void buildBlas(const float4* dVertices, uint32_t numTriangles, cudaStream_t stream, DeviceBvh& out, bool idsInVertices = false, int* setting = nullptr);
 // The bottom levels of several meshes in one call: the builds run side by side on a few streams and the host waits once
 // per phase instead of several times per mesh.  buildMs of every `out` = its share (by triangle count) of the batch time.
-struct BlasBuildRequest { const float4* vertices; uint32_t ntris; DeviceBvh* out; bool idsInVertices; };
+// setting (optional, in / out): which treelet setting to build a small level with; -1 = try them all (see kCandidates in
+// bvh_build.cu) and report the one that won, so that a level that is rebuilt again and again (the world level, at every
+// gsb_scene_set_instances) pays for the comparison once.
+struct BlasBuildRequest { const float4* vertices; uint32_t ntris; DeviceBvh* out; bool idsInVertices; int* setting = nullptr; };
 void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t stream);
 
 // Bake rule (shared with the checker): in gl_InstanceID order an instance whose mesh has at most

@@ -899,7 +899,8 @@ void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t
     std::vector<cudaStream_t> streams;
     cudaEvent_t joined = nullptr;
     bool anySmall = false;
-    for (size_t i = 0; i < count; i++) anySmall = anySmall || (requests[i].ntris >= 16 && requests[i].ntris <= kCandidateMaxTris);
+    for (size_t i = 0; i < count; i++)
+        anySmall = anySmall || (requests[i].ntris >= 16 && requests[i].ntris <= kCandidateMaxTris && !(requests[i].setting && *requests[i].setting >= 0));
     if (count > 1 || (candidates && anySmall)) {
         streams.resize(candidates && anySmall ? kBuildStreams : std::min(count, kBuildStreams));
         for (cudaStream_t& st : streams) {
@@ -919,6 +920,7 @@ void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t
         while (end < count && (end == first || waveTris + requests[end].ntris <= kWaveTriangles)) waveTris += requests[end++].ntris;
         std::vector<std::unique_ptr<BuildJob>> jobs;
         std::vector<std::vector<std::unique_ptr<BuildJob>>> rivals(end - first);   // candidate builds of small levels
+        std::vector<int> winner(end - first, 0);
         const auto tWave = std::chrono::steady_clock::now();
         for (size_t i = first; i < end; i++) {
             const BlasBuildRequest& q = requests[i];
@@ -943,12 +945,14 @@ void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t
                 j.start(plo, phi);
                 return job;
             };
-            jobs.push_back(launch(-1, 0));
+            const int fixed = (q.setting && *q.setting > 0 && *q.setting <= 5) ? *q.setting : 0;
+            jobs.push_back(fixed ? launch(kCandidates[fixed - 1][0], kCandidates[fixed - 1][1]) : launch(-1, 0));
+            winner[i - first] = fixed;
             // A small level is built several times, with different treelet settings, and the tree with the least SAH cost
             // AS AN 8-WIDE TREE (the root entry of the cut tables) is kept: on a few dozen triangles which treelets happen
             // to be formed decides whether the level has three nodes or four, and the binary SAH cost does not see it
             // (Cornell box, r3c: 386.3 against 386.8, but 144.7 against 149.1 as wide trees, 1096 against 1003 Mpaths/s).
-            if (candidates && q.ntris >= 16 && q.ntris <= kCandidateMaxTris)
+            if (candidates && q.ntris >= 16 && q.ntris <= kCandidateMaxTris && !(q.setting && *q.setting >= 0))
                 for (const int* c : {kCandidates[0], kCandidates[1], kCandidates[2], kCandidates[3], kCandidates[4]})
                     rivals[i - first].push_back(launch(c[0], c[1]));
         }
@@ -959,7 +963,8 @@ void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t
             DeviceBvh& out = *q.out;
             const auto tc0 = std::chrono::steady_clock::now();
             jobs[i - first]->collect(out);
-            for (std::unique_ptr<BuildJob>& r : rivals[i - first]) {
+            for (size_t c = 0; c < rivals[i - first].size(); c++) {
+                std::unique_ptr<BuildJob>& r = rivals[i - first][c];
                 DeviceBvh other;
                 r->collect(other);
                 if (r->host.wideCost > 0.0f && jobs[i - first]->host.wideCost > 0.0f && r->host.wideCost < jobs[i - first]->host.wideCost) {
@@ -967,8 +972,10 @@ void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t
                     out.sahBefore = other.sahBefore;
                     out.sahAfter = other.sahAfter;
                     jobs[i - first].swap(r);
+                    winner[i - first] = (int)c + 1;
                 }
             }
+            if (q.setting && (!rivals[i - first].empty() || *q.setting < 0)) *q.setting = winner[i - first];
             rivals[i - first].clear();
             BuildJob& j = *jobs[i - first];
             const auto tc1 = std::chrono::steady_clock::now();
@@ -1008,8 +1015,8 @@ void buildBlasBatch(const BlasBuildRequest* requests, size_t count, cudaStream_t
     cudaEventDestroy(e1);
 }
 
-void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out, bool idsInVertices) {
-    const BlasBuildRequest q = {dVertices, ntris, &out, idsInVertices};
+void buildBlas(const float4* dVertices, uint32_t ntris, cudaStream_t s, DeviceBvh& out, bool idsInVertices, int* setting) {
+    const BlasBuildRequest q = {dVertices, ntris, &out, idsInVertices, setting};
     buildBlasBatch(&q, 1, s);
 }
 
