@@ -9,9 +9,11 @@ if len(sys.argv) > 1 and sys.argv[1] == "gamma":
 if len(sys.argv) > 1 and sys.argv[1] == "small":
     CONFIGS = [("gamma %d passes %d leaf %d" % (g_, p_, l_), {"GSB_TREELET_GAMMA": str(g_), "GSB_TREELET_PASSES": str(p_), "GSB_MAX_LEAF": str(l_)})
                for l_ in (3, 2) for g_, p_ in ((7, 1), (14, 1), (7, 0), (7, 2), (14, 2), (24, 1))]
+if len(sys.argv) > 1 and sys.argv[1] == "inst":
+    CONFIGS = [("inst cost %.1f" % c, {"GSB_SAH_COST_INST": str(c)}) for c in (0.5, 1.0, 2.0, 4.0, 8.0)] + [("tlas leaf 2", {"GSB_MAX_LEAF_TLAS": "2"})]
 if len(sys.argv) > 1 and sys.argv[1] == "costs":
     CONFIGS = [("greedy", {"GSB_COLLAPSE_SAH": "0"})] + [("sah prim %.2f" % c, {"GSB_COLLAPSE_SAH": "1", "GSB_SAH_COST_PRIM": str(c)}) for c in (0.5, 0.75, 1.0, 1.5, 2.5)]
-for name, spp in ((("cornell", 64),) if len(sys.argv) > 1 and sys.argv[1] == "small" else (("cornell", 64), ("gallery", 32), ("field", 16))):
+for name, spp in ((("cornell", 64),) if len(sys.argv) > 1 and sys.argv[1] == "small" else (("field", 16),) if len(sys.argv) > 1 and sys.argv[1] == "inst" else (("cornell", 64), ("gallery", 32), ("field", 16))):
     s = g.Scene.builtin(name)
     for label, env in CONFIGS:
         os.environ.update(env)
