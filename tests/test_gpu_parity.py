@@ -95,6 +95,53 @@ def test_treelet_refinement_keeps_hits_and_lowers_sah(gsb, orc, monkeypatch):
         assert st["unique_triangles"] == stats[0]["unique_triangles"] and st["num_instances"] == stats[0]["num_instances"]
 
 
+def test_build_variants_keep_hits(gsb, monkeypatch):
+    """Everything the build may choose between re-shapes the BVH and nothing else: the SAH-table cut of the 8-wide collapse
+    against the greedy one, the candidate builds of small levels on / off, the bottom levels of a scene built side by side on
+    8 streams or one after the other.  Hits (ids, t, barycentrics) bit-identical, occlusion identical; the node counts differ."""
+    for name, n in (("field_medium", 30000), ("cornell", 30000), ("gallery", 20000)):
+        s = host_scene(name)
+        rays = random_rays(s, n, seed=31)
+        results, stats = [], []
+        for env in ({}, {"GSB_COLLAPSE_SAH": "0", "GSB_COLLAPSE_SAH_TLAS": "0"}, {"GSB_BUILD_CANDIDATES": "0"}, {"GSB_BUILD_STREAMS": "1"},
+                    {"GSB_TREELET_GAMMA": "7", "GSB_TREELET_PASSES": "2"}):
+            for k in ("GSB_COLLAPSE_SAH", "GSB_COLLAPSE_SAH_TLAS", "GSB_BUILD_CANDIDATES", "GSB_BUILD_STREAMS", "GSB_TREELET_GAMMA", "GSB_TREELET_PASSES"):
+                monkeypatch.delenv(k, raising=False)
+            for k, v in env.items():
+                monkeypatch.setenv(k, v)
+            with gsb.Context(0) as c:
+                c.upload(s)
+                c.upload(s)                      # the second build of a small world level uses the remembered setting
+                stats.append(c.bvh_stats())
+                results.append(c.trace_batch(rays))
+                occl = c.trace_batch(rays, any_hit=True)
+                assert np.array_equal(occl["inst"] != gsb.NO_HIT, results[-1]["inst"] != gsb.NO_HIT)
+        for r in results[1:]:
+            for k in ("inst", "prim", "t", "u", "v"):
+                assert np.array_equal(r[k], results[0][k]), (name, k)
+        assert (results[0]["inst"] != gsb.NO_HIT).mean() > 0.3
+        nodes = [st["blas_nodes"] + st["world_nodes"] + st["tlas_nodes"] for st in stats]
+        assert nodes[3] == nodes[0]              # streams change the schedule, not the trees
+        if name != "cornell":
+            assert nodes[1] != nodes[0]          # the two cuts choose different nodes
+        for st in stats:
+            assert st["unique_triangles"] == stats[0]["unique_triangles"]
+
+
+def test_mesh_without_instances_builds_nothing(gsb):
+    """A mesh that no instance list ever traces through gets no bottom level; creating and destroying it is enough."""
+    s = host_scene("field_medium")          # meshes of 20 480 triangles: traced through their own bottom levels, not baked
+    with gsb.Context(0) as c:
+        pos, nrm = s.mesh(0)
+        m = c.mesh_create(pos, nrm)
+        assert c.bvh_stats()["blas_nodes"] == 0
+        c.upload(s)
+        first = c.bvh_stats()
+        c.upload(s)
+        assert c.bvh_stats()["blas_nodes"] == first["blas_nodes"] > 0
+        assert m is not None
+
+
 def test_closest_hit_vs_float64(gsb, orc, ctx):
     """Independent check of the rule itself: float64 Moeller-Trumbore brute force. ids may differ only
     where two candidates are within rounding distance; t within 16 ulp of float32 at the hit distance."""
