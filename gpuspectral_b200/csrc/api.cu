@@ -398,11 +398,19 @@ static void choosePolicy(gsb_context* ctx) {
     if (const char* e = getenv("GSB_POOL_REFILL")) poolRefill = (uint32_t)std::min(32, std::max(1, atoi(e)));
     // idle lanes that trigger a refill straight from the source (measured, r2e: taking a ray is two loads since k_regen
     // starts the paths, so refilling early pays: Cornell 24 -> 12 lanes = -10 % k_extend; two-level scenes 8 for both kernels;
-    // the any-hit kernel of world-only scenes stays at 24).  GSB_REFILL / GSB_SHADOW_REFILL override.
+    // the any-hit kernel of world-only scenes 16).  GSB_REFILL / GSB_SHADOW_REFILL override.
     const bool twoLevel = ctx->numTraceInstances > 0;
     const uint32_t direct = ctx->directRefill ? ctx->directRefill : (twoLevel ? 8u : 12u);
-    const uint32_t directShadow = ctx->shadowRefill ? ctx->shadowRefill : (twoLevel ? 8u : 24u);
+    const uint32_t directShadow = ctx->shadowRefill ? ctx->shadowRefill : (twoLevel ? 8u : 16u);   // r3j: 24 -> 16, Cornell k_shadow 62.5 -> 59.1 ms, gallery flat
     ctx->refillMin = (ctx->refillMin & ~0xffu) | (ctx->poolExtend ? poolRefill : direct);
+    // Phase quorum of the closest-hit kernel (traverse.cuh: a node / triangle round runs when at least `vote` lanes want it;
+    // a triangle round also when at least `triMin` triangles wait): 2 and 8, and a quorum of 1 for a world level of a few
+    // nodes, where the lanes are in step anyway and waiting for company only idles them (r3j, Cornell k_extend per step:
+    // 4 / 4: 104.1 ms, 2 / 8: 101.9, 1 / 8: 100.4; gallery 198.7 / 195.9 / 200.2 (1 / 4); field 99.0 / 98.9 / 100.3 (1 / 4)).
+    // GSB_VOTE / GSB_TRIMIN override.
+    const bool tinyWorld = !twoLevel && ctx->world.numNodes <= 8u;
+    if (!ctx->voteFromEnv) ctx->refillMin = (ctx->refillMin & ~0xff00u) | ((tinyWorld ? 1u : 2u) << 8);
+    if (!ctx->triMinFromEnv) ctx->refillMin = (ctx->refillMin & ~0xff0000u) | (8u << 16);
     ctx->shadowControl = ctx->poolShadow ? poolRefill : directShadow;
     // Ray sorting between bounces (wavefront.cu: sortKey): pays when the BVH is much larger than the caches, i.e. when
     // incoherent rays cost memory latency and lane divergence; GSB_SORT = grid bits per axis (0 = off) overrides.
@@ -533,11 +541,11 @@ gsb_status gsb_create(int device_ordinal, gsb_context** out_ctx) {
         }
         if (const char* e = getenv("GSB_VOTE")) {
             const long v = atol(e);
-            if (v >= 0 && v <= 32) ctx->refillMin = (ctx->refillMin & ~0xff00u) | ((uint32_t)v << 8);
+            if (v >= 0 && v <= 32) { ctx->refillMin = (ctx->refillMin & ~0xff00u) | ((uint32_t)v << 8); ctx->voteFromEnv = true; }
         }
         if (const char* e = getenv("GSB_TRIMIN")) {
             const long v = atol(e);
-            if (v >= 0 && v <= 32) ctx->refillMin = (ctx->refillMin & ~0xff0000u) | ((uint32_t)v << 16);
+            if (v >= 0 && v <= 32) { ctx->refillMin = (ctx->refillMin & ~0xff0000u) | ((uint32_t)v << 16); ctx->triMinFromEnv = true; }
         }
         if (const char* e = getenv("GSB_SHADE_DIRECT")) {
             const long v = atol(e);

@@ -78,6 +78,7 @@ struct gsb_context {
     uint32_t numBakedTriangles = 0;
     float4* dNrmSoup = nullptr;        //   the same normals in bake order (kept: a moved baked instance is re-baked in place)
     std::vector<uint64_t> bakeOffset;  // per instance: first world-level triangle (bake order), ~0 = not baked
+    bool voteFromEnv = false, triMinFromEnv = false;   // GSB_VOTE / GSB_TRIMIN given: choosePolicy leaves those bits alone
     int worldSetting = -1;             // treelet setting that won the world level's build comparison (-1: not compared yet)
     uint64_t worldSettingTris = ~0ull; // ... for a world level of this many triangles
     std::vector<int32_t> traceIndex;   // per instance: its position in hostTrace, -1 = baked
