@@ -412,6 +412,13 @@ static void choosePolicy(gsb_context* ctx) {
     if (!ctx->voteFromEnv) ctx->refillMin = (ctx->refillMin & ~0xff00u) | ((tinyWorld ? 1u : 2u) << 8);
     if (!ctx->triMinFromEnv) ctx->refillMin = (ctx->refillMin & ~0xff0000u) | (8u << 16);
     ctx->shadowControl = ctx->poolShadow ? poolRefill : directShadow;
+    // The any-hit kernel runs without a lane quorum for its phases (a quorum of 1 or 2 cost Cornell's k_shadow 59.0 -> 60.3 /
+    // 61.0 ms) but leaves its triangle loop when fewer than 4 lanes still have triangles waiting (r3k, k_shadow per step:
+    // Cornell 59.0 -> 57.9 ms, gallery 110.5 -> 103.4, field 36.2 -> 34.6; 2 .. 6 are equal).  GSB_SHADOW_VOTE / GSB_SHADOW_TRIMIN.
+    uint32_t shadowVote = 0u, shadowTriMin = 4u;
+    if (const char* e = getenv("GSB_SHADOW_VOTE")) shadowVote = (uint32_t)std::min(32, std::max(0, atoi(e)));
+    if (const char* e = getenv("GSB_SHADOW_TRIMIN")) shadowTriMin = (uint32_t)std::min(32, std::max(0, atoi(e)));
+    ctx->shadowControl |= (shadowVote << 8) | (shadowTriMin << 16);
     // Ray sorting between bounces (wavefront.cu: sortKey): pays when the BVH is much larger than the caches, i.e. when
     // incoherent rays cost memory latency and lane divergence; GSB_SORT = grid bits per axis (0 = off) overrides.
     ctx->sortBits = ctx->numTraceInstances > 0 ? 6u : 0u;

@@ -121,7 +121,7 @@ struct gsb_context {
     uint32_t refillMin = 24u | (4u << 8) | (4u << 16);
     uint32_t directRefill = 0u;    // idle lanes that trigger a refill straight from the source (GSB_REFILL); 0 = per-scene default (api.cu: choosePolicy)
     uint32_t shadowRefill = 0u;    // the same for the any-hit kernel (GSB_SHADOW_REFILL)
-    uint32_t shadowControl = 24u;  // the any-hit kernel's control word (no phase quorum measured best)
+    uint32_t shadowControl = 16u | (4u << 16);  // the any-hit kernel's control word (api.cu: choosePolicy)
     uint32_t sortBits = 0;         // ray sorting: grid bits per axis of the origin cell in the sort key; 0 = rays are traced in slot order
     bool poolExtend = false, poolShadow = false;   // traverse.cuh: ray pool (true) or direct refill; chosen per scene in gsb_scene_set_instances, GSB_POOL overrides
     uint32_t shadeDirectMin = 32;  // k_shade: matching lanes from which a tile is shaded in place (GSB_SHADE_DIRECT; measured flat from 12 to 32)
